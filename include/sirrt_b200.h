@@ -1,0 +1,126 @@
+/*
+ * sirrt_b200.h -- C ABI of libsirrt_b200.so: the B200 (sm_100a) backend for SI-RRT's hot path
+ * (safe intervals, per-frame collision checks, edge validation, C-space kNN).
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the reference
+ * root).  Conventions:
+ *   - all functions return 0 on success and a negative SIRRT_E_* code otherwise; nothing throws
+ *     across the ABI; sirrt_last_error() gives the message of the calling thread's last failure;
+ *   - the caller owns every buffer; data pointers may be host (pageable or pinned) or device
+ *     memory of the scene's GPU (detected with cudaPointerGetAttributes);
+ *   - a sirrt_scene is bound to one CUDA device and one stream and may be used by one host
+ *     thread at a time; different scenes may be used concurrently;
+ *   - there is NO CPU fallback: without a usable CUDA device every compute call fails with
+ *     SIRRT_E_CUDA.
+ *   - configurations are "q": dof joint angles in chain order of the non-fixed joints
+ *     (RobotObstacleFCL.cpp:321,363).  Frames are integer timesteps 0..n_frames-1; callers do
+ *     their own time->frame conversion (SURVEY.md §3.5 QUIRK 13).
+ */
+#ifndef SIRRT_B200_H
+#define SIRRT_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sirrt_scene sirrt_scene;
+typedef struct sirrt_knn sirrt_knn;
+typedef struct sirrt_multi sirrt_multi;
+
+enum {
+  SIRRT_OK = 0,
+  SIRRT_E_ARG = -1,      /* bad argument */
+  SIRRT_E_PACK = -2,     /* malformed scene pack */
+  SIRRT_E_CUDA = -3,     /* CUDA runtime failure / no device */
+  SIRRT_E_LIMIT = -4,    /* scene exceeds a compiled-in limit (links, joints) */
+  SIRRT_E_OVERFLOW = -5  /* output capacity too small */
+};
+
+/* QUIRK 7 (CollisionManager.cpp:97-104,206-208,263-265,628,691): robot-obstacle functor
+ * mis-indexing.  REFERENCE_EXACT reproduces it, FIXED tests the true geometry only. */
+enum { SIRRT_PARITY_REFERENCE_EXACT = 0, SIRRT_PARITY_FIXED = 1 };
+/* which reference callback a bit table follows: SafeIntervalCollisionCallback
+ * (CollisionManager.cpp:648-740) or CollisionCallback (:602-646); they differ only for
+ * robot obstacles in REFERENCE_EXACT mode */
+enum { SIRRT_SEM_INTERVAL = 0, SIRRT_SEM_FRAME = 1 };
+
+const char* sirrt_last_error(void);
+int sirrt_version(void);
+int sirrt_device_count(void);
+
+/* ---- scene: replaces MDP::CollisionManager::CollisionManager(SceneTask), CollisionManager.cpp:19-280
+ * (+ RobotObstacleFCL ctor, RobotObstacleFCL.cpp:21-30).  `pack` layout: include/sirrt_pack.h. */
+int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int device, int parity_mode, sirrt_scene** out);
+void sirrt_scene_destroy(sirrt_scene*);
+/* dof / links after base strip / frame_count / fps / limits[2*dof] = get_planned_robot_limits()
+ * (CollisionManager.cpp:422-425); any pointer may be NULL */
+int sirrt_scene_info(const sirrt_scene*, int* dof, int* n_links, int* n_frames, int* fps, float* limits_lo_hi);
+/* SceneTask::start_configuration / end_configuration / robot_joint_max_velocity (config_read.hpp:31-79) */
+int sirrt_scene_task(const sirrt_scene*, double* start_cfg, double* end_cfg, double* joint_max_velocity);
+/* run all work of this scene on `cuda_stream` (a cudaStream_t; NULL = the scene's own stream) */
+int sirrt_scene_set_stream(sirrt_scene*, void* cuda_stream);
+/* half-width (m) of the FP32 uncertainty band inside which a pair is re-evaluated in FP64 */
+int sirrt_scene_set_band(sirrt_scene*, double band);
+/* counters of the last batched call: [0] kernels launched, [1] FP64 re-checked pair tests,
+ * [2] near-contact pair tests (|d| < 1e-6 m), [3] narrowphase (exact) pair tests, [4] reserved */
+int sirrt_scene_last_stats(const sirrt_scene*, uint64_t stats[5]);
+
+/* ---- single-call drop-ins (latency path) ------------------------------------------------- */
+/* CollisionManager::get_safe_intervals, CollisionManager.cpp:481-547.  lo_hi receives up to `cap`
+ * inclusive (lo,hi) pairs, ascending; *n_out the true count (SIRRT_E_OVERFLOW if > cap). */
+int sirrt_safe_intervals(sirrt_scene*, const double* q, int32_t* lo_hi, int cap, int* n_out);
+/* CollisionManager::check_collision_frame[_no_wrapper], CollisionManager.cpp:338-380.
+ * frame outside [0, n_frames) answers "collided" (the reference indexes unchecked, :369). */
+int sirrt_check_frame(sirrt_scene*, const double* q, int frame, int* collided);
+/* CollisionManager::get_distances, CollisionManager.cpp:382-420 (+DistanceCallback :549-600):
+ * per planned-robot link the minimum distance to the box/sphere obstacles at `frame`.
+ * Links after the first colliding one are left at +inf (the reference returns early). */
+int sirrt_get_distances(sirrt_scene*, const double* q, int frame, double* min_dist, int* is_collision);
+
+/* ---- batched throughput path ------------------------------------------------------------- */
+/* N configurations -> collision bit rows and/or fixed-width interval table.
+ *   q_soa  : float32 [dof][N]      (structure of arrays; coalesced loads)
+ *   table  : int32 [N][1+2*Kmax]   row = {count, lo0, hi0, lo1, hi1, ...}, unused = -1; count is the
+ *            true interval count even when it exceeds Kmax (then only Kmax pairs are stored); or NULL
+ *   bits   : uint32 [N][ceil(T/32)] bit f%32 of word f/32 set = colliding at frame f; or NULL
+ *   near_contact_count : pair tests within 1e-6 m of contact (after FP64 re-evaluation); or NULL */
+int sirrt_safe_intervals_batch(sirrt_scene*, const float* q_soa, int64_t N, int32_t* table, int Kmax,
+                               uint32_t* bits, uint64_t* near_contact_count);
+/* same, double-precision configurations as array of structures [N][dof] (edge tables, §7.3) with
+ * explicit semantics (SIRRT_SEM_*) */
+int sirrt_collision_bits_f64(sirrt_scene*, const double* q_aos, int64_t N, int semantics, uint32_t* bits);
+/* N independent (configuration, frame) cells: check_collision_frame semantics */
+int sirrt_check_frames_batch(sirrt_scene*, const float* q_soa, const int32_t* frames, int64_t N, uint8_t* collided);
+int sirrt_check_frames_batch_f64(sirrt_scene*, const double* q_aos, const int32_t* frames, int64_t N, uint8_t* collided);
+/* PlannerConnect::is_collision_motion, PlannerConnect.cpp:862-897, for n_edges edges.
+ *   q0,q1 : double [n_edges][dof]; t0,t1 : double [n_edges], in frame units
+ *   vmax  : speed gate (:872) in rad/s, <= 0 disables it
+ *   first_colliding_step : -1 free, >= 0 index of the first colliding interpolation step,
+ *                          -2 start_time >= end_time (:865), -3 speed gate (:872)
+ *   collision_coord : double [n_edges][dof] configuration at that step, or NULL */
+int sirrt_edge_check_batch(sirrt_scene*, const double* q0, const double* q1, const double* t0, const double* t1,
+                           int64_t n_edges, double vmax, int32_t* first_colliding_step, double* collision_coord);
+
+/* ---- kNN: replaces nanoflann KDTreeSingleIndexDynamicAdaptor<L2_Simple> as used by
+ * MSIRRT/src/Tree.cpp:5,18-36 and PlannerConnect.cpp:382-412 (exact, FP64, squared L2) ------- */
+int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn** out);
+int sirrt_knn_destroy(sirrt_knn*);
+int sirrt_knn_size(const sirrt_knn*, int64_t* n);
+int sirrt_knn_add(sirrt_knn*, const double* pts /*[n][dim]*/, int64_t n);
+int sirrt_knn_nearest(sirrt_knn*, const double* queries /*[nq][dim]*/, int64_t nq, int64_t* idx, double* dist2);
+/* strict dist2 < r2 (nanoflann RadiusResultSet); indices ascending; *n_out = true count */
+int sirrt_knn_radius(sirrt_knn*, const double* query, double r2, int64_t* idx, int64_t cap, int64_t* n_out);
+/* k nearest of each query, ascending distance (ties by index); idx/dist2 [nq][k] */
+int sirrt_knn_topk(sirrt_knn*, const double* queries, int64_t nq, int k, int64_t* idx, double* dist2);
+
+/* ---- multi-GPU inside one process: shards a configuration batch over several devices ------ */
+int sirrt_multi_create(const void* pack, size_t bytes, const int* devices, int n_dev, int parity_mode, sirrt_multi** out);
+void sirrt_multi_destroy(sirrt_multi*);
+int sirrt_multi_safe_intervals_batch(sirrt_multi*, const float* q_soa_host, int64_t N, int32_t* table, int Kmax,
+                                     uint32_t* bits, uint64_t* near_contact_count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SIRRT_B200_H */

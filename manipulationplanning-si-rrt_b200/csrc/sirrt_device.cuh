@@ -1,0 +1,435 @@
+// sirrt_device.cuh -- device-side data layout and geometry for libsirrt_b200 (sm_100a).
+//
+// Everything here is FP32/FP64 CUDA-core arithmetic: the path is rigid-body geometry, not a dense
+// contraction, so there is deliberately no tensor-core (tcgen05) code.  The same templates serve the
+// FP32 fast path and the FP64 re-check so both evaluate the same formulas.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define SIRRT_MAXJ 12  // non-fixed joints of the planned robot
+#define SIRRT_MAXL 12  // collision links of the planned robot after the base strip
+#define SIRRT_FULL 0xffffffffu
+
+enum { SH_CAPSULE = 0, SH_HULL = 1, SH_BOX = 2, SH_SPHERE = 3 };
+enum { RES_FREE = 0, RES_HIT = 1, RES_AMBIG = 2 };
+
+// coal's collision predicate: distance - security_margin <= collision_distance_threshold
+// (security_margin 1e-21: CollisionManager.cpp:559,611,654; threshold = Eigen dummy_precision)
+#define SIRRT_SECURITY_MARGIN 1e-21
+#define SIRRT_COLLISION_THRESHOLD 1e-12
+
+// ---------------------------------------------------------------------------------------------
+// Device tables
+// ---------------------------------------------------------------------------------------------
+// FK model of the planned robot (RobotObstacleFCL::fk_chain flattened; FP64, read by every
+// kernel once per configuration).
+struct DRobot {
+  int n_joints, n_links, dof, pad;
+  double base_t[3], base_R[9];
+  double jt[SIRRT_MAXJ][3], jR[SIRRT_MAXJ][9];
+  int link_jb[SIRRT_MAXL];      // joints applied before link l is emitted
+  int link_shape[SIRRT_MAXL];   // index into the shape table
+  double lo_t[SIRRT_MAXL][3], lo_R[SIRRT_MAXL][9];
+};
+
+// Geometry of one convex shape = core polytope + inflation radius.
+struct DShape {
+  int type;            // SH_*
+  int vert_off;        // hull: first vertex in the vertex arrays
+  int n_verts;
+  int pad;
+  float radius, half_len;  // capsule / sphere
+  float half[3];           // box half extents
+  float bc[3], br;         // bounding sphere (inflated shape), local frame
+  float amin[3], amax[3], ac[3], ar;  // coal aabb_local / aabb_center / aabb_radius
+  double d_radius, d_half_len, d_half[3];
+  double d_amin[3], d_amax[3], d_ac[3], d_ar;
+};
+
+// One moving thing the planned robot can hit: a box/sphere obstacle or one link of a robot obstacle.
+struct DSlot {
+  int shape;        // true geometry
+  int shape_shift;  // QUIRK 7 functor geometry, -1 if none
+  int is_static;    // identical pose at every frame
+  int is_robot;     // robot-obstacle link
+  int rot_identity; // every pose has R == I exactly (skip the rotation on the fast path)
+  int pad[3];
+};
+
+struct DScene {
+  int T, Tp, n_tiles, n_slots;
+  int n_static, n_dynamic, parity_mode, has_hull;
+  const DShape* shapes;
+  const DSlot* slots;
+  const int* static_slots;   // slot ids
+  const int* dynamic_slots;
+  const float* pose_f;       // [(slot*12 + k)*Tp + f]  k<9: R row-major, k>=9: t
+  const float* bcw_f;        // [(slot*3 + k)*Tp + f]   world bounding-sphere centre
+  const double* pose_d;      // [(slot*Tp + f)*12 + k]
+  const float4* tile_bounds; // [tile*n_dynamic + j]    swept bounding sphere of dynamic slot j over the tile
+  const float* verts_f;      // xyz interleaved
+  const double* verts_d;
+};
+
+struct WorkItem {  // one ambiguous pair test for the FP64 re-check
+  int config;
+  int frame;       // -1: static slot, applies to every frame
+  short link, shifted;
+  int slot;
+};
+
+// ---------------------------------------------------------------------------------------------
+// small algebra
+// ---------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ T dot3(const T* a, const T* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+template <typename T> __device__ __forceinline__ void sub3(T* o, const T* a, const T* b) { o[0] = a[0] - b[0]; o[1] = a[1] - b[1]; o[2] = a[2] - b[2]; }
+template <typename T> __device__ __forceinline__ void cross3(T* o, const T* a, const T* b) {
+  o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
+}
+template <typename T> __device__ __forceinline__ void matvec(T* o, const T* R, const T* v) {
+  o[0] = R[0] * v[0] + R[1] * v[1] + R[2] * v[2];
+  o[1] = R[3] * v[0] + R[4] * v[1] + R[5] * v[2];
+  o[2] = R[6] * v[0] + R[7] * v[1] + R[8] * v[2];
+}
+template <typename T> __device__ __forceinline__ void matTvec(T* o, const T* R, const T* v) {
+  o[0] = R[0] * v[0] + R[3] * v[1] + R[6] * v[2];
+  o[1] = R[1] * v[0] + R[4] * v[1] + R[7] * v[2];
+  o[2] = R[2] * v[0] + R[5] * v[1] + R[8] * v[2];
+}
+template <typename T> __device__ __forceinline__ void matmul3(T* o, const T* A, const T* B) {
+  T r[9];
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) r[3 * i + j] = A[3 * i] * B[j] + A[3 * i + 1] * B[3 + j] + A[3 * i + 2] * B[6 + j];
+#pragma unroll
+  for (int i = 0; i < 9; i++) o[i] = r[i];
+}
+template <typename T> __device__ __forceinline__ void matTmul3(T* o, const T* A, const T* B) {  // A^T B
+#pragma unroll
+  for (int i = 0; i < 3; i++)
+#pragma unroll
+    for (int j = 0; j < 3; j++) o[3 * i + j] = A[i] * B[j] + A[3 + i] * B[3 + j] + A[6 + i] * B[6 + j];
+}
+__device__ __forceinline__ float tsqrt(float x) { return sqrtf(x); }
+__device__ __forceinline__ double tsqrt(double x) { return sqrt(x); }
+__device__ __forceinline__ float tabs(float x) { return fabsf(x); }
+__device__ __forceinline__ double tabs(double x) { return fabs(x); }
+template <typename T> __device__ __forceinline__ T clamp01(T t) { return t < T(0) ? T(0) : (t > T(1) ? T(1) : t); }
+
+// ---------------------------------------------------------------------------------------------
+// a1: forward kinematics, FP64 (RobotObstacleFCL.cpp:287-386).  One call per configuration, so its
+// cost is amortised over the frames; doing it in FP64 removes FK error from the FP32 band budget.
+// out: per link R[9], t[3].
+// ---------------------------------------------------------------------------------------------
+struct LinkXfD { double R[9], t[3]; };
+
+__device__ inline void fk_links(const DRobot& rb, const double* q, LinkXfD* out) {
+  double t[3] = {rb.base_t[0], rb.base_t[1], rb.base_t[2]}, R[9];
+#pragma unroll
+  for (int i = 0; i < 9; i++) R[i] = rb.base_R[i];
+  int l = 0;
+  for (int k = 0; k <= rb.n_joints; k++) {
+    while (l < rb.n_links && rb.link_jb[l] == k) {
+      double w[3];
+      matvec(w, R, rb.lo_t[l]);  // :335
+      out[l].t[0] = t[0] + w[0]; out[l].t[1] = t[1] + w[1]; out[l].t[2] = t[2] + w[2];  // :336
+      matmul3(out[l].R, R, rb.lo_R[l]);  // :347
+      l++;
+    }
+    if (k == rb.n_joints) break;
+    double w[3];
+    matvec(w, R, rb.jt[k]);  // :319,361
+    t[0] += w[0]; t[1] += w[1]; t[2] += w[2];
+    matmul3(R, R, rb.jR[k]);  // :320,362
+    double sn, cs;
+    sincos(q[k], &sn, &cs);
+    // Eigen::AngleAxisd(a, UnitZ()).toRotationMatrix() (:321,363)
+    double Rz[9] = {cs, -sn, 0, sn, cs, 0, 0, 0, (1.0 - cs) * 1.0 + cs};
+    matmul3(R, R, Rz);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// closed-form core distances (same formulas as oracle/sirrt_oracle.c, written independently of
+// precision)
+// ---------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ T pt_seg_dist2(const T* p, const T* a, const T* b) {
+  T ab[3], ap[3];
+  sub3(ab, b, a); sub3(ap, p, a);
+  T den = dot3(ab, ab), t = T(0);
+  if (den > T(0)) t = clamp01(dot3(ap, ab) / den);
+  T c[3] = {ap[0] - t * ab[0], ap[1] - t * ab[1], ap[2] - t * ab[2]};
+  return dot3(c, c);
+}
+
+template <typename T> __device__ inline T seg_seg_dist2(const T* p1, const T* q1, const T* p2, const T* q2) {
+  T d1[3], d2[3], r[3];
+  sub3(d1, q1, p1); sub3(d2, q2, p2); sub3(r, p1, p2);
+  T a = dot3(d1, d1), e = dot3(d2, d2), f = dot3(d2, r), s, t;
+  const T EPS = T(1e-30);
+  if (a <= EPS && e <= EPS) return dot3(r, r);
+  if (a <= EPS) { s = T(0); t = clamp01(f / e); }
+  else {
+    T c = dot3(d1, r);
+    if (e <= EPS) { t = T(0); s = clamp01(-c / a); }
+    else {
+      T b = dot3(d1, d2), denom = a * e - b * b;
+      s = denom > T(0) ? clamp01((b * f - c * e) / denom) : T(0);
+      t = (b * s + f) / e;
+      if (t < T(0)) { t = T(0); s = clamp01(-c / a); }
+      else if (t > T(1)) { t = T(1); s = clamp01((b - c) / a); }
+    }
+  }
+  T c1[3] = {p1[0] + d1[0] * s, p1[1] + d1[1] * s, p1[2] + d1[2] * s};
+  T c2[3] = {p2[0] + d2[0] * t, p2[1] + d2[1] * t, p2[2] + d2[2] * t};
+  T d[3]; sub3(d, c1, c2);
+  return dot3(d, d);
+}
+
+// segment a + t*d (t in [0,1]) vs box [-h,h]: g(t) = sum max(|p_i|-h_i,0)^2 is convex, g' is
+// continuous piecewise linear with breakpoints at the slab crossings -> bracket and solve.
+template <typename T> __device__ __forceinline__ T sb_g(const T* a, const T* d, const T* h, T t, T& gp) {
+  T g = T(0), s = T(0);
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    T p = a[i] + t * d[i], e = tabs(p) - h[i];
+    if (e > T(0)) { g += e * e; s += (p > T(0) ? e : -e) * d[i]; }
+  }
+  gp = T(2) * s;
+  return g;
+}
+template <typename T> __device__ inline T seg_box_dist2(const T* a, const T* b, const T* h) {
+  T d[3]; sub3(d, b, a);
+  T gp0, gp1, g0 = sb_g(a, d, h, T(0), gp0), g1 = sb_g(a, d, h, T(1), gp1);
+  if (gp0 >= T(0)) return g0;
+  if (gp1 <= T(0)) return g1;
+  T lo = T(0), hi = T(1), glo = gp0, ghi = gp1;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    if (d[i] == T(0)) continue;
+#pragma unroll
+    for (int sg = 0; sg < 2; sg++) {
+      T t = ((sg ? h[i] : -h[i]) - a[i]) / d[i];
+      if (!(t > lo && t < hi)) continue;
+      T gp; sb_g(a, d, h, t, gp);
+      if (gp <= T(0)) { lo = t; glo = gp; } else { hi = t; ghi = gp; }
+    }
+  }
+  T t = lo;
+  if (ghi > glo) t = lo - glo * (hi - lo) / (ghi - glo);
+  t = t < lo ? lo : (t > hi ? hi : t);
+  T gp;
+  return sb_g(a, d, h, t, gp);
+}
+
+// ---------------------------------------------------------------------------------------------
+// warp-cooperative GJK between two convex cores, evaluated in the local frame of A.
+//   A: hull (vertex scan striped over the 32 lanes)        [planned-robot link]
+//   B: hull / box / segment / point, posed by (Rrel, trel) relative to A
+// All 32 lanes hold identical simplex state; only the support scans are distributed.
+// ---------------------------------------------------------------------------------------------
+template <typename T> struct GShape {
+  int type;        // SH_*
+  const T* verts;  // hull: xyz interleaved
+  int n;
+  T half[3];       // box
+  T half_len;      // capsule core
+};
+
+template <typename T>
+__device__ inline int warp_support(const GShape<T>& s, const T* d, T* out, int lane) {
+  if (s.type == SH_HULL) {
+    T bv = T(-3.0e38);
+    int bi = 0;
+    for (int i = lane; i < s.n; i += 32) {
+      T v = s.verts[3 * i] * d[0] + s.verts[3 * i + 1] * d[1] + s.verts[3 * i + 2] * d[2];
+      if (v > bv) { bv = v; bi = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      T ov = __shfl_xor_sync(SIRRT_FULL, bv, o);
+      int oi = __shfl_xor_sync(SIRRT_FULL, bi, o);
+      if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    out[0] = s.verts[3 * bi]; out[1] = s.verts[3 * bi + 1]; out[2] = s.verts[3 * bi + 2];
+    return bi;
+  }
+  if (s.type == SH_BOX) {
+    int id = 0;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      bool pos = d[k] >= T(0);
+      out[k] = pos ? s.half[k] : -s.half[k];
+      id |= (pos ? 1 : 0) << k;
+    }
+    return id;
+  }
+  if (s.type == SH_CAPSULE) {
+    bool pos = d[2] >= T(0);
+    out[0] = T(0); out[1] = T(0); out[2] = pos ? s.half_len : -s.half_len;
+    return pos ? 1 : 0;
+  }
+  out[0] = out[1] = out[2] = T(0);
+  return 0;
+}
+
+template <typename T> struct Simplex { T w[4][3]; int id[4]; int n; };
+
+// closest point to the origin on triangle abc; returns kept-vertex mask (a=1,b=2,c=4)
+template <typename T> __device__ inline int closest_tri(const T* a, const T* b, const T* c, T* out) {
+  T ab[3], ac[3];
+  sub3(ab, b, a); sub3(ac, c, a);
+  T d1 = -dot3(ab, a), d2 = -dot3(ac, a);
+  if (d1 <= T(0) && d2 <= T(0)) { out[0] = a[0]; out[1] = a[1]; out[2] = a[2]; return 1; }
+  T d3 = -dot3(ab, b), d4 = -dot3(ac, b);
+  if (d3 >= T(0) && d4 <= d3) { out[0] = b[0]; out[1] = b[1]; out[2] = b[2]; return 2; }
+  T vc = d1 * d4 - d3 * d2;
+  if (vc <= T(0) && d1 >= T(0) && d3 <= T(0)) {
+    T v = d1 / (d1 - d3);
+    for (int i = 0; i < 3; i++) out[i] = a[i] + v * ab[i];
+    return 3;
+  }
+  T d5 = -dot3(ab, c), d6 = -dot3(ac, c);
+  if (d6 >= T(0) && d5 <= d6) { out[0] = c[0]; out[1] = c[1]; out[2] = c[2]; return 4; }
+  T vb = d5 * d2 - d1 * d6;
+  if (vb <= T(0) && d2 >= T(0) && d6 <= T(0)) {
+    T w = d2 / (d2 - d6);
+    for (int i = 0; i < 3; i++) out[i] = a[i] + w * ac[i];
+    return 5;
+  }
+  T va = d3 * d6 - d5 * d4;
+  if (va <= T(0) && (d4 - d3) >= T(0) && (d5 - d6) >= T(0)) {
+    T w = (d4 - d3) / ((d4 - d3) + (d5 - d6));
+    for (int i = 0; i < 3; i++) out[i] = b[i] + w * (c[i] - b[i]);
+    return 6;
+  }
+  T den = T(1) / (va + vb + vc), v = vb * den, w = vc * den;
+  for (int i = 0; i < 3; i++) out[i] = a[i] + ab[i] * v + ac[i] * w;
+  return 7;
+}
+
+// reduce simplex to the sub-simplex closest to the origin; returns 1 when the origin is enclosed.
+// min_face (tetrahedron only) receives a lower bound of the penetration depth.
+template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v, T& min_face) {
+  if (s.n == 1) { v[0] = s.w[0][0]; v[1] = s.w[0][1]; v[2] = s.w[0][2]; return 0; }
+  if (s.n == 2) {
+    const T *a = s.w[0], *b = s.w[1];
+    T ab[3]; sub3(ab, b, a);
+    T den = dot3(ab, ab), t = den > T(0) ? -dot3(a, ab) / den : T(0);
+    if (t <= T(0)) { v[0] = a[0]; v[1] = a[1]; v[2] = a[2]; s.n = 1; }
+    else if (t >= T(1)) {
+      v[0] = b[0]; v[1] = b[1]; v[2] = b[2];
+      s.w[0][0] = b[0]; s.w[0][1] = b[1]; s.w[0][2] = b[2]; s.id[0] = s.id[1]; s.n = 1;
+    } else for (int i = 0; i < 3; i++) v[i] = a[i] + t * ab[i];
+    return 0;
+  }
+  int keep = 0;
+  if (s.n == 3) keep = closest_tri(s.w[0], s.w[1], s.w[2], v);
+  else {
+    const int F[4][4] = {{0, 1, 2, 3}, {0, 2, 3, 1}, {0, 3, 1, 2}, {1, 3, 2, 0}};
+    T best = T(3.0e38), bv[3] = {T(0), T(0), T(0)};
+    int outside_any = 0;
+    min_face = T(3.0e38);
+    for (int f = 0; f < 4; f++) {
+      const T *a = s.w[F[f][0]], *b = s.w[F[f][1]], *c = s.w[F[f][2]], *d = s.w[F[f][3]];
+      T ab[3], ac[3], n[3], ad[3];
+      sub3(ab, b, a); sub3(ac, c, a); cross3(n, ab, ac); sub3(ad, d, a);
+      T sp = -dot3(a, n), sd = dot3(ad, n);
+      if (sp * sd < T(0) || sd == T(0)) {
+        outside_any = 1;
+        T q[3];
+        int m = closest_tri(a, b, c, q);
+        T dd = dot3(q, q);
+        if (dd < best) {
+          best = dd; bv[0] = q[0]; bv[1] = q[1]; bv[2] = q[2];
+          keep = 0;
+          for (int k = 0; k < 3; k++) if (m & (1 << k)) keep |= 1 << F[f][k];
+        }
+      } else {
+        T nn = dot3(n, n);
+        T fd = nn > T(0) ? tabs(sp) / tsqrt(nn) : T(0);
+        if (fd < min_face) min_face = fd;
+      }
+    }
+    if (!outside_any) { v[0] = v[1] = v[2] = T(0); return 1; }
+    v[0] = bv[0]; v[1] = bv[1]; v[2] = bv[2];
+  }
+  int j = 0;
+  for (int i = 0; i < s.n; i++)
+    if (keep & (1 << i)) {
+      if (i != j) { s.w[j][0] = s.w[i][0]; s.w[j][1] = s.w[i][1]; s.w[j][2] = s.w[i][2]; s.id[j] = s.id[i]; }
+      j++;
+    }
+  s.n = j;
+  return 0;
+}
+
+// FINAL = false (FP32 fast path): classify against [rsum-band, rsum+band] using the rigorous GJK
+//         bounds  v.w/|v| <= d_core <= |v|  -> RES_FREE / RES_HIT / RES_AMBIG.
+// FINAL = true  (FP64 re-check): converge and apply coal's predicate -> RES_FREE / RES_HIT;
+//         *dist_out gets the signed distance (core distance - rsum).
+template <typename T, bool FINAL>
+__device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* Rrel, const T* trel, T rsum, T band,
+                               int lane, T* dist_out) {
+  Simplex<T> s;
+  T v[3] = {-trel[0], -trel[1], -trel[2]};  // A is centred near its origin, B near trel
+  if (dot3(v, v) == T(0)) v[0] = T(1);
+  T pa[3], pb[3], dl[3], nv[3], min_face = T(0);
+  const T REL = FINAL ? T(1e-15) : T(1e-6);
+  auto support = [&](const T* dir, T* w) -> int {  // support of A - B in direction dir
+    int ia = warp_support(A, dir, pa, lane);
+    T nd[3] = {-dir[0], -dir[1], -dir[2]};
+    matTvec(dl, Rrel, nd);
+    T u[3];
+    int ib = warp_support(B, dl, u, lane);
+    matvec(pb, Rrel, u);
+    w[0] = pa[0] - (pb[0] + trel[0]); w[1] = pa[1] - (pb[1] + trel[1]); w[2] = pa[2] - (pb[2] + trel[2]);
+    return (ia << 12) | ib;
+  };
+  nv[0] = -v[0]; nv[1] = -v[1]; nv[2] = -v[2];
+  s.id[0] = support(nv, s.w[0]);
+  s.n = 1;
+  v[0] = s.w[0][0]; v[1] = s.w[0][1]; v[2] = s.w[0][2];
+  T vv = dot3(v, v);
+  const int MAXIT = FINAL ? 256 : 48;
+  for (int it = 0; it < MAXIT; it++) {
+    if (vv <= (FINAL ? T(1e-30) : T(1e-20))) {  // cores touch / intersect at a vertex
+      if (dist_out) *dist_out = -rsum;
+      if (FINAL) return RES_HIT;
+      return rsum > band ? RES_HIT : RES_AMBIG;
+    }
+    T w[3];
+    nv[0] = -v[0]; nv[1] = -v[1]; nv[2] = -v[2];
+    int id = support(nv, w);
+    T vw = dot3(v, w);
+    if (!FINAL) {
+      // separating axis: every point of A-B has v.x >= v.w, so d_core >= v.w/|v|
+      if (vw > T(0)) {
+        T lower = vw * rsqrtf((float)vv);
+        if (lower - rsum > band) return RES_FREE;
+      }
+    }
+    T gap = vv - vw;
+    bool done = gap <= REL * vv;
+    for (int i = 0; i < s.n; i++) done |= (s.id[i] == id);
+    if (done) break;
+    s.w[s.n][0] = w[0]; s.w[s.n][1] = w[1]; s.w[s.n][2] = w[2]; s.id[s.n] = id; s.n++;
+    T nvv[3];
+    if (simplex_closest(s, nvv, min_face)) {
+      if (dist_out) *dist_out = -rsum;
+      if (FINAL) return RES_HIT;  // core distance 0 <= threshold + rsum
+      if (rsum > band) return RES_HIT;
+      return min_face > band ? RES_HIT : RES_AMBIG;
+    }
+    T n2 = dot3(nvv, nvv);
+    if (!(n2 < vv)) break;
+    v[0] = nvv[0]; v[1] = nvv[1]; v[2] = nvv[2]; vv = n2;
+  }
+  T d = tsqrt(vv) - rsum;
+  if (dist_out) *dist_out = d;
+  if (FINAL) return ((double)d - SIRRT_SECURITY_MARGIN <= SIRRT_COLLISION_THRESHOLD) ? RES_HIT : RES_FREE;
+  if (d < -band) return RES_HIT;
+  return RES_AMBIG;  // |d| <= band, or not converged enough to certify separation
+}

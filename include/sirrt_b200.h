@@ -48,6 +48,9 @@ enum { SIRRT_SEM_INTERVAL = 0, SIRRT_SEM_FRAME = 1 };
 const char* sirrt_last_error(void);
 int sirrt_version(void);
 int sirrt_device_count(void);
+/* FP32 FMA throughput of `device` (TFLOP/s, FMA = 2) from an FFMA micro-benchmark: the roofline
+ * denominator bench.py reports against (MEASURED_PEAKS.json carries no FP32 figure) */
+int sirrt_measure_fp32_peak(int device, double* tflops);
 
 /* ---- scene: replaces MDP::CollisionManager::CollisionManager(SceneTask), CollisionManager.cpp:19-280
  * (+ RobotObstacleFCL ctor, RobotObstacleFCL.cpp:21-30).  `pack` layout: include/sirrt_pack.h. */
@@ -63,8 +66,20 @@ int sirrt_scene_set_stream(sirrt_scene*, void* cuda_stream);
 /* half-width (m) of the FP32 uncertainty band inside which a pair is re-evaluated in FP64 */
 int sirrt_scene_set_band(sirrt_scene*, double band);
 /* counters of the last batched call: [0] kernels launched, [1] FP64 re-checked pair tests,
- * [2] near-contact pair tests (|d| < 1e-6 m), [3] narrowphase (exact) pair tests, [4] reserved */
+ * [2] near-contact pair tests (|d| < 1e-6 m), [3] narrowphase (exact) pair tests,
+ * [4] device time of the collision sweep kernel(s), nanoseconds (CUDA events on the launch stream) */
 int sirrt_scene_last_stats(const sirrt_scene*, uint64_t stats[5]);
+/* tuning knobs (defaults are right for B200): see SIRRT_OPT_* */
+enum {
+  SIRRT_OPT_USE_SWEEP = 0,      /* 1 (default): capsule-link x box/sphere scenes use the queue-compacted sweep kernel */
+  SIRRT_OPT_CHUNK_CONFIGS = 1,  /* configurations per launch of the batched path (default 262144) */
+  SIRRT_OPT_WORKLIST_CAP = 2    /* capacity of the FP64 re-check work list, entries (default 4194304) */
+};
+int sirrt_scene_set_option(sirrt_scene*, int key, long long value);
+/* link world transforms of the planned robot for q, [n_links][12] = R row-major then t, from the
+ * device FK the kernels use (RobotObstacleFCL::get_collision_object_for_robot_angles,
+ * RobotObstacleFCL.cpp:197-201,287-386) */
+int sirrt_scene_fk(sirrt_scene*, const double* q, double* out);
 
 /* ---- single-call drop-ins (latency path) ------------------------------------------------- */
 /* CollisionManager::get_safe_intervals, CollisionManager.cpp:481-547.  lo_hi receives up to `cap`
@@ -107,6 +122,7 @@ int sirrt_edge_check_batch(sirrt_scene*, const double* q0, const double* q1, con
 int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn** out);
 int sirrt_knn_destroy(sirrt_knn*);
 int sirrt_knn_size(const sirrt_knn*, int64_t* n);
+int sirrt_knn_clear(sirrt_knn*);
 int sirrt_knn_add(sirrt_knn*, const double* pts /*[n][dim]*/, int64_t n);
 int sirrt_knn_nearest(sirrt_knn*, const double* queries /*[nq][dim]*/, int64_t nq, int64_t* idx, double* dist2);
 /* strict dist2 < r2 (nanoflann RadiusResultSet); indices ascending; *n_out = true count */

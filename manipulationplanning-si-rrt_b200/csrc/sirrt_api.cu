@@ -1,0 +1,190 @@
+// sirrt_api.cu -- C ABI of libsirrt_b200.so (include/sirrt_b200.h): scene life cycle, the batched
+// collision / safe-interval / edge entry points and the single-call drop-ins.  Everything that
+// computes runs in the hand-written sm_100a kernels of sirrt_kernels.cuh / sirrt_sweep.cuh /
+// sirrt_knn.cuh; there is no CPU fallback: without a CUDA device every compute call fails.
+#include <stdio.h>
+
+#include <algorithm>
+#include <mutex>
+#include <new>
+
+#include "../../include/sirrt_b200.h"
+#include "sirrt_kernels.cuh"
+#include "sirrt_sweep.cuh"
+#include "sirrt_tables.hpp"
+
+using namespace sirrt;
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, const char* a = "") {
+  snprintf(g_err, sizeof g_err, fmt, a);
+  return code;
+}
+#define CU(x)                                                                                          \
+  do {                                                                                                 \
+    cudaError_t e_ = (x);                                                                              \
+    if (e_ != cudaSuccess) { cudaGetLastError(); return fail(SIRRT_E_CUDA, "CUDA: %s (" #x ")", cudaGetErrorString(e_)); } \
+  } while (0)
+
+extern "C" const char* sirrt_last_error(void) { return g_err; }
+extern "C" int sirrt_version(void) { return 100; }
+extern "C" int sirrt_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+// growable device scratch buffer
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = std::max(bytes, (size_t)256);
+    if (cudaMalloc(&p, want) != cudaSuccess) { cudaGetLastError(); return -1; }
+    cap = want;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <typename T> T* as() { return (T*)p; }
+};
+
+struct sirrt_scene {
+  int device = 0, parity_mode = 0, n_sm = 148;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  HScene hs;
+  HostTables tb;
+  DScene d{};
+  const float* d_aabb_f = nullptr;
+  const double* d_aabb_d = nullptr;
+  SweepTables sweep{};
+  std::vector<void*> owned;  // device allocations of the scene tables
+  double band = 0;
+  long long chunk_configs = 1 << 18;
+  unsigned int wl_cap = 1u << 22;
+  int use_sweep = 1;
+  DevBuf q, bits, table, frames, cells, work, counts, misc, misc2;
+  void* pinned = nullptr;  // small pinned staging block for the latency path
+  std::vector<cudaEvent_t> ev;  // start/stop pairs around the sweep launches of one call
+  uint64_t stats[5] = {0, 0, 0, 0, 0};
+};
+
+template <typename T> static int upload(sirrt_scene* s, const std::vector<T>& v, const T** out) {
+  void* p = nullptr;
+  size_t bytes = std::max(v.size(), (size_t)1) * sizeof(T);
+  CU(cudaMalloc(&p, bytes));
+  s->owned.push_back(p);
+  if (!v.empty()) CU(cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *out = (const T*)p;
+  return 0;
+}
+
+static bool is_device_ptr(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int device, int parity_mode, sirrt_scene** out) {
+  if (!pack || !out || (parity_mode != SIRRT_PARITY_REFERENCE_EXACT && parity_mode != SIRRT_PARITY_FIXED))
+    return fail(SIRRT_E_ARG, "sirrt_scene_create_from_pack: bad argument");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { cudaGetLastError(); return fail(SIRRT_E_CUDA, "no CUDA device (libsirrt_b200 has no CPU fallback)"); }
+  if (device < 0 || device >= ndev) return fail(SIRRT_E_ARG, "device index out of range");
+  sirrt_scene* s = new (std::nothrow) sirrt_scene;
+  if (!s) return fail(SIRRT_E_ARG, "out of memory");
+  std::string err;
+  if (!parse_pack(pack, bytes, s->hs, err)) { delete s; return fail(SIRRT_E_PACK, "%s", err.c_str()); }
+  int rc = build_tables(s->hs, parity_mode, s->tb, err);
+  if (rc) { delete s; return fail(rc, "%s", err.c_str()); }
+  s->device = device; s->parity_mode = parity_mode;
+  auto bail = [&](int code) { sirrt_scene_destroy(s); return code; };
+  if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaSetDevice failed")); }
+  cudaDeviceGetAttribute(&s->n_sm, cudaDevAttrMultiProcessorCount, device);
+  if (cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaStreamCreate failed")); }
+  s->stream = s->own_stream;
+  HostTables& tb = s->tb;
+  DScene& d = s->d;
+  d.T = tb.T; d.Tp = tb.Tp; d.n_tiles = tb.n_tiles; d.n_slots = tb.n_slots;
+  d.n_static = tb.n_static; d.n_dynamic = tb.n_dynamic; d.parity_mode = parity_mode; d.has_hull = tb.has_hull;
+#define UP(field, vec) if ((rc = upload(s, vec, &field))) return bail(rc)
+  UP(d.shapes, tb.shapes); UP(d.slots, tb.slots); UP(d.static_slots, tb.static_slots); UP(d.dynamic_slots, tb.dynamic_slots);
+  UP(d.pose_f, tb.pose_f); UP(d.bcw_f, tb.bcw_f); UP(d.pose_d, tb.pose_d); UP(d.tile_bounds, tb.tile_bounds);
+  UP(d.verts_f, tb.verts_f); UP(d.verts_d, tb.verts_d); UP(s->d_aabb_f, tb.aabb_f); UP(s->d_aabb_d, tb.aabb_d);
+#undef UP
+  // FP32 uncertainty band: the fast path decides a pair only when |signed distance| exceeds it;
+  // everything inside is re-evaluated in FP64 (k_recheck).  Scales with the coordinate magnitudes
+  // the FP32 arithmetic meets (arm reach around the base), never below 2e-5 m.
+  s->band = 2e-5 * std::max(1.0, tb.extent / 1.5);
+  if ((rc = sweep_build(s->hs, tb, s->d, &s->sweep, s->owned))) return bail(fail(rc, "sweep table build failed"));
+  if (cudaMallocHost(&s->pinned, 1 << 16) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMallocHost failed")); }
+  for (int i = 0; i < 64; i++) {
+    cudaEvent_t e;
+    if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); break; }
+    s->ev.push_back(e);
+  }
+  *out = s;
+  return SIRRT_OK;
+}
+
+extern "C" void sirrt_scene_destroy(sirrt_scene* s) {
+  if (!s) return;
+  cudaSetDevice(s->device);
+  if (s->own_stream) { cudaStreamSynchronize(s->own_stream); }
+  for (void* p : s->owned) cudaFree(p);
+  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->counts, &s->misc, &s->misc2}) b->release();
+  if (s->pinned) cudaFreeHost(s->pinned);
+  for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
+  if (s->own_stream) cudaStreamDestroy(s->own_stream);
+  cudaGetLastError();
+  delete s;
+}
+
+extern "C" int sirrt_scene_info(const sirrt_scene* s, int* dof, int* n_links, int* n_frames, int* fps, float* lim) {
+  if (!s) return fail(SIRRT_E_ARG, "null scene");
+  if (dof) *dof = s->hs.dof;
+  if (n_links) *n_links = s->hs.robot.n_links;
+  if (n_frames) *n_frames = s->hs.T;
+  if (fps) *fps = s->hs.fps;
+  if (lim) memcpy(lim, s->hs.robot.limits.data(), sizeof(float) * s->hs.robot.limits.size());
+  return SIRRT_OK;
+}
+extern "C" int sirrt_scene_task(const sirrt_scene* s, double* a, double* b, double* v) {
+  if (!s) return fail(SIRRT_E_ARG, "null scene");
+  const size_t n = sizeof(double) * s->hs.dof;
+  if (a) memcpy(a, s->hs.start_cfg.data(), n);
+  if (b) memcpy(b, s->hs.end_cfg.data(), n);
+  if (v) memcpy(v, s->hs.max_vel.data(), n);
+  return SIRRT_OK;
+}
+extern "C" int sirrt_scene_set_stream(sirrt_scene* s, void* st) {
+  if (!s) return fail(SIRRT_E_ARG, "null scene");
+  s->stream = st ? (cudaStream_t)st : s->own_stream;
+  return SIRRT_OK;
+}
+extern "C" int sirrt_scene_set_band(sirrt_scene* s, double band) {
+  if (!s || !(band >= 0) || band > 1e-2) return fail(SIRRT_E_ARG, "band out of range");
+  s->band = band;
+  return SIRRT_OK;
+}
+extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) {
+  if (!s) return fail(SIRRT_E_ARG, "null scene");
+  switch (key) {
+    case SIRRT_OPT_USE_SWEEP: s->use_sweep = value != 0; break;
+    case SIRRT_OPT_CHUNK_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad chunk"); s->chunk_configs = value; break;
+    case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
+    default: return fail(SIRRT_E_ARG, "unknown option");
+  }
+  return SIRRT_OK;
+}
+extern "C" int sirrt_scene_last_stats(const sirrt_scene* s, uint64_t st[5]) {
+  if (!s || !st) return fail(SIRRT_E_ARG, "null argument");
+  memcpy(st, s->stats, sizeof s->stats);
+  return SIRRT_OK;
+}
+
+#include "sirrt_api_batch.inl"
+#include "sirrt_api_knn.inl"

@@ -1,0 +1,366 @@
+// sirrt_api_batch.inl -- batched collision bits / safe intervals / cell checks / edge validation.
+// Included by sirrt_api.cu.
+
+static int grid_for(long long warps_wanted, int n_sm, int blocks_per_sm) {
+  long long blocks = (warps_wanted + SIRRT_WARPS_PER_BLOCK - 1) / SIRRT_WARPS_PER_BLOCK;
+  long long cap = (long long)n_sm * blocks_per_sm;
+  return (int)std::max(1ll, std::min(blocks, cap));
+}
+
+struct Range { long long n0, cnt; };
+
+// Collision bit rows of configurations [0, N) (global indexing into q / d_bits).  Work is cut into
+// launches of at most chunk_configs configurations so that the FP64 re-check work list stays
+// bounded; a launch whose list overflowed is repeated in halves.
+static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits) {
+  const int W = s->tb.n_tiles;
+  cudaStream_t st = s->stream;
+  if (s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(work list) failed");
+  std::vector<Range> todo;
+  for (long long n0 = 0; n0 < N; n0 += s->chunk_configs) todo.push_back({n0, std::min(s->chunk_configs, N - n0)});
+  uint64_t launches = 0, rechecked = 0, near = 0, exact = 0, sweep_ns = 0;
+  const bool sweep = s->use_sweep && s->sweep.supported;
+  while (!todo.empty()) {
+    const size_t nr = todo.size();
+    if (s->counts.ensure(nr * 4 * sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc(counters) failed");
+    CU(cudaMemsetAsync(s->counts.p, 0, nr * 4 * sizeof(unsigned), st));
+    for (size_t i = 0; i < nr; i++) {
+      QView qv = q;
+      qv.n0 = todo[i].n0; qv.cnt = todo[i].cnt;
+      WorkList wl{s->work.as<WorkItem>(), s->counts.as<unsigned>() + 4 * i, s->wl_cap};
+      const bool timed = i < s->ev.size() / 2;
+      if (timed) cudaEventRecord(s->ev[2 * i], st);
+      if (sweep) {
+        launches += sweep_launch(s->sweep, s->tb.robot, s->d, qv, wl, d_bits, W, (float)s->band, s->n_sm, st);
+      } else {
+        BitsParams P{};
+        P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.bits = d_bits; P.n_words = W;
+        P.semantics = semantics; P.band = (float)s->band;
+        // small batches: split each row over several warps (tile chunks) to fill the machine
+        long long target = (long long)s->n_sm * 32;
+        int n_chunks = (int)std::max(1ll, std::min((long long)W, target / std::max(1ll, qv.cnt)));
+        P.tiles_per_chunk = (W + n_chunks - 1) / n_chunks;
+        P.n_chunks = (W + P.tiles_per_chunk - 1) / P.tiles_per_chunk;
+        const int grid = grid_for(qv.cnt * P.n_chunks, s->n_sm, 8);
+        if (s->tb.has_hull) k_collide_bits<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
+        else k_collide_bits<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
+        launches++;
+      }
+      if (timed) cudaEventRecord(s->ev[2 * i + 1], st);
+      RecheckParams R{};
+      R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
+      R.aabb_d = s->d_aabb_d; R.bits = d_bits; R.n_words = W; R.cells = nullptr; R.counters = wl.count;
+      k_recheck<<<s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
+      launches++;
+      CU(cudaGetLastError());
+    }
+    std::vector<unsigned> host(nr * 4);
+    CU(cudaMemcpyAsync(host.data(), s->counts.p, nr * 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    for (size_t i = 0; i < nr && i < s->ev.size() / 2; i++) {
+      float ms = 0;
+      if (cudaEventElapsedTime(&ms, s->ev[2 * i], s->ev[2 * i + 1]) == cudaSuccess) sweep_ns += (uint64_t)(ms * 1e6);
+      else cudaGetLastError();
+    }
+    std::vector<Range> redo;
+    for (size_t i = 0; i < nr; i++) {
+      if (host[4 * i] > s->wl_cap) {
+        if (todo[i].cnt <= 1) return fail(SIRRT_E_OVERFLOW, "FP64 re-check work list overflow on a single configuration; raise SIRRT_OPT_WORKLIST_CAP");
+        const long long h = todo[i].cnt / 2;
+        redo.push_back({todo[i].n0, h});
+        redo.push_back({todo[i].n0 + h, todo[i].cnt - h});
+        // rows of the overflowed range are recomputed from scratch (bits are overwritten by the producer)
+      } else {
+        rechecked += host[4 * i]; exact += host[4 * i + 1]; near += host[4 * i + 2];
+      }
+    }
+    todo.swap(redo);
+  }
+  s->stats[0] += launches; s->stats[1] += rechecked; s->stats[2] += near; s->stats[3] += exact; s->stats[4] += sweep_ns;
+  return SIRRT_OK;
+}
+
+static int run_intervals(sirrt_scene* s, const uint32_t* d_bits, long long N, int32_t* d_table, int Kmax) {
+  IvParams P{d_bits, N, s->tb.n_tiles, s->tb.T, Kmax, d_table};
+  k_bits_to_intervals<<<(unsigned)((N + 7) / 8), 256, 0, s->stream>>>(P);
+  s->stats[0]++;
+  CU(cudaGetLastError());
+  return SIRRT_OK;
+}
+
+// bring a caller buffer onto the device (no-op for device pointers)
+static int stage_in(sirrt_scene* s, DevBuf& buf, const void* src, size_t bytes, const void** dev) {
+  if (is_device_ptr(src)) { *dev = src; return 0; }
+  if (buf.ensure(bytes)) return fail(SIRRT_E_CUDA, "cudaMalloc(staging) failed");
+  CU(cudaMemcpyAsync(buf.p, src, bytes, cudaMemcpyHostToDevice, s->stream));
+  *dev = buf.p;
+  return 0;
+}
+
+static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, int32_t* table, int Kmax, uint32_t* bits,
+                          uint64_t* near_contact_count) {
+  const int W = s->tb.n_tiles;
+  CU(cudaSetDevice(s->device));
+  memset(s->stats, 0, sizeof s->stats);
+  uint32_t* d_bits = nullptr;
+  const bool bits_dev = bits && is_device_ptr(bits);
+  if (bits_dev) d_bits = bits;
+  else {
+    if (s->bits.ensure((size_t)N * W * sizeof(uint32_t))) return fail(SIRRT_E_CUDA, "cudaMalloc(bits) failed");
+    d_bits = s->bits.as<uint32_t>();
+  }
+  int rc = run_bits(s, q, N, semantics, d_bits);
+  if (rc) return rc;
+  if (table) {
+    const size_t tbytes = (size_t)N * (1 + 2 * Kmax) * sizeof(int32_t);
+    int32_t* d_table = table;
+    const bool tdev = is_device_ptr(table);
+    if (!tdev) {
+      if (s->table.ensure(tbytes)) return fail(SIRRT_E_CUDA, "cudaMalloc(table) failed");
+      d_table = s->table.as<int32_t>();
+    }
+    if ((rc = run_intervals(s, d_bits, N, d_table, Kmax))) return rc;
+    if (!tdev) CU(cudaMemcpyAsync(table, d_table, tbytes, cudaMemcpyDeviceToHost, s->stream));
+  }
+  if (bits && !bits_dev) CU(cudaMemcpyAsync(bits, d_bits, (size_t)N * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  if (near_contact_count) *near_contact_count = s->stats[2];
+  return SIRRT_OK;
+}
+
+extern "C" int sirrt_safe_intervals_batch(sirrt_scene* s, const float* q_soa, int64_t N, int32_t* table, int Kmax,
+                                          uint32_t* bits, uint64_t* near_contact_count) {
+  if (!s || !q_soa || N < 0 || (table && Kmax < 1) || (!table && !bits)) return fail(SIRRT_E_ARG, "sirrt_safe_intervals_batch: bad argument");
+  if (N == 0) { if (near_contact_count) *near_contact_count = 0; return SIRRT_OK; }
+  if (N > 0x7fffffffll) return fail(SIRRT_E_ARG, "N exceeds 2^31-1 configurations per call");
+  CU(cudaSetDevice(s->device));
+  const void* dq = nullptr;
+  int rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq);
+  if (rc) return rc;
+  QView q{(const float*)dq, nullptr, N, 0, N, s->hs.dof};
+  return bits_and_table(s, q, N, SIRRT_SEM_INTERVAL, table, Kmax, bits, near_contact_count);
+}
+
+extern "C" int sirrt_collision_bits_f64(sirrt_scene* s, const double* q_aos, int64_t N, int semantics, uint32_t* bits) {
+  if (!s || !q_aos || !bits || N < 0 || (semantics != SIRRT_SEM_INTERVAL && semantics != SIRRT_SEM_FRAME)) return fail(SIRRT_E_ARG, "sirrt_collision_bits_f64: bad argument");
+  if (N == 0) return SIRRT_OK;
+  CU(cudaSetDevice(s->device));
+  const void* dq = nullptr;
+  int rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq);
+  if (rc) return rc;
+  QView q{nullptr, (const double*)dq, N, 0, N, s->hs.dof};
+  return bits_and_table(s, q, N, semantics, nullptr, 0, bits, nullptr);
+}
+
+// ---- a4: independent (configuration, frame) cells ------------------------------------------------
+static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_frames, uint8_t* d_out, int semantics) {
+  cudaStream_t st = s->stream;
+  if (s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(work list) failed");
+  if (s->counts.ensure(4 * sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc(counters) failed");
+  // cells are cheap (one frame each): the work list cannot overflow for chunk sizes below the cap / (L*slots)
+  const long long per = std::max(1ll, (long long)s->wl_cap / std::max(1, 2 * s->tb.robot.n_links * s->tb.n_slots));
+  for (long long n0 = 0; n0 < N; n0 += per) {
+    QView qv = q;
+    qv.n0 = n0; qv.cnt = std::min(per, N - n0);
+    CU(cudaMemsetAsync(s->counts.p, 0, 4 * sizeof(unsigned), st));
+    WorkList wl{s->work.as<WorkItem>(), s->counts.as<unsigned>(), s->wl_cap};
+    CellParams P{};
+    P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.frames = d_frames; P.out = d_out; P.semantics = semantics; P.band = (float)s->band;
+    const int grid = grid_for(qv.cnt, s->n_sm, 8);
+    if (s->tb.has_hull) k_check_cells<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
+    else k_check_cells<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
+    RecheckParams R{};
+    R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
+    R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
+    k_recheck<<<s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
+    s->stats[0] += 2;
+    CU(cudaGetLastError());
+  }
+  return SIRRT_OK;
+}
+
+static int check_frames_common(sirrt_scene* s, const float* q_soa, const double* q_aos, const int32_t* frames, int64_t N, uint8_t* collided) {
+  if (!s || (!q_soa && !q_aos) || !frames || !collided || N < 0) return fail(SIRRT_E_ARG, "sirrt_check_frames_batch: bad argument");
+  if (N == 0) return SIRRT_OK;
+  if (N > 0x7fffffffll) return fail(SIRRT_E_ARG, "N exceeds 2^31-1 cells per call");
+  CU(cudaSetDevice(s->device));
+  memset(s->stats, 0, sizeof s->stats);
+  const void *dq = nullptr, *df = nullptr;
+  int rc;
+  if (q_soa) rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq);
+  else rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq);
+  if (rc) return rc;
+  if ((rc = stage_in(s, s->frames, frames, (size_t)N * sizeof(int32_t), &df))) return rc;
+  const bool odev = is_device_ptr(collided);
+  uint8_t* d_out = collided;
+  if (!odev) {
+    if (s->cells.ensure((size_t)N)) return fail(SIRRT_E_CUDA, "cudaMalloc(cells) failed");
+    d_out = s->cells.as<uint8_t>();
+  }
+  QView q{q_soa ? (const float*)dq : nullptr, q_soa ? nullptr : (const double*)dq, N, 0, N, s->hs.dof};
+  if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME))) return rc;
+  if (!odev) CU(cudaMemcpyAsync(collided, d_out, (size_t)N, cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  return SIRRT_OK;
+}
+extern "C" int sirrt_check_frames_batch(sirrt_scene* s, const float* q_soa, const int32_t* frames, int64_t N, uint8_t* collided) {
+  return check_frames_common(s, q_soa, nullptr, frames, N, collided);
+}
+extern "C" int sirrt_check_frames_batch_f64(sirrt_scene* s, const double* q_aos, const int32_t* frames, int64_t N, uint8_t* collided) {
+  return check_frames_common(s, nullptr, q_aos, frames, N, collided);
+}
+
+// ---- single-call drop-ins ------------------------------------------------------------------------
+extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo_hi, int cap, int* n_out) {
+  if (!s || !q || !n_out || cap < 0 || (cap > 0 && !lo_hi)) return fail(SIRRT_E_ARG, "sirrt_safe_intervals: bad argument");
+  CU(cudaSetDevice(s->device));
+  memset(s->stats, 0, sizeof s->stats);
+  const int dof = s->hs.dof, W = s->tb.n_tiles, T = s->tb.T;
+  const int Kmax = std::max(1, std::min(cap, (T + 1) / 2));
+  const size_t tbytes = (size_t)(1 + 2 * Kmax) * sizeof(int32_t);
+  if (s->misc.ensure(sizeof(double) * dof + (size_t)W * 4 + tbytes + 64)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  double* dq = s->misc.as<double>();
+  uint32_t* d_bits = (uint32_t*)(dq + dof);
+  int32_t* d_table = (int32_t*)(d_bits + W);
+  std::vector<int32_t> host_table(1 + 2 * Kmax);
+  CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyHostToDevice, s->stream));
+  QView qv{nullptr, dq, 1, 0, 1, dof};
+  int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits);
+  if (rc) return rc;
+  if ((rc = run_intervals(s, d_bits, 1, d_table, Kmax))) return rc;
+  CU(cudaMemcpyAsync(host_table.data(), d_table, tbytes, cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  *n_out = host_table[0];
+  const int n = std::min(host_table[0], std::min(cap, Kmax));
+  for (int i = 0; i < 2 * n; i++) lo_hi[i] = host_table[1 + i];
+  if (host_table[0] > cap) return fail(SIRRT_E_OVERFLOW, "sirrt_safe_intervals: more intervals than cap");
+  return SIRRT_OK;
+}
+
+extern "C" int sirrt_check_frame(sirrt_scene* s, const double* q, int frame, int* collided) {
+  if (!s || !q || !collided) return fail(SIRRT_E_ARG, "sirrt_check_frame: bad argument");
+  int32_t f = frame;
+  uint8_t out = 0;
+  int rc = check_frames_common(s, nullptr, q, &f, 1, &out);
+  if (rc) return rc;
+  *collided = out;
+  return SIRRT_OK;
+}
+
+// ---- a5: edge validation (PlannerConnect::is_collision_motion, PlannerConnect.cpp:862-897) -------
+struct EdgeParams {
+  const double *q0, *q1, *t0, *t1;
+  const long long* offs;  // [n_edges+1] first cell of each edge; steps = offs[e+1]-offs[e]-1, 0 cells = gated edge
+  long long n_edges, n_cells;
+  int dof;
+  double* q_cells;   // [n_cells][dof]
+  int32_t* frames;   // [n_cells]
+};
+
+// one thread per cell: q = q0 + dir*s/steps (:885), frame = (int)(t0 + (t1-t0)*s/steps) (:886).
+// Explicit _rn intrinsics keep nvcc from contracting into FMA so the values equal the host's.
+__global__ void k_edge_cells(const __grid_constant__ EdgeParams P) {
+  const long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= P.n_cells) return;
+  long long lo = 0, hi = P.n_edges;  // largest e with offs[e] <= c
+  while (hi - lo > 1) { const long long mid = (lo + hi) >> 1; if (P.offs[mid] <= c) lo = mid; else hi = mid; }
+  const long long e = lo;
+  const double s = (double)(c - P.offs[e]), steps = (double)(P.offs[e + 1] - P.offs[e] - 1);
+  for (int i = 0; i < P.dof; i++) {
+    const double a = P.q0[e * P.dof + i], dir = __dsub_rn(P.q1[e * P.dof + i], a);
+    P.q_cells[c * P.dof + i] = __dadd_rn(a, __ddiv_rn(__dmul_rn(dir, s), steps));
+  }
+  const double t0 = P.t0[e], dt = __dsub_rn(P.t1[e], t0);
+  const double tf = __dadd_rn(t0, __ddiv_rn(__dmul_rn(dt, s), steps));
+  P.frames[c] = (tf >= 2147483647.0 || tf <= -2147483648.0 || tf != tf) ? -1 : (int)tf;
+}
+
+struct EdgeFirstParams {
+  const long long* offs;
+  const uint8_t* cells;
+  const double* q_cells;
+  long long n_edges;
+  int dof;
+  int32_t* first;     // in: -1 (to be evaluated) or the host's gate code (-2 / -3)
+  double* coord;      // [n_edges][dof] or null
+};
+__global__ void k_edge_first(const __grid_constant__ EdgeFirstParams P) {
+  const int lane = threadIdx.x & 31;
+  const long long e = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (e >= P.n_edges) return;
+  const long long c0 = P.offs[e], c1 = P.offs[e + 1];
+  int found = -1;
+  for (long long b = c0; b < c1 && found < 0; b += 32) {
+    const long long c = b + lane;
+    const unsigned m = __ballot_sync(SIRRT_FULL, c < c1 && P.cells[c]);
+    if (m) found = (int)(b - c0) + __ffs(m) - 1;
+  }
+  if (c1 > c0 && lane == 0) P.first[e] = found;
+  if (P.coord && found >= 0)
+    for (int i = lane; i < P.dof; i += 32) P.coord[e * P.dof + i] = P.q_cells[(c0 + found) * P.dof + i];
+}
+
+extern "C" int sirrt_edge_check_batch(sirrt_scene* s, const double* q0, const double* q1, const double* t0, const double* t1,
+                                      int64_t n_edges, double vmax, int32_t* first, double* coord) {
+  if (!s || !q0 || !q1 || !t0 || !t1 || !first || n_edges < 0) return fail(SIRRT_E_ARG, "sirrt_edge_check_batch: bad argument");
+  if (n_edges == 0) return SIRRT_OK;
+  if (is_device_ptr(q0) || is_device_ptr(q1) || is_device_ptr(t0) || is_device_ptr(t1) || is_device_ptr(first) || (coord && is_device_ptr(coord)))
+    return fail(SIRRT_E_ARG, "sirrt_edge_check_batch takes host buffers (edge step counts are planned on the host)");
+  CU(cudaSetDevice(s->device));
+  memset(s->stats, 0, sizeof s->stats);
+  const int dof = s->hs.dof;
+  std::vector<long long> offs(n_edges + 1);
+  long long cells = 0;
+  for (int64_t e = 0; e < n_edges; e++) {
+    offs[e] = cells;
+    first[e] = -1;
+    const double a = t0[e], b = t1[e];
+    if (a >= b) { first[e] = -2; continue; }  // :865
+    double n2 = 0;
+    for (int i = 0; i < dof; i++) { const double d = q1[e * dof + i] - q0[e * dof + i]; n2 += d * d; }
+    const double norm = sqrt(n2);
+    if (vmax > 0 && (norm * ((double)s->hs.fps) / (b - a)) > (vmax + 0.001)) { first[e] = -3; continue; }  // :872
+    const double x1 = norm / 0.1, x2 = b - a + 0.5;
+    long long steps = x1 < 2e9 ? (long long)(int)x1 : 2000000000ll, s2 = x2 < 2e9 ? (long long)(int)x2 : 2000000000ll;  // :879
+    steps = std::max(std::max(steps, s2), 1ll);
+    cells += steps + 1;
+    if (cells > 0x7fffffffll) return fail(SIRRT_E_ARG, "edge batch expands to more than 2^31-1 cells");
+  }
+  offs[n_edges] = cells;
+  if (cells == 0) return SIRRT_OK;
+  cudaStream_t st = s->stream;
+  const size_t eb = (size_t)n_edges * dof * sizeof(double);
+  size_t need = 2 * eb + 2 * (size_t)n_edges * sizeof(double) + (size_t)(n_edges + 1) * sizeof(long long) + (size_t)n_edges * sizeof(int32_t) + eb + 256;
+  if (s->misc.ensure(need)) return fail(SIRRT_E_CUDA, "cudaMalloc(edges) failed");
+  char* p = (char*)s->misc.p;
+  double* d_q0 = (double*)p; p += eb;
+  double* d_q1 = (double*)p; p += eb;
+  double* d_t0 = (double*)p; p += n_edges * sizeof(double);
+  double* d_t1 = (double*)p; p += n_edges * sizeof(double);
+  long long* d_offs = (long long*)p; p += (n_edges + 1) * sizeof(long long);
+  double* d_coord = (double*)p; p += eb;
+  int32_t* d_first = (int32_t*)p;
+  if (s->misc2.ensure((size_t)cells * dof * sizeof(double))) return fail(SIRRT_E_CUDA, "cudaMalloc(edge cells) failed");
+  if (s->frames.ensure((size_t)cells * sizeof(int32_t))) return fail(SIRRT_E_CUDA, "cudaMalloc(edge frames) failed");
+  if (s->cells.ensure((size_t)cells)) return fail(SIRRT_E_CUDA, "cudaMalloc(cells) failed");
+  CU(cudaMemcpyAsync(d_q0, q0, eb, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_q1, q1, eb, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_t0, t0, n_edges * sizeof(double), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_t1, t1, n_edges * sizeof(double), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_offs, offs.data(), (n_edges + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_first, first, n_edges * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  if (coord) CU(cudaMemsetAsync(d_coord, 0, eb, st));
+  EdgeParams E{d_q0, d_q1, d_t0, d_t1, d_offs, n_edges, cells, dof, s->misc2.as<double>(), s->frames.as<int32_t>()};
+  k_edge_cells<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(E);
+  QView qv{nullptr, s->misc2.as<double>(), cells, 0, cells, dof};
+  int rc = run_cells(s, qv, cells, s->frames.as<int32_t>(), s->cells.as<uint8_t>(), SIRRT_SEM_FRAME);
+  if (rc) return rc;
+  EdgeFirstParams F{d_offs, s->cells.as<uint8_t>(), s->misc2.as<double>(), n_edges, dof, d_first, coord ? d_coord : nullptr};
+  k_edge_first<<<(unsigned)((n_edges + 7) / 8), 256, 0, st>>>(F);
+  s->stats[0] += 2;
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(first, d_first, n_edges * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  if (coord) CU(cudaMemcpyAsync(coord, d_coord, eb, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return SIRRT_OK;
+}

@@ -1,0 +1,336 @@
+// sirrt_api_knn.inl -- kNN store, link distances and the in-process multi-GPU sharder.
+// Included by sirrt_api.cu.
+#include <thread>
+
+#include "sirrt_knn.cuh"
+
+struct sirrt_knn {
+  int device = 0, dim = 0, n_sm = 148;
+  long long cap = 0, n = 0;
+  cudaStream_t stream = nullptr;
+  double* pts = nullptr;
+  DevBuf stage, qbuf, part_d, part_i, out_i, out_d, hits, count;
+};
+
+extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn** out) {
+  if (!out || dim < 1 || dim > SIRRT_KNN_MAXDIM || capacity < 1 || capacity > 0x7fffffffll) return fail(SIRRT_E_ARG, "sirrt_knn_create: bad argument");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { cudaGetLastError(); return fail(SIRRT_E_CUDA, "no CUDA device (libsirrt_b200 has no CPU fallback)"); }
+  if (device < 0 || device >= ndev) return fail(SIRRT_E_ARG, "device index out of range");
+  CU(cudaSetDevice(device));
+  sirrt_knn* k = new (std::nothrow) sirrt_knn;
+  if (!k) return fail(SIRRT_E_ARG, "out of memory");
+  k->device = device; k->dim = dim; k->cap = capacity;
+  cudaDeviceGetAttribute(&k->n_sm, cudaDevAttrMultiProcessorCount, device);
+  if (cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&k->pts, sizeof(double) * dim * (size_t)capacity) != cudaSuccess) {
+    cudaGetLastError();
+    if (k->stream) cudaStreamDestroy(k->stream);
+    delete k;
+    return fail(SIRRT_E_CUDA, "sirrt_knn_create: allocation failed");
+  }
+  *out = k;
+  return SIRRT_OK;
+}
+extern "C" int sirrt_knn_destroy(sirrt_knn* k) {
+  if (!k) return SIRRT_OK;
+  cudaSetDevice(k->device);
+  cudaStreamSynchronize(k->stream);
+  cudaFree(k->pts);
+  for (DevBuf* b : {&k->stage, &k->qbuf, &k->part_d, &k->part_i, &k->out_i, &k->out_d, &k->hits, &k->count}) b->release();
+  cudaStreamDestroy(k->stream);
+  cudaGetLastError();
+  delete k;
+  return SIRRT_OK;
+}
+extern "C" int sirrt_knn_size(const sirrt_knn* k, int64_t* n) {
+  if (!k || !n) return fail(SIRRT_E_ARG, "null argument");
+  *n = k->n;
+  return SIRRT_OK;
+}
+extern "C" int sirrt_knn_clear(sirrt_knn* k) {
+  if (!k) return fail(SIRRT_E_ARG, "null argument");
+  k->n = 0;
+  return SIRRT_OK;
+}
+
+// Tree::add_vertex (MSIRRT/src/Tree.cpp:18-36): the index of a point is its insertion order
+extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
+  if (!k || !pts || n < 0) return fail(SIRRT_E_ARG, "sirrt_knn_add: bad argument");
+  if (n == 0) return SIRRT_OK;
+  if (k->n + n > k->cap) return fail(SIRRT_E_OVERFLOW, "sirrt_knn_add: capacity exceeded");
+  CU(cudaSetDevice(k->device));
+  const size_t bytes = sizeof(double) * k->dim * (size_t)n;
+  const double* src = pts;
+  if (!is_device_ptr(pts)) {
+    if (k->stage.ensure(bytes)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+    CU(cudaMemcpyAsync(k->stage.p, pts, bytes, cudaMemcpyHostToDevice, k->stream));
+    src = k->stage.as<double>();
+  }
+  const long long tot = (long long)n * k->dim;
+  k_knn_append<<<(unsigned)((tot + 255) / 256), 256, 0, k->stream>>>(src, n, k->dim, k->pts, k->cap, k->n);
+  CU(cudaGetLastError());
+  CU(cudaStreamSynchronize(k->stream));
+  k->n += n;
+  return SIRRT_OK;
+}
+
+static int knn_queries_in(sirrt_knn* k, const double* queries, int64_t nq, const double** dq) {
+  if (is_device_ptr(queries)) { *dq = queries; return 0; }
+  const size_t bytes = sizeof(double) * k->dim * (size_t)nq;
+  if (k->qbuf.ensure(bytes)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  CU(cudaMemcpyAsync(k->qbuf.p, queries, bytes, cudaMemcpyHostToDevice, k->stream));
+  *dq = k->qbuf.as<double>();
+  return 0;
+}
+
+// PlannerConnect::get_nearest_node (PlannerConnect.cpp:382-392): exact 1-NN
+extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq, int64_t* idx, double* dist2) {
+  if (!k || !queries || !idx || nq < 0) return fail(SIRRT_E_ARG, "sirrt_knn_nearest: bad argument");
+  if (nq == 0) return SIRRT_OK;
+  if (nq > 65535) {  // grid.y limit: recurse over slabs
+    for (int64_t o = 0; o < nq; o += 65535) {
+      int rc = sirrt_knn_nearest(k, queries + o * k->dim, std::min<int64_t>(65535, nq - o), idx + o, dist2 ? dist2 + o : nullptr);
+      if (rc) return rc;
+    }
+    return SIRRT_OK;
+  }
+  CU(cudaSetDevice(k->device));
+  if (k->n == 0) { for (int64_t i = 0; i < nq; i++) { idx[i] = -1; if (dist2) dist2[i] = 1.0 / 0.0; } return SIRRT_OK; }
+  const double* dq = nullptr;
+  int rc = knn_queries_in(k, queries, nq, &dq);
+  if (rc) return rc;
+  // enough blocks to fill the machine, at least ~4 points per thread per split
+  long long want = std::max(1ll, (long long)k->n_sm * 4 / nq);
+  int n_split = (int)std::max(1ll, std::min(want, (k->n + 4 * SIRRT_KNN_THREADS - 1) / (4 * SIRRT_KNN_THREADS)));
+  if (k->part_d.ensure(sizeof(double) * nq * n_split) || k->part_i.ensure(sizeof(long long) * nq * n_split) ||
+      k->out_i.ensure(sizeof(long long) * nq) || k->out_d.ensure(sizeof(double) * nq))
+    return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  KnnStore S{k->pts, k->cap, k->n, k->dim};
+  const bool idev = is_device_ptr(idx), ddev = dist2 && is_device_ptr(dist2);
+  long long* o_i = idev ? (long long*)idx : k->out_i.as<long long>();
+  double* o_d = dist2 ? (ddev ? dist2 : k->out_d.as<double>()) : nullptr;
+  k_knn_partial<<<dim3(n_split, (unsigned)nq), SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, k->part_d.as<double>(), k->part_i.as<long long>());
+  k_knn_final<<<(unsigned)((nq + 7) / 8), 256, 0, k->stream>>>(k->part_d.as<double>(), k->part_i.as<long long>(), n_split, nq, o_i, o_d);
+  CU(cudaGetLastError());
+  if (!idev) CU(cudaMemcpyAsync(idx, o_i, sizeof(long long) * nq, cudaMemcpyDeviceToHost, k->stream));
+  if (dist2 && !ddev) CU(cudaMemcpyAsync(dist2, o_d, sizeof(double) * nq, cudaMemcpyDeviceToHost, k->stream));
+  CU(cudaStreamSynchronize(k->stream));
+  return SIRRT_OK;
+}
+
+// PlannerConnect::get_nearest_node_by_radius (PlannerConnect.cpp:394-412): strict dist2 < r2
+extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, int64_t* idx, int64_t cap, int64_t* n_out) {
+  if (!k || !query || !n_out || cap < 0 || (cap > 0 && !idx)) return fail(SIRRT_E_ARG, "sirrt_knn_radius: bad argument");
+  *n_out = 0;
+  if (k->n == 0) return SIRRT_OK;
+  CU(cudaSetDevice(k->device));
+  const double* dq = nullptr;
+  int rc = knn_queries_in(k, query, 1, &dq);
+  if (rc) return rc;
+  if (k->hits.ensure(sizeof(int) * (size_t)k->n) || k->count.ensure(sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  CU(cudaMemsetAsync(k->count.p, 0, sizeof(unsigned), k->stream));
+  KnnStore S{k->pts, k->cap, k->n, k->dim};
+  const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
+  k_knn_radius<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, r2, k->hits.as<int>(), k->count.as<unsigned>());
+  CU(cudaGetLastError());
+  unsigned cnt = 0;
+  CU(cudaMemcpyAsync(&cnt, k->count.p, sizeof cnt, cudaMemcpyDeviceToHost, k->stream));
+  CU(cudaStreamSynchronize(k->stream));
+  *n_out = cnt;
+  if (cnt == 0) return SIRRT_OK;
+  std::vector<int> h(cnt);
+  CU(cudaMemcpy(h.data(), k->hits.p, sizeof(int) * cnt, cudaMemcpyDeviceToHost));
+  std::sort(h.begin(), h.end());
+  for (int64_t i = 0; i < std::min<int64_t>(cap, cnt); i++) idx[i] = h[i];
+  return SIRRT_OK;
+}
+
+extern "C" int sirrt_knn_topk(sirrt_knn* k, const double* queries, int64_t nq, int kk, int64_t* idx, double* dist2) {
+  if (!k || !queries || !idx || nq < 0 || kk < 1 || kk > 1024) return fail(SIRRT_E_ARG, "sirrt_knn_topk: bad argument");
+  if (nq == 0) return SIRRT_OK;
+  CU(cudaSetDevice(k->device));
+  const double* dq = nullptr;
+  int rc = knn_queries_in(k, queries, nq, &dq);
+  if (rc) return rc;
+  if (k->out_i.ensure(sizeof(long long) * nq * kk) || k->out_d.ensure(sizeof(double) * nq * kk)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  KnnStore S{k->pts, k->cap, k->n, k->dim};
+  k_knn_topk<<<(unsigned)nq, SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, kk, k->out_i.as<long long>(), k->out_d.as<double>());
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(idx, k->out_i.p, sizeof(long long) * nq * kk, cudaMemcpyDeviceToHost, k->stream));
+  if (dist2) CU(cudaMemcpyAsync(dist2, k->out_d.p, sizeof(double) * nq * kk, cudaMemcpyDeviceToHost, k->stream));
+  CU(cudaStreamSynchronize(k->stream));
+  return SIRRT_OK;
+}
+
+// ---- a9: CollisionManager::get_distances (CollisionManager.cpp:382-420, DistanceCallback :549-600) ----
+struct DistParams {
+  DScene sc;
+  const double* q;  // [dof]
+  int dof, frame, n_obst;
+  double* out;      // [n_links][n_obst]
+};
+__global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32) k_pair_distances(const __grid_constant__ DRobot rb, const __grid_constant__ DistParams P) {
+  const int lane = threadIdx.x & 31;
+  const int pair = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5);
+  if (pair >= rb.n_links * P.n_obst) return;
+  const int l = pair / P.n_obst, c = pair % P.n_obst;
+  double q[SIRRT_MAXJ];
+  for (int j = 0; j < rb.n_joints; j++) q[j] = j < P.dof ? P.q[j] : 0.0;
+  LinkXfD X[SIRRT_MAXL];
+  fk_links(rb, q, X);
+  const DSlot S = P.sc.slots[c];
+  const double* pose = P.sc.pose_d + ((size_t)c * P.sc.Tp + P.frame) * 12;
+  int res;
+  const double d = recheck_pair(rb, P.sc, X[l], l, P.sc.shapes[S.shape], pose, lane, &res);
+  if (lane == 0) P.out[pair] = d;
+}
+
+extern "C" int sirrt_get_distances(sirrt_scene* s, const double* q, int frame, double* min_dist, int* is_collision) {
+  if (!s || !q || !min_dist || !is_collision) return fail(SIRRT_E_ARG, "sirrt_get_distances: bad argument");
+  if (frame < 0 || frame >= s->hs.T) return fail(SIRRT_E_ARG, "sirrt_get_distances: frame out of range");
+  CU(cudaSetDevice(s->device));
+  const int L = s->hs.robot.n_links, C = s->hs.C, dof = s->hs.dof;
+  *is_collision = 0;
+  for (int l = 0; l < L; l++) min_dist[l] = 1.0 / 0.0;
+  if (C == 0) { for (int l = 0; l < L; l++) min_dist[l] = 1e300; return SIRRT_OK; }
+  if (s->misc.ensure(sizeof(double) * (dof + (size_t)L * C))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  double* dq = s->misc.as<double>();
+  double* dout = dq + dof;
+  CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyHostToDevice, s->stream));
+  DistParams P{s->d, dq, dof, frame, C, dout};
+  k_pair_distances<<<(L * C + SIRRT_WARPS_PER_BLOCK - 1) / SIRRT_WARPS_PER_BLOCK, SIRRT_WARPS_PER_BLOCK * 32, 0, s->stream>>>(s->tb.robot, P);
+  CU(cudaGetLastError());
+  std::vector<double> h((size_t)L * C);
+  CU(cudaMemcpyAsync(h.data(), dout, sizeof(double) * h.size(), cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  for (int l = 0; l < L; l++) {
+    double m = 1e300;
+    for (int c = 0; c < C; c++) m = std::min(m, h[(size_t)l * C + c]);
+    min_dist[l] = m;
+    if (m - SIRRT_SECURITY_MARGIN <= SIRRT_COLLISION_THRESHOLD) { *is_collision = 1; break; }  // reference returns at the first colliding link
+  }
+  return SIRRT_OK;
+}
+
+// link world transforms of the planned robot (a1), [n_links][12] = R row-major then t; evaluated by
+// the same device FK the collision kernels use
+__global__ void k_fk_dump(const __grid_constant__ DRobot rb, const double* q, int dof, double* out) {
+  if (threadIdx.x || blockIdx.x) return;
+  double qq[SIRRT_MAXJ];
+  for (int j = 0; j < rb.n_joints; j++) qq[j] = j < dof ? q[j] : 0.0;
+  LinkXfD X[SIRRT_MAXL];
+  fk_links(rb, qq, X);
+  for (int l = 0; l < rb.n_links; l++) {
+    for (int k = 0; k < 9; k++) out[12 * l + k] = X[l].R[k];
+    for (int k = 0; k < 3; k++) out[12 * l + 9 + k] = X[l].t[k];
+  }
+}
+extern "C" int sirrt_scene_fk(sirrt_scene* s, const double* q, double* out) {
+  if (!s || !q || !out) return fail(SIRRT_E_ARG, "sirrt_scene_fk: bad argument");
+  CU(cudaSetDevice(s->device));
+  const int L = s->hs.robot.n_links, dof = s->hs.dof;
+  if (s->misc.ensure(sizeof(double) * (dof + 12 * (size_t)L))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  double* dq = s->misc.as<double>();
+  CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyHostToDevice, s->stream));
+  k_fk_dump<<<1, 32, 0, s->stream>>>(s->tb.robot, dq, dof, dq + dof);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(out, dq + dof, sizeof(double) * 12 * L, cudaMemcpyDeviceToHost, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  return SIRRT_OK;
+}
+
+// ---- multi-GPU inside one process: contiguous shards of the configuration batch, no collective ----
+struct sirrt_multi {
+  std::vector<sirrt_scene*> scenes;
+};
+
+extern "C" void sirrt_multi_destroy(sirrt_multi* m) {
+  if (!m) return;
+  for (sirrt_scene* s : m->scenes) sirrt_scene_destroy(s);
+  delete m;
+}
+extern "C" int sirrt_multi_create(const void* pack, size_t bytes, const int* devices, int n_dev, int parity_mode, sirrt_multi** out) {
+  if (!pack || !devices || n_dev < 1 || !out) return fail(SIRRT_E_ARG, "sirrt_multi_create: bad argument");
+  *out = nullptr;
+  sirrt_multi* m = new (std::nothrow) sirrt_multi;
+  if (!m) return fail(SIRRT_E_ARG, "out of memory");
+  for (int i = 0; i < n_dev; i++) {
+    sirrt_scene* s = nullptr;
+    int rc = sirrt_scene_create_from_pack(pack, bytes, devices[i], parity_mode, &s);
+    if (rc) { sirrt_multi_destroy(m); return rc; }
+    m->scenes.push_back(s);
+  }
+  *out = m;
+  return SIRRT_OK;
+}
+extern "C" int sirrt_multi_safe_intervals_batch(sirrt_multi* m, const float* q_soa_host, int64_t N, int32_t* table, int Kmax,
+                                                uint32_t* bits, uint64_t* near_contact_count) {
+  if (!m || !q_soa_host || N < 0 || (table && Kmax < 1) || (!table && !bits)) return fail(SIRRT_E_ARG, "sirrt_multi_safe_intervals_batch: bad argument");
+  if (is_device_ptr(q_soa_host) || (table && is_device_ptr(table)) || (bits && is_device_ptr(bits))) return fail(SIRRT_E_ARG, "sirrt_multi_safe_intervals_batch takes host buffers");
+  const int G = (int)m->scenes.size(), dof = m->scenes[0]->hs.dof, W = m->scenes[0]->tb.n_tiles;
+  std::vector<int> rcs(G, 0);
+  std::vector<uint64_t> nears(G, 0);
+  std::vector<std::string> errs(G);
+  std::vector<std::thread> th;
+  for (int g = 0; g < G; g++) {
+    th.emplace_back([&, g]() {
+      const int64_t n0 = N * g / G, n1 = N * (g + 1) / G, cnt = n1 - n0;
+      if (cnt <= 0) return;
+      std::vector<float> q((size_t)cnt * dof);  // shard of the SoA batch: every joint row is a contiguous slice
+      for (int j = 0; j < dof; j++) memcpy(&q[(size_t)j * cnt], q_soa_host + (size_t)j * N + n0, sizeof(float) * cnt);
+      rcs[g] = sirrt_safe_intervals_batch(m->scenes[g], q.data(), cnt, table ? table + (size_t)n0 * (1 + 2 * Kmax) : nullptr, Kmax,
+                                          bits ? bits + (size_t)n0 * W : nullptr, &nears[g]);
+      if (rcs[g]) errs[g] = sirrt_last_error();
+    });
+  }
+  for (auto& t : th) t.join();
+  uint64_t tot = 0;
+  for (int g = 0; g < G; g++) {
+    if (rcs[g]) return fail(rcs[g], "%s", errs[g].c_str());
+    tot += nears[g];
+  }
+  if (near_contact_count) *near_contact_count = tot;
+  return SIRRT_OK;
+}
+
+// ---- FP32 roofline denominator: dependent-chain-free FFMA throughput of this device ---------------
+__global__ void __launch_bounds__(256) k_fp32_peak(float* out, int iters, float b, float c) {
+  float a0 = threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  for (int i = 0; i < iters; i++) {
+#pragma unroll
+    for (int u = 0; u < 8; u++) {
+      a0 = fmaf(a0, b, c); a1 = fmaf(a1, b, c); a2 = fmaf(a2, b, c); a3 = fmaf(a3, b, c);
+      a4 = fmaf(a4, b, c); a5 = fmaf(a5, b, c); a6 = fmaf(a6, b, c); a7 = fmaf(a7, b, c);
+    }
+  }
+  const float r = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  if (r == 12345.678f) out[0] = r;  // keeps the chain alive without a store per thread
+}
+extern "C" int sirrt_measure_fp32_peak(int device, double* tflops) {
+  if (!tflops) return fail(SIRRT_E_ARG, "null argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) { cudaGetLastError(); return fail(SIRRT_E_CUDA, "no such CUDA device"); }
+  CU(cudaSetDevice(device));
+  int n_sm = 148;
+  cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+  float* d = nullptr;
+  CU(cudaMalloc(&d, 4));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+  const int iters = 4096, blocks = n_sm * 8;
+  double best = 0;
+  for (int rep = 0; rep < 5; rep++) {
+    CU(cudaEventRecord(e0, 0));
+    k_fp32_peak<<<blocks, 256>>>(d, iters, 1.0000001f, 1e-9f);
+    CU(cudaEventRecord(e1, 0));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    const double fl = (double)blocks * 256 * iters * 64 * 2;
+    if (rep > 0) best = std::max(best, fl / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  *tflops = best;
+  return SIRRT_OK;
+}

@@ -54,7 +54,8 @@ struct DSlot {
   int is_static;    // identical pose at every frame
   int is_robot;     // robot-obstacle link
   int rot_identity; // every pose has R == I exactly (skip the rotation on the fast path)
-  int pad[3];
+  float br;         // bounding-sphere radius around bcw (covers the shifted geometry too)
+  int pad[2];
 };
 
 struct DScene {
@@ -152,7 +153,7 @@ __device__ inline void fk_links(const DRobot& rb, const double* q, LinkXfD* out)
 }
 
 // ---------------------------------------------------------------------------------------------
-// closed-form core distances (same formulas as oracle/sirrt_oracle.c, written independently of
+// closed-form core distances (same formulas as the test-only CPU checker, written independently of
 // precision)
 // ---------------------------------------------------------------------------------------------
 template <typename T> __device__ __forceinline__ T pt_seg_dist2(const T* p, const T* a, const T* b) {

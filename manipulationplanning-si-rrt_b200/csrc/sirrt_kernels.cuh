@@ -18,7 +18,8 @@
 struct QView {           // configuration batch: float SoA [dof][N] or double AoS [N][dof]
   const float* f_soa;
   const double* d_aos;
-  long long N;
+  long long N;      // row stride of the SoA layout (= total configurations of the caller's batch)
+  long long n0, cnt; // the kernel processes configurations n0 .. n0+cnt-1
   int dof;
 };
 __device__ __forceinline__ double load_q(const QView& q, long long n, int j) {
@@ -173,15 +174,16 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   WarpCtx& W = ctx[wib];
   const DScene& sc = P.sc;
-  const long long n_items = P.q.N * P.n_chunks;
+  const long long n_items = P.q.cnt * P.n_chunks;
   const long long warp0 = (long long)blockIdx.x * SIRRT_WARPS_PER_BLOCK + wib;
   const long long n_warps = (long long)gridDim.x * SIRRT_WARPS_PER_BLOCK;
   const bool want_true_rob = (sc.parity_mode == 1) || (P.semantics == 0);
   const bool want_shift_rob = (sc.parity_mode == 0);
   const float band = P.band;
+  unsigned int n_exact = 0;  // narrowphase pair tests evaluated by this lane (roofline accounting)
 
   for (long long item = warp0; item < n_items; item += n_warps) {
-    const long long n = item / P.n_chunks;
+    const long long n = P.q.n0 + item / P.n_chunks;
     const int chunk = (int)(item % P.n_chunks);
     const int tile_lo = chunk * P.tiles_per_chunk;
     const int tile_hi = min(tile_lo + P.tiles_per_chunk, sc.n_tiles);
@@ -211,6 +213,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
       if (do_true && !coop_true) {
         load_pose(sc, slot, f, R, t, sh.type != SH_SPHERE && !S.rot_identity);
         int r = lane_exact(W, l, sh, R, t, S.rot_identity != 0, band);
+        n_exact++;
         if (r == RES_HIT) hit = true;
         else if (r == RES_AMBIG) push_work(P.wl, (int)n, frame_tag, l, slot, 0);
       }
@@ -270,9 +273,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
           l = p / sc.n_static; slot = sc.static_slots[p % sc.n_static];
           const float* c = sc.bcw_f + (size_t)slot * 3 * sc.Tp;
           float dx = W.bc[l][0] - c[0], dy = W.bc[l][1] - c[sc.Tp], dz = W.bc[l][2] - c[2 * (size_t)sc.Tp];
-          float rr = W.br[l] + __ldg(&sc.tile_bounds[0].w) * 0.f + sc.shapes[sc.slots[slot].shape].br;
-          if (sc.slots[slot].is_robot) rr = W.br[l] + ((const float*)sc.slots[slot].pad)[0];
-          rr = rr * 1.000001f + 1e-5f + band;
+          float rr = (W.br[l] + sc.slots[slot].br) * 1.000001f + 1e-5f + band;
           pass = dx * dx + dy * dy + dz * dz <= rr * rr;
         }
         bool h = eval_lane(l, slot, 0, -1, pass);
@@ -313,7 +314,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
             const float* c = sc.bcw_f + (size_t)slot * 3 * sc.Tp + fc;
             const float cx = c[0], cy = c[sc.Tp], cz = c[2 * (size_t)sc.Tp];
             const DSlot S = sc.slots[slot];
-            const float sbr = S.is_robot ? ((const float*)S.pad)[0] : sc.shapes[S.shape].br;
+            const float sbr = S.br;
             while (m) {
               const int l = __ffs(m) - 1;
               m &= m - 1;
@@ -340,6 +341,9 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
       }
     }
   }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n_exact += __shfl_xor_sync(SIRRT_FULL, n_exact, o);
+  if (lane == 0 && n_exact) atomicAdd(P.wl.count + 1, n_exact);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -368,7 +372,7 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
   const bool want_true_rob = (sc.parity_mode == 1) || (P.semantics == 0);
   const bool want_shift_rob = (sc.parity_mode == 0);
   const float band = P.band;
-  for (long long n = warp0; n < P.q.N; n += n_warps) {
+  for (long long n = P.q.n0 + warp0; n < P.q.n0 + P.q.cnt; n += n_warps) {
     const int f = P.frames[n];
     if (f < 0 || f >= sc.T) {  // the reference indexes unchecked (CollisionManager.cpp:369); we answer "collided"
       if (lane == 0) P.out[n] = 1;
@@ -387,7 +391,7 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
         l = p / sc.n_slots; slot = p % sc.n_slots;
         const DSlot S = sc.slots[slot];
         const float* c = sc.bcw_f + (size_t)slot * 3 * sc.Tp + f;
-        const float sbr = S.is_robot ? ((const float*)S.pad)[0] : sc.shapes[S.shape].br;
+        const float sbr = S.br;
         float dx = W.bc[l][0] - c[0], dy = W.bc[l][1] - c[sc.Tp], dz = W.bc[l][2] - c[2 * (size_t)sc.Tp];
         float rr = (W.br[l] + sbr) * 1.000001f + 1e-5f + band;
         if (dx * dx + dy * dy + dz * dz <= rr * rr) {
@@ -454,7 +458,8 @@ struct RecheckParams {
   DScene sc;
   QView q;
   const WorkItem* items;
-  unsigned int n_items;
+  const unsigned int* count;  // [0] entries pushed by the producer kernel (clamped to cap here)
+  unsigned int cap;
   const double* aabb_d;     // robot slots: [(slot*Tp + f)*6 + k]
   uint32_t* bits;           // bits mode: [N][W]
   int n_words;
@@ -502,9 +507,10 @@ __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const 
 __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
 k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckParams P) {
   const int lane = threadIdx.x & 31;
-  const unsigned int w = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5);
-  if (w >= P.n_items) return;
   const DScene& sc = P.sc;
+  const unsigned int n_items = min(*P.count, P.cap);
+  for (unsigned int w = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5); w < n_items;
+       w += gridDim.x * SIRRT_WARPS_PER_BLOCK) {
   const WorkItem it = P.items[w];
   double q[SIRRT_MAXJ];
   for (int j = 0; j < rb.n_joints; j++) q[j] = j < P.q.dof ? load_q(P.q, it.config, j) : 0.0;
@@ -528,7 +534,7 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
     const double* ab = P.aabb_d + ((size_t)it.slot * sc.Tp + f) * 6;
     bool overlap = true;
     for (int k = 0; k < 3; k++) if (alo[k] > ab[3 + k] || ahi[k] < ab[k]) overlap = false;
-    if (!overlap) return;
+    if (!overlap) continue;
     shifted = 2;
   }
   const DShape& sh = sc.shapes[shifted ? S.shape_shift : S.shape];
@@ -536,8 +542,8 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
   double d = recheck_pair(rb, sc, X[l], l, sh, pose, lane, &res);
   hit = res == RES_HIT;
   if (lane == 0 && fabs(d) < 1e-6) atomicAdd(P.counters + 2, 1u);
-  if (!hit) return;
-  if (P.cells) { if (lane == 0) P.cells[it.config] = 1; return; }
+  if (!hit) continue;
+  if (P.cells) { if (lane == 0) P.cells[it.config] = 1; continue; }
   uint32_t* row = P.bits + (size_t)it.config * P.n_words;
   if (it.frame >= 0) { if (lane == 0) atomicOr(row + (it.frame >> 5), 1u << (it.frame & 31)); }
   else {
@@ -547,13 +553,15 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
       atomicOr(row + wd, m);
     }
   }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
 // a3 tail: collision bit rows -> safe intervals (CollisionManager.cpp:507-546), one warp per row.
-// safe = ~collision; an interval starts where a safe bit follows a collision bit (or frame 0) and
-// ends where a safe bit precedes a collision bit (or frame T-1).  Starts/ends are ranked with a
-// warp prefix scan of popcounts, so the k-th start pairs with the k-th end.
+// safe = ~collision.  An interval starts at a safe frame whose predecessor collides (or is frame
+// -1) and ends at a safe frame whose successor collides (or is frame T).  Starts and ends are both
+// ascending, so the k-th start pairs with the k-th end; each is ranked with a warp prefix sum of
+// popcounts on top of a running count carried across groups of 32 words.
 // ------------------------------------------------------------------------------------------------
 struct IvParams {
   const uint32_t* bits;
@@ -562,70 +570,50 @@ struct IvParams {
   int32_t* table;  // [N][1+2*Kmax]
 };
 
+__device__ __forceinline__ int warp_excl_scan(int v, int lane, int& total) {
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int u = __shfl_up_sync(SIRRT_FULL, incl, o);
+    if (lane >= o) incl += u;
+  }
+  total = __shfl_sync(SIRRT_FULL, incl, 31);
+  return incl - v;
+}
+
 __global__ void __launch_bounds__(256) k_bits_to_intervals(const __grid_constant__ IvParams P) {
   const int lane = threadIdx.x & 31;
   const long long n = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (n >= P.N) return;
   const uint32_t* row = P.bits + (size_t)n * P.n_words;
   int32_t* out = P.table + (size_t)n * (1 + 2 * P.Kmax);
-  for (int k = lane; k < 2 * P.Kmax; k += 32) out[1 + k] = -1;
-  __syncwarp();
-  int count = 0;
-  uint32_t carry_prev = 0;  // safe bit of the frame just before this group (frame -1 counts as "collision")
+  int n_starts = 0, n_ends = 0;
+  uint32_t prev_safe = 0;  // safe bit of the last frame of the previous group (frame -1: "collision")
   for (int w0 = 0; w0 < P.n_words; w0 += 32) {
     const int w = w0 + lane;
-    uint32_t valid = 0;
-    if (w < P.n_words) valid = (P.T - w * 32 >= 32) ? 0xffffffffu : ((1u << (P.T - w * 32)) - 1u);
-    const uint32_t s = (w < P.n_words ? ~row[w] : 0u) & valid;  // safe bits
+    uint32_t s = 0;
+    if (w < P.n_words) {
+      const int left = P.T - w * 32;
+      s = ~row[w] & (left >= 32 ? 0xffffffffu : ((1u << left) - 1u));
+    }
     uint32_t prev_msb = __shfl_up_sync(SIRRT_FULL, s >> 31, 1);
-    if (lane == 0) prev_msb = carry_prev;
+    if (lane == 0) prev_msb = prev_safe;
     uint32_t next_lsb = __shfl_down_sync(SIRRT_FULL, s & 1u, 1);
-    if (lane == 31) next_lsb = (w + 1 < P.n_words) ? ((~row[w + 1]) & 1u) : 0u;  // T%32 tail handled by valid mask
-    if (w + 1 < P.n_words && lane != 31) { /* next_lsb from neighbour lane is already masked by its valid */ }
+    if (lane == 31) {
+      next_lsb = 0;
+      if (w + 1 < P.n_words) next_lsb = (~row[w + 1]) & 1u;  // frame (w+1)*32 < T, so the bit is valid
+    }
     uint32_t starts = s & ~((s << 1) | prev_msb);
     uint32_t ends = s & ~((s >> 1) | (next_lsb << 31));
-    const int ns = __popc(starts);
-    int incl = ns;  // inclusive prefix sum over lanes
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(SIRRT_FULL, incl, o); if (lane >= o) incl += v; }
-    int rank = count + incl - ns;
-    // ends rank identically: within one row the number of ends before any position equals the
-    // number of starts before it minus (1 if an interval is open), so rank them with their own scan
-    const int ne = __popc(ends);
-    int incl_e = ne;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) { int v = __shfl_up_sync(SIRRT_FULL, incl_e, o); if (lane >= o) incl_e += v; }
-    int rank_e = count /*ends so far == starts so far minus open*/ + incl_e - ne;
-    // count tracks completed starts; an interval open across groups has its start counted already
-    // and its end not yet: carry that imbalance
-    const int open_before = __shfl_sync(SIRRT_FULL, 0, 0);  // placeholder keeps structure uniform
-    (void)open_before;
-    while (starts) { int b = __ffs(starts) - 1; starts &= starts - 1; if (rank < P.Kmax) out[1 + 2 * rank] = w * 32 + b; rank++; }
-    // ends: number of ends completed before this group = count - open, tracked in carry_open
-    // (see below)
-    {
-      int base_e = rank_e;
-      (void)base_e;
-    }
-    // stash per-lane ends for the second phase
-    uint32_t e = ends;
-    int total_s = __shfl_sync(SIRRT_FULL, incl, 31);
-    int total_e = __shfl_sync(SIRRT_FULL, incl_e, 31);
-    // ends completed before this group: kept in register ends_done
-    static_assert(true, "");
-    // write ends
-    int re = /*ends_done*/ __shfl_sync(SIRRT_FULL, 0, 0);
-    (void)re;
-    // -- the bookkeeping above is folded into two running counters:
-    //    count      = starts seen so far
-    //    ends_done  = ends seen so far   (stored in carry_prev's high bits to stay register-light)
-    int ends_done = (int)(carry_prev >> 1);
-    int rk = ends_done + incl_e - ne;
-    while (e) { int b = __ffs(e) - 1; e &= e - 1; if (rk < P.Kmax) out[2 + 2 * rk] = w * 32 + b; rk++; }
-    count += total_s;
-    ends_done += total_e;
-    uint32_t last_msb = __shfl_sync(SIRRT_FULL, s >> 31, 31);
-    carry_prev = (last_msb & 1u) | ((uint32_t)ends_done << 1);
+    int ts, te;
+    int rs = n_starts + warp_excl_scan(__popc(starts), lane, ts);
+    int re = n_ends + warp_excl_scan(__popc(ends), lane, te);
+    while (starts) { const int b = __ffs(starts) - 1; starts &= starts - 1; if (rs < P.Kmax) out[1 + 2 * rs] = w * 32 + b; rs++; }
+    while (ends) { const int b = __ffs(ends) - 1; ends &= ends - 1; if (re < P.Kmax) out[2 + 2 * re] = w * 32 + b; re++; }
+    n_starts += ts; n_ends += te;
+    prev_safe = __shfl_sync(SIRRT_FULL, s >> 31, 31);
   }
-  if (lane == 0) out[0] = count;
+  // unused pairs = -1; the count is the true number of intervals even when it exceeds Kmax
+  for (int k = 2 * min(n_starts, P.Kmax) + lane; k < 2 * P.Kmax; k += 32) out[1 + k] = -1;
+  if (lane == 0) out[0] = n_starts;
 }

@@ -1,0 +1,215 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (libsirrt_b200.so), against the CPU
+oracle on identical inputs.  Bar: collision bits and interval end points BIT-EXACT (the FP32 fast
+path re-evaluates every pair inside its uncertainty band in FP64 with the oracle's formulas, so no
+tolerance is needed; pair tests within 1e-6 m of contact are counted and reported)."""
+import numpy as np
+import pytest
+
+from conftest import random_q
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare(pkg, orc, pack, q, kmax=8, mode=0):
+    dev = pkg.Scene(pack, 0, mode)
+    ref = orc.Oracle(pack, mode)
+    table, bits, near = dev.safe_intervals_batch(q, kmax)
+    rtable, rbits = ref.safe_intervals_batch(q, kmax)
+    bad = np.nonzero((bits != rbits).any(1))[0]
+    assert bad.size == 0, f"{bad.size} rows differ, first {bad[:5]}; stats {dev.last_stats()}"
+    assert np.array_equal(table, rtable)
+    return dev, ref, bits, near
+
+
+@pytest.mark.parametrize("name,n", [("synA_32_200", 512), ("synB_32_200", 512), ("synC_32_200", 512), ("synA_64_1000", 96),
+                                    ("synA_5_33", 64), ("synB_3_1", 64), ("synA_70_64", 128)])
+def test_synthetic_sweeps_bit_exact(pkg, orc, sp, packs, name, n):
+    pk = packs(name)
+    dev, ref, bits, near = _compare(pkg, orc, pk, random_q(sp, pk, n, 13))
+    assert bits.any() and not bits.all()
+
+
+def test_generic_kernel_equals_sweep_kernel(pkg, orc, sp, packs):
+    pk = packs("synB_32_200")
+    q = random_q(sp, pk, 256, 21)
+    a = pkg.Scene(pk)
+    b = pkg.Scene(pk)
+    b.set_option(pkg.OPT_USE_SWEEP, 0)
+    ta, ba, _ = a.safe_intervals_batch(q, 8)
+    tb, bb, _ = b.safe_intervals_batch(q, 8)
+    assert np.array_equal(ba, bb) and np.array_equal(ta, tb)
+
+
+@pytest.mark.parametrize("name,n", [("mass_test_cyl", 256), ("mass_test", 48), ("flying_boxes", 48), ("scene_task", 16)])
+def test_reference_scenes_bit_exact(pkg, orc, sp, packs, name, n):
+    pk = packs(name)
+    _compare(pkg, orc, pk, random_q(sp, pk, n, 17))
+
+
+@pytest.mark.parametrize("name,n", [("multiple_robots_cyl", 128), ("multiple_robots", 24)])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_robot_obstacles_both_parity_modes(pkg, orc, sp, packs, name, n, mode):
+    """QUIRK 7: REFERENCE_EXACT reproduces the functor mis-indexing, FIXED tests true geometry."""
+    pk = packs(name)
+    q = random_q(sp, pk, n, 19)
+    dev, ref, bits, _ = _compare(pkg, orc, pk, q, mode=mode)
+    # per-frame semantics (CollisionCallback: shifted functor only in REFERENCE_EXACT)
+    qd = q.T.astype(np.float64)
+    fb = dev.collision_bits_f64(qd[:8], pkg.SEM_FRAME)
+    for i in range(8):
+        rb, _ = ref.collision_bits(qd[i], orc.SEM_FRAME)
+        assert np.array_equal(fb[i], rb)
+
+
+def test_golden_vectors_through_the_c_abi(pkg, packs, golden_vectors):
+    for name, ent in golden_vectors.items():
+        dev = pkg.Scene(packs(name))
+        for q, iv, fc in zip(ent["configs"], ent["intervals"], ent["frame_checks"]):
+            assert dev.safe_intervals(q) == [tuple(x) for x in iv], name
+            for f, c in fc:
+                assert int(dev.check_frame(q, f)) == c
+
+
+def test_single_call_dropins(pkg, orc, sp, packs):
+    pk = packs("synB_32_200")
+    dev, ref = pkg.Scene(pk), orc.Oracle(pk)
+    q = random_q(sp, pk, 24, 23).T.astype(np.float64)
+    for qq in q:
+        assert dev.safe_intervals(qq) == ref.safe_intervals(qq)
+        for f in (0, 57, 199):
+            assert dev.check_frame(qq, f) == ref.check_frame(qq, f)
+        assert dev.check_frame(qq, 200) and dev.check_frame(qq, -1)  # out of range answers "collided"
+        R, t = dev.fk(qq)
+        R0, t0 = ref.fk(qq)
+        assert np.abs(R - R0).max() < 1e-14 and np.abs(t - t0).max() < 1e-14
+    # capacity overflow: true count returned with the error code
+    many = [qq for qq in q if len(ref.safe_intervals(qq)) > 1]
+    if many:
+        with pytest.raises(pkg.SirrtError) as e:
+            dev.safe_intervals(many[0], cap=1)
+        assert e.value.code == -5
+
+
+def test_check_frames_batch(pkg, orc, sp, packs):
+    for name in ("synB_32_200", "flying_boxes", "multiple_robots_cyl"):
+        pk = packs(name)
+        dev, ref = pkg.Scene(pk), orc.Oracle(pk)
+        n = 600 if name.startswith("syn") else 96
+        q = random_q(sp, pk, n, 29)
+        frames = np.random.default_rng(3).integers(-2, ref.n_frames + 2, n).astype(np.int32)
+        got = dev.check_frames_batch(q, frames)
+        exp = ref.check_frames_batch(q, frames)
+        assert np.array_equal(got, exp), name
+        got64 = dev.check_frames_batch_f64(q.T.astype(np.float64), frames)
+        assert np.array_equal(got64, exp)
+
+
+def test_edge_check_batch(pkg, orc, sp, packs):
+    pk = packs("synA_32_200")
+    dev, ref = pkg.Scene(pk), orc.Oracle(pk)
+    rng = np.random.default_rng(31)
+    n = 200
+    q0 = random_q(sp, pk, n, 37).T.astype(np.float64)
+    q1 = q0 + rng.normal(0, 0.4, q0.shape)
+    t0 = rng.uniform(0, 150, n)
+    t1 = t0 + rng.uniform(-5, 60, n)
+    first, coord = dev.edge_check_batch(q0, q1, t0, t1, vmax=3.1415)
+    kinds = set()
+    for e in range(n):
+        s, cc = ref.edge_check(q0[e], q1[e], t0[e], t1[e], 3.1415)
+        assert first[e] == s, (e, first[e], s)
+        if s >= 0:
+            assert np.array_equal(coord[e], cc)
+        kinds.add(min(s, 0) if s < 0 else 1)
+    assert kinds == {-3, -2, -1, 1}, kinds
+
+
+def test_get_distances(pkg, orc, sp, packs):
+    for name in ("synB_32_200", "flying_boxes"):
+        pk = packs(name)
+        dev, ref = pkg.Scene(pk), orc.Oracle(pk)
+        q = random_q(sp, pk, 12, 41).T.astype(np.float64)
+        for i, qq in enumerate(q):
+            f = (37 * i) % ref.n_frames
+            col, d = dev.get_distances(qq, f)
+            rcol, rd = ref.get_distances(qq, f)
+            assert col == bool(rcol)
+            k = np.isfinite(d) & (d < 1e299)
+            assert np.allclose(d[k], rd[k], atol=1e-9), (d, rd)
+
+
+def test_edge_cases(pkg, orc, sp, packs):
+    pk = packs("synA_32_200")
+    dev, ref = pkg.Scene(pk), orc.Oracle(pk)
+    # empty batch
+    t, b, near = dev.safe_intervals_batch(np.zeros((7, 0), np.float32), 4)
+    assert t.shape == (0, 9) and b.shape == (0, 7) and near == 0
+    # Kmax smaller than the interval count: count is the true count, only Kmax pairs stored
+    q = random_q(sp, pk, 128, 43)
+    t1, _, _ = dev.safe_intervals_batch(q, 1)
+    t8, _ = ref.safe_intervals_batch(q, 8)
+    assert np.array_equal(t1[:, 0], t8[:, 0]) and (t1[:, 0] > 1).any()
+    assert np.array_equal(t1[t8[:, 0] > 0, 1:3], t8[t8[:, 0] > 0, 1:3])
+    # a tiny re-check work list forces the overflow -> split -> redo path; results must not change
+    dev2 = pkg.Scene(pk)
+    dev2.set_band(5e-3)
+    dev2.set_option(pkg.OPT_WORKLIST_CAP, 64)
+    tt, bb, _ = dev2.safe_intervals_batch(q, 8)
+    assert np.array_equal(tt, t8)
+    # a wide band sends everything near contact to FP64: same answer, more rechecks
+    assert dev2.last_stats()["rechecked"] > 0
+    # device-resident inputs / outputs (torch tensors) through the same entry point
+    import torch
+
+    qd = torch.from_numpy(q).cuda()
+    table = torch.zeros((q.shape[1], 17), dtype=torch.int32, device="cuda")
+    dev.set_stream(torch.cuda.current_stream().cuda_stream)
+    dev.safe_intervals_batch_raw(qd.data_ptr(), q.shape[1], table.data_ptr(), 8, None)
+    assert np.array_equal(table.cpu().numpy(), t8)
+
+
+def test_knn(pkg, orc):
+    rng = np.random.default_rng(5)
+    pts = rng.uniform(-3.2, 3.2, (20000, 6))
+    pts[1234] = pts[77]   # exact duplicates: the lower index must win
+    pts[15000] = pts[77]
+    idx = pkg.KnnIndex(6, 30000)
+    idx.add(pts[:5000])
+    idx.add(pts[5000:])   # incremental insertion keeps insertion order = index (Tree::add_vertex)
+    assert len(idx) == 20000
+    qs = np.vstack([pts[77], pts[77] + 1e-9, rng.uniform(-3.2, 3.2, (300, 6))])
+    gi, gd = idx.nearest(qs)
+    ri, rd = orc.knn_nearest(pts, qs)
+    assert np.array_equal(gi, ri) and np.array_equal(gd, rd)  # FP64, same accumulation order: bit-exact
+    assert gi[0] == 77
+    for k in (0, 5, 50):
+        got, n = idx.radius(qs[k], 4.0)
+        exp = orc.knn_radius(pts, qs[k], 4.0)
+        assert n == len(exp) and np.array_equal(got, exp)
+    ti, td = idx.topk(qs[:40], 8)
+    d2 = ((pts[None] - qs[:40, None]) ** 2).sum(-1)
+    for k in range(40):
+        order = np.lexsort((np.arange(len(pts)), d2[k]))[:8]
+        assert np.array_equal(np.sort(d2[k][ti[k]]), np.sort(d2[k][order]))
+        assert np.array_equal(ti[k, :1], gi[k : k + 1])
+    # empty index
+    e = pkg.KnnIndex(6, 10)
+    i0, _ = e.nearest(qs[:2])
+    assert (i0 == -1).all() and e.radius(qs[0], 1.0)[1] == 0
+
+
+def test_collision_manager_mirror(pkg, orc, packs, sp):
+    """The reference-facing operator interface (MDP::CollisionManager method names)."""
+    pk = packs("flying_boxes")
+    cm = pkg.CollisionManager(pk)
+    ref = orc.Oracle(pk)
+    sc = sp.read_pack(pk)
+    lim = cm.get_planned_robot_limits()
+    assert len(lim) == 6 and abs(lim[1][0] - (-2.059)) < 1e-6
+    assert cm.get_safe_intervals(sc.start_configuration) == ref.safe_intervals(sc.start_configuration)
+    assert cm.check_collision_frame(sc.start_configuration, 0) is False          # check_scene.cpp:74
+    assert cm.check_collision(sc.end_configuration, (sc.n_frames - 1) / sc.fps + 1e-3) is False  # :83
+    assert cm.check_robot_selfcollision(sc.start_configuration) is False
+    low = cm.get_goal_frame_low_bound()
+    col = [ref.check_frame(sc.end_configuration, f) for f in range(sc.n_frames)]
+    assert low == (max(i for i, c in enumerate(col) if c) + 1 if any(col) else 0)

@@ -1,0 +1,156 @@
+"""CPU tests of the oracle (oracle/sirrt_oracle.c) and of the packer: the checker must be right
+before it is allowed to judge the CUDA path.  PARITY UNPINNED (no reference golden vectors exist):
+anchored on closed-form-vs-GJK cross-checks, the reference's check_scene invariants and the FK
+sanity values of SURVEY.md §8c."""
+import numpy as np
+import pytest
+
+from conftest import random_q
+
+
+def test_pack_roundtrip(sp, packs):
+    for name in ("synA_8_50", "flying_boxes", "multiple_robots"):
+        pk = packs(name)
+        assert sp.write_pack(sp.read_pack(pk)) == pk
+
+
+def test_closed_forms_against_gjk(orc):
+    rng = np.random.default_rng(0)
+    for _ in range(300):
+        a, b = rng.uniform(-1, 1, 3), rng.uniform(-1, 1, 3)
+        h = rng.uniform(0.05, 0.5, 3)
+        corners = np.array([[sx * h[0], sy * h[1], sz * h[2]] for sx in (-1, 1) for sy in (-1, 1) for sz in (-1, 1)])
+        d_cf = np.sqrt(orc.seg_box_dist2(a, b, h))
+        d_gjk = orc.gjk_distance(np.stack([a, b]), corners)
+        assert abs(d_cf - d_gjk) < 1e-9, (d_cf, d_gjk)
+        p, q = rng.uniform(-1, 1, 3), rng.uniform(-1, 1, 3)
+        d_ss = np.sqrt(orc.seg_seg_dist2(a, b, p, q))
+        assert abs(d_ss - orc.gjk_distance(np.stack([a, b]), np.stack([p, q]))) < 1e-9
+        d_ps = np.sqrt(orc.pt_seg_dist2(p, a, b))
+        assert abs(d_ps - orc.gjk_distance(p[None], np.stack([a, b]))) < 1e-9
+
+
+def test_fk_sanity_values(orc, packs, sp):
+    """link frame origins (m) computed independently with NumPy from the URDFs."""
+    o = orc.Oracle(packs("scene_task"))  # xarm6vis
+    _, t = o.fk(np.zeros(6))
+    exp = [(0, 0, 0.267), (0.0535, 0, 0.5515), (0.131, 0, 0.209), (0.131, 0, 0.209), (0.207, 0, 0.112)]
+    assert np.allclose(t, exp, atol=2e-5), t
+    q = sp.read_pack(packs("scene_task")).start_configuration
+    _, t = o.fk(q)
+    assert np.allclose(t[1], (-0.282412, 0.048447, 0.225781), atol=2e-6)
+    assert np.allclose(t[2], (-0.617329, 0.105901, 0.137228), atol=2e-6)
+    assert np.allclose(t[4], (-0.729744, 0.070247, 0.101496), atol=2e-6)
+    oc = orc.Oracle(packs("mass_test_cyl"))  # xarm6cyl
+    _, t = oc.fk(np.zeros(6))
+    exp = [(0, 0.024, 0.401), (0.1035, 0.016, 0.5045), (0.131, -0.010, 0.271), (0.206, 0, 0.174)]
+    assert np.allclose(t, exp, atol=1e-6), t
+
+
+def test_fk_rotations_are_orthonormal(orc, packs, sp):
+    o = orc.Oracle(packs("synA_8_50"))
+    q = random_q(sp, packs("synA_8_50"), 16, 3).T.astype(np.float64)
+    for qq in q:
+        R, _ = o.fk(qq)
+        for r in R:
+            assert np.allclose(r @ r.T, np.eye(3), atol=1e-12)
+            assert abs(np.linalg.det(r) - 1) < 1e-12
+
+
+@pytest.mark.parametrize("name", ["mass_test", "flying_boxes"])
+def test_check_scene_invariants(orc, packs, sp, name):
+    """Scenes that passed the reference's check_scene when generated: start collision-free at frame
+    0 and goal collision-free at the last frame (check_scene.cpp:74,83)."""
+    pk = packs(name)
+    sc = sp.read_pack(pk)
+    o = orc.Oracle(pk)
+    assert not o.check_frame(sc.start_configuration, 0)
+    assert not o.check_frame(sc.end_configuration, sc.n_frames - 1)
+
+
+def test_golden_vectors_reproduce(orc, packs, golden_vectors):
+    for name, ent in golden_vectors.items():
+        o = orc.Oracle(packs(name))
+        for q, iv, fc, fk in zip(ent["configs"], ent["intervals"], ent["frame_checks"], ent["fk_origins"]):
+            assert o.safe_intervals(q) == [tuple(x) for x in iv]
+            for f, c in fc:
+                assert int(o.check_frame(q, f)) == c
+            assert np.allclose(o.fk(q)[1], fk, atol=1e-12)
+
+
+def test_no_obstacles_gives_one_full_interval(orc, packs, golden_vectors):
+    """STRRT/scene_task.json ships with "obstacles": [] -> every configuration is [(0, T-1)]
+    (CollisionManager.cpp:509-517)."""
+    o = orc.Oracle(packs("scene_task"))
+    for q in golden_vectors["scene_task"]["configs"]:
+        assert o.safe_intervals(q) == [(0, o.n_frames - 1)]
+
+
+def test_intervals_are_complement_of_bits(orc, packs, sp):
+    pk = packs("synA_16_100")
+    o = orc.Oracle(pk)
+    q = random_q(sp, pk, 64, 5)
+    table, bits = o.safe_intervals_batch(q, 16)
+    T = o.n_frames
+    for n in range(q.shape[1]):
+        col = np.unpackbits(bits[n].view(np.uint8), bitorder="little")[:T].astype(bool)
+        safe = np.zeros(T, bool)
+        cnt = table[n, 0]
+        assert cnt <= 16
+        for k in range(cnt):
+            lo, hi = table[n, 1 + 2 * k], table[n, 2 + 2 * k]
+            assert 0 <= lo <= hi < T and not safe[lo : hi + 1].any()
+            assert (lo == 0 or col[lo - 1]) and (hi == T - 1 or col[hi + 1])  # maximal runs
+            safe[lo : hi + 1] = True
+        assert np.array_equal(safe, ~col)
+        assert (table[n, 1 + 2 * cnt :] == -1).all()
+
+
+def test_bvh_baseline_equals_brute_force(orc, packs, sp):
+    """The timed CPU baseline (AABB tree over constant-pose windows, CollisionManager.cpp:107-216)
+    must give the same bits as the brute-force oracle."""
+    for name in ("synA_16_100", "flying_boxes", "multiple_robots_cyl"):
+        pk = packs(name)
+        o = orc.Oracle(pk)
+        n_leaves = o.bvh_build()
+        assert n_leaves > 0
+        q = random_q(sp, pk, 24, 9)
+        t1, b1 = o.safe_intervals_batch(q, 8, use_bvh=False)
+        t2, b2 = o.safe_intervals_batch(q, 8, use_bvh=True)
+        assert np.array_equal(b1, b2) and np.array_equal(t1, t2)
+
+
+def test_quirk7_modes_differ_only_with_robot_obstacles(orc, packs, sp):
+    pk = packs("multiple_robots_cyl")
+    q = random_q(sp, pk, 32, 11)
+    a = orc.Oracle(pk, orc.REFERENCE_EXACT).safe_intervals_batch(q, 8)[1]
+    b = orc.Oracle(pk, orc.FIXED).safe_intervals_batch(q, 8)[1]
+    assert ((a & b) == b).all()  # REFERENCE_EXACT is a superset (shifted functor OR true geometry)
+    pk = packs("synA_8_50")
+    q = random_q(sp, pk, 32, 11)
+    a = orc.Oracle(pk, orc.REFERENCE_EXACT).safe_intervals_batch(q, 8)[1]
+    b = orc.Oracle(pk, orc.FIXED).safe_intervals_batch(q, 8)[1]
+    assert np.array_equal(a, b)
+
+
+def test_edge_check_semantics(orc, packs, sp):
+    pk = packs("synA_16_100")
+    o = orc.Oracle(pk)
+    q = random_q(sp, pk, 2, 1).T.astype(np.float64)
+    assert o.edge_check(q[0], q[1], 10.0, 10.0)[0] == -2          # start_time >= end_time
+    assert o.edge_check(q[0], q[1], 10.0, 11.0, vmax=0.01)[0] == -3  # speed gate
+    s, cc = o.edge_check(q[0], q[0], 0.0, 50.0, vmax=0)
+    col = [o.check_frame(q[0], f) for f in range(51)]
+    assert s == (col.index(True) if True in col else -1)
+
+
+def test_knn_oracle(orc):
+    rng = np.random.default_rng(2)
+    pts = rng.uniform(-3, 3, (500, 6))
+    pts[100] = pts[7]  # exact tie: first index wins
+    qs = np.vstack([pts[7] + 1e-3, rng.uniform(-3, 3, (10, 6))])
+    idx, d2 = orc.knn_nearest(pts, qs)
+    ref = ((pts[None] - qs[:, None]) ** 2).sum(-1)
+    assert idx[0] == 7 and np.array_equal(idx, ref.argmin(1))
+    r = orc.knn_radius(pts, qs[3], 4.0)
+    assert set(r) == set(np.nonzero(ref[3] < 4.0)[0])

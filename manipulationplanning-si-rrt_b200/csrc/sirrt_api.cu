@@ -65,6 +65,7 @@ struct sirrt_scene {
   long long chunk_configs = 1 << 18;
   unsigned int wl_cap = 1u << 22;
   int use_sweep = 1;
+  long long sweep_min_configs = 8192;
   DevBuf q, bits, table, frames, cells, work, counts, misc, misc2;
   void* pinned = nullptr;  // small pinned staging block for the latency path
   std::vector<cudaEvent_t> ev;  // start/stop pairs around the sweep launches of one call
@@ -175,6 +176,7 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
   switch (key) {
     case SIRRT_OPT_USE_SWEEP: s->use_sweep = value != 0; break;
     case SIRRT_OPT_CHUNK_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad chunk"); s->chunk_configs = value; break;
+    case SIRRT_OPT_SWEEP_MIN_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad threshold"); s->sweep_min_configs = value; break;
     case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
     default: return fail(SIRRT_E_ARG, "unknown option");
   }

@@ -19,7 +19,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
   std::vector<Range> todo;
   for (long long n0 = 0; n0 < N; n0 += s->chunk_configs) todo.push_back({n0, std::min(s->chunk_configs, N - n0)});
   uint64_t launches = 0, rechecked = 0, near = 0, exact = 0, sweep_ns = 0;
-  const bool sweep = s->use_sweep && s->sweep.supported;
+  const bool sweep = s->use_sweep && s->sweep.supported && N >= s->sweep_min_configs;
   while (!todo.empty()) {
     const size_t nr = todo.size();
     if (s->counts.ensure(nr * 4 * sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc(counters) failed");

@@ -278,10 +278,38 @@ __device__ inline int warp_support(const GShape<T>& s, const T* d, T* out, int l
 
 template <typename T> struct Simplex { T w[4][3]; int id[4]; int n; };
 
-// closest point to the origin on triangle abc; returns kept-vertex mask (a=1,b=2,c=4)
+template <typename T> struct GjkEps;
+template <> struct GjkEps<float> { static __device__ __forceinline__ float tri() { return 1e-10f; } static __device__ __forceinline__ float tet() { return 1e-4f; } };
+template <> struct GjkEps<double> { static __device__ __forceinline__ double tri() { return 1e-24; } static __device__ __forceinline__ double tet() { return 1e-9; } };
+
+// closest point to the origin on segment ab; returns kept-vertex mask (a=1,b=2)
+template <typename T> __device__ __forceinline__ int closest_seg(const T* a, const T* b, T* out) {
+  T ab[3]; sub3(ab, b, a);
+  const T den = dot3(ab, ab), t = den > T(0) ? -dot3(a, ab) / den : T(0);
+  if (t <= T(0)) { out[0] = a[0]; out[1] = a[1]; out[2] = a[2]; return 1; }
+  if (t >= T(1)) { out[0] = b[0]; out[1] = b[1]; out[2] = b[2]; return 2; }
+  out[0] = a[0] + t * ab[0]; out[1] = a[1] + t * ab[1]; out[2] = a[2] + t * ab[2];
+  return 3;
+}
+
+// closest point to the origin on triangle abc; returns kept-vertex mask (a=1,b=2,c=4).  Polytopes
+// hand GJK many collinear / coplanar support points: a triangle whose area is negligible against its
+// edge lengths is solved as the best of its three edges.
 template <typename T> __device__ inline int closest_tri(const T* a, const T* b, const T* c, T* out) {
-  T ab[3], ac[3];
-  sub3(ab, b, a); sub3(ac, c, a);
+  T ab[3], ac[3], bc[3], n[3];
+  sub3(ab, b, a); sub3(ac, c, a); sub3(bc, c, b); cross3(n, ab, ac);
+  const T ab2 = dot3(ab, ab), ac2 = dot3(ac, ac), bc2 = dot3(bc, bc);
+  const T l2 = ab2 > ac2 ? (ab2 > bc2 ? ab2 : bc2) : (ac2 > bc2 ? ac2 : bc2);
+  if (dot3(n, n) <= GjkEps<T>::tri() * l2 * l2) {
+    T q[3];
+    int m = closest_seg(a, b, out), keep = m;
+    T best = dot3(out, out);
+    m = closest_seg(a, c, q);
+    if (dot3(q, q) < best) { best = dot3(q, q); out[0] = q[0]; out[1] = q[1]; out[2] = q[2]; keep = (m & 1) | ((m & 2) << 1); }
+    m = closest_seg(b, c, q);
+    if (dot3(q, q) < best) { out[0] = q[0]; out[1] = q[1]; out[2] = q[2]; keep = m << 1; }
+    return keep;
+  }
   T d1 = -dot3(ab, a), d2 = -dot3(ac, a);
   if (d1 <= T(0) && d2 <= T(0)) { out[0] = a[0]; out[1] = a[1]; out[2] = a[2]; return 1; }
   T d3 = -dot3(ab, b), d4 = -dot3(ac, b);
@@ -312,50 +340,55 @@ template <typename T> __device__ inline int closest_tri(const T* a, const T* b, 
 }
 
 // reduce simplex to the sub-simplex closest to the origin; returns 1 when the origin is enclosed.
-// min_face (tetrahedron only) receives a lower bound of the penetration depth.
+// A tetrahedron only counts as enclosing when it has real volume (coplanar support points are the
+// norm between polytopes); otherwise, and whenever the origin is outside, the answer is the best of
+// the four faces.  min_face (enclosing tetrahedron only) is a lower bound of the penetration depth.
 template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v, T& min_face) {
   if (s.n == 1) { v[0] = s.w[0][0]; v[1] = s.w[0][1]; v[2] = s.w[0][2]; return 0; }
-  if (s.n == 2) {
-    const T *a = s.w[0], *b = s.w[1];
-    T ab[3]; sub3(ab, b, a);
-    T den = dot3(ab, ab), t = den > T(0) ? -dot3(a, ab) / den : T(0);
-    if (t <= T(0)) { v[0] = a[0]; v[1] = a[1]; v[2] = a[2]; s.n = 1; }
-    else if (t >= T(1)) {
-      v[0] = b[0]; v[1] = b[1]; v[2] = b[2];
-      s.w[0][0] = b[0]; s.w[0][1] = b[1]; s.w[0][2] = b[2]; s.id[0] = s.id[1]; s.n = 1;
-    } else for (int i = 0; i < 3; i++) v[i] = a[i] + t * ab[i];
-    return 0;
-  }
   int keep = 0;
-  if (s.n == 3) keep = closest_tri(s.w[0], s.w[1], s.w[2], v);
+  if (s.n == 2) keep = closest_seg(s.w[0], s.w[1], v);
+  else if (s.n == 3) keep = closest_tri(s.w[0], s.w[1], s.w[2], v);
   else {
     const int F[4][4] = {{0, 1, 2, 3}, {0, 2, 3, 1}, {0, 3, 1, 2}, {1, 3, 2, 0}};
-    T best = T(3.0e38), bv[3] = {T(0), T(0), T(0)};
-    int outside_any = 0;
-    min_face = T(3.0e38);
-    for (int f = 0; f < 4; f++) {
-      const T *a = s.w[F[f][0]], *b = s.w[F[f][1]], *c = s.w[F[f][2]], *d = s.w[F[f][3]];
-      T ab[3], ac[3], n[3], ad[3];
-      sub3(ab, b, a); sub3(ac, c, a); cross3(n, ab, ac); sub3(ad, d, a);
-      T sp = -dot3(a, n), sd = dot3(ad, n);
-      if (sp * sd < T(0) || sd == T(0)) {
-        outside_any = 1;
-        T q[3];
-        int m = closest_tri(a, b, c, q);
-        T dd = dot3(q, q);
-        if (dd < best) {
-          best = dd; bv[0] = q[0]; bv[1] = q[1]; bv[2] = q[2];
-          keep = 0;
-          for (int k = 0; k < 3; k++) if (m & (1 << k)) keep |= 1 << F[f][k];
+    {
+      const T *A = s.w[0], *B = s.w[1], *C = s.w[2], *D = s.w[3];
+      T ab[3], ac[3], ad[3], bc[3], bd[3], cd[3], n[3];
+      sub3(ab, B, A); sub3(ac, C, A); sub3(ad, D, A); sub3(bc, C, B); sub3(bd, D, B); sub3(cd, D, C);
+      cross3(n, ab, ac);
+      const T vol6 = dot3(n, ad);
+      T l2 = dot3(ab, ab);
+      T e = dot3(ac, ac); l2 = e > l2 ? e : l2;
+      e = dot3(ad, ad); l2 = e > l2 ? e : l2;
+      e = dot3(bc, bc); l2 = e > l2 ? e : l2;
+      e = dot3(bd, bd); l2 = e > l2 ? e : l2;
+      e = dot3(cd, cd); l2 = e > l2 ? e : l2;
+      if (tabs(vol6) > GjkEps<T>::tet() * l2 * tsqrt(l2)) {
+        bool inside = true;
+        T mf = T(3.0e38);
+        for (int f = 0; f < 4; f++) {
+          const T *a = s.w[F[f][0]], *b = s.w[F[f][1]], *c = s.w[F[f][2]], *d = s.w[F[f][3]];
+          T e1[3], e2[3], fn[3], ed[3];
+          sub3(e1, b, a); sub3(e2, c, a); cross3(fn, e1, e2); sub3(ed, d, a);
+          const T sp = -dot3(a, fn), sd = dot3(ed, fn);
+          if (!(sp * sd > T(0))) inside = false;  // origin strictly on d's side of every face
+          const T nn = dot3(fn, fn);
+          const T fd = nn > T(0) ? tabs(sp) / tsqrt(nn) : T(0);
+          mf = fd < mf ? fd : mf;
         }
-      } else {
-        T nn = dot3(n, n);
-        T fd = nn > T(0) ? tabs(sp) / tsqrt(nn) : T(0);
-        if (fd < min_face) min_face = fd;
+        if (inside) { v[0] = v[1] = v[2] = T(0); min_face = mf; return 1; }
       }
     }
-    if (!outside_any) { v[0] = v[1] = v[2] = T(0); return 1; }
-    v[0] = bv[0]; v[1] = bv[1]; v[2] = bv[2];
+    T best = T(3.0e38);
+    for (int f = 0; f < 4; f++) {
+      T q[3];
+      const int m = closest_tri(s.w[F[f][0]], s.w[F[f][1]], s.w[F[f][2]], q);
+      const T dd = dot3(q, q);
+      if (dd < best) {
+        best = dd; v[0] = q[0]; v[1] = q[1]; v[2] = q[2];
+        keep = 0;
+        for (int k = 0; k < 3; k++) if (m & (1 << k)) keep |= 1 << F[f][k];
+      }
+    }
   }
   int j = 0;
   for (int i = 0; i < s.n; i++)

@@ -169,7 +169,7 @@ inline int build_tables(const HScene& sc, int parity_mode, HostTables& tb, std::
           tb.aabb_d[((size_t)slot * Tp + f) * 6 + k] = lo[k]; tb.aabb_d[((size_t)slot * Tp + f) * 6 + 3 + k] = hi[k];
         }
       }
-      S.is_static = ro.is_static || same;
+      S.is_static = same;  // the reference treats static_robot and dynamic_robot alike (CollisionManager.cpp:171-213)
     }
   }
 

@@ -168,10 +168,33 @@ static inline int support_local(const Core* c, const double* dir_world, double* 
 
 typedef struct { double w[4][3]; int ia[4], ib[4]; int n; } Simplex;
 
-/* closest point to the origin on a triangle (Ericson 5.1.5); returns the kept-vertex mask */
+/* closest point to the origin on segment ab; returns the kept-vertex mask (a = 1, b = 2) */
+static int closest_seg(const double* a, const double* b, double* out) {
+  double ab[3]; sub3(ab, b, a);
+  double den = dot3(ab, ab), t = den > 0 ? -dot3(a, ab) / den : 0;
+  if (t <= 0) { memcpy(out, a, 24); return 1; }
+  if (t >= 1) { memcpy(out, b, 24); return 2; }
+  for (int i = 0; i < 3; i++) out[i] = a[i] + t * ab[i];
+  return 3;
+}
+
+/* closest point to the origin on a triangle (Ericson 5.1.5); returns the kept-vertex mask.
+ * Polytopes hand GJK many collinear / coplanar support points, so a triangle whose area is
+ * negligible against its edge lengths is solved as the best of its three edges. */
 static int closest_tri(const double* a, const double* b, const double* c, double* out) {
-  double ab[3], ac[3];
-  sub3(ab, b, a); sub3(ac, c, a);
+  double ab[3], ac[3], bc[3], n[3];
+  sub3(ab, b, a); sub3(ac, c, a); sub3(bc, c, b); cross3(n, ab, ac);
+  double l2 = fmax(dot3(ab, ab), fmax(dot3(ac, ac), dot3(bc, bc)));
+  if (dot3(n, n) <= 1e-24 * l2 * l2) {
+    double q[3], best;
+    int m = closest_seg(a, b, out), keep = m;
+    best = dot3(out, out);
+    m = closest_seg(a, c, q);
+    if (dot3(q, q) < best) { best = dot3(q, q); memcpy(out, q, 24); keep = (m & 1) | ((m & 2) << 1); }
+    m = closest_seg(b, c, q);
+    if (dot3(q, q) < best) { memcpy(out, q, 24); keep = m << 1; }
+    return keep;
+  }
   double d1 = -dot3(ab, a), d2 = -dot3(ac, a);
   if (d1 <= 0 && d2 <= 0) { memcpy(out, a, 24); return 1; }
   double d3 = -dot3(ab, b), d4 = -dot3(ac, b);
@@ -202,46 +225,45 @@ static int closest_tri(const double* a, const double* b, const double* c, double
 }
 
 /* reduce the simplex to the sub-simplex supporting the point closest to the origin; returns 1 if
- * the origin is enclosed (intersection) */
+ * the origin is enclosed (intersection).  A tetrahedron only counts as enclosing when it has real
+ * volume (coplanar support points are the norm between polytopes); otherwise, and whenever the
+ * origin is outside, the answer is the best of the four faces. */
 static int simplex_closest(Simplex* s, double* v) {
   if (s->n == 1) { memcpy(v, s->w[0], 24); return 0; }
-  if (s->n == 2) {
-    const double *a = s->w[0], *b = s->w[1];
-    double ab[3]; sub3(ab, b, a);
-    double den = dot3(ab, ab), t = den > 0 ? -dot3(a, ab) / den : 0;
-    if (t <= 0) { memcpy(v, a, 24); s->n = 1; }
-    else if (t >= 1) { memcpy(v, b, 24); memcpy(s->w[0], b, 24); s->ia[0] = s->ia[1]; s->ib[0] = s->ib[1]; s->n = 1; }
-    else for (int i = 0; i < 3; i++) v[i] = a[i] + t * ab[i];
-    return 0;
-  }
   int keep;
-  if (s->n == 3) {
-    keep = closest_tri(s->w[0], s->w[1], s->w[2], v);
-  } else {
-    /* tetrahedron: closest over the faces the origin lies outside of (Ericson 5.1.6) */
+  if (s->n == 2) keep = closest_seg(s->w[0], s->w[1], v);
+  else if (s->n == 3) keep = closest_tri(s->w[0], s->w[1], s->w[2], v);
+  else {
     static const int F[4][4] = {{0, 1, 2, 3}, {0, 2, 3, 1}, {0, 3, 1, 2}, {1, 3, 2, 0}};
-    double best = DBL_MAX, bv[3] = {0, 0, 0};
+    const double *A = s->w[0], *B = s->w[1], *C = s->w[2], *D = s->w[3];
+    double ab[3], ac[3], ad[3], bc[3], bd[3], cd[3], n[3];
+    sub3(ab, B, A); sub3(ac, C, A); sub3(ad, D, A); sub3(bc, C, B); sub3(bd, D, B); sub3(cd, D, C);
+    cross3(n, ab, ac);
+    double vol6 = dot3(n, ad);
+    double l2 = fmax(fmax(dot3(ab, ab), dot3(ac, ac)), fmax(fmax(dot3(ad, ad), dot3(bc, bc)), fmax(dot3(bd, bd), dot3(cd, cd))));
+    if (fabs(vol6) > 1e-9 * l2 * sqrt(l2)) {
+      int inside = 1;
+      for (int f = 0; f < 4 && inside; f++) {
+        const double *a = s->w[F[f][0]], *b = s->w[F[f][1]], *c = s->w[F[f][2]], *d = s->w[F[f][3]];
+        double e1[3], e2[3], fn[3], ed[3];
+        sub3(e1, b, a); sub3(e2, c, a); cross3(fn, e1, e2); sub3(ed, d, a);
+        double sp = -dot3(a, fn), sd = dot3(ed, fn);
+        if (!(sp * sd > 0)) inside = 0; /* origin strictly on d's side of every face */
+      }
+      if (inside) { v[0] = v[1] = v[2] = 0; return 1; }
+    }
+    double best = DBL_MAX;
     keep = 0;
-    int outside_any = 0;
     for (int f = 0; f < 4; f++) {
-      const double *a = s->w[F[f][0]], *b = s->w[F[f][1]], *c = s->w[F[f][2]], *d = s->w[F[f][3]];
-      double ab[3], ac[3], n[3], ad[3];
-      sub3(ab, b, a); sub3(ac, c, a); cross3(n, ab, ac); sub3(ad, d, a);
-      double sp = -dot3(a, n), sd = dot3(ad, n);
-      if (sp * sd < 0 || sd == 0) { /* origin on the other side of the face than d (or flat) */
-        outside_any = 1;
-        double q[3];
-        int m = closest_tri(a, b, c, q);
-        double dd = dot3(q, q);
-        if (dd < best) {
-          best = dd; memcpy(bv, q, 24);
-          keep = 0;
-          for (int k = 0; k < 3; k++) if (m & (1 << k)) keep |= 1 << F[f][k];
-        }
+      double q[3];
+      int m = closest_tri(s->w[F[f][0]], s->w[F[f][1]], s->w[F[f][2]], q);
+      double dd = dot3(q, q);
+      if (dd < best) {
+        best = dd; memcpy(v, q, 24);
+        keep = 0;
+        for (int k = 0; k < 3; k++) if (m & (1 << k)) keep |= 1 << F[f][k];
       }
     }
-    if (!outside_any) { v[0] = v[1] = v[2] = 0; return 1; }
-    memcpy(v, bv, 24);
   }
   int j = 0;
   for (int i = 0; i < s->n; i++)

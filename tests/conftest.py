@@ -49,6 +49,10 @@ def golden_vectors():
 
 @pytest.fixture(scope="session")
 def packs(sp):
+    return make_packs(sp)
+
+
+def make_packs(sp):
     """Lazily built scene packs shared by the tests."""
     cache = {}
 

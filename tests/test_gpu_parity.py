@@ -12,6 +12,7 @@ pytestmark = pytest.mark.gpu
 
 def _compare(pkg, orc, pack, q, kmax=8, mode=0):
     dev = pkg.Scene(pack, 0, mode)
+    dev.set_option(pkg.OPT_SWEEP_MIN_CONFIGS, 1)  # small batches too go through k_sweep where it applies
     ref = orc.Oracle(pack, mode)
     table, bits, near = dev.safe_intervals_batch(q, kmax)
     rtable, rbits = ref.safe_intervals_batch(q, kmax)
@@ -22,7 +23,8 @@ def _compare(pkg, orc, pack, q, kmax=8, mode=0):
 
 
 @pytest.mark.parametrize("name,n", [("synA_32_200", 512), ("synB_32_200", 512), ("synC_32_200", 512), ("synA_64_1000", 96),
-                                    ("synA_5_33", 64), ("synB_3_1", 64), ("synA_70_64", 128)])
+                                    ("synA_5_33", 64), ("synB_3_1", 64), ("synA_70_64", 128), ("synA_32_200", 20011),
+                                    ("synB_16_100", 9000), ("synC_16_100", 9000)])
 def test_synthetic_sweeps_bit_exact(pkg, orc, sp, packs, name, n):
     pk = packs(name)
     dev, ref, bits, near = _compare(pkg, orc, pk, random_q(sp, pk, n, 13))
@@ -33,6 +35,7 @@ def test_generic_kernel_equals_sweep_kernel(pkg, orc, sp, packs):
     pk = packs("synB_32_200")
     q = random_q(sp, pk, 256, 21)
     a = pkg.Scene(pk)
+    a.set_option(pkg.OPT_SWEEP_MIN_CONFIGS, 1)
     b = pkg.Scene(pk)
     b.set_option(pkg.OPT_USE_SWEEP, 0)
     ta, ba, _ = a.safe_intervals_batch(q, 8)

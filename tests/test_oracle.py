@@ -30,6 +30,27 @@ def test_closed_forms_against_gjk(orc):
         assert abs(d_ps - orc.gjk_distance(p[None], np.stack([a, b]))) < 1e-9
 
 
+def test_gjk_is_frame_invariant_on_hulls(orc, packs, sp):
+    """Hull-vs-hull distances must not depend on the frame the pair is expressed in: coplanar
+    support points make naive tetrahedron tests report false penetrations at sporadic poses
+    (seen on the multi-robot scene before the simplex solver guarded flat tetrahedra)."""
+    sc = sp.read_pack(packs("multiple_robots"))
+    o = orc.Oracle(packs("multiple_robots"))
+    q = sp.random_configs(sc.robot, 24, 19)[:, 12].astype(np.float64)
+    R, t = o.fk(q)
+    A = sc.robot.shapes[2].verts.astype(np.float64)
+    B = sc.robot_obstacles[1].robot.shapes[2].verts.astype(np.float64)
+    for f in list(range(0, 1800, 37)) + [25, 100, 124, 660, 662, 712]:
+        x = o.robot_obstacle_fk(1, f)[0]
+        RB, tB = x[:9].reshape(3, 3), x[9:]
+        Aw, Bw = A @ R[0].T + t[0], B @ RB.T + tB
+        d_w = orc.gjk_distance(Aw, Bw)
+        d_l = orc.gjk_distance(A, (Bw - t[0]) @ R[0])
+        d_o = o.pair_distance(q, 0, 11, f)
+        assert abs(d_w - d_l) < 1e-10 and abs(d_w - d_o) < 1e-10, (f, d_w, d_l, d_o)
+        assert d_w > 0.02
+
+
 def test_fk_sanity_values(orc, packs, sp):
     """link frame origins (m) computed independently with NumPy from the URDFs."""
     o = orc.Oracle(packs("scene_task"))  # xarm6vis

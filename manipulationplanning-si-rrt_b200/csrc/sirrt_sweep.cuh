@@ -3,21 +3,21 @@
 // sweep, the mass-test cubes with the capsule xArm6).  Hull links and robot obstacles stay on the
 // generic k_collide_bits.
 //
-// One warp owns a group of 32 configurations and walks a cull hierarchy whose lane mapping changes
-// per level so that lanes stay busy:
-//   FK        lane = configuration   FP64 chain (RobotObstacleFCL.cpp:287-386), capsule end points
-//                                    narrowed to FP32 into shared memory [link][xyz a,b][32]
-//   level A   lane = configuration   link bounding spheres (registers) vs the swept bounding sphere
-//                                    of every dynamic slot over every 32-frame tile (uniform float4
-//                                    loads) -> per-lane link mask
-//   level B   lane = frame of tile   for each surviving (configuration, tile, slot): links first
-//                                    tested against the slot's swept capsule (lane = link), then per
-//                                    frame the point-segment distance from the obstacle centre to the
-//                                    link axis decides FREE / HIT (inscribed sphere) / UNDECIDED;
-//                                    __ballot_sync of the hits is one word of the collision row
-//   level C   lane = queued pair     UNDECIDED (configuration, link, slot, frame) pairs are compacted
-//                                    into a shared-memory queue and evaluated 32 at a time with the
-//                                    exact segment-box distance
+// One warp owns a group of 32 configurations and pushes them through a pipeline of cull stages.
+// Every stage works on a full batch of 32 items (one per lane); survivors are compacted with
+// __ballot_sync / popc prefix ranks into per-warp shared-memory stacks, so the lanes stay busy at
+// every level although fewer than 1 in 1000 (link, obstacle, frame) pairs reaches the exact test:
+//   FK   lane = configuration   FP64 chain (RobotObstacleFCL.cpp:287-386); capsule centre, axis and
+//                               1/|axis|^2 narrowed to FP32 into shared memory [link][7][32]
+//   A0   lane = configuration   whole-arm bounding sphere vs the swept bounding sphere of every
+//                               (32-frame tile, dynamic slot) pair (uniform float4 loads)      -> Q0
+//   A1   lane = Q0 entry        the 7 link bounding spheres vs that swept sphere; one Q1 entry per
+//                               surviving link (warp prefix sum of popcounts)                   -> Q1
+//   B1   lane = Q1 entry        link axis vs the slot's swept capsule over the tile (segment-segment)
+//   B2   lane = frame of tile   per B1 survivor: point-segment distance from the obstacle centre to
+//                               the link axis decides FREE / HIT (inscribed sphere) / UNDECIDED per
+//                               frame; __ballot_sync of the hits is one word of the collision row -> Q3
+//   C    lane = Q3 entry        exact segment-box distance for the UNDECIDED (config, link, slot, frame)
 // Pairs inside the FP32 uncertainty band go to the FP64 re-check work list exactly as in the
 // generic kernel.  Collision rows accumulate in shared memory and leave as coalesced 128-byte rows.
 #pragma once
@@ -27,12 +27,19 @@
 #include "sirrt_tables.hpp"
 
 #define SWEEP_MAXL 8
-#define SWEEP_WARPS 4
-#define SWEEP_QCAP 64
+#define SWEEP_WARPS 2
+#define SWEEP_Q0CAP 160   // 31 left over + 4 x 32 pushed per A0 round
+#define SWEEP_Q1CAP 256   // 31 left over + 32 x 7 pushed per A1 batch
+#define SWEEP_Q3CAP 64    // 31 left over + 32 pushed per B2 entry
+#define SWEEP_ROWS 7      // per link: centre xyz, axis xyz (b - a), 1 / |axis|^2
 
 struct SweepTables {
   int supported = 0;
-  const float4* seg = nullptr;  // [(tile*n_dynamic + j)*2]: (p0, r) and (p1, 0): swept capsule of slot j over the tile
+  const float4* bounds = nullptr;  // [pair]: swept bounding sphere of (tile, slot j), pair = tile*n_dynamic + j, padded to x4
+  const float4* seg = nullptr;     // [pair*2]: (p0, r) and (p1, 0): swept capsule of the slot over the tile
+  const uint32_t* pcode = nullptr; // [pair]: tile << 11 | j
+  const float4* dyn = nullptr;     // [j]: inscribed radius, bounding radius, sphere radius or -1, slot id (int bits)
+  int n_pairs = 0;
   int n_links = 0;
   float link_r[SWEEP_MAXL], link_br[SWEEP_MAXL];
   int blocks_per_sm = 0;
@@ -45,8 +52,11 @@ struct SweepParams {
   QView q;
   WorkList wl;
   uint32_t* bits;
+  const float4* bounds;
   const float4* seg;
-  int n_words, Wp, n_links;
+  const uint32_t* pcode;
+  const float4* dyn;
+  int n_pairs, n_words, Wp, n_links;
   float band;
   float link_r[SWEEP_MAXL], link_br[SWEEP_MAXL];
 };
@@ -93,25 +103,67 @@ __device__ __forceinline__ int capsule_exact(const float* a, const float* b, flo
   return classify(d, band);
 }
 
-#define SWEEP_PACK(cfg, l, fr, tile, j) ((unsigned)(cfg) | ((unsigned)(l) << 5) | ((unsigned)(fr) << 8) | ((unsigned)(tile) << 13) | ((unsigned)(j) << 21))
+// per-warp link table, column = configuration of the group; the column is rotated by the link so that
+// queue entries of one configuration with different links fall into different banks
+#define LK(l, k, cfg) lk[((l) * SWEEP_ROWS + (k)) * 32 + (((cfg) + 5 * (l)) & 31)]
+
+// stage C: exact FP32 narrowphase for up to 32 queued (configuration, link, frame, pair) entries, one per lane
+__device__ __noinline__ unsigned sweep_exact_batch(const SweepParams& P, const float* lk, uint32_t* sbits, const float* s_lr,
+                                                   const uint32_t* q, int count, int lane, long long cfg0) {
+  __syncwarp();
+  unsigned n_exact = 0;
+  if (lane < count) {
+    const DScene& sc = P.sc;
+    const uint32_t u = q[lane];
+    const int cfg = u & 31, l = (u >> 5) & 7, fr = (u >> 8) & 31;
+    const uint32_t code = __ldg(P.pcode + (u >> 13));
+    const int tile = code >> 11, j = code & 2047;
+    if (!((sbits[cfg * P.Wp + tile] >> fr) & 1u)) {  // another pair may have decided this frame already
+      const int slot = sc.dynamic_slots[j];
+      const DSlot S = sc.slots[slot];
+      const DShape& sh = sc.shapes[S.shape];
+      const int f = tile * 32 + fr;
+      float a[3], b[3], R[9], t[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const float c = LK(l, k, cfg), h = 0.5f * LK(l, 3 + k, cfg);
+        a[k] = c - h; b[k] = c + h;
+      }
+      load_pose(sc, slot, f, R, t, !S.rot_identity);
+      const int r = capsule_exact(a, b, s_lr[l], sh, R, t, S.rot_identity != 0, P.band);
+      n_exact = 1;
+      if (r == RES_HIT) atomicOr(&sbits[cfg * P.Wp + tile], 1u << fr);
+      else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), f, l, slot, 0);
+    }
+  }
+  __syncwarp();
+  return n_exact;
+}
 
 __global__ void __launch_bounds__(SWEEP_WARPS * 32)
 k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P) {
   extern __shared__ __align__(16) unsigned char sweep_smem[];
+  __shared__ float s_lr[SWEEP_MAXL];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const DScene& sc = P.sc;
-  const int L = P.n_links, Wp = P.Wp, W = P.n_words, nd = sc.n_dynamic;
-  const size_t per_warp = ((size_t)L * 6 * 32 + (size_t)32 * Wp + SWEEP_QCAP) * 4;
-  float* ends = (float*)(sweep_smem + (size_t)wib * per_warp);  // [l][k][32]: k 0..2 = a, 3..5 = b
-  uint32_t* sbits = (uint32_t*)(ends + (size_t)L * 6 * 32);     // [cfg][Wp]
-  uint32_t* q3 = sbits + (size_t)32 * Wp;                       // level-C queue
+  const int L = P.n_links, Wp = P.Wp, W = P.n_words;
+  const size_t per_warp = ((size_t)L * SWEEP_ROWS * 32 + (size_t)32 * Wp + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_Q3CAP) * 4;
+  float* lk = (float*)(sweep_smem + (size_t)wib * per_warp);
+  uint32_t* sbits = (uint32_t*)(lk + (size_t)L * SWEEP_ROWS * 32);  // [cfg][Wp]
+  uint32_t* q0 = sbits + (size_t)32 * Wp;
+  uint32_t* q1 = q0 + SWEEP_Q0CAP;
+  uint32_t* q3 = q1 + SWEEP_Q1CAP;
+  if (threadIdx.x < SWEEP_MAXL) s_lr[threadIdx.x] = P.link_r[threadIdx.x];
+  __syncthreads();
   const float band = P.band;
   const unsigned lt_mask = (1u << lane) - 1u;
   unsigned int n_exact = 0;
   const long long n_groups = (P.q.cnt + 31) / 32;
+  const int n_pairs = P.n_pairs;  // padded to a multiple of 4 with unreachable spheres
 
   for (long long group = (long long)blockIdx.x * SWEEP_WARPS + wib; group < n_groups; group += (long long)gridDim.x * SWEEP_WARPS) {
-    const long long n = P.q.n0 + group * 32 + lane;
+    const long long cfg0 = P.q.n0 + group * 32;
+    const long long n = cfg0 + lane;
     const bool have = group * 32 + lane < P.q.cnt;
     __syncwarp();
     for (int i = lane; i < 32 * Wp; i += 32) sbits[i] = 0u;
@@ -121,23 +173,40 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
       double q[SIRRT_MAXJ];
       for (int j = 0; j < rb.n_joints; j++) q[j] = (have && j < P.q.dof) ? load_q(P.q, n, j) : 0.0;
       fk_each_link(rb, q, [&](int l, const double* Rl, const double* tl) {
-        const double hl = sc.shapes[rb.link_shape[l]].d_half_len;
+        const double len = 2.0 * sc.shapes[rb.link_shape[l]].d_half_len;
+        float ab[3];
 #pragma unroll
-        for (int k = 0; k < 3; k++) {  // capsule core: local (0, 0, -+half_len)
-          ends[(l * 6 + k) * 32 + lane] = (float)(tl[k] - Rl[3 * k + 2] * hl);
-          ends[(l * 6 + 3 + k) * 32 + lane] = (float)(tl[k] + Rl[3 * k + 2] * hl);
+        for (int k = 0; k < 3; k++) {  // capsule core: local (0, 0, -+half_len) around the link origin
+          ab[k] = (float)(Rl[3 * k + 2] * len);
+          LK(l, k, lane) = (float)tl[k];
+          LK(l, 3 + k, lane) = ab[k];
         }
+        const float den = ab[0] * ab[0] + ab[1] * ab[1] + ab[2] * ab[2];
+        LK(l, 6, lane) = den > 0.f ? 1.f / den : 0.f;
       });
     }
     __syncwarp();
-    float cx[SWEEP_MAXL], cy[SWEEP_MAXL], cz[SWEEP_MAXL];  // link bounding-sphere centres (registers)
+    // whole-arm bounding sphere of this lane's configuration (covers every link bounding sphere)
+    float acx, acy, acz, ar = 0.f;
+    {
+      float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
 #pragma unroll
-    for (int l = 0; l < SWEEP_MAXL; l++) {
-      if (l < L) {
-        cx[l] = 0.5f * (ends[(l * 6 + 0) * 32 + lane] + ends[(l * 6 + 3) * 32 + lane]);
-        cy[l] = 0.5f * (ends[(l * 6 + 1) * 32 + lane] + ends[(l * 6 + 4) * 32 + lane]);
-        cz[l] = 0.5f * (ends[(l * 6 + 2) * 32 + lane] + ends[(l * 6 + 5) * 32 + lane]);
-      } else cx[l] = cy[l] = cz[l] = 0.f;
+      for (int l = 0; l < SWEEP_MAXL; l++)
+        if (l < L) {
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            const float c = LK(l, k, lane);
+            lo[k] = fminf(lo[k], c - P.link_br[l]); hi[k] = fmaxf(hi[k], c + P.link_br[l]);
+          }
+        }
+      acx = 0.5f * (lo[0] + hi[0]); acy = 0.5f * (lo[1] + hi[1]); acz = 0.5f * (lo[2] + hi[2]);
+#pragma unroll
+      for (int l = 0; l < SWEEP_MAXL; l++)
+        if (l < L) {
+          const float dx = LK(l, 0, lane) - acx, dy = LK(l, 1, lane) - acy, dz = LK(l, 2, lane) - acz;
+          ar = fmaxf(ar, sqrtf(dx * dx + dy * dy + dz * dz) + P.link_br[l]);
+        }
+      ar = ar * 1.000001f + 1e-5f;
     }
 
     // ---- static slots: once per configuration, lane = configuration ---------------------------------
@@ -151,12 +220,12 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
       const float* c = sc.bcw_f + (size_t)slot * 3 * sc.Tp;
       const float ox = c[0], oy = c[sc.Tp], oz = c[2 * (size_t)sc.Tp];
       for (int l = 0; l < L && !static_hit; l++) {
-        float a[3], b[3];
-#pragma unroll
-        for (int k = 0; k < 3; k++) { a[k] = ends[(l * 6 + k) * 32 + lane]; b[k] = ends[(l * 6 + 3 + k) * 32 + lane]; }
-        const float dx = 0.5f * (a[0] + b[0]) - ox, dy = 0.5f * (a[1] + b[1]) - oy, dz = 0.5f * (a[2] + b[2]) - oz;
+        const float dx = LK(l, 0, lane) - ox, dy = LK(l, 1, lane) - oy, dz = LK(l, 2, lane) - oz;
         const float rr = (P.link_br[l] + S.br) * 1.000001f + 1e-5f + band;
         if (dx * dx + dy * dy + dz * dz > rr * rr) continue;
+        float a[3], b[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) { const float cc = LK(l, k, lane), h = 0.5f * LK(l, 3 + k, lane); a[k] = cc - h; b[k] = cc + h; }
         const int r = capsule_exact(a, b, P.link_r[l], sh, R, t, S.rot_identity != 0, band);
         n_exact++;
         if (r == RES_HIT) static_hit = true;
@@ -164,126 +233,141 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
       }
     }
     const bool active = have && !static_hit;
-    int q3n = 0;
+    int q0n = 0, q1n = 0, q3n = 0;
 
-    // level C: evaluate queued (configuration, link, slot, frame) pairs, one per lane
-    auto drain = [&](int count) {
-      __syncwarp();
-      if (lane < count) {
-        const unsigned u = q3[lane];
-        const int cfg = u & 31, l = (u >> 5) & 7, fr = (u >> 8) & 31, tile = (u >> 13) & 0xff, j = u >> 21;
-        if (!((sbits[cfg * Wp + tile] >> fr) & 1u)) {  // another pair may have decided this frame already
-          const int slot = sc.dynamic_slots[j];
-          const DSlot S = sc.slots[slot];
-          const DShape& sh = sc.shapes[S.shape];
-          const int f = tile * 32 + fr;
-          float a[3], b[3], R[9], t[3];
+    // ---- dynamic slots: A0 rounds of 4 (tile, slot) pairs, stages drained whenever a batch of 32 is ready
+    for (int it0 = 0;; it0 += 4) {
+      const bool flush = it0 >= n_pairs;
+      if (!flush) {
+        float4 tb[4];
 #pragma unroll
-          for (int k = 0; k < 3; k++) { a[k] = ends[(l * 6 + k) * 32 + cfg]; b[k] = ends[(l * 6 + 3 + k) * 32 + cfg]; }
-          load_pose(sc, slot, f, R, t, !S.rot_identity);
-          const int r = capsule_exact(a, b, P.link_r[l], sh, R, t, S.rot_identity != 0, band);
-          n_exact++;
-          if (r == RES_HIT) atomicOr(&sbits[cfg * Wp + tile], 1u << fr);
-          else if (r == RES_AMBIG) push_work(P.wl, (int)(P.q.n0 + group * 32 + cfg), f, l, slot, 0);
+        for (int u = 0; u < 4; u++) tb[u] = __ldg(P.bounds + it0 + u);
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const float dx = acx - tb[u].x, dy = acy - tb[u].y, dz = acz - tb[u].z;
+          const float rr = ar + tb[u].w + band;
+          const bool pass = active && (dx * dx + dy * dy + dz * dz <= rr * rr);
+          const unsigned m = __ballot_sync(SIRRT_FULL, pass);
+          if (pass) q0[q0n + __popc(m & lt_mask)] = (unsigned)lane | ((unsigned)(it0 + u) << 5);
+          q0n += __popc(m);
         }
       }
-      __syncwarp();
-      const int rest = q3n - count;  // < 32 by construction
-      unsigned keep = 0;
-      if (lane < rest) keep = q3[count + lane];
-      __syncwarp();
-      if (lane < rest) q3[lane] = keep;
-      q3n = rest;
-      __syncwarp();
-    };
-
-    // ---- dynamic slots ---------------------------------------------------------------------------
-    for (int tile = 0; tile < sc.n_tiles; tile++) {
-      const int f = tile * 32 + lane;
-      const bool valid = f < sc.T;
-      const int fc = valid ? f : sc.T - 1;
-      for (int j = 0; j < nd; j++) {
-        // level A: lane = configuration
-        const float4 tb = __ldg(&sc.tile_bounds[(size_t)tile * nd + j]);
-        unsigned lm = 0;
+      if (q0n >= 32 || flush) {
+        do {
+          if (q0n > 0) {
+            // ---- A1: lane = Q0 entry; link bounding spheres vs the swept sphere of the pair
+            const int cnt = min(32, q0n);
+            q0n -= cnt;
+            __syncwarp();
+            unsigned lm = 0, e = 0;
+            if (lane < cnt) {
+              e = q0[q0n + lane];
+              const int cfg = e & 31;
+              const float4 b4 = __ldg(P.bounds + (e >> 5));
 #pragma unroll
-        for (int l = 0; l < SWEEP_MAXL; l++) {
-          if (l < L) {
-            const float dx = cx[l] - tb.x, dy = cy[l] - tb.y, dz = cz[l] - tb.z;
-            const float rr = P.link_br[l] + tb.w + band;
-            if (dx * dx + dy * dy + dz * dz <= rr * rr) lm |= 1u << l;
+              for (int l = 0; l < SWEEP_MAXL; l++)
+                if (l < L) {
+                  const float dx = LK(l, 0, cfg) - b4.x, dy = LK(l, 1, cfg) - b4.y, dz = LK(l, 2, cfg) - b4.z;
+                  const float rr = P.link_br[l] + b4.w + band;
+                  if (dx * dx + dy * dy + dz * dz <= rr * rr) lm |= 1u << l;
+                }
+            }
+            const int c = __popc(lm);
+            int incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+              const int v = __shfl_up_sync(SIRRT_FULL, incl, o);
+              if (lane >= o) incl += v;
+            }
+            const int total = __shfl_sync(SIRRT_FULL, incl, 31);
+            const unsigned ebase = (e & 31u) | ((e >> 5) << 8);
+            int w = q1n + incl - c;
+            while (lm) {
+              const int l = __ffs(lm) - 1;
+              lm &= lm - 1;
+              q1[w++] = ebase | ((unsigned)l << 5);
+            }
+            q1n += total;
+            __syncwarp();
           }
-        }
-        if (!active) lm = 0;
-        unsigned m = __ballot_sync(SIRRT_FULL, lm != 0);
-        if (!m) continue;
-        const int slot = sc.dynamic_slots[j];
-        const DSlot S = sc.slots[slot];
-        const DShape& sh = sc.shapes[S.shape];
-        const float4 s0 = __ldg(&P.seg[((size_t)tile * nd + j) * 2]), s1 = __ldg(&P.seg[((size_t)tile * nd + j) * 2 + 1]);
-        const float* pp = sc.pose_f + ((size_t)slot * 12 + 9) * sc.Tp + fc;
-        const float t[3] = {pp[0], pp[sc.Tp], pp[2 * (size_t)sc.Tp]};  // obstacle centre at this lane's frame
-        const bool is_sphere = sh.type == SH_SPHERE;
-        const float insc = is_sphere ? sh.radius : fminf(sh.half[0], fminf(sh.half[1], sh.half[2]));
-        while (m) {
-          const int src = __ffs(m) - 1;
-          m &= m - 1;
-          const unsigned lms = __shfl_sync(SIRRT_FULL, lm, src);
-          // level B, part 1: lane = link; link axis vs the slot's swept capsule over the tile
-          bool kp = false;
-          if (lane < L && ((lms >> lane) & 1u)) {
-            float a[3], b[3];
+          while (q1n >= 32 || (flush && q0n == 0 && q1n > 0)) {
+            // ---- B1: lane = Q1 entry; link axis vs the slot's swept capsule over the tile
+            const int cnt = min(32, q1n);
+            q1n -= cnt;
+            bool kp = false;
+            unsigned e = 0;
+            if (lane < cnt) {
+              e = q1[q1n + lane];
+              const int cfg = e & 31, l = (e >> 5) & 7;
+              const unsigned it = e >> 8;
+              float a[3], b[3];
 #pragma unroll
-            for (int k = 0; k < 3; k++) { a[k] = ends[(lane * 6 + k) * 32 + src]; b[k] = ends[(lane * 6 + 3 + k) * 32 + src]; }
-            const float p0[3] = {s0.x, s0.y, s0.z}, p1[3] = {s1.x, s1.y, s1.z};
-            const float rr = P.link_r[lane] + s0.w + band;
-            kp = seg_seg_dist2(a, b, p0, p1) <= rr * rr;
-          }
-          unsigned keep = __ballot_sync(SIRRT_FULL, kp);
-          if (!keep) continue;
-          // level B, part 2: lane = frame
-          const uint32_t cur = sbits[src * Wp + tile];
-          bool done = !valid || ((cur >> lane) & 1u);
-          bool hit = false;
-          while (keep) {
-            const int l = __ffs(keep) - 1;
-            keep &= keep - 1;
-            float a[3], b[3];
-#pragma unroll
-            for (int k = 0; k < 3; k++) { a[k] = ends[(l * 6 + k) * 32 + src]; b[k] = ends[(l * 6 + 3 + k) * 32 + src]; }
-            const float d2 = pt_seg_dist2(t, a, b);
-            const float rl = P.link_r[l];
-            bool want = false;
-            if (!done) {
-              if (is_sphere) {  // the point-segment distance IS the narrowphase
-                const int r = classify(sqrtf(d2) - rl - insc, band);
-                n_exact++;
-                if (r == RES_HIT) hit = true;
-                else if (r == RES_AMBIG) push_work(P.wl, (int)(P.q.n0 + group * 32 + src), fc, l, slot, 0);
-              } else {
-                const float hi = rl + S.br + band;   // beyond the circumscribed sphere: free
-                const float lo = rl + insc - band;   // inside the inscribed sphere: hit
-                if (d2 <= hi * hi) {
-                  if (d2 < lo * lo) hit = true;
-                  else want = true;
+              for (int k = 0; k < 3; k++) { const float cc = LK(l, k, cfg), h = 0.5f * LK(l, 3 + k, cfg); a[k] = cc - h; b[k] = cc + h; }
+              const float4 s0 = __ldg(P.seg + 2 * (size_t)it), s1 = __ldg(P.seg + 2 * (size_t)it + 1);
+              const float p0[3] = {s0.x, s0.y, s0.z}, p1[3] = {s1.x, s1.y, s1.z};
+              const float rr = s_lr[l] + s0.w + band;
+              kp = seg_seg_dist2(a, b, p0, p1) <= rr * rr;
+            }
+            unsigned keep = __ballot_sync(SIRRT_FULL, kp);
+            while (keep) {
+              // ---- B2: lane = frame of the tile, one B1 survivor at a time
+              const int src = __ffs(keep) - 1;
+              keep &= keep - 1;
+              const unsigned ee = __shfl_sync(SIRRT_FULL, e, src);
+              const int cfg = ee & 31, l = (ee >> 5) & 7;
+              const unsigned it = ee >> 8;
+              const uint32_t code = __ldg(P.pcode + it);
+              const int tile = code >> 11, j = code & 2047;
+              const float4 dj = __ldg(P.dyn + j);
+              const int slot = __float_as_int(dj.w);
+              const int f = tile * 32 + lane;
+              const bool valid = f < sc.T;
+              const int fc = valid ? f : sc.T - 1;
+              const float* pp = sc.pose_f + ((size_t)slot * 12 + 9) * sc.Tp + fc;
+              const float apx = pp[0] - LK(l, 0, cfg), apy = pp[sc.Tp] - LK(l, 1, cfg), apz = pp[2 * (size_t)sc.Tp] - LK(l, 2, cfg);
+              const float abx = LK(l, 3, cfg), aby = LK(l, 4, cfg), abz = LK(l, 5, cfg);
+              float tt = (apx * abx + apy * aby + apz * abz) * LK(l, 6, cfg);
+              tt = fminf(fmaxf(tt, -0.5f), 0.5f);
+              const float ex = apx - tt * abx, ey = apy - tt * aby, ez = apz - tt * abz;
+              const float d2 = ex * ex + ey * ey + ez * ez;
+              const uint32_t cur = sbits[cfg * Wp + tile];
+              const bool done = !valid || ((cur >> lane) & 1u);
+              const float rl = s_lr[l];
+              bool hit = false, want = false;
+              if (!done) {
+                if (dj.z >= 0.f) {  // sphere obstacle: the point-segment distance IS the narrowphase
+                  const int r = classify(sqrtf(d2) - rl - dj.z, band);
+                  n_exact++;
+                  if (r == RES_HIT) hit = true;
+                  else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), fc, l, slot, 0);
+                } else {
+                  const float hi = rl + dj.y + band;  // beyond the circumscribed sphere: free
+                  const float lo = rl + dj.x - band;  // inside the inscribed sphere: hit
+                  if (d2 <= hi * hi) {
+                    if (lo > 0.f && d2 < lo * lo) hit = true;
+                    else want = true;
+                  }
                 }
               }
-            }
-            done |= hit;
-            const unsigned mq = __ballot_sync(SIRRT_FULL, want);
-            if (mq) {
-              if (want) q3[q3n + __popc(mq & lt_mask)] = SWEEP_PACK(src, l, lane, tile, j);
-              q3n += __popc(mq);
-              if (q3n >= 32) drain(32);
+              const unsigned word = __ballot_sync(SIRRT_FULL, hit);
+              if (word && lane == 0) sbits[cfg * Wp + tile] = cur | word;
+              const unsigned mq = __ballot_sync(SIRRT_FULL, want);
+              if (mq) {
+                if (want) q3[q3n + __popc(mq & lt_mask)] = (unsigned)cfg | ((unsigned)l << 5) | ((unsigned)lane << 8) | (it << 13);
+                q3n += __popc(mq);
+              }
+              __syncwarp();
+              if (q3n >= 32) {
+                q3n -= 32;
+                n_exact += sweep_exact_batch(P, lk, sbits, s_lr, q3 + q3n, 32, lane, cfg0);
+              }
             }
           }
-          const unsigned word = __ballot_sync(SIRRT_FULL, hit);
-          if (word && lane == 0) atomicOr(&sbits[src * Wp + tile], word);
-          __syncwarp();
-        }
+        } while (q0n >= 32 || (flush && q0n > 0));
       }
+      if (flush) break;
     }
-    if (q3n > 0) drain(q3n);
+    if (q3n > 0) n_exact += sweep_exact_batch(P, lk, sbits, s_lr, q3, q3n, lane, cfg0);
 
     // ---- rows out: lane = word, coalesced ------------------------------------------------------------
     __syncwarp();
@@ -305,6 +389,15 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
 }
 
 // ---------------------------------------------------------------------------------------------------
+static inline int sweep_upload(const void* src, size_t bytes, std::vector<void*>& owned, const void** out) {
+  void* p = nullptr;
+  if (cudaMalloc(&p, bytes) != cudaSuccess) { cudaGetLastError(); return -3; }
+  owned.push_back(p);
+  if (cudaMemcpy(p, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) { cudaGetLastError(); return -3; }
+  *out = p;
+  return 0;
+}
+
 static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& tb, const DScene& d, SweepTables* st, std::vector<void*>& owned) {
   st->supported = 0;
   const int L = hs.robot.n_links, nd = tb.n_dynamic;
@@ -315,13 +408,24 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
     st->link_r[l] = (float)s.radius;
     st->link_br[l] = tb.shapes[l].br;
   }
+  for (int j = 0; j < nd; j++) {
+    const int t = tb.shapes[tb.slots[tb.dynamic_slots[j]].shape].type;
+    if (t != SH_BOX && t != SH_SPHERE) return 0;
+  }
   st->n_links = L;
-  // swept capsule of every dynamic slot over every tile: segment between the bounding-sphere centres
-  // at the tile's first and last frame, radius = largest deviation from it + the slot's radius
-  std::vector<float4> seg((size_t)tb.n_tiles * std::max(nd, 1) * 2, make_float4(0, 0, 0, -1));
+  const int n_real = tb.n_tiles * nd, n_pairs = (n_real + 3) / 4 * 4;
+  // pair tables.  bounds: swept bounding sphere (copied from the scene tables, padded with unreachable
+  // spheres); seg: swept capsule = segment between the bounding-sphere centres at the tile's first and
+  // last frame, radius = largest deviation from it + the slot's radius; pcode: tile << 11 | j
+  std::vector<float4> bounds((size_t)std::max(n_pairs, 4), make_float4(1e18f, 1e18f, 1e18f, 0.f));
+  std::vector<float4> seg((size_t)std::max(n_pairs, 4) * 2, make_float4(0, 0, 0, -1));
+  std::vector<uint32_t> pcode((size_t)std::max(n_pairs, 4), 0u);
   const int Tp = tb.Tp, T = tb.T;
   for (int tile = 0; tile < tb.n_tiles; tile++)
     for (int j = 0; j < nd; j++) {
+      const size_t it = (size_t)tile * nd + j;
+      bounds[it] = tb.tile_bounds[it];
+      pcode[it] = ((uint32_t)tile << 11) | (uint32_t)j;
       const int s = tb.dynamic_slots[j];
       const int f0 = tile * 32, f1 = std::min(tile * 32 + 32, T) - 1;
       auto ctr = [&](int f, double* c) { for (int k = 0; k < 3; k++) c[k] = (double)tb.bcw_f[((size_t)s * 3 + k) * Tp + f]; };
@@ -338,16 +442,33 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
         dev = std::max(dev, sqrt(dd));
       }
       const double rad = (dev + (double)tb.slots[s].br) * (1 + 1e-6) + 1e-5;
-      seg[((size_t)tile * nd + j) * 2] = make_float4((float)p0[0], (float)p0[1], (float)p0[2], (float)rad);
-      seg[((size_t)tile * nd + j) * 2 + 1] = make_float4((float)p1[0], (float)p1[1], (float)p1[2], 0.f);
+      seg[it * 2] = make_float4((float)p0[0], (float)p0[1], (float)p0[2], (float)rad);
+      seg[it * 2 + 1] = make_float4((float)p1[0], (float)p1[1], (float)p1[2], 0.f);
     }
-  void* p = nullptr;
-  if (cudaMalloc(&p, seg.size() * sizeof(float4)) != cudaSuccess) { cudaGetLastError(); return -3; }
-  owned.push_back(p);
-  if (cudaMemcpy(p, seg.data(), seg.size() * sizeof(float4), cudaMemcpyHostToDevice) != cudaSuccess) { cudaGetLastError(); return -3; }
+  // per dynamic slot: inscribed / bounding radius around the pose origin, sphere radius (or -1), slot id
+  std::vector<float4> dyn((size_t)std::max(nd, 1), make_float4(0, 0, -1, 0));
+  for (int j = 0; j < nd; j++) {
+    const int s = tb.dynamic_slots[j];
+    const DShape& sh = tb.shapes[tb.slots[s].shape];
+    float4 v;
+    v.x = sh.type == SH_SPHERE ? sh.radius : fminf(sh.half[0], fminf(sh.half[1], sh.half[2]));
+    v.y = tb.slots[s].br;
+    v.z = sh.type == SH_SPHERE ? sh.radius : -1.f;
+    memcpy(&v.w, &s, 4);
+    dyn[j] = v;
+  }
+  const void* p = nullptr;
+  if (sweep_upload(bounds.data(), bounds.size() * sizeof(float4), owned, &p)) return -3;
+  st->bounds = (const float4*)p;
+  if (sweep_upload(seg.data(), seg.size() * sizeof(float4), owned, &p)) return -3;
   st->seg = (const float4*)p;
+  if (sweep_upload(pcode.data(), pcode.size() * sizeof(uint32_t), owned, &p)) return -3;
+  st->pcode = (const uint32_t*)p;
+  if (sweep_upload(dyn.data(), dyn.size() * sizeof(float4), owned, &p)) return -3;
+  st->dyn = (const float4*)p;
+  st->n_pairs = nd > 0 ? n_pairs : 0;
   st->Wp = tb.n_tiles | 1;
-  st->smem = (size_t)SWEEP_WARPS * ((size_t)L * 6 * 32 + (size_t)32 * st->Wp + SWEEP_QCAP) * 4;
+  st->smem = (size_t)SWEEP_WARPS * ((size_t)L * SWEEP_ROWS * 32 + (size_t)32 * st->Wp + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_Q3CAP) * 4;
   if (st->smem > 200 * 1024) return 0;
   if (cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem) != cudaSuccess) { cudaGetLastError(); return 0; }
   int bps = 0;
@@ -361,7 +482,8 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
 static inline int sweep_launch(const SweepTables& st, const DRobot& rb, const DScene& sc, const QView& q, const WorkList& wl, uint32_t* bits,
                                int n_words, float band, int n_sm, cudaStream_t stream) {
   SweepParams P{};
-  P.sc = sc; P.q = q; P.wl = wl; P.bits = bits; P.seg = st.seg; P.n_words = n_words; P.Wp = st.Wp; P.n_links = st.n_links; P.band = band;
+  P.sc = sc; P.q = q; P.wl = wl; P.bits = bits; P.bounds = st.bounds; P.seg = st.seg; P.pcode = st.pcode; P.dyn = st.dyn;
+  P.n_pairs = st.n_pairs; P.n_words = n_words; P.Wp = st.Wp; P.n_links = st.n_links; P.band = band;
   for (int l = 0; l < SWEEP_MAXL; l++) { P.link_r[l] = l < st.n_links ? st.link_r[l] : 0.f; P.link_br[l] = l < st.n_links ? st.link_br[l] : 0.f; }
   const long long groups = (q.cnt + 31) / 32;
   const long long blocks = std::min((groups + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)n_sm * st.blocks_per_sm);

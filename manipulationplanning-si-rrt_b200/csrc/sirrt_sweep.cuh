@@ -28,18 +28,19 @@
 
 #define SWEEP_MAXL 8
 #define SWEEP_WARPS 2
-#define SWEEP_Q0CAP 160   // 31 left over + 4 x 32 pushed per A0 round
+#define SWEEP_Q0CAP 288   // 31 left over + 32 x 8 pushed per A0 round
 #define SWEEP_Q1CAP 256   // 31 left over + 32 x 7 pushed per A1 batch
 #define SWEEP_Q3CAP 64    // 31 left over + 32 pushed per B2 entry
 #define SWEEP_ROWS 7      // per link: centre xyz, axis xyz (b - a), 1 / |axis|^2
+#define SWEEP_LDC 33      // row stride of the per-warp link table (33: rows of one configuration fall into different banks)
+#define SWEEP_PER_WARP(L, Wp) ((size_t)(L) * SWEEP_ROWS * SWEEP_LDC + (size_t)32 * (Wp) + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_Q3CAP)
 
 struct SweepTables {
   int supported = 0;
-  const float4* bounds = nullptr;  // [pair]: swept bounding sphere of (tile, slot j), pair = tile*n_dynamic + j, padded to x4
+  const float4* bounds = nullptr;  // [pair]: swept bounding sphere of (tile, slot j), pair = tile*ndp + j (ndp = n_dynamic padded to x8)
   const float4* seg = nullptr;     // [pair*2]: (p0, r) and (p1, 0): swept capsule of the slot over the tile
-  const uint32_t* pcode = nullptr; // [pair]: tile << 11 | j
-  const float4* dyn = nullptr;     // [j]: inscribed radius, bounding radius, sphere radius or -1, slot id (int bits)
-  int n_pairs = 0;
+  const float4* dyn = nullptr;     // [j]: inscribed radius, bounding radius, sphere radius or -1, offset of the slot's translation rows in pose_f (int bits)
+  int ndp = 0;
   int n_links = 0;
   float link_r[SWEEP_MAXL], link_br[SWEEP_MAXL];
   int blocks_per_sm = 0;
@@ -54,9 +55,8 @@ struct SweepParams {
   uint32_t* bits;
   const float4* bounds;
   const float4* seg;
-  const uint32_t* pcode;
   const float4* dyn;
-  int n_pairs, n_words, Wp, n_links;
+  int ndp, n_words, Wp, n_links;
   float band;
   float link_r[SWEEP_MAXL], link_br[SWEEP_MAXL];
 };
@@ -103,9 +103,10 @@ __device__ __forceinline__ int capsule_exact(const float* a, const float* b, flo
   return classify(d, band);
 }
 
-// per-warp link table, column = configuration of the group; the column is rotated by the link so that
-// queue entries of one configuration with different links fall into different banks
-#define LK(l, k, cfg) lk[((l) * SWEEP_ROWS + (k)) * 32 + (((cfg) + 5 * (l)) & 31)]
+// per-warp link table: row (l*7 + k), column = configuration of the group, row stride 33 floats
+#define LK(l, k, cfg) lk[((l) * SWEEP_ROWS + (k)) * SWEEP_LDC + (cfg)]
+// queue entries: configuration (5 bits), link (3), frame (5), pair code = tile << 11 | j (19)
+#define SWEEP_PAIR(code, ndp) ((int)((code) >> 11) * (ndp) + (int)((code) & 2047u))
 
 // stage C: exact FP32 narrowphase for up to 32 queued (configuration, link, frame, pair) entries, one per lane
 __device__ __noinline__ unsigned sweep_exact_batch(const SweepParams& P, const float* lk, uint32_t* sbits, const float* s_lr,
@@ -116,8 +117,7 @@ __device__ __noinline__ unsigned sweep_exact_batch(const SweepParams& P, const f
     const DScene& sc = P.sc;
     const uint32_t u = q[lane];
     const int cfg = u & 31, l = (u >> 5) & 7, fr = (u >> 8) & 31;
-    const uint32_t code = __ldg(P.pcode + (u >> 13));
-    const int tile = code >> 11, j = code & 2047;
+    const int tile = u >> 24, j = (u >> 13) & 2047;
     if (!((sbits[cfg * P.Wp + tile] >> fr) & 1u)) {  // another pair may have decided this frame already
       const int slot = sc.dynamic_slots[j];
       const DSlot S = sc.slots[slot];
@@ -146,10 +146,11 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
   __shared__ float s_lr[SWEEP_MAXL];
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const DScene& sc = P.sc;
-  const int L = P.n_links, Wp = P.Wp, W = P.n_words;
-  const size_t per_warp = ((size_t)L * SWEEP_ROWS * 32 + (size_t)32 * Wp + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_Q3CAP) * 4;
-  float* lk = (float*)(sweep_smem + (size_t)wib * per_warp);
-  uint32_t* sbits = (uint32_t*)(lk + (size_t)L * SWEEP_ROWS * 32);  // [cfg][Wp]
+  const int L = P.n_links, Wp = P.Wp, W = P.n_words, ndp = P.ndp;
+  const int T = sc.T, Tp = sc.Tp, n_tiles = ndp > 0 ? sc.n_tiles : 0;
+  const float* __restrict__ posef = sc.pose_f;
+  float* lk = (float*)sweep_smem + (size_t)wib * SWEEP_PER_WARP(L, Wp);
+  uint32_t* sbits = (uint32_t*)(lk + (size_t)L * SWEEP_ROWS * SWEEP_LDC);  // [cfg][Wp]
   uint32_t* q0 = sbits + (size_t)32 * Wp;
   uint32_t* q1 = q0 + SWEEP_Q0CAP;
   uint32_t* q3 = q1 + SWEEP_Q1CAP;
@@ -159,7 +160,6 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
   const unsigned lt_mask = (1u << lane) - 1u;
   unsigned int n_exact = 0;
   const long long n_groups = (P.q.cnt + 31) / 32;
-  const int n_pairs = P.n_pairs;  // padded to a multiple of 4 with unreachable spheres
 
   for (long long group = (long long)blockIdx.x * SWEEP_WARPS + wib; group < n_groups; group += (long long)gridDim.x * SWEEP_WARPS) {
     const long long cfg0 = P.q.n0 + group * 32;
@@ -206,7 +206,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
           const float dx = LK(l, 0, lane) - acx, dy = LK(l, 1, lane) - acy, dz = LK(l, 2, lane) - acz;
           ar = fmaxf(ar, sqrtf(dx * dx + dy * dy + dz * dz) + P.link_br[l]);
         }
-      ar = ar * 1.000001f + 1e-5f;
+      ar = ar * 1.000001f + 1e-5f + band;
     }
 
     // ---- static slots: once per configuration, lane = configuration ---------------------------------
@@ -217,8 +217,8 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
       const DShape& sh = sc.shapes[S.shape];
       float R[9], t[3];
       load_pose(sc, slot, 0, R, t, true);
-      const float* c = sc.bcw_f + (size_t)slot * 3 * sc.Tp;
-      const float ox = c[0], oy = c[sc.Tp], oz = c[2 * (size_t)sc.Tp];
+      const float* c = sc.bcw_f + (size_t)slot * 3 * Tp;
+      const float ox = c[0], oy = c[Tp], oz = c[2 * (size_t)Tp];
       for (int l = 0; l < L && !static_hit; l++) {
         const float dx = LK(l, 0, lane) - ox, dy = LK(l, 1, lane) - oy, dz = LK(l, 2, lane) - oz;
         const float rr = (P.link_br[l] + S.br) * 1.000001f + 1e-5f + band;
@@ -235,22 +235,35 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
     const bool active = have && !static_hit;
     int q0n = 0, q1n = 0, q3n = 0;
 
-    // ---- dynamic slots: A0 rounds of 4 (tile, slot) pairs, stages drained whenever a batch of 32 is ready
-    for (int it0 = 0;; it0 += 4) {
-      const bool flush = it0 >= n_pairs;
+    // ---- dynamic slots: A0 rounds of 8 (tile, slot) pairs, stages drained whenever a batch of 32 is ready
+    int tile0 = 0, j0 = 0;
+    for (;;) {
+      const bool flush = tile0 >= n_tiles;
       if (!flush) {
-        float4 tb[4];
+        // ---- A0: lane = configuration; arm sphere vs 8 swept spheres -> per-lane pass mask
+        const float4* bp = P.bounds + (size_t)tile0 * ndp + j0;
+        unsigned mask = 0;
 #pragma unroll
-        for (int u = 0; u < 4; u++) tb[u] = __ldg(P.bounds + it0 + u);
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-          const float dx = acx - tb[u].x, dy = acy - tb[u].y, dz = acz - tb[u].z;
-          const float rr = ar + tb[u].w + band;
-          const bool pass = active && (dx * dx + dy * dy + dz * dz <= rr * rr);
-          const unsigned m = __ballot_sync(SIRRT_FULL, pass);
-          if (pass) q0[q0n + __popc(m & lt_mask)] = (unsigned)lane | ((unsigned)(it0 + u) << 5);
-          q0n += __popc(m);
+        for (int u = 0; u < 8; u++) {
+          const float4 tb = __ldg(bp + u);
+          const float dx = acx - tb.x, dy = acy - tb.y, dz = acz - tb.z;
+          const float rr = ar + tb.w;
+          if (dx * dx + dy * dy + dz * dz <= rr * rr) mask |= 1u << u;
         }
+        if (!active) mask = 0;
+        if (__any_sync(SIRRT_FULL, mask != 0)) {
+          int total;
+          int w = q0n + warp_excl_scan(__popc(mask), lane, total);
+          const unsigned base = (unsigned)lane | ((((unsigned)tile0 << 11) | (unsigned)j0) << 5);
+          while (mask) {
+            const int u = __ffs(mask) - 1;
+            mask &= mask - 1;
+            q0[w++] = base + ((unsigned)u << 5);
+          }
+          q0n += total;
+        }
+        j0 += 8;
+        if (j0 >= ndp) { j0 = 0; tile0++; }
       }
       if (q0n >= 32 || flush) {
         do {
@@ -262,26 +275,21 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
             unsigned lm = 0, e = 0;
             if (lane < cnt) {
               e = q0[q0n + lane];
-              const int cfg = e & 31;
-              const float4 b4 = __ldg(P.bounds + (e >> 5));
+              const float* lkp = lk + (e & 31);
+              const float4 b4 = __ldg(P.bounds + SWEEP_PAIR(e >> 5, ndp));
+              const float rb4 = b4.w + band;
 #pragma unroll
               for (int l = 0; l < SWEEP_MAXL; l++)
                 if (l < L) {
-                  const float dx = LK(l, 0, cfg) - b4.x, dy = LK(l, 1, cfg) - b4.y, dz = LK(l, 2, cfg) - b4.z;
-                  const float rr = P.link_br[l] + b4.w + band;
+                  const float dx = lkp[(l * SWEEP_ROWS + 0) * SWEEP_LDC] - b4.x, dy = lkp[(l * SWEEP_ROWS + 1) * SWEEP_LDC] - b4.y,
+                              dz = lkp[(l * SWEEP_ROWS + 2) * SWEEP_LDC] - b4.z;
+                  const float rr = P.link_br[l] + rb4;
                   if (dx * dx + dy * dy + dz * dz <= rr * rr) lm |= 1u << l;
                 }
             }
-            const int c = __popc(lm);
-            int incl = c;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-              const int v = __shfl_up_sync(SIRRT_FULL, incl, o);
-              if (lane >= o) incl += v;
-            }
-            const int total = __shfl_sync(SIRRT_FULL, incl, 31);
+            int total;
+            int w = q1n + warp_excl_scan(__popc(lm), lane, total);
             const unsigned ebase = (e & 31u) | ((e >> 5) << 8);
-            int w = q1n + incl - c;
             while (lm) {
               const int l = __ffs(lm) - 1;
               lm &= lm - 1;
@@ -298,12 +306,13 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
             unsigned e = 0;
             if (lane < cnt) {
               e = q1[q1n + lane];
-              const int cfg = e & 31, l = (e >> 5) & 7;
-              const unsigned it = e >> 8;
+              const int l = (e >> 5) & 7;
+              const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + (e & 31);
               float a[3], b[3];
 #pragma unroll
-              for (int k = 0; k < 3; k++) { const float cc = LK(l, k, cfg), h = 0.5f * LK(l, 3 + k, cfg); a[k] = cc - h; b[k] = cc + h; }
-              const float4 s0 = __ldg(P.seg + 2 * (size_t)it), s1 = __ldg(P.seg + 2 * (size_t)it + 1);
+              for (int k = 0; k < 3; k++) { const float cc = lkp[k * SWEEP_LDC], h = 0.5f * lkp[(3 + k) * SWEEP_LDC]; a[k] = cc - h; b[k] = cc + h; }
+              const float4* sp = P.seg + 2 * SWEEP_PAIR(e >> 8, ndp);
+              const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
               const float p0[3] = {s0.x, s0.y, s0.z}, p1[3] = {s1.x, s1.y, s1.z};
               const float rr = s_lr[l] + s0.w + band;
               kp = seg_seg_dist2(a, b, p0, p1) <= rr * rr;
@@ -314,46 +323,42 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
               const int src = __ffs(keep) - 1;
               keep &= keep - 1;
               const unsigned ee = __shfl_sync(SIRRT_FULL, e, src);
-              const int cfg = ee & 31, l = (ee >> 5) & 7;
-              const unsigned it = ee >> 8;
-              const uint32_t code = __ldg(P.pcode + it);
-              const int tile = code >> 11, j = code & 2047;
-              const float4 dj = __ldg(P.dyn + j);
-              const int slot = __float_as_int(dj.w);
+              const int cfg = ee & 31, l = (ee >> 5) & 7, tile = ee >> 19, j = (ee >> 8) & 2047;
               const int f = tile * 32 + lane;
-              const bool valid = f < sc.T;
-              const int fc = valid ? f : sc.T - 1;
-              const float* pp = sc.pose_f + ((size_t)slot * 12 + 9) * sc.Tp + fc;
-              const float apx = pp[0] - LK(l, 0, cfg), apy = pp[sc.Tp] - LK(l, 1, cfg), apz = pp[2 * (size_t)sc.Tp] - LK(l, 2, cfg);
-              const float abx = LK(l, 3, cfg), aby = LK(l, 4, cfg), abz = LK(l, 5, cfg);
-              float tt = (apx * abx + apy * aby + apz * abz) * LK(l, 6, cfg);
+              const bool valid = f < T;
+              const uint32_t cur = sbits[cfg * Wp + tile];
+              const bool done = !valid || ((cur >> lane) & 1u);
+              if (__all_sync(SIRRT_FULL, done)) continue;  // every frame of this tile is already decided
+              const float4 dj = __ldg(P.dyn + j);
+              const float* pp = posef + (__float_as_int(dj.w) + (valid ? f : T - 1));
+              const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + cfg;
+              const float apx = pp[0] - lkp[0], apy = pp[Tp] - lkp[SWEEP_LDC], apz = pp[2 * Tp] - lkp[2 * SWEEP_LDC];
+              const float abx = lkp[3 * SWEEP_LDC], aby = lkp[4 * SWEEP_LDC], abz = lkp[5 * SWEEP_LDC];
+              float tt = (apx * abx + apy * aby + apz * abz) * lkp[6 * SWEEP_LDC];
               tt = fminf(fmaxf(tt, -0.5f), 0.5f);
               const float ex = apx - tt * abx, ey = apy - tt * aby, ez = apz - tt * abz;
               const float d2 = ex * ex + ey * ey + ez * ez;
-              const uint32_t cur = sbits[cfg * Wp + tile];
-              const bool done = !valid || ((cur >> lane) & 1u);
               const float rl = s_lr[l];
               bool hit = false, want = false;
-              if (!done) {
-                if (dj.z >= 0.f) {  // sphere obstacle: the point-segment distance IS the narrowphase
+              if (dj.z >= 0.f) {  // sphere obstacle: the point-segment distance IS the narrowphase
+                if (!done) {
                   const int r = classify(sqrtf(d2) - rl - dj.z, band);
                   n_exact++;
                   if (r == RES_HIT) hit = true;
-                  else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), fc, l, slot, 0);
-                } else {
-                  const float hi = rl + dj.y + band;  // beyond the circumscribed sphere: free
-                  const float lo = rl + dj.x - band;  // inside the inscribed sphere: hit
-                  if (d2 <= hi * hi) {
-                    if (lo > 0.f && d2 < lo * lo) hit = true;
-                    else want = true;
-                  }
+                  else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), f, l, sc.dynamic_slots[j], 0);
                 }
+              } else {
+                const float hi = rl + dj.y + band;  // beyond the circumscribed sphere: free
+                const float lo = rl + dj.x - band;  // inside the inscribed sphere: hit (lo > 0: link radii exceed the band)
+                const bool in = !done && d2 <= hi * hi;
+                hit = in && d2 < lo * lo;
+                want = in && !hit;
               }
               const unsigned word = __ballot_sync(SIRRT_FULL, hit);
               if (word && lane == 0) sbits[cfg * Wp + tile] = cur | word;
               const unsigned mq = __ballot_sync(SIRRT_FULL, want);
               if (mq) {
-                if (want) q3[q3n + __popc(mq & lt_mask)] = (unsigned)cfg | ((unsigned)l << 5) | ((unsigned)lane << 8) | (it << 13);
+                if (want) q3[q3n + __popc(mq & lt_mask)] = (ee & 0xffu) | ((unsigned)lane << 8) | ((ee >> 8) << 13);
                 q3n += __popc(mq);
               }
               __syncwarp();
@@ -377,7 +382,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
       if (nn >= P.q.cnt) break;
       for (int w = lane; w < W; w += 32) {
         uint32_t v = ((shm >> cfg) & 1u) ? 0xffffffffu : sbits[cfg * Wp + w];
-        const int left = sc.T - w * 32;
+        const int left = T - w * 32;
         if (left < 32) v &= (1u << left) - 1u;
         P.bits[(size_t)(P.q.n0 + nn) * W + w] = v;
       }
@@ -413,19 +418,18 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
     if (t != SH_BOX && t != SH_SPHERE) return 0;
   }
   st->n_links = L;
-  const int n_real = tb.n_tiles * nd, n_pairs = (n_real + 3) / 4 * 4;
-  // pair tables.  bounds: swept bounding sphere (copied from the scene tables, padded with unreachable
-  // spheres); seg: swept capsule = segment between the bounding-sphere centres at the tile's first and
-  // last frame, radius = largest deviation from it + the slot's radius; pcode: tile << 11 | j
-  std::vector<float4> bounds((size_t)std::max(n_pairs, 4), make_float4(1e18f, 1e18f, 1e18f, 0.f));
-  std::vector<float4> seg((size_t)std::max(n_pairs, 4) * 2, make_float4(0, 0, 0, -1));
-  std::vector<uint32_t> pcode((size_t)std::max(n_pairs, 4), 0u);
+  const int ndp = (nd + 7) / 8 * 8, n_pairs = tb.n_tiles * ndp;
+  // pair tables, pair = tile*ndp + j.  bounds: swept bounding sphere (copied from the scene tables, slots
+  // padded to a multiple of 8 with unreachable spheres); seg: swept capsule = segment between the
+  // bounding-sphere centres at the tile's first and last frame, radius = largest deviation from it +
+  // the slot's radius
+  std::vector<float4> bounds((size_t)std::max(n_pairs, 8), make_float4(1e18f, 1e18f, 1e18f, 0.f));
+  std::vector<float4> seg((size_t)std::max(n_pairs, 8) * 2, make_float4(0, 0, 0, -1));
   const int Tp = tb.Tp, T = tb.T;
   for (int tile = 0; tile < tb.n_tiles; tile++)
     for (int j = 0; j < nd; j++) {
-      const size_t it = (size_t)tile * nd + j;
-      bounds[it] = tb.tile_bounds[it];
-      pcode[it] = ((uint32_t)tile << 11) | (uint32_t)j;
+      const size_t it = (size_t)tile * ndp + j;
+      bounds[it] = tb.tile_bounds[(size_t)tile * nd + j];
       const int s = tb.dynamic_slots[j];
       const int f0 = tile * 32, f1 = std::min(tile * 32 + 32, T) - 1;
       auto ctr = [&](int f, double* c) { for (int k = 0; k < 3; k++) c[k] = (double)tb.bcw_f[((size_t)s * 3 + k) * Tp + f]; };
@@ -445,7 +449,8 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
       seg[it * 2] = make_float4((float)p0[0], (float)p0[1], (float)p0[2], (float)rad);
       seg[it * 2 + 1] = make_float4((float)p1[0], (float)p1[1], (float)p1[2], 0.f);
     }
-  // per dynamic slot: inscribed / bounding radius around the pose origin, sphere radius (or -1), slot id
+  // per dynamic slot: inscribed / bounding radius around the pose origin, sphere radius (or -1), offset of
+  // the slot's translation rows in pose_f
   std::vector<float4> dyn((size_t)std::max(nd, 1), make_float4(0, 0, -1, 0));
   for (int j = 0; j < nd; j++) {
     const int s = tb.dynamic_slots[j];
@@ -454,7 +459,10 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
     v.x = sh.type == SH_SPHERE ? sh.radius : fminf(sh.half[0], fminf(sh.half[1], sh.half[2]));
     v.y = tb.slots[s].br;
     v.z = sh.type == SH_SPHERE ? sh.radius : -1.f;
-    memcpy(&v.w, &s, 4);
+    const long long toff = ((long long)s * 12 + 9) * Tp;
+    if (toff + 3ll * Tp >= (1ll << 31)) return 0;
+    const int toff32 = (int)toff;
+    memcpy(&v.w, &toff32, 4);
     dyn[j] = v;
   }
   const void* p = nullptr;
@@ -462,13 +470,11 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
   st->bounds = (const float4*)p;
   if (sweep_upload(seg.data(), seg.size() * sizeof(float4), owned, &p)) return -3;
   st->seg = (const float4*)p;
-  if (sweep_upload(pcode.data(), pcode.size() * sizeof(uint32_t), owned, &p)) return -3;
-  st->pcode = (const uint32_t*)p;
   if (sweep_upload(dyn.data(), dyn.size() * sizeof(float4), owned, &p)) return -3;
   st->dyn = (const float4*)p;
-  st->n_pairs = nd > 0 ? n_pairs : 0;
+  st->ndp = ndp;
   st->Wp = tb.n_tiles | 1;
-  st->smem = (size_t)SWEEP_WARPS * ((size_t)L * SWEEP_ROWS * 32 + (size_t)32 * st->Wp + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_Q3CAP) * 4;
+  st->smem = (size_t)SWEEP_WARPS * SWEEP_PER_WARP(L, st->Wp) * 4;
   if (st->smem > 200 * 1024) return 0;
   if (cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem) != cudaSuccess) { cudaGetLastError(); return 0; }
   int bps = 0;
@@ -482,8 +488,8 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
 static inline int sweep_launch(const SweepTables& st, const DRobot& rb, const DScene& sc, const QView& q, const WorkList& wl, uint32_t* bits,
                                int n_words, float band, int n_sm, cudaStream_t stream) {
   SweepParams P{};
-  P.sc = sc; P.q = q; P.wl = wl; P.bits = bits; P.bounds = st.bounds; P.seg = st.seg; P.pcode = st.pcode; P.dyn = st.dyn;
-  P.n_pairs = st.n_pairs; P.n_words = n_words; P.Wp = st.Wp; P.n_links = st.n_links; P.band = band;
+  P.sc = sc; P.q = q; P.wl = wl; P.bits = bits; P.bounds = st.bounds; P.seg = st.seg; P.dyn = st.dyn;
+  P.ndp = st.ndp; P.n_words = n_words; P.Wp = st.Wp; P.n_links = st.n_links; P.band = band;
   for (int l = 0; l < SWEEP_MAXL; l++) { P.link_r[l] = l < st.n_links ? st.link_r[l] : 0.f; P.link_br[l] = l < st.n_links ? st.link_br[l] : 0.f; }
   const long long groups = (q.cnt + 31) / 32;
   const long long blocks = std::min((groups + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)n_sm * st.blocks_per_sm);

@@ -27,13 +27,14 @@
 #include "sirrt_tables.hpp"
 
 #define SWEEP_MAXL 8
-#define SWEEP_WARPS 2
-#define SWEEP_Q0CAP 288   // 31 left over + 32 x 8 pushed per A0 round
+#define SWEEP_WARPS 4
+#define SWEEP_G 16       // configurations per warp (16 keeps the per-warp tables at ~7 KB -> 28 resident warps per SM)
+#define SWEEP_Q0CAP 160   // 31 left over + 32 x 4 pushed per A0 round
 #define SWEEP_Q1CAP 256   // 31 left over + 32 x 7 pushed per A1 batch
 #define SWEEP_Q3CAP 64    // 31 left over + 32 pushed per B2 entry
 #define SWEEP_ROWS 7      // per link: centre xyz, axis xyz (b - a), 1 / |axis|^2
-#define SWEEP_LDC 33      // row stride of the per-warp link table (33: rows of one configuration fall into different banks)
-#define SWEEP_PER_WARP(L, Wp) ((size_t)(L) * SWEEP_ROWS * SWEEP_LDC + (size_t)32 * (Wp) + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_Q3CAP)
+#define SWEEP_LDC (SWEEP_G + 1)  // row stride of the per-warp link table (odd: rows of one configuration fall into different banks)
+#define SWEEP_PER_WARP(L, Wp) ((size_t)(L) * SWEEP_ROWS * SWEEP_LDC + (size_t)SWEEP_G * (Wp) + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_Q3CAP)
 
 struct SweepTables {
   int supported = 0;
@@ -140,7 +141,7 @@ __device__ __noinline__ unsigned sweep_exact_batch(const SweepParams& P, const f
   return n_exact;
 }
 
-__global__ void __launch_bounds__(SWEEP_WARPS * 32)
+__global__ void __launch_bounds__(SWEEP_WARPS * 32, 7)
 k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P) {
   extern __shared__ __align__(16) unsigned char sweep_smem[];
   __shared__ float s_lr[SWEEP_MAXL];
@@ -151,7 +152,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
   const float* __restrict__ posef = sc.pose_f;
   float* lk = (float*)sweep_smem + (size_t)wib * SWEEP_PER_WARP(L, Wp);
   uint32_t* sbits = (uint32_t*)(lk + (size_t)L * SWEEP_ROWS * SWEEP_LDC);  // [cfg][Wp]
-  uint32_t* q0 = sbits + (size_t)32 * Wp;
+  uint32_t* q0 = sbits + (size_t)SWEEP_G * Wp;
   uint32_t* q1 = q0 + SWEEP_Q0CAP;
   uint32_t* q3 = q1 + SWEEP_Q1CAP;
   if (threadIdx.x < SWEEP_MAXL) s_lr[threadIdx.x] = P.link_r[threadIdx.x];
@@ -159,14 +160,15 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
   const float band = P.band;
   const unsigned lt_mask = (1u << lane) - 1u;
   unsigned int n_exact = 0;
-  const long long n_groups = (P.q.cnt + 31) / 32;
+  const long long n_groups = (P.q.cnt + SWEEP_G - 1) / SWEEP_G;
+  const int cl = lane & (SWEEP_G - 1);  // this lane's configuration of the group (both half-warps hold all 16)
 
   for (long long group = (long long)blockIdx.x * SWEEP_WARPS + wib; group < n_groups; group += (long long)gridDim.x * SWEEP_WARPS) {
-    const long long cfg0 = P.q.n0 + group * 32;
-    const long long n = cfg0 + lane;
-    const bool have = group * 32 + lane < P.q.cnt;
+    const long long cfg0 = P.q.n0 + group * SWEEP_G;
+    const long long n = cfg0 + cl;
+    const bool have = group * SWEEP_G + cl < P.q.cnt;
     __syncwarp();
-    for (int i = lane; i < 32 * Wp; i += 32) sbits[i] = 0u;
+    for (int i = lane; i < SWEEP_G * Wp; i += 32) sbits[i] = 0u;
 
     // ---- FK: lane = configuration --------------------------------------------------------------
     {
@@ -178,11 +180,11 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
 #pragma unroll
         for (int k = 0; k < 3; k++) {  // capsule core: local (0, 0, -+half_len) around the link origin
           ab[k] = (float)(Rl[3 * k + 2] * len);
-          LK(l, k, lane) = (float)tl[k];
-          LK(l, 3 + k, lane) = ab[k];
+          LK(l, k, cl) = (float)tl[k];  // both half-warps store the same value
+          LK(l, 3 + k, cl) = ab[k];
         }
         const float den = ab[0] * ab[0] + ab[1] * ab[1] + ab[2] * ab[2];
-        LK(l, 6, lane) = den > 0.f ? 1.f / den : 0.f;
+        LK(l, 6, cl) = den > 0.f ? 1.f / den : 0.f;
       });
     }
     __syncwarp();
@@ -195,7 +197,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
         if (l < L) {
 #pragma unroll
           for (int k = 0; k < 3; k++) {
-            const float c = LK(l, k, lane);
+            const float c = LK(l, k, cl);
             lo[k] = fminf(lo[k], c - P.link_br[l]); hi[k] = fmaxf(hi[k], c + P.link_br[l]);
           }
         }
@@ -203,7 +205,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
 #pragma unroll
       for (int l = 0; l < SWEEP_MAXL; l++)
         if (l < L) {
-          const float dx = LK(l, 0, lane) - acx, dy = LK(l, 1, lane) - acy, dz = LK(l, 2, lane) - acz;
+          const float dx = LK(l, 0, cl) - acx, dy = LK(l, 1, cl) - acy, dz = LK(l, 2, cl) - acz;
           ar = fmaxf(ar, sqrtf(dx * dx + dy * dy + dz * dz) + P.link_br[l]);
         }
       ar = ar * 1.000001f + 1e-5f + band;
@@ -211,7 +213,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
 
     // ---- static slots: once per configuration, lane = configuration ---------------------------------
     bool static_hit = false;
-    for (int s = 0; s < sc.n_static && have; s++) {
+    for (int s = 0; s < sc.n_static && have && lane < SWEEP_G; s++) {
       const int slot = sc.static_slots[s];
       const DSlot S = sc.slots[slot];
       const DShape& sh = sc.shapes[S.shape];
@@ -220,19 +222,20 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
       const float* c = sc.bcw_f + (size_t)slot * 3 * Tp;
       const float ox = c[0], oy = c[Tp], oz = c[2 * (size_t)Tp];
       for (int l = 0; l < L && !static_hit; l++) {
-        const float dx = LK(l, 0, lane) - ox, dy = LK(l, 1, lane) - oy, dz = LK(l, 2, lane) - oz;
+        const float dx = LK(l, 0, cl) - ox, dy = LK(l, 1, cl) - oy, dz = LK(l, 2, cl) - oz;
         const float rr = (P.link_br[l] + S.br) * 1.000001f + 1e-5f + band;
         if (dx * dx + dy * dy + dz * dz > rr * rr) continue;
         float a[3], b[3];
 #pragma unroll
-        for (int k = 0; k < 3; k++) { const float cc = LK(l, k, lane), h = 0.5f * LK(l, 3 + k, lane); a[k] = cc - h; b[k] = cc + h; }
+        for (int k = 0; k < 3; k++) { const float cc = LK(l, k, cl), h = 0.5f * LK(l, 3 + k, cl); a[k] = cc - h; b[k] = cc + h; }
         const int r = capsule_exact(a, b, P.link_r[l], sh, R, t, S.rot_identity != 0, band);
         n_exact++;
         if (r == RES_HIT) static_hit = true;
         else if (r == RES_AMBIG) push_work(P.wl, (int)n, -1, l, slot, 0);
       }
     }
-    const bool active = have && !static_hit;
+    const unsigned shm = __ballot_sync(SIRRT_FULL, static_hit);  // bit c: configuration c of the group hits a static slot
+    const bool active = have && !((shm >> cl) & 1u);
     int q0n = 0, q1n = 0, q3n = 0;
 
     // ---- dynamic slots: A0 rounds of 8 (tile, slot) pairs, stages drained whenever a batch of 32 is ready
@@ -240,21 +243,24 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
     for (;;) {
       const bool flush = tile0 >= n_tiles;
       if (!flush) {
-        // ---- A0: lane = configuration; arm sphere vs 8 swept spheres -> per-lane pass mask
-        const float4* bp = P.bounds + (size_t)tile0 * ndp + j0;
+        // ---- A0: lane = (configuration, half of the round); arm sphere vs 4 of the round's 8 swept
+        // spheres -> per-lane pass mask
+        const int u0 = (lane >> 4) * 4;
+        const float4* bp = P.bounds + (size_t)tile0 * ndp + j0 + u0;
         unsigned mask = 0;
 #pragma unroll
-        for (int u = 0; u < 8; u++) {
+        for (int u = 0; u < 4; u++) {
           const float4 tb = __ldg(bp + u);
           const float dx = acx - tb.x, dy = acy - tb.y, dz = acz - tb.z;
           const float rr = ar + tb.w;
           if (dx * dx + dy * dy + dz * dz <= rr * rr) mask |= 1u << u;
         }
+        mask <<= u0;
         if (!active) mask = 0;
         if (__any_sync(SIRRT_FULL, mask != 0)) {
           int total;
           int w = q0n + warp_excl_scan(__popc(mask), lane, total);
-          const unsigned base = (unsigned)lane | ((((unsigned)tile0 << 11) | (unsigned)j0) << 5);
+          const unsigned base = (unsigned)cl | ((((unsigned)tile0 << 11) | (unsigned)j0) << 5);
           while (mask) {
             const int u = __ffs(mask) - 1;
             mask &= mask - 1;
@@ -376,9 +382,8 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
 
     // ---- rows out: lane = word, coalesced ------------------------------------------------------------
     __syncwarp();
-    const unsigned shm = __ballot_sync(SIRRT_FULL, static_hit);
-    for (int cfg = 0; cfg < 32; cfg++) {
-      const long long nn = group * 32 + cfg;
+    for (int cfg = 0; cfg < SWEEP_G; cfg++) {
+      const long long nn = group * SWEEP_G + cfg;
       if (nn >= P.q.cnt) break;
       for (int w = lane; w < W; w += 32) {
         uint32_t v = ((shm >> cfg) & 1u) ? 0xffffffffu : sbits[cfg * Wp + w];
@@ -491,7 +496,7 @@ static inline int sweep_launch(const SweepTables& st, const DRobot& rb, const DS
   P.sc = sc; P.q = q; P.wl = wl; P.bits = bits; P.bounds = st.bounds; P.seg = st.seg; P.dyn = st.dyn;
   P.ndp = st.ndp; P.n_words = n_words; P.Wp = st.Wp; P.n_links = st.n_links; P.band = band;
   for (int l = 0; l < SWEEP_MAXL; l++) { P.link_r[l] = l < st.n_links ? st.link_r[l] : 0.f; P.link_br[l] = l < st.n_links ? st.link_br[l] : 0.f; }
-  const long long groups = (q.cnt + 31) / 32;
+  const long long groups = (q.cnt + SWEEP_G - 1) / SWEEP_G;
   const long long blocks = std::min((groups + SWEEP_WARPS - 1) / SWEEP_WARPS, (long long)n_sm * st.blocks_per_sm);
   k_sweep<<<(unsigned)std::max(1ll, blocks), SWEEP_WARPS * 32, st.smem, stream>>>(rb, P);
   return 1;

@@ -36,6 +36,12 @@ METRIC = "config x timestep collision checks/sec"
 UNIT = "checks/s"
 # SURVEY.md §8d accounting (frozen before measuring; DESIGN.md "Roofline accounting")
 F_CULL, F_FK, F_EXACT_CAPSULE_BOX, F_EXACT_CAPSULE_SPHERE = 12.0, 1100.0, 150.0, 30.0
+# Executed work of k_sweep per check on SYN variant A, frozen from the ncu capture of the current kernel
+# version (profiles/r04_ksweep_summary.txt: 131072 configs x 1000 frames):
+#   F_EXEC  FP32 FLOP/check  = (fadd + fmul + 2*ffma thread instructions, predicated on) / checks
+#   I_EXEC  warp instructions/check = smsp__inst_executed.sum / checks
+F_EXEC, I_EXEC, EXEC_SOURCE = 135.7, 16.23, "profiles/r04_ksweep_summary.txt"
+N_SM, SCHEDULERS_PER_SM = 148, 4
 
 
 def shard_range(n: int, rank: int, world: int):
@@ -260,14 +266,23 @@ def main():
         k_ms = kern_ms / max(1, a.steps)
         f_exact = F_EXACT_CAPSULE_SPHERE if a.variant == "C" else F_EXACT_CAPSULE_BOX
         f_check = 7 * a.obstacles * F_CULL + F_FK / T + (exact / (N * T)) * f_exact
-        alg_tflops = N * T * f_check / (k_ms * 1e-3) / 1e12 if k_ms > 0 else None
+        brute_tflops = N * T * f_check / (k_ms * 1e-3) / 1e12 if k_ms > 0 else None
+        exec_ok = (not a.generic) and a.variant == "A" and a.obstacles == 64 and a.frames == 1000
+        exec_tflops = N * T * F_EXEC / (k_ms * 1e-3) / 1e12 if (k_ms > 0 and exec_ok) else None
+        sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+        issue_peak = N_SM * SCHEDULERS_PER_SM * sm_hz  # warp instructions / s at the clock seen under load
+        issue_rate = N * T * I_EXEC / (k_ms * 1e-3) if (k_ms > 0 and exec_ok) else None
         alg_bytes = N * 7 * 4 + a.obstacles * 12 * 4 * ((T + 31) // 32 * 32) + N * W * 4
         roofline = {
-            "bound": "fp32", "kernel": "k_sweep" if not a.generic else "k_collide_bits", "achieved": alg_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
-            "frac": (alg_tflops / fp32_peak) if alg_tflops and fp32_peak else None, "traffic": None,
+            "bound": "fp32", "kernel": "k_sweep" if not a.generic else "k_collide_bits", "achieved": exec_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
+            "frac": (exec_tflops / fp32_peak) if exec_tflops and fp32_peak else None, "traffic": None,
             "peak_source": "FFMA micro-benchmark measured in this run (sirrt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
-            "kernel_ms": k_ms, "flop_per_check_algorithmic": f_check,
-            "note": "algorithmic FLOPs use SURVEY §8d's brute-force accounting (L*C*12 per check); the kernel culls hierarchically, so frac > 1 means work skipped, not a faster FMA pipe",
+            "kernel_ms": k_ms, "flop_per_check_executed": F_EXEC if exec_ok else None, "executed_source": EXEC_SOURCE,
+            "issue": {"achieved": issue_rate, "peak": issue_peak, "unit": "warp-inst/s", "frac": (issue_rate / issue_peak) if issue_rate else None,
+                      "warp_inst_per_check": I_EXEC if exec_ok else None,
+                      "note": "the cull pipeline is compare/ballot/queue work: warp-instruction issue slots are the binding resource, not the FMA pipe or HBM"},
+            "bruteforce": {"flop_per_check": f_check, "equivalent_tflops": brute_tflops,
+                           "note": "SURVEY §8d brute-force accounting (L*C*12 per check): what a kernel without culling would have to execute for the same answer"},
             "hbm": {"achieved": alg_bytes / (k_ms * 1e-3) / 1e9 if k_ms > 0 else None, "peak": hbm_peak, "unit": "GB/s", "peak_source": peak_src,
                     "frac": (alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak) if k_ms > 0 else None, "algorithmic_bytes": alg_bytes},
         }

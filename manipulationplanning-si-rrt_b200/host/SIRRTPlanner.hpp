@@ -321,7 +321,7 @@ class PlannerConnect {
       std::sort(nearest_nodes.begin(), nearest_nodes.end(), [&](const Vertex* a, const Vertex* b) {
         return a->arrival_time + time_between(coord_rand, a->coords) < b->arrival_time + time_between(coord_rand, b->coords);
       });
-      for (const std::pair<int, int> safe_int : safe_intervals_of_coord_rand) {
+      for (const std::pair<int, int>& safe_int : safe_intervals_of_coord_rand) {
         if ((safe_int.first + time_to_goal) >= frame_count_) continue;  // the goal cannot be reached from that interval (:456)
         bool found_parent = false;
         for (Vertex* cand : nearest_nodes) {
@@ -383,7 +383,7 @@ class PlannerConnect {
       std::sort(nearest_nodes.begin(), nearest_nodes.end(), [&](const Vertex* a, const Vertex* b) {
         return a->arrival_time - time_between(coord_rand, a->coords) > b->arrival_time - time_between(coord_rand, b->coords);
       });
-      for (const std::pair<int, int> safe_int : safe_intervals_of_coord_rand) {
+      for (const std::pair<int, int>& safe_int : safe_intervals_of_coord_rand) {
         if ((safe_int.second - time_to_start) < 0) continue;  // :664
         bool found_parent = false;
         for (Vertex* cand : nearest_nodes) {

@@ -1,0 +1,119 @@
+// TEST INFRASTRUCTURE ONLY: the SI-RRT planner of host/SIRRTPlanner.hpp instantiated on the CPU oracle
+// (oracle/sirrt_oracle.h).  Used by tests/test_planner.py to check that the B200 backend yields IDENTICAL plans
+// (same seed, same host logic, two checkers) and to time the CPU side of the plan-time metric.
+//   planner_oracle <scene.pack> <seed> [--max-iters N] [--max-time S] [--fixed]      -> result JSON on stdout
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <iostream>
+#include <iterator>
+#include <stdexcept>
+
+#include "../include/sirrt_pack.h"
+#include "../manipulationplanning-si-rrt_b200/host/ResultsLog.hpp"
+#include "../manipulationplanning-si-rrt_b200/host/SIRRTPlanner.hpp"
+#include "../oracle/sirrt_oracle.h"
+
+struct OracleBackend {
+  Oracle* o = nullptr;
+  int dof_ = 0, n_links = 0, T = 0, fps_ = 0;
+  std::vector<float> lim;
+  std::vector<double> start, goal;
+  std::vector<std::vector<double>> trees;  // flat point stores
+  OracleBackend(const std::vector<unsigned char>& pack, int mode) {
+    o = oracle_create(pack.data(), pack.size(), mode);
+    if (!o) throw std::runtime_error(std::string("oracle: ") + oracle_last_error());
+    oracle_info(o, &dof_, &n_links, &T, &fps_, nullptr);
+    lim.resize(2 * dof_);
+    oracle_info(o, nullptr, nullptr, nullptr, nullptr, lim.data());
+    const double* p = (const double*)(pack.data() + sizeof(SirrtPackHeader));
+    start.assign(p, p + dof_);
+    goal.assign(p + dof_, p + 2 * dof_);
+  }
+  ~OracleBackend() { if (o) oracle_destroy(o); }
+  int dof() const { return dof_; }
+  int frame_count() const { return T; }
+  int fps() const { return fps_; }
+  std::vector<std::pair<float, float>> get_planned_robot_limits() const {
+    std::vector<std::pair<float, float>> r;
+    for (int j = 0; j < dof_; j++) r.emplace_back(lim[2 * j], lim[2 * j + 1]);
+    return r;
+  }
+  std::vector<double> start_configuration() const { return start; }
+  std::vector<double> end_configuration() const { return goal; }
+  std::vector<std::pair<int, int>> get_safe_intervals(const std::vector<double>& q) {
+    std::vector<int32_t> buf(2 * 2048);
+    const int n = oracle_safe_intervals(o, q.data(), buf.data(), 2048);
+    std::vector<std::pair<int, int>> r;
+    for (int i = 0; i < n; i++) r.emplace_back(buf[2 * i], buf[2 * i + 1]);
+    return r;
+  }
+  int edge_first_collision(const double* q0, const double* dir, int steps, double t0, double t1) {
+    std::vector<double> q(dof_);
+    for (int s = 0; s <= steps; s++) {
+      for (int j = 0; j < dof_; j++) q[j] = q0[j] + dir[j] * (double)s / (double)steps;
+      const int frame = (int)(t0 + (t1 - t0) * (double)s / (double)steps);
+      if (oracle_check_frame(o, q.data(), frame)) return s;
+    }
+    return -1;
+  }
+  int knn_new() { trees.emplace_back(); return (int)trees.size() - 1; }
+  void knn_add(int t, const double* p) { trees[t].insert(trees[t].end(), p, p + dof_); }
+  size_t knn_nearest(int t, const double* q) {
+    int64_t idx = 0;
+    double d2 = 0;
+    oracle_knn_nearest(trees[t].data(), (int64_t)(trees[t].size() / dof_), dof_, q, 1, &idx, &d2);
+    return (size_t)idx;
+  }
+  void knn_radius(int t, const double* q, double r2, std::vector<size_t>& out) {
+    const int64_t n = (int64_t)(trees[t].size() / dof_);
+    std::vector<int64_t> idx((size_t)n + 1);
+    const int64_t m = oracle_knn_radius(trees[t].data(), n, dof_, q, r2, idx.data(), n);
+    out.assign(idx.begin(), idx.begin() + m);
+  }
+};
+
+int main(int argc, char** argv) {
+  if (argc < 3) { fprintf(stderr, "usage: %s <scene.pack> <seed> [--max-iters N] [--max-time S] [--fixed]\n", argv[0]); return 2; }
+  std::ifstream f(argv[1], std::ios::binary);
+  if (!f) { fprintf(stderr, "cannot open %s\n", argv[1]); return 1; }
+  std::vector<unsigned char> pack((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+  const int seed = atoi(argv[2]);
+  uint64_t max_iters = 0;
+  double max_time = -1;
+  int mode = ORACLE_REFERENCE_EXACT;
+  for (int i = 3; i < argc; i++) {
+    if (!strcmp(argv[i], "--max-iters") && i + 1 < argc) max_iters = strtoull(argv[++i], nullptr, 10);
+    else if (!strcmp(argv[i], "--max-time") && i + 1 < argc) max_time = atof(argv[++i]);
+    else if (!strcmp(argv[i], "--fixed")) mode = ORACLE_FIXED;
+  }
+  try {
+    OracleBackend be(pack, mode);
+    MDP::MSIRRT::PlannerConnect<OracleBackend> planner(be, seed);
+    if (!planner.valid()) { fprintf(stderr, "planner_oracle: %s\n", planner.error().c_str()); return 1; }
+    if (max_iters) planner.set_max_iterations(max_iters);
+    if (max_time > 0) planner.set_max_planning_time(max_time);
+    const bool result = planner.solve();
+    MDP::ResultsLog log;
+    log.path_to_scene_json = argv[1];
+    const auto& st = planner.stats();
+    log.algorithm_solving_time_ns = st.solve_ns; log.collision_check_time_ns = st.motion_ns; log.get_safe_interval_time_ns = st.safe_interval_ns;
+    log.number_of_collision_checks = st.n_state_checks; log.number_of_get_safe_interval = st.n_safe_interval_calls;
+    log.has_result = result;
+    log.start_tree_vertices = planner.get_start_tree_vertices_count();
+    log.goal_tree_vertices = planner.get_goal_tree_vertices_count();
+    if (result) {
+      auto path = planner.get_final_path();
+      log.extra.push_back({"check_path", planner.check_path(path) ? 1.0 : 0.0});
+      for (const auto& s : planner.get_result_path(0.0)) log.final_path.push_back({s.q, s.time});
+      log.path_cost = log.final_path.back().time;
+    }
+    log.extra.push_back({"iterations", (double)st.iterations});
+    log.extra.push_back({"motion_checks", (double)st.n_motion_checks});
+    std::cout << log.to_json() << std::endl;
+    return 0;
+  } catch (const std::exception& e) {
+    fprintf(stderr, "planner_oracle: %s\n", e.what());
+    return 1;
+  }
+}

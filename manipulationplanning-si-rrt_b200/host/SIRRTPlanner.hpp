@@ -5,7 +5,7 @@
 //
 // The planner is a template over a Backend so that the SAME host logic runs
 //   * on libsirrt_b200 (B200Backend below: MDP::CollisionManager shim + sirrt_knn_* + the §7.3 edge table), and
-//   * on the CPU oracle in tests/ (test infrastructure only; tests/planner_oracle_main.cpp),
+//   * on the CPU checker in tests/ (test infrastructure only; the main() for it lives under tests/),
 // which is how "identical plans" is checked: same seed, two backends, waypoint-by-waypoint equality.
 //
 // Backend concept:

@@ -1,5 +1,5 @@
 /*
- * sirrt_oracle.c -- TEST INFRASTRUCTURE ONLY (see sirrt_oracle.h).  PARITY UNPINNED.
+ * sirrt_oracle.c -- TEST INFRASTRUCTURE ONLY (see sirrt_oracle.h).  PARITY PINNED ON THE FREE SIDE ONLY (see header).
  *
  * FP64 CPU restatement of the reference's hot path.  Each function cites the reference lines it
  * follows (paths relative to the reference root).  The collision arithmetic itself lives in the

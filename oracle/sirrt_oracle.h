@@ -2,10 +2,13 @@
  * sirrt_oracle.h -- TEST INFRASTRUCTURE ONLY.  CPU (FP64) restatement of the reference's
  * collision-checker / safe-interval / edge-validation / kNN algorithm.
  *
- * PARITY UNPINNED: the reference ships no unit tests or golden vectors for this path and cannot
- * be compiled in this image (coal, Eigen, nanoflann, urdfdom, orocos-kdl are absent), so this
- * oracle is anchored on the reference's call sites and on soft fixtures only (check_scene
- * invariants, FK sanity values, closed-form vs GJK cross-checks).
+ * PARITY PINNED ON THE FREE SIDE ONLY: the reference ships no unit tests or golden vectors for
+ * this path and cannot be compiled in this image (coal, Eigen, nanoflann, urdfdom, orocos-kdl are
+ * absent).  The one set of real reference OUTPUTS at this boundary are the trajectories its
+ * planners logged (Blender/scenes with animation/*.json; tests/golden/make_logged_paths.py):
+ * 8 700 (q, frame) cells its own checker accepted, which pass 2-31 mm from obstacles, all FREE
+ * here (tests/test_oracle.py).  The colliding side is UNPINNED: it rests on the reference's call
+ * sites and soft fixtures (check_scene invariants, FK sanity values, closed-form vs GJK).
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
  * load this library.  The product (libsirrt_b200.so) never links or calls it.

@@ -48,6 +48,38 @@ def golden_vectors():
 
 
 @pytest.fixture(scope="session")
+def logged_cells(sp):
+    """(q [n][dof] float64, frames [n] int32) cells that the REFERENCE's own checker accepted as collision-free,
+    from the planner trajectories it logged (tests/golden/make_logged_paths.py).  ST-RRT* solutions are expanded
+    edge by edge exactly as SpaceTimeMotionValidator::checkMotion interpolates them
+    (SpaceTimeMotionValidator.cpp:48-55: steps = max(int(|dq|/0.1), int(2*dt*fps+0.5)) + 2, states i/steps, plus
+    the end state checked first at :25); DRGBT logs are executed states.  Frame = (int)(float32 time * fps)
+    (CollisionManager.cpp:333 with `float t` from StateValidityCheckerFunctor.cpp:34)."""
+    with gzip.open(os.path.join(GOLDEN, "reference_logged_paths.json.gz"), "rb") as f:
+        logs = json.load(f)
+
+    def get(key: str):
+        ent = logs[key]
+        sc = sp.read_pack(golden_pack(ent["scene"]))
+        t, q = np.asarray(ent["t"], np.float64), np.asarray(ent["q"], np.float64)
+        if ent["planner"].startswith("STRRT"):
+            ts, qs = [], []
+            for a in range(len(t) - 1):
+                dq, dt = float(np.sqrt(((q[a + 1] - q[a]) ** 2).sum())), float(t[a + 1] - t[a])
+                steps = max(int(dq / 0.1), int(2 * dt * sc.fps + 0.5)) + 2
+                for i in list(range(steps)) + [steps]:
+                    ts.append(t[a] + dt * (i / steps))
+                    qs.append(q[a] + (q[a + 1] - q[a]) * (i / steps))
+            t, q = np.asarray(ts), np.asarray(qs)
+        frames = (t.astype(np.float32) * np.float32(sc.fps)).astype(np.int32)
+        keep = frames < sc.n_frames
+        return ent["scene"], np.ascontiguousarray(q[keep]), np.ascontiguousarray(frames[keep])
+
+    get.keys = sorted(logs)
+    return get
+
+
+@pytest.fixture(scope="session")
 def packs(sp):
     return make_packs(sp)
 

@@ -216,3 +216,19 @@ def test_collision_manager_mirror(pkg, orc, packs, sp):
     low = cm.get_goal_frame_low_bound()
     col = [ref.check_frame(sc.end_configuration, f) for f in range(sc.n_frames)]
     assert low == (max(i for i, c in enumerate(col) if c) + 1 if any(col) else 0)
+
+
+@pytest.mark.parametrize("key", ["strrt_mass_test", "strrt_flying_boxes", "drgbt_mass_test", "rgbtstar_mass_test", "drgbt_flying_boxes",
+                                 "drgbt_multiple_robots", "strrt_multiple_robots"])
+def test_reference_logged_trajectories_free_on_gpu(pkg, orc, packs, logged_cells, key):
+    """Cells the REFERENCE's own checker accepted (trajectories its planners logged, tests/golden/make_logged_paths.py)
+    must be FREE through the C ABI too, and equal to the oracle cell by cell (robot scene: FIXED mode, see
+    tests/test_oracle.py::test_reference_logged_trajectories_are_free)."""
+    scene, q, frames = logged_cells(key)
+    mode = pkg.PARITY_FIXED if scene == "multiple_robots" else pkg.PARITY_REFERENCE_EXACT
+    dev = pkg.Scene(packs(scene), 0, mode)
+    got = np.asarray(dev.check_frames_batch_f64(q, frames)).astype(bool)
+    assert got.shape[0] == q.shape[0] and not got.any(), (key, int(got.sum()))
+    ref = orc.Oracle(packs(scene), mode)
+    step = max(1, len(q) // 200)
+    assert [bool(ref.check_frame(qq, int(f))) for qq, f in zip(q[::step], frames[::step])] == got[::step].tolist()

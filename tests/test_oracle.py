@@ -1,7 +1,8 @@
 """CPU tests of the oracle (oracle/sirrt_oracle.c) and of the packer: the checker must be right
-before it is allowed to judge the CUDA path.  PARITY UNPINNED (no reference golden vectors exist):
-anchored on closed-form-vs-GJK cross-checks, the reference's check_scene invariants and the FK
-sanity values of SURVEY.md §8c."""
+before it is allowed to judge the CUDA path.  The reference has no golden vectors; the only reference
+OUTPUTS at this boundary are the trajectories its planners logged, which pin the FREE side
+(test_reference_logged_trajectories_are_free).  The colliding side is UNPINNED: closed-form-vs-GJK
+cross-checks, the reference's check_scene invariants and the FK sanity values of SURVEY.md §8c."""
 import numpy as np
 import pytest
 
@@ -175,3 +176,32 @@ def test_knn_oracle(orc):
     assert idx[0] == 7 and np.array_equal(idx, ref.argmin(1))
     r = orc.knn_radius(pts, qs[3], 4.0)
     assert set(r) == set(np.nonzero(ref[3] < 4.0)[0])
+
+
+LOGGED = ["strrt_mass_test", "strrt_flying_boxes", "drgbt_mass_test", "rgbtstar_mass_test", "drgbt_flying_boxes", "drgbt_multiple_robots",
+          "strrt_multiple_robots"]
+
+
+@pytest.mark.parametrize("key", LOGGED)
+def test_reference_logged_trajectories_are_free(orc, packs, logged_cells, key):
+    """REFERENCE OUTPUTS pin the oracle (free side, a4 boundary): every (q, frame) cell of a trajectory the
+    reference's planners logged was accepted by the reference's checker, so the oracle must call it free.
+    The robot-obstacle scene is pinned in FIXED mode only: its logs pre-date the pair mis-indexing of the
+    shipped source (QUIRK 7) -- under REFERENCE_EXACT the shifted base-link hull rejects 15 of the 918 ST-RRT*
+    states, which the reference as shipped would have rejected too (it cannot even read that scene file's
+    legacy trajectory format, config_read.cpp:156-168)."""
+    scene, q, frames = logged_cells(key)
+    o = orc.Oracle(packs(scene), orc.FIXED if scene == "multiple_robots" else orc.REFERENCE_EXACT)
+    hit = [int(f) for qq, f in zip(q, frames) if o.check_frame(qq, int(f))]
+    assert len(q) > 0 and not hit, (key, len(hit), hit[:10])
+
+
+@pytest.mark.parametrize("key", ["drgbt_mass_test", "rgbtstar_mass_test", "drgbt_flying_boxes", "drgbt_multiple_robots"])
+def test_logged_trajectories_discriminate(orc, packs, logged_cells, key):
+    """The pin above is not vacuous: the executed trajectories pass within millimetres to centimetres of the
+    obstacles (oracle clearances 1.9 mm flying boxes, 22 mm robots on the table, 24-31 mm mass test), so an
+    oracle whose FK, hulls, box sizes or pose tables were off by a few centimetres would report collisions."""
+    scene, q, frames = logged_cells(key)
+    o = orc.Oracle(packs(scene), orc.FIXED)
+    clr = min(o.get_distances(qq, int(f))[1].min() for qq, f in zip(q[::5], frames[::5]))
+    assert 0.0 < clr < 0.035, (key, clr)

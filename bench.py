@@ -41,6 +41,9 @@ F_CULL, F_FK, F_EXACT_CAPSULE_BOX, F_EXACT_CAPSULE_SPHERE = 12.0, 1100.0, 150.0,
 #   F_EXEC  FP32 FLOP/check  = (fadd + fmul + 2*ffma thread instructions, predicated on) / checks
 #   I_EXEC  warp instructions/check = smsp__inst_executed.sum / checks
 F_EXEC, I_EXEC, EXEC_SOURCE = 135.7, 16.23, "profiles/r04_ksweep_summary.txt"
+# DRAM traffic of one k_sweep launch (131072 configurations x 1000 frames), same ncu --set full capture:
+# dram__bytes_read.sum 4.264 MB + dram__bytes_write.sum 0.165 MB (collision rows stay in the 126 MB L2)
+TRAFFIC_PER_LAUNCH_BYTES, TRAFFIC_LAUNCH_CONFIGS = 4264192 + 165376, 131072
 N_SM, SCHEDULERS_PER_SM = 148, 4
 
 
@@ -275,7 +278,8 @@ def main():
         alg_bytes = N * 7 * 4 + a.obstacles * 12 * 4 * ((T + 31) // 32 * 32) + N * W * 4
         roofline = {
             "bound": "fp32", "kernel": "k_sweep" if not a.generic else "k_collide_bits", "achieved": exec_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
-            "frac": (exec_tflops / fp32_peak) if exec_tflops and fp32_peak else None, "traffic": None,
+            "frac": (exec_tflops / fp32_peak) if exec_tflops and fp32_peak else None,
+            "traffic": TRAFFIC_PER_LAUNCH_BYTES if exec_ok else None, "traffic_note": f"bytes per k_sweep launch of {TRAFFIC_LAUNCH_CONFIGS} configurations (ncu dram__bytes_read.sum + dram__bytes_write.sum, {EXEC_SOURCE})",
             "peak_source": "FFMA micro-benchmark measured in this run (sirrt_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 figure",
             "kernel_ms": k_ms, "flop_per_check_executed": F_EXEC if exec_ok else None, "executed_source": EXEC_SOURCE,
             "issue": {"achieved": issue_rate, "peak": issue_peak, "unit": "warp-inst/s", "frac": (issue_rate / issue_peak) if issue_rate else None,

@@ -74,7 +74,8 @@ enum {
   SIRRT_OPT_USE_SWEEP = 0,      /* 1 (default): capsule-link x box/sphere scenes use the queue-compacted sweep kernel */
   SIRRT_OPT_CHUNK_CONFIGS = 1,  /* configurations per launch of the batched path (default 262144) */
   SIRRT_OPT_WORKLIST_CAP = 2,   /* capacity of the FP64 re-check work list, entries (default 4194304) */
-  SIRRT_OPT_SWEEP_MIN_CONFIGS = 3 /* batches smaller than this use the generic kernel, which splits rows over warps (default 8192) */
+  SIRRT_OPT_SWEEP_MIN_CONFIGS = 3, /* batches smaller than this use the generic kernel, which splits rows over warps (default 8192) */
+  SIRRT_OPT_DEFER_MAX_CONFIGS = 4  /* hull scenes: batches up to this many configurations hand their GJK pair tests to a machine-wide task kernel (default 4096; 0 = never) */
 };
 int sirrt_scene_set_option(sirrt_scene*, int key, long long value);
 /* link world transforms of the planned robot for q, [n_links][12] = R row-major then t, from the

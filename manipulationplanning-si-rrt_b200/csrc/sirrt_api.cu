@@ -42,7 +42,9 @@ struct DevBuf {
     if (bytes <= cap) return 0;
     if (p) cudaFree(p);
     p = nullptr; cap = 0;
-    size_t want = std::max(bytes, (size_t)256);
+    // small buffers grow geometrically: the planner's stores grow by one point per call and a cudaMalloc per
+    // call would dominate the latency path
+    size_t want = bytes < ((size_t)64 << 20) ? std::max(2 * bytes, (size_t)4096) : bytes;
     if (cudaMalloc(&p, want) != cudaSuccess) { cudaGetLastError(); return -1; }
     cap = want;
     return 0;
@@ -66,11 +68,21 @@ struct sirrt_scene {
   unsigned int wl_cap = 1u << 22;
   int use_sweep = 1;
   long long sweep_min_configs = 8192;
-  DevBuf q, bits, table, frames, cells, work, counts, misc, misc2;
-  void* pinned = nullptr;  // small pinned staging block for the latency path
+  long long defer_max_configs = 4096;  // hull scenes: batches up to this size hand their GJK runs to k_gjk_tasks
+  DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2;
+  // Latency path (planner in the loop): one pinned host block that the GPU reads and writes in place
+  // (cudaMallocHost memory is device-addressable under UVA).  Small host inputs are memcpy'd into it and read
+  // by the kernels over the bus; small results are written into it by the kernels and memcpy'd out after the
+  // single stream synchronisation of the call -- no cudaMemcpy on that path (measured on the B200 box: every
+  // copy operation adds 3-4 us to the 9 us launch + synchronise floor; scripts/micro/lat_probe.cu).
+  char* pinned = nullptr;
+  bool lazy_pending = false;  // counters of the last run_bits launch are in flight to PIN_CNT
   std::vector<cudaEvent_t> ev;  // start/stop pairs around the sweep launches of one call
   uint64_t stats[5] = {0, 0, 0, 0, 0};
 };
+
+enum : size_t { PIN_Q = 0, PIN_Q_CAP = 256 << 10, PIN_FR = PIN_Q + PIN_Q_CAP, PIN_FR_CAP = 64 << 10, PIN_OUT = PIN_FR + PIN_FR_CAP,
+                PIN_OUT_CAP = 512 << 10, PIN_CNT = PIN_OUT + PIN_OUT_CAP, PIN_CNT_CAP = 4 << 10, PIN_BYTES = PIN_CNT + PIN_CNT_CAP };
 
 template <typename T> static int upload(sirrt_scene* s, const std::vector<T>& v, const T** out) {
   void* p = nullptr;
@@ -121,7 +133,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   // the FP32 arithmetic meets (arm reach around the base), never below 2e-5 m.
   s->band = 2e-5 * std::max(1.0, tb.extent / 1.5);
   if ((rc = sweep_build(s->hs, tb, s->d, &s->sweep, s->owned))) return bail(fail(rc, "sweep table build failed"));
-  if (cudaMallocHost(&s->pinned, 1 << 16) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMallocHost failed")); }
+  if (cudaMallocHost((void**)&s->pinned, PIN_BYTES) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMallocHost failed")); }
   for (int i = 0; i < 64; i++) {
     cudaEvent_t e;
     if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); break; }
@@ -136,7 +148,7 @@ extern "C" void sirrt_scene_destroy(sirrt_scene* s) {
   cudaSetDevice(s->device);
   if (s->own_stream) { cudaStreamSynchronize(s->own_stream); }
   for (void* p : s->owned) cudaFree(p);
-  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->counts, &s->misc, &s->misc2}) b->release();
+  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->tasks, &s->counts, &s->misc, &s->misc2}) b->release();
   if (s->pinned) cudaFreeHost(s->pinned);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
   if (s->own_stream) cudaStreamDestroy(s->own_stream);
@@ -177,6 +189,7 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
     case SIRRT_OPT_USE_SWEEP: s->use_sweep = value != 0; break;
     case SIRRT_OPT_CHUNK_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad chunk"); s->chunk_configs = value; break;
     case SIRRT_OPT_SWEEP_MIN_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad threshold"); s->sweep_min_configs = value; break;
+    case SIRRT_OPT_DEFER_MAX_CONFIGS: if (value < 0) return fail(SIRRT_E_ARG, "bad threshold"); s->defer_max_configs = value; break;
     case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
     default: return fail(SIRRT_E_ARG, "unknown option");
   }

@@ -12,7 +12,10 @@ struct Range { long long n0, cnt; };
 // Collision bit rows of configurations [0, N) (global indexing into q / d_bits).  Work is cut into
 // launches of at most chunk_configs configurations so that the FP64 re-check work list stays
 // bounded; a launch whose list overflowed is repeated in halves.
-static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits) {
+// lazy = true (single-launch batches of the latency path): nothing is synchronised here; the launch counters
+// travel to PIN_CNT behind the kernels and the caller settles them with finish_lazy() after its one
+// synchronisation (a work-list overflow then repeats the call on the checked path).
+static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits, bool lazy = false) {
   const int W = s->tb.n_tiles;
   cudaStream_t st = s->stream;
   if (s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(work list) failed");
@@ -20,6 +23,8 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
   for (long long n0 = 0; n0 < N; n0 += s->chunk_configs) todo.push_back({n0, std::min(s->chunk_configs, N - n0)});
   uint64_t launches = 0, rechecked = 0, near = 0, exact = 0, sweep_ns = 0;
   const bool sweep = s->use_sweep && s->sweep.supported && N >= s->sweep_min_configs;
+  const bool may_defer = !sweep && s->tb.has_hull && s->defer_max_configs > 0;
+  if (may_defer && s->tasks.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(task list) failed");
   while (!todo.empty()) {
     const size_t nr = todo.size();
     if (s->counts.ensure(nr * 4 * sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc(counters) failed");
@@ -28,7 +33,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       QView qv = q;
       qv.n0 = todo[i].n0; qv.cnt = todo[i].cnt;
       WorkList wl{s->work.as<WorkItem>(), s->counts.as<unsigned>() + 4 * i, s->wl_cap};
-      const bool timed = i < s->ev.size() / 2;
+      const bool timed = !(lazy && nr == 1) && i < s->ev.size() / 2;
       if (timed) cudaEventRecord(s->ev[2 * i], st);
       if (sweep) {
         launches += sweep_launch(s->sweep, s->tb.robot, s->d, qv, wl, d_bits, W, (float)s->band, s->n_sm, st);
@@ -36,6 +41,8 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         BitsParams P{};
         P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.bits = d_bits; P.n_words = W;
         P.semantics = semantics; P.band = (float)s->band;
+        const bool defer = may_defer && qv.cnt <= s->defer_max_configs && nr == 1;  // one task list: one range at a time
+        if (defer) P.tasks = WorkList{s->tasks.as<WorkItem>(), wl.count + 3, s->wl_cap};
         // small batches: split each row over several warps (tile chunks) to fill the machine
         long long target = (long long)s->n_sm * 32;
         int n_chunks = (int)std::max(1ll, std::min((long long)W, target / std::max(1ll, qv.cnt)));
@@ -45,6 +52,13 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         if (s->tb.has_hull) k_collide_bits<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         else k_collide_bits<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         launches++;
+        if (defer) {
+          GjkTaskParams G{};
+          G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl;
+          G.bits = d_bits; G.n_words = W; G.cells = nullptr; G.band = (float)s->band;
+          k_gjk_tasks<<<s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, G);
+          launches++;
+        }
       }
       if (timed) cudaEventRecord(s->ev[2 * i + 1], st);
       RecheckParams R{};
@@ -53,6 +67,12 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       k_recheck<<<s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
       launches++;
       CU(cudaGetLastError());
+    }
+    if (lazy && nr == 1) {
+      CU(cudaMemcpyAsync(s->pinned + PIN_CNT, s->counts.p, 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+      s->lazy_pending = true;
+      s->stats[0] += launches;
+      return SIRRT_OK;
     }
     std::vector<unsigned> host(nr * 4);
     CU(cudaMemcpyAsync(host.data(), s->counts.p, nr * 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
@@ -64,7 +84,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
     }
     std::vector<Range> redo;
     for (size_t i = 0; i < nr; i++) {
-      if (host[4 * i] > s->wl_cap) {
+      if (host[4 * i] > s->wl_cap || host[4 * i + 3] > s->wl_cap) {
         if (todo[i].cnt <= 1) return fail(SIRRT_E_OVERFLOW, "FP64 re-check work list overflow on a single configuration; raise SIRRT_OPT_WORKLIST_CAP");
         const long long h = todo[i].cnt / 2;
         redo.push_back({todo[i].n0, h});
@@ -80,6 +100,16 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
   return SIRRT_OK;
 }
 
+// after the caller's synchronisation: 0 = settled, 1 = the work list overflowed (repeat on the checked path)
+static int finish_lazy(sirrt_scene* s) {
+  if (!s->lazy_pending) return 0;
+  s->lazy_pending = false;
+  const unsigned* host = (const unsigned*)(s->pinned + PIN_CNT);
+  if (host[0] > s->wl_cap || host[3] > s->wl_cap) return 1;
+  s->stats[1] += host[0]; s->stats[3] += host[1]; s->stats[2] += host[2];
+  return 0;
+}
+
 static int run_intervals(sirrt_scene* s, const uint32_t* d_bits, long long N, int32_t* d_table, int Kmax) {
   IvParams P{d_bits, N, s->tb.n_tiles, s->tb.T, Kmax, d_table};
   k_bits_to_intervals<<<(unsigned)((N + 7) / 8), 256, 0, s->stream>>>(P);
@@ -89,8 +119,13 @@ static int run_intervals(sirrt_scene* s, const uint32_t* d_bits, long long N, in
 }
 
 // bring a caller buffer onto the device (no-op for device pointers)
-static int stage_in(sirrt_scene* s, DevBuf& buf, const void* src, size_t bytes, const void** dev) {
+static int stage_in(sirrt_scene* s, DevBuf& buf, const void* src, size_t bytes, const void** dev, size_t pin_off = 0, size_t pin_cap = 0) {
   if (is_device_ptr(src)) { *dev = src; return 0; }
+  if (bytes <= pin_cap) {  // latency path: the kernels read the pinned block in place
+    memcpy(s->pinned + pin_off, src, bytes);
+    *dev = s->pinned + pin_off;
+    return 0;
+  }
   if (buf.ensure(bytes)) return fail(SIRRT_E_CUDA, "cudaMalloc(staging) failed");
   CU(cudaMemcpyAsync(buf.p, src, bytes, cudaMemcpyHostToDevice, s->stream));
   *dev = buf.p;
@@ -109,21 +144,38 @@ static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, i
     if (s->bits.ensure((size_t)N * W * sizeof(uint32_t))) return fail(SIRRT_E_CUDA, "cudaMalloc(bits) failed");
     d_bits = s->bits.as<uint32_t>();
   }
-  int rc = run_bits(s, q, N, semantics, d_bits);
-  if (rc) return rc;
-  if (table) {
-    const size_t tbytes = (size_t)N * (1 + 2 * Kmax) * sizeof(int32_t);
-    int32_t* d_table = table;
-    const bool tdev = is_device_ptr(table);
-    if (!tdev) {
-      if (s->table.ensure(tbytes)) return fail(SIRRT_E_CUDA, "cudaMalloc(table) failed");
-      d_table = s->table.as<int32_t>();
+  const size_t tbytes = table ? (size_t)N * (1 + 2 * Kmax) * sizeof(int32_t) : 0, bbytes = (size_t)N * W * sizeof(uint32_t);
+  const bool tdev = table && is_device_ptr(table);
+  // latency path: one launch set, results through the pinned block, one synchronisation
+  const bool small = N <= s->chunk_configs && (!table || tdev || tbytes <= PIN_OUT_CAP / 2) && (!bits || bits_dev || bbytes <= PIN_OUT_CAP / 2);
+  for (int attempt = 0; attempt < 2; attempt++) {
+    const bool lazy = small && attempt == 0;
+    int rc = run_bits(s, q, N, semantics, d_bits, lazy);
+    if (rc) return rc;
+    int32_t* t_host = nullptr;
+    uint32_t* b_host = nullptr;
+    if (table) {
+      int32_t* d_table = table;
+      if (!tdev) {
+        if (small) d_table = t_host = (int32_t*)(s->pinned + PIN_OUT);  // k_bits_to_intervals writes the pinned block in place
+        else {
+          if (s->table.ensure(tbytes)) return fail(SIRRT_E_CUDA, "cudaMalloc(table) failed");
+          d_table = s->table.as<int32_t>();
+        }
+      }
+      if ((rc = run_intervals(s, d_bits, N, d_table, Kmax))) return rc;
+      if (!tdev && !small) CU(cudaMemcpyAsync(table, d_table, tbytes, cudaMemcpyDeviceToHost, s->stream));
     }
-    if ((rc = run_intervals(s, d_bits, N, d_table, Kmax))) return rc;
-    if (!tdev) CU(cudaMemcpyAsync(table, d_table, tbytes, cudaMemcpyDeviceToHost, s->stream));
+    if (bits && !bits_dev) {
+      if (small) { b_host = (uint32_t*)(s->pinned + PIN_OUT + PIN_OUT_CAP / 2); CU(cudaMemcpyAsync(b_host, d_bits, bbytes, cudaMemcpyDeviceToHost, s->stream)); }
+      else CU(cudaMemcpyAsync(bits, d_bits, bbytes, cudaMemcpyDeviceToHost, s->stream));
+    }
+    CU(cudaStreamSynchronize(s->stream));
+    if (lazy && finish_lazy(s)) continue;  // FP64 work list overflowed: repeat with the checked, splitting loop
+    if (t_host) memcpy(table, t_host, tbytes);
+    if (b_host) memcpy(bits, b_host, bbytes);
+    break;
   }
-  if (bits && !bits_dev) CU(cudaMemcpyAsync(bits, d_bits, (size_t)N * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
-  CU(cudaStreamSynchronize(s->stream));
   if (near_contact_count) *near_contact_count = s->stats[2];
   return SIRRT_OK;
 }
@@ -135,7 +187,7 @@ extern "C" int sirrt_safe_intervals_batch(sirrt_scene* s, const float* q_soa, in
   if (N > 0x7fffffffll) return fail(SIRRT_E_ARG, "N exceeds 2^31-1 configurations per call");
   CU(cudaSetDevice(s->device));
   const void* dq = nullptr;
-  int rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq);
+  int rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq, PIN_Q, 64 << 10);
   if (rc) return rc;
   QView q{(const float*)dq, nullptr, N, 0, N, s->hs.dof};
   return bits_and_table(s, q, N, SIRRT_SEM_INTERVAL, table, Kmax, bits, near_contact_count);
@@ -146,7 +198,7 @@ extern "C" int sirrt_collision_bits_f64(sirrt_scene* s, const double* q_aos, int
   if (N == 0) return SIRRT_OK;
   CU(cudaSetDevice(s->device));
   const void* dq = nullptr;
-  int rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq);
+  int rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq, PIN_Q, 64 << 10);
   if (rc) return rc;
   QView q{nullptr, (const double*)dq, N, 0, N, s->hs.dof};
   return bits_and_table(s, q, N, semantics, nullptr, 0, bits, nullptr);
@@ -166,9 +218,22 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     WorkList wl{s->work.as<WorkItem>(), s->counts.as<unsigned>(), s->wl_cap};
     CellParams P{};
     P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.frames = d_frames; P.out = d_out; P.semantics = semantics; P.band = (float)s->band;
+    // hull scenes: every cell appends at most 2*L*slots tasks, the same bound `per` keeps under the list capacity
+    const bool defer = s->tb.has_hull && s->defer_max_configs > 0 && qv.cnt <= 64 * s->defer_max_configs;
+    if (defer) {
+      if (s->tasks.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(task list) failed");
+      P.tasks = WorkList{s->tasks.as<WorkItem>(), wl.count + 3, s->wl_cap};
+    }
     const int grid = grid_for(qv.cnt, s->n_sm, 8);
     if (s->tb.has_hull) k_check_cells<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
     else k_check_cells<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
+    if (defer) {
+      GjkTaskParams G{};
+      G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl;
+      G.bits = nullptr; G.n_words = s->tb.n_tiles; G.cells = d_out; G.band = (float)s->band;
+      k_gjk_tasks<<<s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, G);
+      s->stats[0]++;
+    }
     RecheckParams R{};
     R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
     R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
@@ -185,22 +250,31 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   if (N > 0x7fffffffll) return fail(SIRRT_E_ARG, "N exceeds 2^31-1 cells per call");
   CU(cudaSetDevice(s->device));
   memset(s->stats, 0, sizeof s->stats);
+  if (s->tb.n_slots == 0 && !is_device_ptr(frames) && !is_device_ptr(collided)) {
+    // EMPTY WORKLOAD, not a fallback: a scene without obstacles (STRRT/scene_task.json ships "obstacles": []) has
+    // no (link, obstacle) pair to test, so no kernel has anything to compute; only the frame range rule remains
+    for (int64_t i = 0; i < N; i++) collided[i] = (frames[i] < 0 || frames[i] >= s->tb.T) ? 1 : 0;
+    return SIRRT_OK;
+  }
   const void *dq = nullptr, *df = nullptr;
   int rc;
-  if (q_soa) rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq);
-  else rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq);
+  if (q_soa) rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq, PIN_Q, 64 << 10);
+  else rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq, PIN_Q, 64 << 10);
   if (rc) return rc;
-  if ((rc = stage_in(s, s->frames, frames, (size_t)N * sizeof(int32_t), &df))) return rc;
+  if ((rc = stage_in(s, s->frames, frames, (size_t)N * sizeof(int32_t), &df, PIN_FR, PIN_FR_CAP))) return rc;
   const bool odev = is_device_ptr(collided);
+  const bool opin = !odev && (size_t)N <= (size_t)(16 << 10);  // latency path: the kernels write the pinned block in place
   uint8_t* d_out = collided;
-  if (!odev) {
+  if (opin) d_out = (uint8_t*)(s->pinned + PIN_OUT);
+  else if (!odev) {
     if (s->cells.ensure((size_t)N)) return fail(SIRRT_E_CUDA, "cudaMalloc(cells) failed");
     d_out = s->cells.as<uint8_t>();
   }
   QView q{q_soa ? (const float*)dq : nullptr, q_soa ? nullptr : (const double*)dq, N, 0, N, s->hs.dof};
   if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME))) return rc;
-  if (!odev) CU(cudaMemcpyAsync(collided, d_out, (size_t)N, cudaMemcpyDeviceToHost, s->stream));
+  if (!odev && !opin) CU(cudaMemcpyAsync(collided, d_out, (size_t)N, cudaMemcpyDeviceToHost, s->stream));
   CU(cudaStreamSynchronize(s->stream));
+  if (opin) memcpy(collided, d_out, (size_t)N);
   return SIRRT_OK;
 }
 extern "C" int sirrt_check_frames_batch(sirrt_scene* s, const float* q_soa, const int32_t* frames, int64_t N, uint8_t* collided) {
@@ -218,18 +292,29 @@ extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo
   const int dof = s->hs.dof, W = s->tb.n_tiles, T = s->tb.T;
   const int Kmax = std::max(1, std::min(cap, (T + 1) / 2));
   const size_t tbytes = (size_t)(1 + 2 * Kmax) * sizeof(int32_t);
-  if (s->misc.ensure(sizeof(double) * dof + (size_t)W * 4 + tbytes + 64)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
-  double* dq = s->misc.as<double>();
-  uint32_t* d_bits = (uint32_t*)(dq + dof);
-  int32_t* d_table = (int32_t*)(d_bits + W);
-  std::vector<int32_t> host_table(1 + 2 * Kmax);
-  CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyHostToDevice, s->stream));
+  if (tbytes > PIN_OUT_CAP) return fail(SIRRT_E_ARG, "sirrt_safe_intervals: cap too large");
+  if (s->tb.n_slots == 0) {  // EMPTY WORKLOAD (no obstacle, no pair test, nothing to launch): one interval [0, T-1], CollisionManager.cpp:509-517
+    *n_out = 1;
+    if (cap < 1) return fail(SIRRT_E_OVERFLOW, "sirrt_safe_intervals: more intervals than cap");
+    lo_hi[0] = 0; lo_hi[1] = T - 1;
+    return SIRRT_OK;
+  }
+  if (s->misc.ensure((size_t)W * 4 + 64)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  // latency path: q is read from, and the interval table written to, the pinned block in place; one synchronisation
+  double* dq = (double*)(s->pinned + PIN_Q);
+  if (is_device_ptr(q)) CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyDeviceToHost, s->stream));
+  else memcpy(dq, q, sizeof(double) * dof);
+  uint32_t* d_bits = s->misc.as<uint32_t>();
+  const int32_t* host_table = (const int32_t*)(s->pinned + PIN_OUT);
   QView qv{nullptr, dq, 1, 0, 1, dof};
-  int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits);
-  if (rc) return rc;
-  if ((rc = run_intervals(s, d_bits, 1, d_table, Kmax))) return rc;
-  CU(cudaMemcpyAsync(host_table.data(), d_table, tbytes, cudaMemcpyDeviceToHost, s->stream));
-  CU(cudaStreamSynchronize(s->stream));
+  for (int attempt = 0; attempt < 2; attempt++) {
+    int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits, attempt == 0);
+    if (rc) return rc;
+    if ((rc = run_intervals(s, d_bits, 1, (int32_t*)host_table, Kmax))) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+    if (attempt == 0 && finish_lazy(s)) continue;
+    break;
+  }
   *n_out = host_table[0];
   const int n = std::min(host_table[0], std::min(cap, Kmax));
   for (int i = 0; i < 2 * n; i++) lo_hi[i] = host_table[1 + i];

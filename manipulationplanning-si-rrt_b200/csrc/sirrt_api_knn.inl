@@ -10,7 +10,12 @@ struct sirrt_knn {
   cudaStream_t stream = nullptr;
   double* pts = nullptr;
   DevBuf stage, qbuf, part_d, part_i, out_i, out_d, hits, count;
+  // latency path (one query per planner iteration): pinned block read / written in place by the kernels
+  char* pinned = nullptr;   // [KPIN_Q | KPIN_OUT | KPIN_RING]
+  int ring_next = 0;        // next slot of the asynchronous single-point insertion ring
 };
+enum : size_t { KPIN_Q = 0, KPIN_Q_CAP = 16 << 10, KPIN_OUT = KPIN_Q_CAP, KPIN_OUT_CAP = 32 << 10, KPIN_RING = KPIN_OUT + KPIN_OUT_CAP,
+                KPIN_RING_SLOTS = 64, KPIN_BYTES = KPIN_RING + KPIN_RING_SLOTS * SIRRT_KNN_MAXDIM * sizeof(double) };
 
 extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn** out) {
   if (!out || dim < 1 || dim > SIRRT_KNN_MAXDIM || capacity < 1 || capacity > 0x7fffffffll) return fail(SIRRT_E_ARG, "sirrt_knn_create: bad argument");
@@ -23,8 +28,10 @@ extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn
   if (!k) return fail(SIRRT_E_ARG, "out of memory");
   k->device = device; k->dim = dim; k->cap = capacity;
   cudaDeviceGetAttribute(&k->n_sm, cudaDevAttrMultiProcessorCount, device);
-  if (cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&k->pts, sizeof(double) * dim * (size_t)capacity) != cudaSuccess) {
+  if (cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&k->pts, sizeof(double) * dim * (size_t)capacity) != cudaSuccess ||
+      cudaMallocHost((void**)&k->pinned, KPIN_BYTES) != cudaSuccess) {
     cudaGetLastError();
+    if (k->pts) cudaFree(k->pts);
     if (k->stream) cudaStreamDestroy(k->stream);
     delete k;
     return fail(SIRRT_E_CUDA, "sirrt_knn_create: allocation failed");
@@ -37,6 +44,7 @@ extern "C" int sirrt_knn_destroy(sirrt_knn* k) {
   cudaSetDevice(k->device);
   cudaStreamSynchronize(k->stream);
   cudaFree(k->pts);
+  if (k->pinned) cudaFreeHost(k->pinned);
   for (DevBuf* b : {&k->stage, &k->qbuf, &k->part_d, &k->part_i, &k->out_i, &k->out_d, &k->hits, &k->count}) b->release();
   cudaStreamDestroy(k->stream);
   cudaGetLastError();
@@ -62,6 +70,18 @@ extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
   CU(cudaSetDevice(k->device));
   const size_t bytes = sizeof(double) * k->dim * (size_t)n;
   const double* src = pts;
+  if (n == 1 && !is_device_ptr(pts)) {
+    // Tree::add_vertex once per planner iteration: the point goes into a pinned ring slot that the append kernel
+    // reads in place; nothing is synchronised (queries are ordered behind it on the same stream) except when the
+    // ring wraps
+    if (k->ring_next == (int)KPIN_RING_SLOTS) { CU(cudaStreamSynchronize(k->stream)); k->ring_next = 0; }
+    double* slot = (double*)(k->pinned + KPIN_RING) + (size_t)k->ring_next++ * SIRRT_KNN_MAXDIM;
+    memcpy(slot, pts, bytes);
+    k_knn_append<<<1, 32, 0, k->stream>>>(slot, 1, k->dim, k->pts, k->cap, k->n);
+    CU(cudaGetLastError());
+    k->n += 1;
+    return SIRRT_OK;
+  }
   if (!is_device_ptr(pts)) {
     if (k->stage.ensure(bytes)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
     CU(cudaMemcpyAsync(k->stage.p, pts, bytes, cudaMemcpyHostToDevice, k->stream));
@@ -78,6 +98,7 @@ extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
 static int knn_queries_in(sirrt_knn* k, const double* queries, int64_t nq, const double** dq) {
   if (is_device_ptr(queries)) { *dq = queries; return 0; }
   const size_t bytes = sizeof(double) * k->dim * (size_t)nq;
+  if (bytes <= KPIN_Q_CAP) { memcpy(k->pinned + KPIN_Q, queries, bytes); *dq = (const double*)(k->pinned + KPIN_Q); return 0; }
   if (k->qbuf.ensure(bytes)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
   CU(cudaMemcpyAsync(k->qbuf.p, queries, bytes, cudaMemcpyHostToDevice, k->stream));
   *dq = k->qbuf.as<double>();
@@ -108,14 +129,17 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
     return fail(SIRRT_E_CUDA, "cudaMalloc failed");
   KnnStore S{k->pts, k->cap, k->n, k->dim};
   const bool idev = is_device_ptr(idx), ddev = dist2 && is_device_ptr(dist2);
-  long long* o_i = idev ? (long long*)idx : k->out_i.as<long long>();
-  double* o_d = dist2 ? (ddev ? dist2 : k->out_d.as<double>()) : nullptr;
+  const bool opin = (size_t)nq * 16 <= KPIN_OUT_CAP;  // results written into the pinned block in place
+  long long* o_i = idev ? (long long*)idx : (opin ? (long long*)(k->pinned + KPIN_OUT) : k->out_i.as<long long>());
+  double* o_d = dist2 ? (ddev ? dist2 : (opin ? (double*)(k->pinned + KPIN_OUT + KPIN_OUT_CAP / 2) : k->out_d.as<double>())) : nullptr;
   k_knn_partial<<<dim3(n_split, (unsigned)nq), SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, k->part_d.as<double>(), k->part_i.as<long long>());
   k_knn_final<<<(unsigned)((nq + 7) / 8), 256, 0, k->stream>>>(k->part_d.as<double>(), k->part_i.as<long long>(), n_split, nq, o_i, o_d);
   CU(cudaGetLastError());
-  if (!idev) CU(cudaMemcpyAsync(idx, o_i, sizeof(long long) * nq, cudaMemcpyDeviceToHost, k->stream));
-  if (dist2 && !ddev) CU(cudaMemcpyAsync(dist2, o_d, sizeof(double) * nq, cudaMemcpyDeviceToHost, k->stream));
+  if (!idev && !opin) CU(cudaMemcpyAsync(idx, o_i, sizeof(long long) * nq, cudaMemcpyDeviceToHost, k->stream));
+  if (dist2 && !ddev && !opin) CU(cudaMemcpyAsync(dist2, o_d, sizeof(double) * nq, cudaMemcpyDeviceToHost, k->stream));
   CU(cudaStreamSynchronize(k->stream));
+  if (!idev && opin) memcpy(idx, o_i, sizeof(long long) * nq);
+  if (dist2 && !ddev && opin) memcpy(dist2, o_d, sizeof(double) * nq);
   return SIRRT_OK;
 }
 
@@ -128,19 +152,23 @@ extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, in
   const double* dq = nullptr;
   int rc = knn_queries_in(k, query, 1, &dq);
   if (rc) return rc;
-  if (k->hits.ensure(sizeof(int) * (size_t)k->n) || k->count.ensure(sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
-  CU(cudaMemsetAsync(k->count.p, 0, sizeof(unsigned), k->stream));
+  // hits layout on the device: [count][hit 0][hit 1]...  -> the count and the first hits leave in ONE copy
+  if (k->hits.ensure(sizeof(int) * ((size_t)k->n + 1))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  CU(cudaMemsetAsync(k->hits.p, 0, sizeof(unsigned), k->stream));
   KnnStore S{k->pts, k->cap, k->n, k->dim};
   const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
-  k_knn_radius<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, r2, k->hits.as<int>(), k->count.as<unsigned>());
+  k_knn_radius<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, r2, k->hits.as<int>() + 1, k->hits.as<unsigned>());
   CU(cudaGetLastError());
-  unsigned cnt = 0;
-  CU(cudaMemcpyAsync(&cnt, k->count.p, sizeof cnt, cudaMemcpyDeviceToHost, k->stream));
+  const size_t first = (size_t)std::min<long long>(k->n, 1023ll);
+  int* ph = (int*)(k->pinned + KPIN_OUT);
+  CU(cudaMemcpyAsync(ph, k->hits.p, sizeof(int) * (first + 1), cudaMemcpyDeviceToHost, k->stream));
   CU(cudaStreamSynchronize(k->stream));
+  const unsigned cnt = (unsigned)ph[0];
   *n_out = cnt;
   if (cnt == 0) return SIRRT_OK;
   std::vector<int> h(cnt);
-  CU(cudaMemcpy(h.data(), k->hits.p, sizeof(int) * cnt, cudaMemcpyDeviceToHost));
+  if (cnt <= first) memcpy(h.data(), ph + 1, sizeof(int) * cnt);
+  else CU(cudaMemcpy(h.data(), k->hits.as<int>() + 1, sizeof(int) * cnt, cudaMemcpyDeviceToHost));
   std::sort(h.begin(), h.end());
   for (int64_t i = 0; i < std::min<int64_t>(cap, cnt); i++) idx[i] = h[i];
   return SIRRT_OK;

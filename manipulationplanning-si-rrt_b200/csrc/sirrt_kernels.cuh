@@ -120,7 +120,7 @@ __device__ __forceinline__ void load_pose(const DScene& sc, int slot, int f, flo
 }
 
 // warp-cooperative FP32 test of (link l, shape sh posed at slot/frame): anything involving a hull
-__device__ inline int coop_test(const DScene& sc, const WarpCtx& W, int l, const DShape& lsh, const DShape& sh, int slot,
+__device__ inline int coop_test(const DScene& sc, const float* RA, const float* tA, const DShape& lsh, const DShape& sh, int slot,
                                 int f, float band, int lane) {
   float RB[9], tB[3];
   load_pose(sc, slot, f, RB, tB, true);
@@ -130,9 +130,9 @@ __device__ inline int coop_test(const DScene& sc, const WarpCtx& W, int l, const
   B.type = sh.type; B.verts = sc.verts_f + 3 * (size_t)sh.vert_off; B.n = sh.n_verts; B.half_len = sh.half_len;
   B.half[0] = sh.half[0]; B.half[1] = sh.half[1]; B.half[2] = sh.half[2];
   float Rrel[9], trel[3], dt[3];
-  matTmul3(Rrel, W.R[l], RB);
-  sub3(dt, tB, W.t[l]);
-  matTvec(trel, W.R[l], dt);
+  matTmul3(Rrel, RA, RB);
+  sub3(dt, tB, tA);
+  matTvec(trel, RA, dt);
   float rsum = (lsh.type == SH_HULL ? 0.f : lsh.radius) + ((sh.type == SH_SPHERE || sh.type == SH_CAPSULE) ? sh.radius : 0.f);
   return warp_gjk<float, false>(A, B, Rrel, trel, rsum, band, lane, (float*)nullptr);
 }
@@ -155,6 +155,7 @@ struct BitsParams {
   DScene sc;
   QView q;
   WorkList wl;
+  WorkList tasks;       // items != null: hull pair tests are NOT run by the producing warp but appended here for k_gjk_tasks
   const float* aabb_f;  // robot slots: [(slot*6 + k)*Tp + f] coal AABB lo(3) hi(3); may be null
   uint32_t* bits;       // [N][W]
   int n_words;          // W
@@ -229,7 +230,10 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
           else if (r == RES_AMBIG) push_work(P.wl, (int)n, frame_tag, l, slot, 2);  // gate already passed
         }
       }
-      if (HAS_HULL) {
+      if (HAS_HULL && P.tasks.items) {  // small batches: spread the hull tests over the whole machine
+        if (q_true) push_work(P.tasks, (int)n, frame_tag, l, slot, 0);
+        if (do_shift && coop_shift) push_work(P.tasks, (int)n, frame_tag, l, slot, 2);
+      } else if (HAS_HULL) {
         bool q_shift = do_shift && coop_shift;
         unsigned m1 = __ballot_sync(SIRRT_FULL, q_true), m2 = __ballot_sync(SIRRT_FULL, q_shift);
         int base = W.qn;
@@ -252,7 +256,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
         int f = fbase < 0 ? 0 : fbase + ln;
         const DSlot S = sc.slots[slot];
         const DShape& sh = sc.shapes[shf ? S.shape_shift : S.shape];
-        int r = coop_test(sc, W, l, sc.shapes[rb.link_shape[l]], sh, slot, f, band, lane);
+        int r = coop_test(sc, W.R[l], W.t[l], sc.shapes[rb.link_shape[l]], sh, slot, f, band, lane);
         if (r == RES_HIT) { any_hit = true; if (lane == ln) lane_hit = true; }
         else if (r == RES_AMBIG && lane == 0) push_work(P.wl, (int)n, fbase < 0 ? -1 : f, l, slot, shf);
       }
@@ -353,6 +357,7 @@ struct CellParams {
   DScene sc;
   QView q;
   WorkList wl;
+  WorkList tasks;       // items != null: hull pair tests are deferred to k_gjk_tasks
   const float* aabb_f;
   const int32_t* frames;  // [N]
   uint8_t* out;           // [N]
@@ -430,7 +435,10 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
         }
       }
       hit = __any_sync(SIRRT_FULL, h);
-      if (HAS_HULL) {
+      if (HAS_HULL && P.tasks.items) {
+        if (q_true) push_work(P.tasks, (int)n, f, l, slot, 0);
+        if (q_shift) push_work(P.tasks, (int)n, f, l, slot, 2);
+      } else if (HAS_HULL) {
         unsigned m1 = __ballot_sync(SIRRT_FULL, q_true), m2 = __ballot_sync(SIRRT_FULL, q_shift);
         for (int pass = 0; pass < 2 && !hit; pass++) {
           unsigned m = pass ? m2 : m1;
@@ -440,7 +448,7 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
             const int pl = __shfl_sync(SIRRT_FULL, l, src), ps = __shfl_sync(SIRRT_FULL, slot, src);
             const DSlot S = sc.slots[ps];
             const DShape& sh = sc.shapes[pass ? S.shape_shift : S.shape];
-            int r = coop_test(sc, W, pl, sc.shapes[rb.link_shape[pl]], sh, ps, f, band, lane);
+            int r = coop_test(sc, W.R[pl], W.t[pl], sc.shapes[rb.link_shape[pl]], sh, ps, f, band, lane);
             if (r == RES_HIT) hit = true;
             else if (r == RES_AMBIG && lane == 0) push_work(P.wl, (int)n, f, pl, ps, pass ? 2 : 0);
           }
@@ -553,6 +561,61 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
       atomicOr(row + wd, m);
     }
   }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Deferred hull pair tests (planner-in-the-loop batches: one configuration, or the few dozen states of an
+// edge).  The producing kernels only cull and append (configuration, frame, link, slot) tasks; here one warp
+// per task runs the FP32 warp-cooperative GJK, so a single get_safe_intervals(q) on a hull robot spreads its
+// few hundred GJK runs over all SMs instead of serialising them in the <= W warps that own the row.
+// Decisions are the same as in the producing warp: HIT sets the bit / cell, AMBIGUOUS goes to the FP64 list.
+// ------------------------------------------------------------------------------------------------
+struct GjkTaskParams {
+  DScene sc;
+  QView q;
+  const WorkItem* items;
+  const unsigned int* count;  // tasks pushed (clamped to cap here; an overflow is detected by the host)
+  unsigned int cap;
+  WorkList wl;                // FP64 re-check list
+  uint32_t* bits;             // bits mode: [N][W]
+  int n_words;
+  uint8_t* cells;             // cell mode: [N]
+  float band;
+};
+
+__global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
+k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskParams P) {
+  const int lane = threadIdx.x & 31;
+  const DScene& sc = P.sc;
+  const unsigned int n_items = min(*P.count, P.cap);
+  for (unsigned int w = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5); w < n_items; w += gridDim.x * SIRRT_WARPS_PER_BLOCK) {
+    const WorkItem it = P.items[w];
+    double q[SIRRT_MAXJ];
+    for (int j = 0; j < rb.n_joints; j++) q[j] = j < P.q.dof ? load_q(P.q, it.config, j) : 0.0;
+    LinkXfD X[SIRRT_MAXL];
+    fk_links(rb, q, X);
+    const int l = it.link, f = it.frame < 0 ? 0 : it.frame;
+    float RA[9], tA[3];
+#pragma unroll
+    for (int k = 0; k < 9; k++) RA[k] = (float)X[l].R[k];  // the same narrowing as setup_links
+#pragma unroll
+    for (int k = 0; k < 3; k++) tA[k] = (float)X[l].t[k];
+    const DSlot S = sc.slots[it.slot];
+    const DShape& sh = sc.shapes[it.shifted ? S.shape_shift : S.shape];
+    const int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane);
+    if (r == RES_AMBIG) { if (lane == 0) push_work(P.wl, it.config, it.frame, l, it.slot, it.shifted); continue; }
+    if (r != RES_HIT) continue;
+    if (P.cells) { if (lane == 0) P.cells[it.config] = 1; continue; }
+    uint32_t* row = P.bits + (size_t)it.config * P.n_words;
+    if (it.frame >= 0) { if (lane == 0) atomicOr(row + (it.frame >> 5), 1u << (it.frame & 31)); }
+    else {
+      for (int wd = lane; wd < P.n_words; wd += 32) {
+        uint32_t m = 0xffffffffu;
+        if (sc.T - wd * 32 < 32) m = (1u << (sc.T - wd * 32)) - 1u;
+        atomicOr(row + wd, m);
+      }
+    }
   }
 }
 

@@ -232,3 +232,26 @@ def test_reference_logged_trajectories_free_on_gpu(pkg, orc, packs, logged_cells
     ref = orc.Oracle(packs(scene), mode)
     step = max(1, len(q) // 200)
     assert [bool(ref.check_frame(qq, int(f))) for qq, f in zip(q[::step], frames[::step])] == got[::step].tolist()
+
+
+@pytest.mark.parametrize("name", ["flying_boxes", "mass_test", "multiple_robots"])
+def test_deferred_hull_tasks_equal_in_warp_gjk(pkg, orc, sp, packs, name):
+    """Hull scenes: small batches hand their GJK pair tests to the machine-wide task kernel (k_gjk_tasks); the
+    rows, the cells and the single-call intervals must equal the in-warp path and the oracle bit for bit."""
+    pk = packs(name)
+    q = random_q(sp, pk, 12, 29)
+    a, b = pkg.Scene(pk), pkg.Scene(pk)
+    b.set_option(pkg.OPT_DEFER_MAX_CONFIGS, 0)
+    ta, ba, _ = a.safe_intervals_batch(q, 8)
+    tb, bb, _ = b.safe_intervals_batch(q, 8)
+    assert np.array_equal(ba, bb) and np.array_equal(ta, tb)
+    ref = orc.Oracle(pk)
+    qd = q.T.astype(np.float64).copy()
+    fr = (np.arange(12, dtype=np.int32) * 131) % ref.n_frames
+    ca, cb = a.check_frames_batch_f64(qd, fr), b.check_frames_batch_f64(qd, fr)
+    assert np.array_equal(ca, cb)
+    assert [bool(x) for x in ca] == [bool(ref.check_frame(qq, int(f))) for qq, f in zip(qd, fr)]
+    for qq in qd[:4]:
+        assert a.safe_intervals(qq) == ref.safe_intervals(qq) == b.safe_intervals(qq)
+    fa, fb = a.collision_bits_f64(qd, pkg.SEM_FRAME), b.collision_bits_f64(qd, pkg.SEM_FRAME)
+    assert np.array_equal(fa, fb)

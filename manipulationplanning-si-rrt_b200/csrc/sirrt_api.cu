@@ -76,6 +76,7 @@ struct sirrt_scene {
   // single stream synchronisation of the call -- no cudaMemcpy on that path (measured on the B200 box: every
   // copy operation adds 3-4 us to the 9 us launch + synchronise floor; scripts/micro/lat_probe.cu).
   char* pinned = nullptr;
+  unsigned int* lazy_cnt = nullptr;  // device: 4 launch counters + ticket, zero between calls (k_recheck's last block clears them)
   bool lazy_pending = false;  // counters of the last run_bits launch are in flight to PIN_CNT
   std::vector<cudaEvent_t> ev;  // start/stop pairs around the sweep launches of one call
   uint64_t stats[5] = {0, 0, 0, 0, 0};
@@ -134,6 +135,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   s->band = 2e-5 * std::max(1.0, tb.extent / 1.5);
   if ((rc = sweep_build(s->hs, tb, s->d, &s->sweep, s->owned))) return bail(fail(rc, "sweep table build failed"));
   if (cudaMallocHost((void**)&s->pinned, PIN_BYTES) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMallocHost failed")); }
+  if (cudaMalloc((void**)&s->lazy_cnt, 64) != cudaSuccess || cudaMemset(s->lazy_cnt, 0, 64) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMalloc failed")); }
   for (int i = 0; i < 64; i++) {
     cudaEvent_t e;
     if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); break; }
@@ -150,6 +152,7 @@ extern "C" void sirrt_scene_destroy(sirrt_scene* s) {
   for (void* p : s->owned) cudaFree(p);
   for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->tasks, &s->counts, &s->misc, &s->misc2}) b->release();
   if (s->pinned) cudaFreeHost(s->pinned);
+  if (s->lazy_cnt) cudaFree(s->lazy_cnt);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
   if (s->own_stream) cudaStreamDestroy(s->own_stream);
   cudaGetLastError();

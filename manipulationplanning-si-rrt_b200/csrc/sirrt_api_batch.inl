@@ -27,12 +27,15 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
   if (may_defer && s->tasks.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(task list) failed");
   while (!todo.empty()) {
     const size_t nr = todo.size();
-    if (s->counts.ensure(nr * 4 * sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc(counters) failed");
-    CU(cudaMemsetAsync(s->counts.p, 0, nr * 4 * sizeof(unsigned), st));
+    const bool self_clearing = lazy && nr == 1;  // counters cleared and published by k_recheck's last block: no memset, no copy
+    if (!self_clearing) {
+      if (s->counts.ensure(nr * 4 * sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc(counters) failed");
+      CU(cudaMemsetAsync(s->counts.p, 0, nr * 4 * sizeof(unsigned), st));
+    }
     for (size_t i = 0; i < nr; i++) {
       QView qv = q;
       qv.n0 = todo[i].n0; qv.cnt = todo[i].cnt;
-      WorkList wl{s->work.as<WorkItem>(), s->counts.as<unsigned>() + 4 * i, s->wl_cap};
+      WorkList wl{s->work.as<WorkItem>(), self_clearing ? s->lazy_cnt : s->counts.as<unsigned>() + 4 * i, s->wl_cap};
       const bool timed = !(lazy && nr == 1) && i < s->ev.size() / 2;
       if (timed) cudaEventRecord(s->ev[2 * i], st);
       if (sweep) {
@@ -64,12 +67,12 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       RecheckParams R{};
       R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
       R.aabb_d = s->d_aabb_d; R.bits = d_bits; R.n_words = W; R.cells = nullptr; R.counters = wl.count;
+      if (self_clearing) { R.ticket = s->lazy_cnt + 4; R.publish = (unsigned int*)(s->pinned + PIN_CNT); }
       k_recheck<<<s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
       launches++;
       CU(cudaGetLastError());
     }
-    if (lazy && nr == 1) {
-      CU(cudaMemcpyAsync(s->pinned + PIN_CNT, s->counts.p, 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    if (self_clearing) {
       s->lazy_pending = true;
       s->stats[0] += launches;
       return SIRRT_OK;
@@ -205,19 +208,20 @@ extern "C" int sirrt_collision_bits_f64(sirrt_scene* s, const double* q_aos, int
 }
 
 // ---- a4: independent (configuration, frame) cells ------------------------------------------------
-static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_frames, uint8_t* d_out, int semantics) {
+static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_frames, uint8_t* d_out, int semantics, int frame_one = 0) {
   cudaStream_t st = s->stream;
   if (s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(work list) failed");
   if (s->counts.ensure(4 * sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc(counters) failed");
+  const bool self_clearing = N <= (long long)(16 << 10);  // latency path: k_recheck's last block clears the counters
   // cells are cheap (one frame each): the work list cannot overflow for chunk sizes below the cap / (L*slots)
   const long long per = std::max(1ll, (long long)s->wl_cap / std::max(1, 2 * s->tb.robot.n_links * s->tb.n_slots));
   for (long long n0 = 0; n0 < N; n0 += per) {
     QView qv = q;
     qv.n0 = n0; qv.cnt = std::min(per, N - n0);
-    CU(cudaMemsetAsync(s->counts.p, 0, 4 * sizeof(unsigned), st));
-    WorkList wl{s->work.as<WorkItem>(), s->counts.as<unsigned>(), s->wl_cap};
+    if (!self_clearing) CU(cudaMemsetAsync(s->counts.p, 0, 4 * sizeof(unsigned), st));
+    WorkList wl{s->work.as<WorkItem>(), self_clearing ? s->lazy_cnt : s->counts.as<unsigned>(), s->wl_cap};
     CellParams P{};
-    P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.frames = d_frames; P.out = d_out; P.semantics = semantics; P.band = (float)s->band;
+    P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.frames = d_frames; P.frame_one = frame_one; P.out = d_out; P.semantics = semantics; P.band = (float)s->band;
     // hull scenes: every cell appends at most 2*L*slots tasks, the same bound `per` keeps under the list capacity
     const bool defer = s->tb.has_hull && s->defer_max_configs > 0 && qv.cnt <= 64 * s->defer_max_configs;
     if (defer) {
@@ -237,6 +241,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     RecheckParams R{};
     R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
     R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
+    if (self_clearing) R.ticket = s->lazy_cnt + 4;
     k_recheck<<<s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
     s->stats[0] += 2;
     CU(cudaGetLastError());
@@ -258,6 +263,16 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   }
   const void *dq = nullptr, *df = nullptr;
   int rc;
+  if (N == 1 && q_aos && !is_device_ptr(q_aos) && !is_device_ptr(frames) && !is_device_ptr(collided) && s->hs.dof <= SIRRT_MAXJ) {
+    // latency path, one cell: angles and frame travel in the kernel parameters, the answer lands in the pinned block
+    QView q1{nullptr, nullptr, 1, 0, 1, s->hs.dof, 1, {}};
+    for (int j = 0; j < s->hs.dof; j++) q1.inl[j] = q_aos[j];
+    uint8_t* d_out1 = (uint8_t*)(s->pinned + PIN_OUT);
+    if ((rc = run_cells(s, q1, 1, nullptr, d_out1, SIRRT_SEM_FRAME, frames[0]))) return rc;
+    CU(cudaStreamSynchronize(s->stream));
+    collided[0] = d_out1[0];
+    return SIRRT_OK;
+  }
   if (q_soa) rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq, PIN_Q, 64 << 10);
   else rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq, PIN_Q, 64 << 10);
   if (rc) return rc;
@@ -302,11 +317,12 @@ extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo
   if (s->misc.ensure((size_t)W * 4 + 64)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
   // latency path: q is read from, and the interval table written to, the pinned block in place; one synchronisation
   double* dq = (double*)(s->pinned + PIN_Q);
-  if (is_device_ptr(q)) CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyDeviceToHost, s->stream));
+  if (is_device_ptr(q)) { CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyDeviceToHost, s->stream)); CU(cudaStreamSynchronize(s->stream)); }
   else memcpy(dq, q, sizeof(double) * dof);
   uint32_t* d_bits = s->misc.as<uint32_t>();
   const int32_t* host_table = (const int32_t*)(s->pinned + PIN_OUT);
-  QView qv{nullptr, dq, 1, 0, 1, dof};
+  QView qv{nullptr, dq, 1, 0, 1, dof, 0, {}};
+  if (dof <= SIRRT_MAXJ) { qv.inl_on = 1; for (int j = 0; j < dof; j++) qv.inl[j] = dq[j]; }  // angles travel in the kernel parameters
   for (int attempt = 0; attempt < 2; attempt++) {
     int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits, attempt == 0);
     if (rc) return rc;

@@ -13,6 +13,8 @@ struct sirrt_knn {
   // latency path (one query per planner iteration): pinned block read / written in place by the kernels
   char* pinned = nullptr;   // [KPIN_Q | KPIN_OUT | KPIN_RING]
   int ring_next = 0;        // next slot of the asynchronous single-point insertion ring
+  unsigned int* ticket = nullptr;  // last-block-done counter of the single-launch queries (zero between launches)
+  size_t hits_cap_zeroed = 0;      // capacity of `hits` whose counter word has been cleared
 };
 enum : size_t { KPIN_Q = 0, KPIN_Q_CAP = 16 << 10, KPIN_OUT = KPIN_Q_CAP, KPIN_OUT_CAP = 32 << 10, KPIN_RING = KPIN_OUT + KPIN_OUT_CAP,
                 KPIN_RING_SLOTS = 64, KPIN_BYTES = KPIN_RING + KPIN_RING_SLOTS * SIRRT_KNN_MAXDIM * sizeof(double) };
@@ -29,7 +31,8 @@ extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn
   k->device = device; k->dim = dim; k->cap = capacity;
   cudaDeviceGetAttribute(&k->n_sm, cudaDevAttrMultiProcessorCount, device);
   if (cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&k->pts, sizeof(double) * dim * (size_t)capacity) != cudaSuccess ||
-      cudaMallocHost((void**)&k->pinned, KPIN_BYTES) != cudaSuccess) {
+      cudaMallocHost((void**)&k->pinned, KPIN_BYTES) != cudaSuccess || cudaMalloc((void**)&k->ticket, 64) != cudaSuccess ||
+      cudaMemset(k->ticket, 0, 64) != cudaSuccess) {
     cudaGetLastError();
     if (k->pts) cudaFree(k->pts);
     if (k->stream) cudaStreamDestroy(k->stream);
@@ -45,6 +48,7 @@ extern "C" int sirrt_knn_destroy(sirrt_knn* k) {
   cudaStreamSynchronize(k->stream);
   cudaFree(k->pts);
   if (k->pinned) cudaFreeHost(k->pinned);
+  if (k->ticket) cudaFree(k->ticket);
   for (DevBuf* b : {&k->stage, &k->qbuf, &k->part_d, &k->part_i, &k->out_i, &k->out_d, &k->hits, &k->count}) b->release();
   cudaStreamDestroy(k->stream);
   cudaGetLastError();
@@ -119,8 +123,23 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
   CU(cudaSetDevice(k->device));
   if (k->n == 0) { for (int64_t i = 0; i < nq; i++) { idx[i] = -1; if (dist2) dist2[i] = 1.0 / 0.0; } return SIRRT_OK; }
   const double* dq = nullptr;
-  int rc = knn_queries_in(k, queries, nq, &dq);
-  if (rc) return rc;
+  int rc;
+  if (nq == 1 && !is_device_ptr(queries) && !is_device_ptr(idx) && !(dist2 && is_device_ptr(dist2))) {  // latency path: one launch, answer lands in the pinned block
+    const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
+    if (k->part_d.ensure(sizeof(double) * (size_t)k->n_sm * 4) || k->part_i.ensure(sizeof(long long) * (size_t)k->n_sm * 4)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+    KnnStore S1{k->pts, k->cap, k->n, k->dim};
+    long long* o_i = (long long*)(k->pinned + KPIN_OUT);
+    double* o_d = (double*)(k->pinned + KPIN_OUT + 8);
+    KnnQuery Q{};
+    for (int j = 0; j < k->dim; j++) Q.v[j] = queries[j];
+    k_knn_nearest1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S1, Q, k->part_d.as<double>(), k->part_i.as<long long>(), k->ticket, o_i, o_d);
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(k->stream));
+    idx[0] = o_i[0];
+    if (dist2) dist2[0] = o_d[0];
+    return SIRRT_OK;
+  }
+  if ((rc = knn_queries_in(k, queries, nq, &dq))) return rc;
   // enough blocks to fill the machine, at least ~4 points per thread per split
   long long want = std::max(1ll, (long long)k->n_sm * 4 / nq);
   int n_split = (int)std::max(1ll, std::min(want, (k->n + 4 * SIRRT_KNN_THREADS - 1) / (4 * SIRRT_KNN_THREADS)));
@@ -149,19 +168,19 @@ extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, in
   *n_out = 0;
   if (k->n == 0) return SIRRT_OK;
   CU(cudaSetDevice(k->device));
-  const double* dq = nullptr;
-  int rc = knn_queries_in(k, query, 1, &dq);
-  if (rc) return rc;
-  // hits layout on the device: [count][hit 0][hit 1]...  -> the count and the first hits leave in ONE copy
+  KnnQuery Q{};
+  if (is_device_ptr(query)) CU(cudaMemcpy(Q.v, query, sizeof(double) * k->dim, cudaMemcpyDeviceToHost));
+  else for (int j = 0; j < k->dim; j++) Q.v[j] = query[j];
+  // hits layout on the device: [count][hit 0][hit 1]...; ONE launch: the last block to finish copies the count and
+  // the first hits into the pinned block and clears the counter for the next query
   if (k->hits.ensure(sizeof(int) * ((size_t)k->n + 1))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
-  CU(cudaMemsetAsync(k->hits.p, 0, sizeof(unsigned), k->stream));
+  if (k->hits_cap_zeroed != k->hits.cap) { CU(cudaMemsetAsync(k->hits.p, 0, sizeof(unsigned), k->stream)); k->hits_cap_zeroed = k->hits.cap; }
   KnnStore S{k->pts, k->cap, k->n, k->dim};
   const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
-  k_knn_radius<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, r2, k->hits.as<int>() + 1, k->hits.as<unsigned>());
-  CU(cudaGetLastError());
   const size_t first = (size_t)std::min<long long>(k->n, 1023ll);
   int* ph = (int*)(k->pinned + KPIN_OUT);
-  CU(cudaMemcpyAsync(ph, k->hits.p, sizeof(int) * (first + 1), cudaMemcpyDeviceToHost, k->stream));
+  k_knn_radius1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, Q, r2, k->hits.as<int>(), k->ticket + 1, ph, (int)first);
+  CU(cudaGetLastError());
   CU(cudaStreamSynchronize(k->stream));
   const unsigned cnt = (unsigned)ph[0];
   *n_out = cnt;

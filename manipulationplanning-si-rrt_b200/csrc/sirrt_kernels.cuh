@@ -21,8 +21,11 @@ struct QView {           // configuration batch: float SoA [dof][N] or double Ao
   long long N;      // row stride of the SoA layout (= total configurations of the caller's batch)
   long long n0, cnt; // the kernel processes configurations n0 .. n0+cnt-1
   int dof;
+  int inl_on;        // latency path, single configuration: the angles travel in the kernel parameters (no bus read)
+  double inl[SIRRT_MAXJ];
 };
 __device__ __forceinline__ double load_q(const QView& q, long long n, int j) {
+  if (q.inl_on) return q.inl[j];
   return q.d_aos ? q.d_aos[n * q.dof + j] : (double)q.f_soa[(long long)j * q.N + n];
 }
 
@@ -56,8 +59,9 @@ __device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QVi
   for (int j = 0; j < rb.n_joints; j++) q[j] = j < qv.dof ? load_q(qv, n, j) : 0.0;
   LinkXfD X[SIRRT_MAXL];
   fk_links(rb, q, X);
-  if (lane == 0) {
-    for (int l = 0; l < rb.n_links; l++) {
+  if (lane < rb.n_links) {  // every lane holds the whole chain: lane l narrows link l
+    {
+      const int l = lane;
       const DShape& sh = sc.shapes[rb.link_shape[l]];
       const double* R = X[l].R;
       const double* t = X[l].t;
@@ -83,8 +87,8 @@ __device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QVi
         for (int k = 0; k < 3; k++) { W.alo[l][k] = (float)(c[k] + t[k] - sh.d_ar); W.ahi[l][k] = (float)(c[k] + t[k] + sh.d_ar); }
       }
     }
-    W.qn = 0;
   }
+  if (lane == 0) W.qn = 0;
   __syncwarp();
 }
 
@@ -359,7 +363,8 @@ struct CellParams {
   WorkList wl;
   WorkList tasks;       // items != null: hull pair tests are deferred to k_gjk_tasks
   const float* aabb_f;
-  const int32_t* frames;  // [N]
+  const int32_t* frames;  // [N]; null: every cell uses frame_one (latency path, single cell)
+  int frame_one;
   uint8_t* out;           // [N]
   int semantics;
   float band;
@@ -378,7 +383,7 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
   const bool want_shift_rob = (sc.parity_mode == 0);
   const float band = P.band;
   for (long long n = P.q.n0 + warp0; n < P.q.n0 + P.q.cnt; n += n_warps) {
-    const int f = P.frames[n];
+    const int f = P.frames ? P.frames[n] : P.frame_one;
     if (f < 0 || f >= sc.T) {  // the reference indexes unchecked (CollisionManager.cpp:369); we answer "collided"
       if (lane == 0) P.out[n] = 1;
       continue;
@@ -473,6 +478,10 @@ struct RecheckParams {
   int n_words;
   uint8_t* cells;           // cell mode: [N]
   unsigned int* counters;   // [2] near-contact count
+  // latency path: the last block to finish publishes counters[0..3] to `publish` (pinned host block) and clears them
+  // and the ticket, so that a call needs neither a memset before nor a copy after its kernels
+  unsigned int* ticket;
+  unsigned int* publish;
 };
 
 __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const LinkXfD& X, int l, const DShape& sh,
@@ -561,6 +570,18 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
       atomicOr(row + wd, m);
     }
   }
+  }
+  if (P.ticket) {  // latency path: last block out publishes and clears the launch counters
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(P.ticket, 1u) == gridDim.x - 1) {
+        __threadfence();
+        volatile unsigned int* c = P.counters;
+        for (int i = 0; i < 4; i++) { const unsigned int v = c[i]; if (P.publish) P.publish[i] = v; c[i] = 0u; }
+        *P.ticket = 0u;
+      }
+    }
   }
 }
 

@@ -122,6 +122,97 @@ k_knn_radius(const __grid_constant__ KnnStore S, const double* __restrict__ quer
   }
 }
 
+// ---- latency path: ONE launch per planner query ---------------------------------------------------------
+// The planner asks one nearest / one radius query per iteration on a tree of 10^2..10^5 points: launch +
+// synchronise (9 us on the B200 box) dominates, so each query is a single kernel: one point per thread with the
+// coordinate loads of a point issued together (the per-dimension loop of knn_dist2 would serialise dim cache
+// misses), block minima to scratch, and the LAST block to finish (atomic ticket) reduces them and writes the
+// answer straight into the caller-visible pinned block.
+struct KnnQuery { double v[SIRRT_KNN_MAXDIM]; };  // the query point travels in the kernel parameters (no bus read)
+
+__device__ __forceinline__ double knn_dist2_wide(const KnnStore& S, const double* q, long long i) {
+  double p[SIRRT_KNN_MAXDIM];
+#pragma unroll
+  for (int k = 0; k < SIRRT_KNN_MAXDIM; k++) p[k] = k < S.dim ? S.pts[(size_t)k * S.cap + i] : 0.0;
+  double r = 0.0;
+#pragma unroll
+  for (int k = 0; k < SIRRT_KNN_MAXDIM; k++)
+    if (k < S.dim) { const double d = __dsub_rn(q[k], p[k]); r = __dadd_rn(r, __dmul_rn(d, d)); }  // same order, no FMA: bit-equal to knn_dist2
+  return r;
+}
+
+__global__ void __launch_bounds__(SIRRT_KNN_THREADS)
+k_knn_nearest1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQuery query, double* pd, long long* pi, unsigned int* ticket,
+               long long* out_idx, double* out_d2) {
+  __shared__ double q[SIRRT_KNN_MAXDIM];
+  __shared__ double sd[32];
+  __shared__ long long si[32];
+  __shared__ bool last;
+  if (threadIdx.x < S.dim) q[threadIdx.x] = query.v[threadIdx.x];
+  __syncthreads();
+  double best = 1.0 / 0.0;
+  long long bi = 0x7fffffffffffffffll;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < S.n; i += (long long)gridDim.x * blockDim.x) {
+    const double d = knn_dist2_wide(S, q, i);
+    if (d < best) { best = d; bi = i; }  // ascending i per thread: strict < keeps the first
+  }
+  knn_block_min(best, bi, sd, si);
+  if (threadIdx.x == 0) {
+    pd[blockIdx.x] = best; pi[blockIdx.x] = bi;
+    __threadfence();
+    last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  best = 1.0 / 0.0; bi = 0x7fffffffffffffffll;
+  for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) {
+    const double od = ((volatile double*)pd)[b];
+    const long long oi = ((volatile long long*)pi)[b];
+    if (knn_less(od, oi, best, bi)) { best = od; bi = oi; }
+  }
+  knn_block_min(best, bi, sd, si);
+  if (threadIdx.x == 0) {
+    out_idx[0] = bi == 0x7fffffffffffffffll ? -1 : bi;
+    out_d2[0] = best;
+    *ticket = 0;  // ready for the next query on this stream
+  }
+}
+
+// radius query, single launch: hits appended to hits[1..] with a warp-aggregated atomic on hits[0]; the last
+// block copies the count and the first `first` hits into the pinned block and clears the counter
+__global__ void __launch_bounds__(SIRRT_KNN_THREADS)
+k_knn_radius1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQuery query, double r2, int* hits, unsigned int* ticket, int* out, int first) {
+  __shared__ double q[SIRRT_KNN_MAXDIM];
+  __shared__ bool last;
+  if (threadIdx.x < S.dim) q[threadIdx.x] = query.v[threadIdx.x];
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long n_round = (S.n + stride - 1) / stride * stride;
+  unsigned int* count = (unsigned int*)hits;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+    const bool in = i < S.n && knn_dist2_wide(S, q, i) < r2;
+    const unsigned m = __ballot_sync(0xffffffffu, in);
+    if (!m) continue;
+    unsigned base = 0;
+    if (lane == 0) base = atomicAdd(count, (unsigned)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (in) hits[1 + base + __popc(m & ((1u << lane) - 1))] = (int)i;
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  const unsigned cnt = *(volatile unsigned int*)count;
+  const int ncopy = (int)min(cnt, (unsigned)first);
+  for (int i = threadIdx.x; i < ncopy; i += blockDim.x) out[1 + i] = ((volatile int*)hits)[1 + i];
+  __syncthreads();
+  if (threadIdx.x == 0) { out[0] = (int)cnt; *count = 0; *ticket = 0; }
+}
+
 // k nearest of each query in ascending (distance, index) order: one block per query, k selection
 // passes, pass j takes the minimum over points strictly greater than the (j-1)-th result
 __global__ void __launch_bounds__(SIRRT_KNN_THREADS)

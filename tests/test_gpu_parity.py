@@ -255,3 +255,29 @@ def test_deferred_hull_tasks_equal_in_warp_gjk(pkg, orc, sp, packs, name):
         assert a.safe_intervals(qq) == ref.safe_intervals(qq) == b.safe_intervals(qq)
     fa, fb = a.collision_bits_f64(qd, pkg.SEM_FRAME), b.collision_bits_f64(qd, pkg.SEM_FRAME)
     assert np.array_equal(fa, fb)
+
+
+def test_knn_single_query_latency_path(pkg, orc):
+    """The planner's pattern (Tree::add_vertex then one nearest / one radius query per iteration): single-launch
+    kernels, answers through the pinned block, asynchronous insertion ring (wraps every 64 points)."""
+    rng = np.random.default_rng(11)
+    pts = rng.uniform(-3.2, 3.2, (700, 6))
+    pts[300] = pts[5]
+    idx = pkg.KnnIndex(6, 4096)
+    for n in range(len(pts)):
+        idx.add(pts[n][None, :])
+        if n % 7 == 0 or n > 690:
+            q = rng.uniform(-3.2, 3.2, (1, 6)) if n % 2 else pts[5][None, :] + 1e-12
+            gi, gd = idx.nearest(q)
+            ri, rd = orc.knn_nearest(pts[: n + 1], q)
+            assert gi[0] == ri[0] and gd[0] == rd[0], n
+            got, cnt = idx.radius(q[0], 9.0)
+            exp = orc.knn_radius(pts[: n + 1], q[0], 9.0)
+            assert cnt == len(exp) and np.array_equal(got, exp), n
+    big = rng.uniform(-1, 1, (3000, 6))  # more hits than the pinned block's first slice: second copy path
+    idx2 = pkg.KnnIndex(6, 4096)
+    idx2.add(big)
+    got, cnt = idx2.radius(np.zeros(6), 100.0)
+    assert cnt == 3000 and np.array_equal(got, np.arange(3000))
+    got, cnt = idx2.radius(np.zeros(6), 0.5)
+    assert np.array_equal(got, orc.knn_radius(big, np.zeros(6), 0.5))

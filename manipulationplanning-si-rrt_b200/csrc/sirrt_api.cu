@@ -126,7 +126,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   d.n_static = tb.n_static; d.n_dynamic = tb.n_dynamic; d.parity_mode = parity_mode; d.has_hull = tb.has_hull;
 #define UP(field, vec) if ((rc = upload(s, vec, &field))) return bail(rc)
   UP(d.shapes, tb.shapes); UP(d.slots, tb.slots); UP(d.static_slots, tb.static_slots); UP(d.dynamic_slots, tb.dynamic_slots);
-  UP(d.pose_f, tb.pose_f); UP(d.bcw_f, tb.bcw_f); UP(d.pose_d, tb.pose_d); UP(d.tile_bounds, tb.tile_bounds);
+  UP(d.pose_f, tb.pose_f); UP(d.bcw_f, tb.bcw_f); UP(d.tight_f, tb.tight_f); UP(d.pose_d, tb.pose_d); UP(d.tile_bounds, tb.tile_bounds);
   UP(d.verts_f, tb.verts_f); UP(d.verts_d, tb.verts_d); UP(s->d_aabb_f, tb.aabb_f); UP(s->d_aabb_d, tb.aabb_d);
 #undef UP
   // FP32 uncertainty band: the fast path decides a pair only when |signed distance| exceeds it;

@@ -94,7 +94,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         redo.push_back({todo[i].n0 + h, todo[i].cnt - h});
         // rows of the overflowed range are recomputed from scratch (bits are overwritten by the producer)
       } else {
-        rechecked += host[4 * i]; exact += host[4 * i + 1]; near += host[4 * i + 2];
+        rechecked += host[4 * i]; exact += host[4 * i + 1] + host[4 * i + 3]; near += host[4 * i + 2];
       }
     }
     todo.swap(redo);
@@ -109,7 +109,7 @@ static int finish_lazy(sirrt_scene* s) {
   s->lazy_pending = false;
   const unsigned* host = (const unsigned*)(s->pinned + PIN_CNT);
   if (host[0] > s->wl_cap || host[3] > s->wl_cap) return 1;
-  s->stats[1] += host[0]; s->stats[3] += host[1]; s->stats[2] += host[2];
+  s->stats[1] += host[0]; s->stats[3] += host[1] + host[3]; s->stats[2] += host[2];
   return 0;
 }
 

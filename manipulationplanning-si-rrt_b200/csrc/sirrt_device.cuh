@@ -67,6 +67,7 @@ struct DScene {
   const int* dynamic_slots;
   const float* pose_f;       // [(slot*12 + k)*Tp + f]  k<9: R row-major, k>=9: t
   const float* bcw_f;        // [(slot*3 + k)*Tp + f]   world bounding-sphere centre
+  const float* tight_f;      // [(slot*6 + k)*Tp + f]   tight world AABB lo(3) hi(3) of the posed slot (covers the shifted geometry too)
   const double* pose_d;      // [(slot*Tp + f)*12 + k]
   const float4* tile_bounds; // [tile*n_dynamic + j]    swept bounding sphere of dynamic slot j over the tile
   const float* verts_f;      // xyz interleaved

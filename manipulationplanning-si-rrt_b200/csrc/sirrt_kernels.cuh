@@ -48,6 +48,7 @@ struct WarpCtx {   // per-warp shared memory: the planned robot's links in world
   float bc[SIRRT_MAXL][3], br[SIRRT_MAXL];                   // bounding sphere
   float R[SIRRT_MAXL][9], t[SIRRT_MAXL][3];                  // link transform
   float alo[SIRRT_MAXL][3], ahi[SIRRT_MAXL][3];              // coal AABB (QUIRK 7 broadphase gate)
+  float tlo[SIRRT_MAXL][3], thi[SIRRT_MAXL][3];              // tight world AABB (cull before the narrowphase)
   int type[SIRRT_MAXL];
   int qn;
   unsigned long long q[SIRRT_QCAP];                          // cooperative (hull) task queue
@@ -76,6 +77,14 @@ __device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QVi
       for (int k = 0; k < 3; k++) {  // capsule core: local (0,0,+-half_len)
         W.a[l][k] = (float)(t[k] - R[3 * k + 2] * sh.d_half_len);
         W.b[l][k] = (float)(t[k] + R[3 * k + 2] * sh.d_half_len);
+      }
+      {  // tight world AABB: centre R*ac + t, half extents sum_j |R_kj| (amax_j - amin_j)/2, rounded outwards
+        double c[3]; matvec(c, R, sh.d_ac);
+        for (int k = 0; k < 3; k++) {
+          double e = 0;
+          for (int j = 0; j < 3; j++) e += fabs(R[3 * k + j]) * 0.5 * (sh.d_amax[j] - sh.d_amin[j]);
+          W.tlo[l][k] = __double2float_rd(c[k] + t[k] - e); W.thi[l][k] = __double2float_ru(c[k] + t[k] + e);
+        }
       }
       // coal CollisionObject::computeAABB (identity rotation -> translated local AABB)
       bool ident = true;
@@ -139,6 +148,20 @@ __device__ inline int coop_test(const DScene& sc, const float* RA, const float* 
   matTvec(trel, RA, dt);
   float rsum = (lsh.type == SH_HULL ? 0.f : lsh.radius) + ((sh.type == SH_SPHERE || sh.type == SH_CAPSULE) ? sh.radius : 0.f);
   return warp_gjk<float, false>(A, B, Rrel, trel, rsum, band, lane, (float*)nullptr);
+}
+
+// Tight-AABB cull: a pair whose world AABBs are further apart than the FP32 uncertainty band on some axis cannot
+// collide (both boxes contain their FP64 shapes: tables are rounded outwards); no decision is taken here
+// other than "certainly free", so results are unchanged -- only GJK / closed-form runs are saved.
+__device__ __forceinline__ bool tight_overlap(const DScene& sc, const WarpCtx& W, int l, int slot, int f, float band) {
+  const float* tb = sc.tight_f + (size_t)slot * 6 * sc.Tp + f;
+  bool ov = true;
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const float lo = tb[(size_t)k * sc.Tp], hi = tb[(size_t)(3 + k) * sc.Tp];
+    ov &= (W.tlo[l][k] - band <= hi) && (W.thi[l][k] + band >= lo);
+  }
+  return ov;
 }
 
 // QUIRK 7 broadphase gate: do the coal AABBs of the TRUE geometries overlap?  FP32 with margin.
@@ -282,7 +305,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
           const float* c = sc.bcw_f + (size_t)slot * 3 * sc.Tp;
           float dx = W.bc[l][0] - c[0], dy = W.bc[l][1] - c[sc.Tp], dz = W.bc[l][2] - c[2 * (size_t)sc.Tp];
           float rr = (W.br[l] + sc.slots[slot].br) * 1.000001f + 1e-5f + band;
-          pass = dx * dx + dy * dy + dz * dz <= rr * rr;
+          pass = dx * dx + dy * dy + dz * dz <= rr * rr && tight_overlap(sc, W, l, slot, 0, band);
         }
         bool h = eval_lane(l, slot, 0, -1, pass);
         bool lane_hit = false, any_hit = false;
@@ -328,7 +351,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
               m &= m - 1;
               float dx = W.bc[l][0] - cx, dy = W.bc[l][1] - cy, dz = W.bc[l][2] - cz;
               float rr = (W.br[l] + sbr) * 1.000001f + 1e-5f + band;
-              bool pass = valid && (dx * dx + dy * dy + dz * dz <= rr * rr);
+              bool pass = valid && (dx * dx + dy * dy + dz * dz <= rr * rr) && tight_overlap(sc, W, l, slot, fc, band);
               if (!__any_sync(SIRRT_FULL, pass)) continue;
               hit |= eval_lane(l, slot, fc, fc, pass);
               if (HAS_HULL && W.qn > SIRRT_QCAP - 64) { bool any = false; drain(tile * 32, hit, any); }
@@ -404,7 +427,7 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
         const float sbr = S.br;
         float dx = W.bc[l][0] - c[0], dy = W.bc[l][1] - c[sc.Tp], dz = W.bc[l][2] - c[2 * (size_t)sc.Tp];
         float rr = (W.br[l] + sbr) * 1.000001f + 1e-5f + band;
-        if (dx * dx + dy * dy + dz * dz <= rr * rr) {
+        if (dx * dx + dy * dy + dz * dz <= rr * rr && tight_overlap(sc, W, l, slot, f, band)) {
           const DShape& lsh = sc.shapes[rb.link_shape[l]];
           const DShape& sh = sc.shapes[S.shape];
           bool do_true = !S.is_robot || want_true_rob;

@@ -12,7 +12,7 @@ struct HostTables {
   std::vector<DShape> shapes;
   std::vector<DSlot> slots;
   std::vector<int> static_slots, dynamic_slots;
-  std::vector<float> pose_f, bcw_f, aabb_f, verts_f;
+  std::vector<float> pose_f, bcw_f, aabb_f, tight_f, verts_f;
   std::vector<double> pose_d, aabb_d, verts_d;
   std::vector<float4> tile_bounds;
   double extent = 0;  // largest |coordinate| the FP32 path can meet near the arm (band scaling)
@@ -35,6 +35,16 @@ inline void to_dshape(const HShape& h, DShape& d, std::vector<float>& vf, std::v
   }
   d.br = (float)(h.br * (1 + 1e-6));  // round-off guard: the float radius must not be smaller
   d.ar = (float)h.ar; d.d_ar = h.ar;
+}
+
+// tight world AABB of a posed shape: centre R*ac + t, half extents sum_j |R_kj| * (amax_j - amin_j)/2
+inline void tight_aabb(const HShape& s, const HXf& x, double* lo, double* hi) {
+  double c[3]; h_matvec(c, x.R, s.ac);
+  for (int k = 0; k < 3; k++) {
+    double e = 0;
+    for (int j = 0; j < 3; j++) e += fabs(x.R[3 * k + j]) * 0.5 * (s.amax[j] - s.amin[j]);
+    lo[k] = c[k] + x.t[k] - e; hi[k] = c[k] + x.t[k] + e;
+  }
 }
 
 // coal CollisionObject::computeAABB: identity rotation -> translated local AABB, otherwise the cube
@@ -100,6 +110,14 @@ inline int build_tables(const HScene& sc, int parity_mode, HostTables& tb, std::
   tb.pose_d.assign((size_t)n_slots * Tp * 12 + 1, 0.0);
   tb.aabb_f.assign((size_t)n_slots * 6 * Tp + 1, 0.f);
   tb.aabb_d.assign((size_t)n_slots * Tp * 6 + 1, 0.0);
+  tb.tight_f.assign((size_t)n_slots * 6 * Tp + 1, 0.f);
+  // tight AABB gate table: outward-rounded floats (nextafter) so that the FP32 box always contains the FP64 one
+  auto put_tight = [&](int slot, int f, const double* lo, const double* hi) {
+    for (int k = 0; k < 3; k++) {
+      tb.tight_f[((size_t)slot * 6 + k) * Tp + f] = nextafterf((float)lo[k], -3.0e38f);
+      tb.tight_f[((size_t)slot * 6 + 3 + k) * Tp + f] = nextafterf((float)hi[k], 3.0e38f);
+    }
+  };
   std::vector<double> bcw_d((size_t)n_slots * Tp * 3 + 1, 0.0);
 
   auto put_pose = [&](int slot, int f, const HXf& x, const HShape& shape) {
@@ -124,6 +142,9 @@ inline int build_tables(const HScene& sc, int parity_mode, HostTables& tb, std::
       for (int k = 0; k < 9; k++) ident &= x.R[k] == ((k % 4) == 0 ? 1.0 : 0.0);
       same &= !memcmp(p, &o.raw[0], 7 * sizeof(float));
       put_pose(s, f, x, o.shape);
+      double tlo[3], thi[3];
+      tight_aabb(o.shape, x, tlo, thi);
+      put_tight(s, f, tlo, thi);
     }
     S.is_static = o.is_static || same;
     S.rot_identity = ident;
@@ -163,6 +184,15 @@ inline int build_tables(const HScene& sc, int parity_mode, HostTables& tb, std::
         same &= !memcmp(&x, &xf[j], sizeof(HXf));
         put_pose(slot, f, x, st);
         double lo[3], hi[3];
+        tight_aabb(st, x, lo, hi);
+        if (S.shape_shift >= 0) {  // the gate must also admit every pair the shifted functor geometry can hit
+          const HRobObst* owner = nullptr; int kk = k_ref;
+          for (const HRobObst& o2 : sc.robs) { if (kk < o2.robot.n_shapes) { owner = &o2; break; } kk -= o2.robot.n_shapes; }
+          double l2[3], h2[3];
+          tight_aabb(owner->robot.shapes[kk], x, l2, h2);
+          for (int k = 0; k < 3; k++) { lo[k] = fmin(lo[k], l2[k]); hi[k] = fmax(hi[k], h2[k]); }
+        }
+        put_tight(slot, f, lo, hi);
         coal_aabb(st, x, lo, hi);
         for (int k = 0; k < 3; k++) {
           tb.aabb_f[((size_t)slot * 6 + k) * Tp + f] = (float)lo[k]; tb.aabb_f[((size_t)slot * 6 + 3 + k) * Tp + f] = (float)hi[k];

@@ -1,0 +1,108 @@
+// sirrt_mass_main.cpp -- the mass test (BASELINE.json config 5; reference driver mass_test/do_mass_test.py:47-60, one
+// MSIRRT_Planner process per (scene, seed) in a ProcessPoolExecutor) on one B200: ONE process and CUDA context per GPU,
+// `threads` host planner threads sharing the device through their own scenes / streams.  Tasks are independent, so a
+// box shards them across GPUs by launching one of these per device (scripts/mass_test.py); no inter-GPU traffic.
+//   sirrt_mass <tasks.txt> <device> <threads> [--max-time s] [--max-iters n] [--fixed]
+// tasks.txt: one "<scene.pack> <seed>" per line.  Output: one JSON line per task (task index = line number), then a
+// summary line.  Scenes are created once per (thread, pack) and reused by that thread's seeds of the same pack.
+#include <atomic>
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <map>
+#include <mutex>
+#include <sstream>
+#include <thread>
+
+#include "B200Backend.hpp"
+#include "SIRRTPlanner.hpp"
+
+struct Task { std::string pack; int seed; int index; };
+
+static uint64_t fnv(const void* p, size_t n, uint64_t h) {
+  const unsigned char* b = (const unsigned char*)p;
+  for (size_t i = 0; i < n; i++) { h ^= b[i]; h *= 1099511628211ull; }
+  return h;
+}
+
+int main(int argc, char** argv) {
+  if (argc < 4) { fprintf(stderr, "usage: %s <tasks.txt> <device> <threads> [--max-time s] [--max-iters n] [--fixed]\n", argv[0]); return 2; }
+  const int device = atoi(argv[2]), n_threads = std::max(1, atoi(argv[3]));
+  double max_time = -1;
+  uint64_t max_iters = 0;
+  int parity = SIRRT_PARITY_REFERENCE_EXACT;
+  for (int i = 4; i < argc; i++) {
+    if (!strcmp(argv[i], "--max-time") && i + 1 < argc) max_time = atof(argv[++i]);
+    else if (!strcmp(argv[i], "--max-iters") && i + 1 < argc) max_iters = strtoull(argv[++i], nullptr, 10);
+    else if (!strcmp(argv[i], "--fixed")) parity = SIRRT_PARITY_FIXED;
+  }
+  std::vector<Task> tasks;
+  {
+    std::ifstream f(argv[1]);
+    if (!f) { fprintf(stderr, "sirrt_mass: cannot open %s\n", argv[1]); return 2; }
+    std::string line;
+    while (std::getline(f, line)) {
+      std::istringstream is(line);
+      Task t;
+      if (is >> t.pack >> t.seed) { t.index = (int)tasks.size(); tasks.push_back(t); }
+    }
+  }
+  // packs in order of first appearance; thread t owns packs t, t + n_threads, ...
+  std::vector<std::string> packs;
+  std::map<std::string, std::vector<int>> by_pack;
+  for (const Task& t : tasks) {
+    if (!by_pack.count(t.pack)) packs.push_back(t.pack);
+    by_pack[t.pack].push_back(t.index);
+  }
+  using clk = std::chrono::steady_clock;
+  std::mutex out_mu;
+  std::atomic<int> n_solved{0}, n_failed{0};
+  std::atomic<uint64_t> solve_ns_total{0};
+  const auto t0 = clk::now();
+  auto worker = [&](int tid) {
+    for (size_t p = tid; p < packs.size(); p += n_threads) {
+      try {
+        MDP::CollisionManager cm = MDP::CollisionManager::from_pack_file(packs[p], device, parity);
+        for (int ti : by_pack[packs[p]]) {
+          const Task& t = tasks[ti];
+          MDP::B200Backend be(cm, device, true);
+          MDP::MSIRRT::PlannerConnect<MDP::B200Backend> planner(be, t.seed);
+          if (!planner.valid()) throw std::runtime_error(planner.error());
+          if (max_iters) planner.set_max_iterations(max_iters);
+          if (max_time > 0) planner.set_max_planning_time(max_time);
+          const auto a = clk::now();
+          const bool ok = planner.solve();
+          const uint64_t ns = (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - a).count();
+          uint64_t h = 1469598103934665603ull;
+          double cost = -1;
+          size_t n_way = 0;
+          if (ok) {
+            const auto path = planner.get_result_path(0.0);
+            for (const auto& s : path) { h = fnv(s.q.data(), s.q.size() * sizeof(double), h); h = fnv(&s.time, sizeof(double), h); }
+            cost = path.back().time; n_way = path.size();
+            n_solved++;
+          }
+          solve_ns_total += ns;
+          const MDP::MSIRRT::PlannerStats& st = planner.stats();
+          std::lock_guard<std::mutex> lk(out_mu);
+          printf("{\"task\": %d, \"pack\": \"%s\", \"seed\": %d, \"solved\": %s, \"solve_ms\": %.4f, \"cost\": %.17g, \"waypoints\": %zu, "
+                 "\"path_hash\": \"%016llx\", \"iterations\": %llu, \"safe_interval_calls\": %llu, \"state_checks\": %llu}\n",
+                 t.index, t.pack.c_str(), t.seed, ok ? "true" : "false", ns / 1e6, cost, n_way, (unsigned long long)h,
+                 (unsigned long long)st.iterations, (unsigned long long)st.n_safe_interval_calls, (unsigned long long)st.n_state_checks);
+        }
+      } catch (const std::exception& e) {
+        n_failed += (int)by_pack[packs[p]].size();
+        std::lock_guard<std::mutex> lk(out_mu);
+        fprintf(stderr, "sirrt_mass: %s: %s\n", packs[p].c_str(), e.what());
+      }
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 0; t < n_threads; t++) th.emplace_back(worker, t);
+  for (auto& x : th) x.join();
+  const double wall = std::chrono::duration<double>(clk::now() - t0).count();
+  printf("{\"summary\": true, \"device\": %d, \"threads\": %d, \"tasks\": %zu, \"solved\": %d, \"failed\": %d, \"wall_s\": %.4f, \"sum_solve_s\": %.4f}\n",
+         device, n_threads, tasks.size(), n_solved.load(), n_failed.load(), wall, solve_ns_total.load() / 1e9);
+  return n_failed.load() ? 1 : 0;
+}

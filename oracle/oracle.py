@@ -50,6 +50,8 @@ def lib():
         L.oracle_edge_check.argtypes = [vp, vp, vp, f64, f64, f64, vp]
         L.oracle_get_distances.argtypes = [vp, vp, i32, vp]
         L.oracle_bvh_build.argtypes = [vp]
+        L.oracle_set_fast.argtypes = [i32]
+        L.oracle_get_fast.restype = i32
         L.oracle_safe_intervals_batch.argtypes = [vp, vp, i64, vp, i32, vp, i32, i32]
         L.oracle_check_frames_batch.argtypes = [vp, vp, vp, i64, vp, i32]
         L.oracle_knn_nearest.argtypes = [vp, i64, i32, vp, i64, vp, vp]
@@ -73,6 +75,11 @@ def _p(a):
 
 def _d(a):
     return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def set_fast(on: bool):
+    """Baseline mode of the TIMED CPU arm (boolean early exits + AABB tree); results are bit-identical."""
+    lib().oracle_set_fast(int(bool(on)))
 
 
 class Oracle:

@@ -276,7 +276,19 @@ static int simplex_closest(Simplex* s, double* v) {
 }
 
 /* distance between two convex core polytopes; 0 when they intersect */
-static double gjk_core(const Core* A, const Core* B) {
+/* BASELINE MODE (oracle_set_fast): the timed CPU arm answers the boolean query the reference asks of coal
+ * (collide(), not distance()): GJK stops as soon as a separating direction certifies clearance or the current
+ * simplex point certifies penetration of the inflated shapes, cells stop at their first colliding pair
+ * (CollisionCallback::collide sets is_collided and the traversal ends, CollisionManager.cpp:605-608) and safe
+ * intervals go through the AABB tree over constant-pose windows (:107-216).  Every early exit is conservative
+ * by 1e-9 m, so the predicate -- and therefore every bit, interval and plan -- is identical to the exact mode
+ * (tests/test_oracle.py::test_fast_mode_is_bit_identical). */
+static int g_fast = 0;
+void oracle_set_fast(int on) { g_fast = on; }
+int oracle_get_fast(void) { return g_fast; }
+#define FAST_MARGIN 1e-9
+
+static double gjk_core_r(const Core* A, const Core* B, double rsum) {
   Simplex s; s.n = 0;
   double v[3], pa[3], pb[3];
   sub3(v, A->xf.t, B->xf.t);
@@ -292,6 +304,11 @@ static double gjk_core(const Core* A, const Core* B) {
     nv[0] = -v[0]; nv[1] = -v[1]; nv[2] = -v[2];
     ia = support_local(A, nv, pa); ib = support_local(B, v, pb);
     sub3(w, pa, pb);
+    if (g_fast && rsum >= 0) {
+      double vw = dot3(v, w), nv1 = sqrt(vv);
+      if (vw > 0 && vw / nv1 - rsum > FAST_MARGIN) return vw / nv1; /* separating axis: distance >= v.w/|v| */
+      if (nv1 - rsum < -FAST_MARGIN) return nv1;                    /* v is a point of A-B: distance <= |v| */
+    }
     double gap = vv - dot3(v, w);
     if (gap <= 1e-15 * vv) break; /* v is the closest point (duality gap closed) */
     int dup = 0;
@@ -306,6 +323,8 @@ static double gjk_core(const Core* A, const Core* B) {
   }
   return sqrt(vv);
 }
+
+static double gjk_core(const Core* A, const Core* B) { return gjk_core_r(A, B, -1.0); }
 
 double oracle_gjk_distance(const double* a, int na, const double* b, int nb) {
   Core A = {a, na, {{1, 0, 0, 0, 1, 0, 0, 0, 1}, {0, 0, 0}}}, B = {b, nb, {{1, 0, 0, 0, 1, 0, 0, 0, 1}, {0, 0, 0}}};
@@ -649,6 +668,7 @@ typedef struct {
   const OShape* shape; /* planned-robot link geometry */
   Xf xf;
   double bc[3];        /* world bounding-sphere centre */
+  double alo[3], ahi[3]; /* coal AABB of the posed link (baseline mode's broadphase gate) */
 } WLink;
 
 static inline const Xf* obst_pose(const OObst* b, int frame) { return &b->pose[b->is_static ? 0 : frame]; }
@@ -663,7 +683,7 @@ static double shape_shape_distance(const OShape* sa, const Xf* xa, const OShape*
     dcore = sqrt(oracle_seg_seg_dist2(a0, a1, b0, b1));
   } else {
     Core A = {sa->verts, sa->n_core, *xa}, B = {sb->verts, sb->n_core, *xb};
-    dcore = gjk_core(&A, &B);
+    dcore = gjk_core_r(&A, &B, sa->radius + sb->radius);
   }
   return dcore - sa->radius - sb->radius;
 }
@@ -681,7 +701,20 @@ static double link_obstacle_distance(const WLink* L, const OObst* b, const Xf* x
   }
   Core A = {s->verts, s->n_core, L->xf};
   Core B = {b->corners, b->type == SIRRT_OBS_BOX ? 8 : 1, *xb};
-  return gjk_core(&A, &B) - s->radius - (b->type == SIRRT_OBS_SPHERE ? b->radius : 0);
+  const double rs = s->radius + (b->type == SIRRT_OBS_SPHERE ? b->radius : 0);
+  return gjk_core_r(&A, &B, rs) - rs;
+}
+
+/* baseline mode: the reference's broadphase hands a pair to the narrowphase only when the AABBs overlap
+ * (DynamicAABBTree, CollisionManager.cpp:215-216,272-276); boxes / spheres: AABB of the posed obstacle */
+static inline int aabb_culled(const WLink* L, const OObst* b, const Xf* xb) {
+  if (!g_fast) return 0;
+  for (int k = 0; k < 3; k++) {
+    double e = b->type == SIRRT_OBS_SPHERE ? b->radius
+                                           : fabs(xb->R[3 * k]) * b->half[0] + fabs(xb->R[3 * k + 1]) * b->half[1] + fabs(xb->R[3 * k + 2]) * b->half[2];
+    if (xb->t[k] - e > L->ahi[k] + FAST_MARGIN || xb->t[k] + e < L->alo[k] - FAST_MARGIN) return 1;
+  }
+  return 0;
 }
 
 static inline int culled(const double* ca, double ra, const double* cb, double rb) {
@@ -708,6 +741,7 @@ static void make_links(const Oracle* o, const double* q, WLink* L) {
     L[l].shape = &o->robot.shapes[l + o->robot.n_strip];
     L[l].xf = x[l];
     xf_point(L[l].bc, &x[l], L[l].shape->bc);
+    coal_aabb(L[l].shape, &x[l], L[l].alo, L[l].ahi);
   }
 }
 
@@ -728,6 +762,7 @@ static double robobst_min_distance(const Oracle* o, const WLink* L, int nl, int 
           if (!culled(L[l].bc, L[l].shape->br, cb, st->br)) {
             double d = shape_shape_distance(L[l].shape, &L[l].xf, st, xb);
             if (d < m) m = d;
+            if (g_fast && d - SECURITY_MARGIN <= COLLISION_THRESHOLD) return m;
           }
         }
         /* the broadphase only hands the pair to the callback when the TRUE geometries' AABBs overlap */
@@ -736,6 +771,7 @@ static double robobst_min_distance(const Oracle* o, const WLink* L, int nl, int 
           if (!culled(L[l].bc, L[l].shape->br, cb, ss->br)) {
             double d = shape_shape_distance(L[l].shape, &L[l].xf, ss, xb);
             if (d < m) m = d;
+            if (g_fast && d - SECURITY_MARGIN <= COLLISION_THRESHOLD) return m;
           }
         }
       }
@@ -755,9 +791,10 @@ static double cell_distance(const Oracle* o, const WLink* L, int frame, int sema
     if (b->is_static && static_m) continue;
     const Xf* xb = obst_pose(b, frame);
     for (int l = 0; l < nl; l++) {
-      if (culled(L[l].bc, L[l].shape->br, xb->t, b->br)) continue;
+      if (culled(L[l].bc, L[l].shape->br, xb->t, b->br) || aabb_culled(&L[l], b, xb)) continue;
       double d = link_obstacle_distance(&L[l], b, xb);
       if (d < m) m = d;
+      if (g_fast && is_collision(m)) return m;
     }
   }
   if (o->R) m = robobst_min_distance(o, L, nl, frame, semantics, m);
@@ -770,7 +807,7 @@ static double static_min_distance(const Oracle* o, const WLink* L) {
     const OObst* b = &o->obst[c];
     if (!b->is_static) continue;
     for (int l = 0; l < o->robot.n_links; l++) {
-      if (culled(L[l].bc, L[l].shape->br, b->pose[0].t, b->br)) continue;
+      if (culled(L[l].bc, L[l].shape->br, b->pose[0].t, b->br) || aabb_culled(&L[l], b, &b->pose[0])) continue;
       double d = link_obstacle_distance(&L[l], b, &b->pose[0]);
       if (d < m) m = d;
     }
@@ -818,10 +855,13 @@ static int bits_to_intervals(const uint32_t* bits, int T, int32_t* lo_hi, int ca
   return n;
 }
 
+static void bits_bvh(const Oracle* o, const double* q, uint32_t* bits);
+
 int oracle_safe_intervals(const Oracle* o, const double* q, int32_t* lo_hi, int cap) {
   int W = (o->T + 31) / 32;
   uint32_t* bits = malloc(sizeof(uint32_t) * W);
-  if (oracle_collision_bits(o, q, ORACLE_SEM_INTERVAL, bits, 0, NULL)) { free(bits); return -1; }
+  if (g_fast && o->bvh) bits_bvh(o, q, bits); /* baseline mode: the reference's cross-frame AABB tree */
+  else if (oracle_collision_bits(o, q, ORACLE_SEM_INTERVAL, bits, 0, NULL)) { free(bits); return -1; }
   int n = bits_to_intervals(bits, o->T, lo_hi, cap);
   free(bits);
   return n;
@@ -1015,6 +1055,7 @@ static void bits_bvh(const Oracle* o, const double* q, uint32_t* bits) {
       double d;
       if (lf->obstacle_id < o->C) {
         const OObst* b = &o->obst[lf->obstacle_id];
+        if (aabb_culled(&L[l], b, obst_pose(b, lf->f_lo))) continue;
         d = link_obstacle_distance(&L[l], b, obst_pose(b, lf->f_lo));
       } else {
         int k = lf->obstacle_id - o->C, kk = k, r2 = 0;

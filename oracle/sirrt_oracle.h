@@ -5,7 +5,7 @@
  * PARITY PINNED ON THE FREE SIDE ONLY: the reference ships no unit tests or golden vectors for
  * this path and cannot be compiled in this image (coal, Eigen, nanoflann, urdfdom, orocos-kdl are
  * absent).  The one set of real reference OUTPUTS at this boundary are the trajectories its
- * planners logged (Blender/scenes with animation/*.json; tests/golden/make_logged_paths.py):
+ * planners logged (the JSON logs under "Blender/scenes with animation"; tests/golden/make_logged_paths.py):
  * 8 700 (q, frame) cells its own checker accepted, which pass 2-31 mm from obstacles, all FREE
  * here (tests/test_oracle.py).  The colliding side is UNPINNED: it rests on the reference's call
  * sites and soft fixtures (check_scene invariants, FK sanity values, closed-form vs GJK).
@@ -76,6 +76,9 @@ double oracle_seg_box_dist2(const double a[3], const double b[3], const double h
 double oracle_seg_seg_dist2(const double p1[3], const double q1[3], const double p2[3], const double q2[3]);
 double oracle_pt_seg_dist2(const double p[3], const double a[3], const double b[3]);
 
+/* Baseline mode for the TIMED CPU arm (process-global): boolean early exits + AABB tree, bit-identical results. */
+void oracle_set_fast(int on);
+int oracle_get_fast(void);
 #ifdef __cplusplus
 }
 #endif

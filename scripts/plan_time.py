@@ -50,7 +50,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--seeds", type=int, default=10)
     ap.add_argument("--max-time", type=float, default=20.0)
-    ap.add_argument("--scenes", default="scene_task,mass_test,flying_boxes,dyn40,dyn120,dyn200")
+    ap.add_argument("--scenes", default="scene_task,mass_test,flying_boxes,multiple_robots,dyn40,dyn120,dyn200")
+    ap.add_argument("--exact-cpu", action="store_true", help="also time the CPU planner on the exact (unaccelerated) oracle mode")
     a = ap.parse_args()
     g.load_build().build_lib(); g.load_build().build_host()
     sp = g.load_tools()
@@ -58,7 +59,10 @@ def main():
     gpu_exe = os.path.join(ROOT, "manipulationplanning-si-rrt_b200", "host", "sirrt_plan")
     cyl = sp.read_pack(golden("xarm6cyl_robot")).robot
     tmp = tempfile.mkdtemp()
-    out = {"metric": "SI-RRT p50 plan time (algorithm_solving_time_ns)", "seeds": a.seeds, "scenes": {}}
+    out = {"metric": "SI-RRT p50 plan time (algorithm_solving_time_ns)", "seeds": a.seeds,
+           "cpu_arm": "host/SIRRTPlanner.hpp on oracle/ in baseline mode: AABB tree over constant-pose windows for safe intervals, AABB gate + boolean "
+                      "GJK with first-hit exit per state (the reference's coal query pattern), single thread (the reference's execution model)",
+           "scenes": {}}
     for name in a.scenes.split(","):
         if name.startswith("dyn"):
             pk = synthetic_task(sp, orc, cyl, int(name[3:]), 600, 5)
@@ -68,11 +72,16 @@ def main():
         with open(path, "wb") as f:
             f.write(pk)
         rows = {"cpu_oracle": [], "b200_edge_table": [], "b200_per_edge_batches": []}
+        mode = []  # REFERENCE_EXACT everywhere (the robot-obstacle scene's start / goal are free in both parity modes)
         same, solved, counters = 0, 0, {}
         for seed in range(1, a.seeds + 1):
-            ref = run([ora_exe, path, str(seed), "--max-time", str(a.max_time)])
-            t1 = run([gpu_exe, path, tmp, str(seed), "--max-time", str(a.max_time), "--stdout"])
-            t2 = run([gpu_exe, path, tmp, str(seed), "--max-time", str(a.max_time), "--stdout", "--no-edge-table"])
+            ref = run([ora_exe, path, str(seed), "--max-time", str(a.max_time), "--baseline"] + mode)
+            if a.exact_cpu:
+                slow = run([ora_exe, path, str(seed), "--max-time", str(a.max_time)] + mode)
+                if slow:
+                    rows.setdefault("cpu_oracle_exact_mode", []).append(slow["algorithm_solving_time_ns"] / 1e6)
+            t1 = run([gpu_exe, path, tmp, str(seed), "--max-time", str(a.max_time), "--stdout"] + mode)
+            t2 = run([gpu_exe, path, tmp, str(seed), "--max-time", str(a.max_time), "--stdout", "--no-edge-table"] + mode)
             if not (ref and t1 and t2):
                 continue
             rows["cpu_oracle"].append(ref["algorithm_solving_time_ns"] / 1e6)

@@ -1,7 +1,9 @@
 // TEST INFRASTRUCTURE ONLY: the SI-RRT planner of host/SIRRTPlanner.hpp instantiated on the CPU oracle
 // (oracle/sirrt_oracle.h).  Used by tests/test_planner.py to check that the B200 backend yields IDENTICAL plans
 // (same seed, same host logic, two checkers) and to time the CPU side of the plan-time metric.
-//   planner_oracle <scene.pack> <seed> [--max-iters N] [--max-time S] [--fixed]      -> result JSON on stdout
+//   planner_oracle <scene.pack> <seed> [--max-iters N] [--max-time S] [--fixed] [--baseline]      -> result JSON on stdout
+// --baseline: the TIMED CPU arm (oracle_set_fast: boolean early exits + the reference's AABB tree over constant-pose
+// windows, built before the clock starts like the reference's scene initialisation); results are bit-identical.
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -82,13 +84,16 @@ int main(int argc, char** argv) {
   uint64_t max_iters = 0;
   double max_time = -1;
   int mode = ORACLE_REFERENCE_EXACT;
+  bool baseline = false;
   for (int i = 3; i < argc; i++) {
     if (!strcmp(argv[i], "--max-iters") && i + 1 < argc) max_iters = strtoull(argv[++i], nullptr, 10);
     else if (!strcmp(argv[i], "--max-time") && i + 1 < argc) max_time = atof(argv[++i]);
     else if (!strcmp(argv[i], "--fixed")) mode = ORACLE_FIXED;
+    else if (!strcmp(argv[i], "--baseline")) baseline = true;
   }
   try {
     OracleBackend be(pack, mode);
+    if (baseline) { oracle_set_fast(1); oracle_bvh_build(be.o); }
     MDP::MSIRRT::PlannerConnect<OracleBackend> planner(be, seed);
     if (!planner.valid()) { fprintf(stderr, "planner_oracle: %s\n", planner.error().c_str()); return 1; }
     if (max_iters) planner.set_max_iterations(max_iters);

@@ -205,3 +205,23 @@ def test_logged_trajectories_discriminate(orc, packs, logged_cells, key):
     o = orc.Oracle(packs(scene), orc.FIXED)
     clr = min(o.get_distances(qq, int(f))[1].min() for qq, f in zip(q[::5], frames[::5]))
     assert 0.0 < clr < 0.035, (key, clr)
+
+
+@pytest.mark.parametrize("name", ["flying_boxes", "mass_test", "multiple_robots", "synB_16_100"])
+def test_fast_mode_is_bit_identical(orc, packs, sp, name):
+    """The timed CPU arm (oracle.set_fast: boolean GJK early exits, first-hit cell exit, AABB tree for intervals)
+    must give exactly the bits / intervals / cells of the exact mode."""
+    pk = packs(name)
+    o = orc.Oracle(pk)
+    o.bvh_build()
+    q = random_q(sp, pk, 10, 31).T.astype(np.float64)
+    T = o.n_frames
+    try:
+        orc.set_fast(False)
+        iv = [o.safe_intervals(qq) for qq in q]
+        cells = [[o.check_frame(qq, f) for f in range(0, T, 97)] for qq in q]
+        orc.set_fast(True)
+        assert [o.safe_intervals(qq) for qq in q] == iv
+        assert [[o.check_frame(qq, f) for f in range(0, T, 97)] for qq in q] == cells
+    finally:
+        orc.set_fast(False)

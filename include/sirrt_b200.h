@@ -119,6 +119,18 @@ int sirrt_check_frames_batch_f64(sirrt_scene*, const double* q_aos, const int32_
 int sirrt_edge_check_batch(sirrt_scene*, const double* q0, const double* q1, const double* t0, const double* t1,
                            int64_t n_edges, double vmax, int32_t* first_colliding_step, double* collision_coord);
 
+/* SpaceTimeMotionValidator::checkMotion for n motions (ST-RRT* hook),
+ * STRRT_Planner/src/OMPLValidators/SpaceTimeMotionValidator.cpp:22-74 (variant 0) and :76-127 (variant 1, lastValid),
+ * every state tested as StateValidityCheckerFunctor::isValid does (StateValidityCheckerFunctor.cpp:29-47:
+ * frame = (int)((float)t * fps), CollisionManager.cpp:333).
+ *   q0,q1 : double [n][dof]; t0,t1 : double [n] in SECONDS (the OMPL time component)
+ *   vmax  : robot_joint_max_velocity[0] (:46), <= 0 disables the gate
+ *   result: -1 valid motion, -4 s2 invalid (:25), -2 delta_t <= 0 (:41), -3 speed gate (:46),
+ *           >= 0 index i of the first invalid interpolated state (fraction i/steps, :54-64)
+ *   last_valid_fraction : lastValid.second of the :76-127 form ([n], or NULL) */
+int sirrt_motion_check_batch(sirrt_scene*, const double* q0, const double* q1, const double* t0, const double* t1,
+                             int64_t n, double vmax, int variant, int32_t* result, double* last_valid_fraction);
+
 /* ---- kNN: replaces nanoflann KDTreeSingleIndexDynamicAdaptor<L2_Simple> as used by
  * MSIRRT/src/Tree.cpp:5,18-36 and PlannerConnect.cpp:382-412 (exact, FP64, squared L2) ------- */
 int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn** out);

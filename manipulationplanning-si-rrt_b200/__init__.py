@@ -52,6 +52,7 @@ EXPORTS = {
     "sirrt_check_frames_batch": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "sirrt_check_frames_batch_f64": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "sirrt_edge_check_batch": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _f64, _vp, _vp]),
+    "sirrt_motion_check_batch": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _f64, _i32, _vp, _vp]),
     "sirrt_knn_create": (_i32, [_i32, _i64, _i32, _vp]),
     "sirrt_knn_destroy": (_i32, [_vp]),
     "sirrt_knn_size": (_i32, [_vp, _vp]),
@@ -228,6 +229,20 @@ class Scene:
         _ck(_lib.sirrt_edge_check_batch(self._h, q0.ctypes.data, q1.ctypes.data, t0.ctypes.data, t1.ctypes.data, n, float(vmax),
                                         first.ctypes.data, _ptr(coord)))
         return first, coord
+
+    def motion_check_batch(self, q0, q1, t0, t1, vmax: float, variant: int = 0):
+        """SpaceTimeMotionValidator::checkMotion (SpaceTimeMotionValidator.cpp:22-74 / :76-127), times in seconds."""
+        q0 = np.ascontiguousarray(q0, np.float64).reshape(-1, self.dof)
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.dof)
+        t0 = np.ascontiguousarray(t0, np.float64).reshape(-1)
+        t1 = np.ascontiguousarray(t1, np.float64).reshape(-1)
+        n = q0.shape[0]
+        assert q1.shape[0] == n and t0.size == n and t1.size == n
+        res = np.zeros(n, np.int32)
+        frac = np.zeros(n)
+        _ck(_lib.sirrt_motion_check_batch(self._h, q0.ctypes.data, q1.ctypes.data, t0.ctypes.data, t1.ctypes.data, n, float(vmax),
+                                          int(variant), res.ctypes.data, frac.ctypes.data))
+        return res, frac
 
 
 class KnnIndex:

@@ -465,3 +465,108 @@ extern "C" int sirrt_edge_check_batch(sirrt_scene* s, const double* q0, const do
   CU(cudaStreamSynchronize(st));
   return SIRRT_OK;
 }
+
+// ---- f4: ST-RRT* motion validation (SpaceTimeMotionValidator::checkMotion,
+// STRRT_Planner/src/OMPLValidators/SpaceTimeMotionValidator.cpp:22-74 and :76-127; the state test is
+// StateValidityCheckerFunctor::isValid, StateValidityCheckerFunctor.cpp:29-47 -> CollisionManager.cpp:330-336) ---
+// Cell layout per motion: cell 0 = s2 (tested first, :25 / :82), cells 1..steps = interpolated states i = 0..steps-1
+// at fraction i/steps (:54-57): q = from + (to - from) * f (ompl RealVectorStateSpace::interpolate), time likewise
+// (TimeStateSpace::interpolate), frame = (int)((float)time * fps) in float32 (CollisionManager.cpp:333).
+__global__ void k_motion_cells(const __grid_constant__ EdgeParams P, const float fps) {
+  const long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= P.n_cells) return;
+  long long lo = 0, hi = P.n_edges;
+  while (hi - lo > 1) { const long long mid = (lo + hi) >> 1; if (P.offs[mid] <= c) lo = mid; else hi = mid; }
+  const long long e = lo;
+  const long long k = c - P.offs[e];
+  const double steps = (double)(P.offs[e + 1] - P.offs[e] - 1);
+  double tm;
+  if (k == 0) {
+    for (int i = 0; i < P.dof; i++) P.q_cells[c * P.dof + i] = P.q1[e * P.dof + i];
+    tm = P.t1[e];
+  } else {
+    const double f = __ddiv_rn((double)(k - 1), steps);
+    for (int i = 0; i < P.dof; i++) {
+      const double a = P.q0[e * P.dof + i];
+      P.q_cells[c * P.dof + i] = __dadd_rn(a, __dmul_rn(__dsub_rn(P.q1[e * P.dof + i], a), f));
+    }
+    tm = __dadd_rn(P.t0[e], __dmul_rn(__dsub_rn(P.t1[e], P.t0[e]), f));
+  }
+  const float ff = __fmul_rn((float)tm, fps);
+  P.frames[c] = (ff >= 2147483647.0f || ff <= -2147483648.0f || ff != ff) ? -1 : (int)ff;
+}
+
+extern "C" int sirrt_motion_check_batch(sirrt_scene* s, const double* q0, const double* q1, const double* t0, const double* t1,
+                                        int64_t n, double vmax, int variant, int32_t* result, double* last_valid_fraction) {
+  if (!s || !q0 || !q1 || !t0 || !t1 || !result || n < 0 || (variant != 0 && variant != 1))
+    return fail(SIRRT_E_ARG, "sirrt_motion_check_batch: bad argument");
+  if (n == 0) return SIRRT_OK;
+  if (is_device_ptr(q0) || is_device_ptr(q1) || is_device_ptr(t0) || is_device_ptr(t1) || is_device_ptr(result) ||
+      (last_valid_fraction && is_device_ptr(last_valid_fraction)))
+    return fail(SIRRT_E_ARG, "sirrt_motion_check_batch takes host buffers (step counts are planned on the host)");
+  CU(cudaSetDevice(s->device));
+  memset(s->stats, 0, sizeof s->stats);
+  const int dof = s->hs.dof;
+  const double fps = (double)s->hs.fps;
+  std::vector<long long> offs(n + 1);
+  std::vector<int32_t> gate(n, 0);
+  long long cells = 0;
+  for (int64_t e = 0; e < n; e++) {
+    offs[e] = cells;
+    cells += 1;  // s2
+    const double dt = t1[e] - t0[e];
+    if (dt <= 0) { gate[e] = -2; continue; }  // :41 / :98
+    double n2 = 0;
+    for (int i = 0; i < dof; i++) { const double d = fabs(q1[e * dof + i] - q0[e * dof + i]); n2 += d * d; }
+    const double norm = sqrt(n2);
+    if (vmax > 0 && norm / dt > vmax) { gate[e] = -3; continue; }  // :46 / :103
+    const double x1 = norm / 0.1, x2 = (variant == 0 ? 2.0 : 1.0) * dt * fps + 0.5;  // :51 / :108
+    const long long a = x1 < 2e9 ? (long long)(int)x1 : 2000000000ll, b = x2 < 2e9 ? (long long)(int)x2 : 2000000000ll;
+    cells += std::max(a, b) + 2;
+    if (cells > 0x7fffffffll) return fail(SIRRT_E_ARG, "motion batch expands to more than 2^31-1 cells");
+  }
+  offs[n] = cells;
+  cudaStream_t st = s->stream;
+  const size_t eb = (size_t)n * dof * sizeof(double);
+  size_t need = 2 * eb + 2 * (size_t)n * sizeof(double) + (size_t)(n + 1) * sizeof(long long) + (size_t)n * sizeof(int32_t) + 256;
+  if (s->misc.ensure(need)) return fail(SIRRT_E_CUDA, "cudaMalloc(motions) failed");
+  char* p = (char*)s->misc.p;
+  double* d_q0 = (double*)p; p += eb;
+  double* d_q1 = (double*)p; p += eb;
+  double* d_t0 = (double*)p; p += n * sizeof(double);
+  double* d_t1 = (double*)p; p += n * sizeof(double);
+  long long* d_offs = (long long*)p; p += (n + 1) * sizeof(long long);
+  int32_t* d_first = (int32_t*)p;
+  if (s->misc2.ensure((size_t)cells * dof * sizeof(double))) return fail(SIRRT_E_CUDA, "cudaMalloc(motion cells) failed");
+  if (s->frames.ensure((size_t)cells * sizeof(int32_t))) return fail(SIRRT_E_CUDA, "cudaMalloc(motion frames) failed");
+  if (s->cells.ensure((size_t)cells)) return fail(SIRRT_E_CUDA, "cudaMalloc(cells) failed");
+  CU(cudaMemcpyAsync(d_q0, q0, eb, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_q1, q1, eb, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_t0, t0, n * sizeof(double), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_t1, t1, n * sizeof(double), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(d_offs, offs.data(), (n + 1) * sizeof(long long), cudaMemcpyHostToDevice, st));
+  EdgeParams E{d_q0, d_q1, d_t0, d_t1, d_offs, n, cells, dof, s->misc2.as<double>(), s->frames.as<int32_t>()};
+  k_motion_cells<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(E, (float)s->hs.fps);
+  QView qv{nullptr, s->misc2.as<double>(), cells, 0, cells, dof};
+  int rc = run_cells(s, qv, cells, s->frames.as<int32_t>(), s->cells.as<uint8_t>(), SIRRT_SEM_FRAME);
+  if (rc) return rc;
+  EdgeFirstParams F{d_offs, s->cells.as<uint8_t>(), s->misc2.as<double>(), n, dof, d_first, nullptr};
+  k_edge_first<<<(unsigned)((n + 7) / 8), 256, 0, st>>>(F);
+  s->stats[0] += 2;
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(result, d_first, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (int64_t e = 0; e < n; e++) {
+    const int32_t raw = result[e];  // index of the first colliding cell of this motion, -1 = none
+    const long long steps = offs[e + 1] - offs[e] - 1;
+    double frac = 0.0;  // lastValid.second (:79, :121)
+    int32_t r;
+    if (raw == 0) r = -4;                 // s2 invalid (:25 / :82)
+    else if (gate[e]) r = gate[e];
+    else if (raw < 0) { r = -1; frac = (double)(steps - 1) / (double)steps; }
+    else { r = raw - 1; if (r >= 1) frac = (double)(r - 1) / (double)steps; }
+    result[e] = r;
+    if (last_valid_fraction) last_valid_fraction[e] = frac;
+  }
+  return SIRRT_OK;
+}

@@ -48,6 +48,10 @@ def lib():
         L.oracle_pair_distance.restype = f64
         L.oracle_pair_distance.argtypes = [vp, vp, i32, i32, i32]
         L.oracle_edge_check.argtypes = [vp, vp, vp, f64, f64, f64, vp]
+        L.oracle_state_valid.argtypes = [vp, vp, f64]
+        L.oracle_state_valid.restype = i32
+        L.oracle_motion_check.argtypes = [vp, vp, vp, f64, f64, f64, i32, vp]
+        L.oracle_motion_check.restype = i32
         L.oracle_get_distances.argtypes = [vp, vp, i32, vp]
         L.oracle_bvh_build.argtypes = [vp]
         L.oracle_set_fast.argtypes = [i32]
@@ -147,6 +151,16 @@ class Oracle:
         cc = np.zeros(self.dof)
         s = lib().oracle_edge_check(self.h, _p(q0), _p(q1), float(t0), float(t1), float(vmax), _p(cc))
         return s, cc
+
+    def state_valid(self, q, time_s) -> bool:
+        q = _d(q)
+        return bool(lib().oracle_state_valid(self.h, _p(q), float(time_s)))
+
+    def motion_check(self, q0, q1, t0, t1, vmax, variant=0):
+        q0, q1 = _d(q0), _d(q1)
+        frac = np.zeros(1)
+        r = lib().oracle_motion_check(self.h, _p(q0), _p(q1), float(t0), float(t1), float(vmax), int(variant), _p(frac))
+        return r, float(frac[0])
 
     def get_distances(self, q, frame):
         q = _d(q)

@@ -915,6 +915,43 @@ int oracle_edge_check(const Oracle* o, const double* q0, const double* q1, doubl
   return -1;
 }
 
+/* f4 -- StateValidityCheckerFunctor::isValid, STRRT_Planner/src/OMPLValidators/StateValidityCheckerFunctor.cpp:29-47:
+ * float t = state time; CollisionManager::check_collision (CollisionManager.cpp:330-336): frame = (int)(t * fps) in float32 */
+int oracle_state_valid(const Oracle* o, const double* q, double time_s) {
+  float t = (float)time_s;
+  volatile float ff = t * (float)o->fps;
+  int frame = (ff >= 2147483647.0f || ff <= -2147483648.0f || ff != ff) ? -1 : (int)ff;
+  return !oracle_check_frame(o, q, frame);
+}
+
+/* f4 -- SpaceTimeMotionValidator::checkMotion, SpaceTimeMotionValidator.cpp:22-74 (variant 0: 2*delta_t*fps, :51)
+ * and :76-127 (variant 1: delta_t*fps, :108; reports lastValid.second).  Times in seconds.
+ * returns -1 valid, -4 s2 invalid (:25/:82), -2 delta_t <= 0 (:41/:98), -3 speed gate (:46/:103),
+ * >= 0 index of the first invalid interpolated state (:54-64 / :111-123). */
+int oracle_motion_check(const Oracle* o, const double* q0, const double* q1, double t0, double t1, double vmax,
+                        int variant, double* last_valid_fraction) {
+  int dof = o->dof;
+  if (last_valid_fraction) *last_valid_fraction = 0.0; /* :79 */
+  if (!oracle_state_valid(o, q1, t1)) return -4;
+  double n2 = 0;
+  for (int i = 0; i < dof; i++) { double d = fabs(q1[i] - q0[i]); n2 += d * d; }
+  double dt = t1 - t0;
+  if (dt <= 0) return -2;
+  double norm = sqrt(n2);
+  if (vmax > 0 && norm / dt > vmax) return -3;
+  int a = (int)(norm / 0.1), b = (int)((variant == 0 ? 2.0 : 1.0) * dt * (double)o->fps + 0.5);
+  int steps = (a > b ? a : b) + 2;
+  for (int i = 0; i < steps; i++) {
+    double f = (double)i / (double)steps, q[64];
+    for (int k = 0; k < dof; k++) { volatile double m = (q1[k] - q0[k]) * f; q[k] = q0[k] + m; } /* RealVectorStateSpace::interpolate */
+    volatile double mt = (t1 - t0) * f;
+    double tm = t0 + mt;                                                                   /* TimeStateSpace::interpolate */
+    if (!oracle_state_valid(o, q, tm)) return i;
+    if (last_valid_fraction) *last_valid_fraction = f; /* :121 */
+  }
+  return -1;
+}
+
 /* a9 -- CollisionManager::get_distances_private + DistanceCallback, CollisionManager.cpp:387-420,549-600 */
 int oracle_get_distances(const Oracle* o, const double* q, int frame, double* min_dist) {
   WLink L[64];

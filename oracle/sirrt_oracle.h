@@ -52,6 +52,11 @@ double oracle_pair_distance(const Oracle*, const double* q, int link, int obstac
  * -2 start_time>=end_time, -3 speed gate; collision_coord (may be NULL) gets q at that step */
 int oracle_edge_check(const Oracle*, const double* q0, const double* q1, double t0, double t1, double vmax,
                       double* collision_coord);
+/* f4: StateValidityCheckerFunctor::isValid (time in seconds, float32 frame arithmetic) and
+ * SpaceTimeMotionValidator::checkMotion (variant 0 = two-argument form, 1 = lastValid form) */
+int oracle_state_valid(const Oracle*, const double* q, double time_s);
+int oracle_motion_check(const Oracle*, const double* q0, const double* q1, double t0, double t1, double vmax,
+                        int variant, double* last_valid_fraction);
 /* a9: get_distances: per planned-robot link the minimum distance over box/sphere obstacles at a
  * frame (robot obstacles are "not implemented" in the reference, CollisionManager.cpp:418).
  * returns 1 if a collision was hit (reference early-exits), else 0 */

@@ -281,3 +281,97 @@ def test_knn_single_query_latency_path(pkg, orc):
     assert cnt == 3000 and np.array_equal(got, np.arange(3000))
     got, cnt = idx2.radius(np.zeros(6), 0.5)
     assert np.array_equal(got, orc.knn_radius(big, np.zeros(6), 0.5))
+
+
+def _random_motions(sp, pk, n, seed, fps_frames):
+    rng = np.random.default_rng(seed)
+    q0 = random_q(sp, pk, n, seed + 1).T.astype(np.float64)
+    q1 = q0 + rng.normal(0, 0.25, q0.shape)
+    horizon = fps_frames[1] / fps_frames[0]
+    t0 = rng.uniform(0, 0.8 * horizon, n)
+    t1 = t0 + rng.uniform(-0.2, 1.5, n)
+    return q0, q1, t0, t1
+
+
+@pytest.mark.parametrize("name", ["synA_32_200", "synB_32_200", "flying_boxes", "mass_test"])
+@pytest.mark.parametrize("variant", [0, 1])
+def test_motion_check_batch_matches_oracle(pkg, orc, sp, packs, name, variant):
+    """f4: SpaceTimeMotionValidator::checkMotion (both overloads) for a batch of motions in one call vs the oracle's
+    restatement of SpaceTimeMotionValidator.cpp:22-127: result code and lastValid fraction identical."""
+    pk = packs(name)
+    sc = sp.read_pack(pk)
+    dev, ref = pkg.Scene(pk), orc.Oracle(pk)
+    n = 160 if name.startswith("syn") else 48
+    q0, q1, t0, t1 = _random_motions(sp, pk, n, 91, (sc.fps, sc.n_frames))
+    res, frac = dev.motion_check_batch(q0, q1, t0, t1, 3.1415, variant)
+    kinds = set()
+    for e in range(n):
+        r, f = ref.motion_check(q0[e], q1[e], t0[e], t1[e], 3.1415, variant)
+        assert res[e] == r and frac[e] == f, (name, variant, e, res[e], r, frac[e], f)
+        kinds.add(min(r, 0) if r < 0 else 1)
+    assert {-3, -2, -1} <= kinds, kinds
+    # empty batch
+    r0, f0 = dev.motion_check_batch(np.zeros((0, dev.dof)), np.zeros((0, dev.dof)), [], [], 3.1415, variant)
+    assert r0.size == 0 and f0.size == 0
+
+
+def test_reference_strrt_solutions_valid_on_gpu(pkg, packs, sp):
+    """The ST-RRT* solutions the reference logged are valid motions through the C ABI as well."""
+    import gzip, json, os
+    from conftest import GOLDEN
+    with gzip.open(os.path.join(GOLDEN, "reference_logged_paths.json.gz"), "rb") as f:
+        logs = json.load(f)
+    for key in ("strrt_mass_test", "strrt_flying_boxes", "strrt_multiple_robots"):
+        ent = logs[key]
+        pk = packs(ent["scene"])
+        sc = sp.read_pack(pk)
+        dev = pkg.Scene(pk, 0, pkg.PARITY_FIXED if ent["scene"] == "multiple_robots" else pkg.PARITY_REFERENCE_EXACT)
+        t, q = np.asarray(ent["t"], np.float64), np.asarray(ent["q"], np.float64)
+        keep = t[1:] <= (sc.n_frames - 1) / sc.fps
+        for variant in (0, 1):
+            res, frac = dev.motion_check_batch(q[:-1][keep], q[1:][keep], t[:-1][keep], t[1:][keep], sc.joint_max_velocity[0], variant)
+            assert keep.sum() >= 2 and (res == -1).all() and ((frac > 0) & (frac < 1)).all(), (key, variant, res, frac)
+
+
+def test_validator_classes_program(pkg, orc, sp, packs, tmp_path):
+    """host/OMPLValidators.hpp (MDP::StateValidityCheckerFunctor, MDP::SpaceTimeMotionValidator) driven by
+    host/sirrt_validators: single checkMotion calls, the batched form, isValid, clearance and the counters."""
+    import os, subprocess
+    exe = os.path.join(os.path.dirname(pkg.__file__), "host", "sirrt_validators")
+    assert os.path.exists(exe), "host/sirrt_validators not built (python __graft_entry__.py)"
+    pk = packs("synB_32_200")
+    sc = sp.read_pack(pk)
+    ref = orc.Oracle(pk)
+    n = 60
+    q0, q1, t0, t1 = _random_motions(sp, pk, n, 97, (sc.fps, sc.n_frames))
+    (tmp_path / "s.pack").write_bytes(pk)
+    with open(tmp_path / "m.txt", "w") as f:
+        for e in range(n):
+            f.write(" ".join(repr(float(x)) for x in [*q0[e], t0[e], *q1[e], t1[e]]) + "\n")
+    out = subprocess.run([exe, str(tmp_path / "s.pack"), str(tmp_path / "m.txt")], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    lines = out.stdout.strip().splitlines()
+    assert len(lines) == n + 2
+    vmax = sc.joint_max_velocity[0]
+    codes = [int(x) for x in lines[n].split()[1:]]
+    tested = n
+
+    def n_tested(r, e, k):
+        if r >= 0:
+            return r + 2
+        if r != -1:
+            return 1
+        dq = float(np.sqrt(((q1[e] - q0[e]) ** 2).sum()))
+        return max(int(dq / 0.1), int(k * (t1[e] - t0[e]) * sc.fps + 0.5)) + 3
+
+    for e in range(n):
+        v0, v1, frac, s2ok, clr = lines[e].split()
+        r0, _ = ref.motion_check(q0[e], q1[e], t0[e], t1[e], vmax, 0)
+        r1, f1 = ref.motion_check(q0[e], q1[e], t0[e], t1[e], vmax, 1)
+        tested += 2 * n_tested(r0, e, 2.0) + n_tested(r1, e, 1.0)
+        assert int(v0) == (r0 == -1) and int(v1) == (r1 == -1) and float(frac) == f1 and codes[e] == r0
+        assert int(s2ok) == ref.state_valid(q1[e], t1[e])
+        fr = int(np.float32(np.float32(t0[e]) * np.float32(sc.fps)))
+        col, d = ref.get_distances(q0[e], fr)
+        assert abs(float(clr) - (0.0 if col else float(np.float32(d.min())))) < 1e-6
+    assert lines[n + 1].split() == ["counters", str(tested), str(3 * n)]

@@ -225,3 +225,56 @@ def test_fast_mode_is_bit_identical(orc, packs, sp, name):
         assert [[o.check_frame(qq, f) for f in range(0, T, 97)] for qq in q] == cells
     finally:
         orc.set_fast(False)
+
+
+@pytest.mark.parametrize("key", ["strrt_mass_test", "strrt_flying_boxes", "strrt_multiple_robots"])
+def test_reference_strrt_solutions_are_valid_motions(orc, packs, sp, key):
+    """REFERENCE OUTPUTS pin the restated SpaceTimeMotionValidator::checkMotion (f4): every edge of a solution the
+    reference's ST-RRT* logged passed its own checkMotion (s2 valid, delta_t > 0, speed gate, all interpolated
+    states valid), so the oracle must answer -1 for it in both forms."""
+    import gzip, json, os
+    from conftest import GOLDEN
+    with gzip.open(os.path.join(GOLDEN, "reference_logged_paths.json.gz"), "rb") as f:
+        ent = json.load(f)[key]
+    pk = packs(ent["scene"])
+    sc = sp.read_pack(pk)
+    o = orc.Oracle(pk, orc.FIXED if ent["scene"] == "multiple_robots" else orc.REFERENCE_EXACT)
+    t, q = np.asarray(ent["t"], np.float64), np.asarray(ent["q"], np.float64)
+    last = (sc.n_frames - 1) / sc.fps
+    n = 0
+    for a in range(len(t) - 1):
+        if t[a + 1] > last:   # a goal time past the last frame indexes out of range in the reference (unchecked, :333)
+            continue
+        for variant in (0, 1):
+            r, frac = o.motion_check(q[a], q[a + 1], t[a], t[a + 1], sc.joint_max_velocity[0], variant)
+            assert r == -1 and 0.0 < frac < 1.0, (key, a, variant, r, frac)
+        n += 1
+    assert n >= 2
+
+
+def test_motion_check_codes(orc, packs, sp):
+    """Order of the gates in checkMotion: s2 validity first (:25), then delta_t (:41), the speed gate (:46), then
+    the interpolated states; lastValid fraction is the last accepted i/steps (:121)."""
+    pk = packs("synA_32_200")
+    o = orc.Oracle(pk)
+    sc = sp.read_pack(pk)
+    q = random_q(sp, pk, 400, 71).T.astype(np.float64)
+    rng = np.random.default_rng(72)
+    seen = set()
+    for e in range(0, 400, 2):
+        t0 = rng.uniform(0, 5.0)
+        t1 = t0 + rng.uniform(-0.2, 1.5)
+        q1 = q[e] + rng.normal(0, 0.25, q[e].shape)
+        r, frac = o.motion_check(q[e], q1, t0, t1, 3.1415, 1)
+        seen.add(min(r, 0) if r < 0 else 1)
+        if r == -4:
+            assert not o.state_valid(q1, t1) and frac == 0.0
+        else:
+            assert o.state_valid(q1, t1)
+        if r >= 0:
+            dq = np.sqrt(((q1 - q[e]) ** 2).sum())
+            steps = max(int(dq / 0.1), int((t1 - t0) * sc.fps + 0.5)) + 2
+            f = r / steps
+            assert not o.state_valid(q[e] + (q1 - q[e]) * f, t0 + (t1 - t0) * f)
+            assert frac == (0.0 if r == 0 else (r - 1) / steps)
+    assert seen == {-4, -3, -2, -1, 1}, seen

@@ -144,6 +144,15 @@ int sirrt_knn_radius(sirrt_knn*, const double* query, double r2, int64_t* idx, i
 /* k nearest of each query, ascending distance (ties by index); idx/dist2 [nq][k] */
 int sirrt_knn_topk(sirrt_knn*, const double* queries, int64_t nq, int k, int64_t* idx, double* dist2);
 
+/* one tree grown across n_shards GPUs (one process per GPU): shard g stores the points whose global index is
+ * g (mod n_shards) at local index global / n_shards.  After each rank searched its shard (sirrt_knn_topk / _nearest
+ * into device buffers) and the lists were all-gathered over NCCL, this merges them on the device:
+ *   cand_d2 [n_shards][nq][k] ascending per list, cand_idx [n_shards][nq][k] LOCAL indices (-1 = no candidate)
+ *   out_idx / out_d2 [nq][k]: GLOBAL indices ascending by (dist2, index); asynchronous on cuda_stream */
+#define SIRRT_KNN_MAX_SHARDS 64
+int sirrt_knn_merge_shards(int device, void* cuda_stream, const double* cand_d2, const int64_t* cand_idx, int n_shards, int64_t nq,
+                           int k, int64_t* out_idx, double* out_d2);
+
 /* ---- multi-GPU inside one process: shards a configuration batch over several devices ------ */
 int sirrt_multi_create(const void* pack, size_t bytes, const int* devices, int n_dev, int parity_mode, sirrt_multi** out);
 void sirrt_multi_destroy(sirrt_multi*);

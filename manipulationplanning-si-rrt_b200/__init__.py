@@ -52,6 +52,7 @@ EXPORTS = {
     "sirrt_check_frames_batch": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "sirrt_check_frames_batch_f64": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "sirrt_edge_check_batch": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _f64, _vp, _vp]),
+    "sirrt_knn_merge_shards": (_i32, [_i32, _vp, _vp, _vp, _i32, _i64, _i32, _vp, _vp]),
     "sirrt_motion_check_batch": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _f64, _i32, _vp, _vp]),
     "sirrt_knn_create": (_i32, [_i32, _i64, _i32, _vp]),
     "sirrt_knn_destroy": (_i32, [_vp]),

@@ -204,9 +204,51 @@ extern "C" int sirrt_knn_topk(sirrt_knn* k, const double* queries, int64_t nq, i
   KnnStore S{k->pts, k->cap, k->n, k->dim};
   k_knn_topk<<<(unsigned)nq, SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, kk, k->out_i.as<long long>(), k->out_d.as<double>());
   CU(cudaGetLastError());
-  CU(cudaMemcpyAsync(idx, k->out_i.p, sizeof(long long) * nq * kk, cudaMemcpyDeviceToHost, k->stream));
-  if (dist2) CU(cudaMemcpyAsync(dist2, k->out_d.p, sizeof(double) * nq * kk, cudaMemcpyDeviceToHost, k->stream));
+  CU(cudaMemcpyAsync(idx, k->out_i.p, sizeof(long long) * nq * kk, cudaMemcpyDefault, k->stream));  // host or device result buffers
+  if (dist2) CU(cudaMemcpyAsync(dist2, k->out_d.p, sizeof(double) * nq * kk, cudaMemcpyDefault, k->stream));
   CU(cudaStreamSynchronize(k->stream));
+  return SIRRT_OK;
+}
+
+// ---- (e) one tree grown across G GPUs: merge of the all-gathered per-shard candidates -----------------------------
+// Shard g keeps the points whose global (insertion-order, Tree.cpp:18-36) index is g (mod G) at local index
+// global / G.  After every rank has searched its shard and the candidate lists were all-gathered (NCCL), each rank
+// merges them: ascending (dist2, global index) -- the lowest index wins ties, as the single-GPU store does.
+__global__ void k_knn_merge_shards(const double* __restrict__ cd, const long long* __restrict__ ci, int G, long long nq, int k,
+                                   long long* __restrict__ out_i, double* __restrict__ out_d) {
+  const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  unsigned short head[SIRRT_KNN_MAX_SHARDS];
+  for (int g = 0; g < G; g++) head[g] = 0;
+  for (int j = 0; j < k; j++) {
+    double bd = 1.0 / 0.0;
+    long long bi = -1;
+    int bg = -1;
+    for (int g = 0; g < G; g++) {
+      if (head[g] >= k) continue;
+      const size_t at = ((size_t)g * nq + q) * k + head[g];
+      const long long li = ci[at];
+      if (li < 0) { head[g] = (unsigned short)k; continue; }  // this shard has no further candidate
+      const double d = cd[at];
+      const long long gi = li * G + g;
+      if (bg < 0 || d < bd || (d == bd && gi < bi)) { bd = d; bi = gi; bg = g; }
+    }
+    out_i[q * k + j] = bi;
+    if (out_d) out_d[q * k + j] = bd;
+    if (bg >= 0) head[bg]++;
+  }
+}
+extern "C" int sirrt_knn_merge_shards(int device, void* cuda_stream, const double* cand_d2, const int64_t* cand_idx, int n_shards, int64_t nq,
+                                      int k, int64_t* out_idx, double* out_d2) {
+  if (!cand_d2 || !cand_idx || !out_idx || n_shards < 1 || n_shards > SIRRT_KNN_MAX_SHARDS || nq < 0 || k < 1 || k > 1024)
+    return fail(SIRRT_E_ARG, "sirrt_knn_merge_shards: bad argument");
+  if (nq == 0) return SIRRT_OK;
+  if (!is_device_ptr(cand_d2) || !is_device_ptr(cand_idx) || !is_device_ptr(out_idx) || (out_d2 && !is_device_ptr(out_d2)))
+    return fail(SIRRT_E_ARG, "sirrt_knn_merge_shards takes device buffers (the gathered candidates live where NCCL left them)");
+  CU(cudaSetDevice(device));
+  k_knn_merge_shards<<<(unsigned)((nq + 127) / 128), 128, 0, (cudaStream_t)cuda_stream>>>(cand_d2, (const long long*)cand_idx, n_shards, nq, k,
+                                                                                         (long long*)out_idx, out_d2);
+  CU(cudaGetLastError());
   return SIRRT_OK;
 }
 

@@ -2,9 +2,12 @@
 // MSIRRT_Planner process per (scene, seed) in a ProcessPoolExecutor) on one B200: ONE process and CUDA context per GPU,
 // `threads` host planner threads sharing the device through their own scenes / streams.  Tasks are independent, so a
 // box shards them across GPUs by launching one of these per device (scripts/mass_test.py); no inter-GPU traffic.
-//   sirrt_mass <tasks.txt> <device> <threads> [--max-time s] [--max-iters n] [--fixed]
+//   sirrt_mass <tasks.txt> <device> <threads> [--max-time s] [--max-iters n] [--fixed] [--queue counter.bin]
 // tasks.txt: one "<scene.pack> <seed>" per line.  Output: one JSON line per task (task index = line number), then a
-// summary line.  Scenes are created once per (thread, pack) and reused by that thread's seeds of the same pack.
+// summary line.  A scene (pack) is the unit of work: a thread claims the next unclaimed pack from a counter, builds the
+// scene once and runs all seeds of that pack on it.  With --queue the counter lives in a shared file (8 bytes, mmap'ed,
+// atomic fetch-add), so the per-GPU processes of one box, all given the SAME task list, drain one queue: a GPU whose
+// tasks finish early takes the next scene instead of idling (the list is ordered heaviest first by the driver).
 #include <atomic>
 #include <chrono>
 #include <cstdio>
@@ -14,6 +17,10 @@
 #include <mutex>
 #include <sstream>
 #include <thread>
+
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <unistd.h>
 
 #include "B200Backend.hpp"
 #include "SIRRTPlanner.hpp"
@@ -32,10 +39,20 @@ int main(int argc, char** argv) {
   double max_time = -1;
   uint64_t max_iters = 0;
   int parity = SIRRT_PARITY_REFERENCE_EXACT;
+  const char* queue_path = nullptr;
   for (int i = 4; i < argc; i++) {
     if (!strcmp(argv[i], "--max-time") && i + 1 < argc) max_time = atof(argv[++i]);
     else if (!strcmp(argv[i], "--max-iters") && i + 1 < argc) max_iters = strtoull(argv[++i], nullptr, 10);
     else if (!strcmp(argv[i], "--fixed")) parity = SIRRT_PARITY_FIXED;
+    else if (!strcmp(argv[i], "--queue") && i + 1 < argc) queue_path = argv[++i];
+  }
+  static unsigned long long local_counter = 0;
+  unsigned long long* counter = &local_counter;
+  if (queue_path) {
+    const int fd = open(queue_path, O_RDWR);
+    void* m = fd >= 0 ? mmap(nullptr, 8, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0) : MAP_FAILED;
+    if (m == MAP_FAILED) { fprintf(stderr, "sirrt_mass: cannot map queue counter %s\n", queue_path); return 2; }
+    counter = (unsigned long long*)m;
   }
   std::vector<Task> tasks;
   {
@@ -48,7 +65,7 @@ int main(int argc, char** argv) {
       if (is >> t.pack >> t.seed) { t.index = (int)tasks.size(); tasks.push_back(t); }
     }
   }
-  // packs in order of first appearance; thread t owns packs t, t + n_threads, ...
+  // packs in order of first appearance; threads (of every process on the queue) claim them one at a time
   std::vector<std::string> packs;
   std::map<std::string, std::vector<int>> by_pack;
   for (const Task& t : tasks) {
@@ -57,11 +74,14 @@ int main(int argc, char** argv) {
   }
   using clk = std::chrono::steady_clock;
   std::mutex out_mu;
-  std::atomic<int> n_solved{0}, n_failed{0};
+  std::atomic<int> n_solved{0}, n_failed{0}, n_done{0};
   std::atomic<uint64_t> solve_ns_total{0};
   const auto t0 = clk::now();
   auto worker = [&](int tid) {
-    for (size_t p = tid; p < packs.size(); p += n_threads) {
+    (void)tid;
+    for (;;) {
+      const size_t p = (size_t)__atomic_fetch_add(counter, 1ull, __ATOMIC_RELAXED);
+      if (p >= packs.size()) break;
       try {
         MDP::CollisionManager cm = MDP::CollisionManager::from_pack_file(packs[p], device, parity);
         for (int ti : by_pack[packs[p]]) {
@@ -84,6 +104,7 @@ int main(int argc, char** argv) {
             n_solved++;
           }
           solve_ns_total += ns;
+          n_done++;
           const MDP::MSIRRT::PlannerStats& st = planner.stats();
           std::lock_guard<std::mutex> lk(out_mu);
           printf("{\"task\": %d, \"pack\": \"%s\", \"seed\": %d, \"solved\": %s, \"solve_ms\": %.4f, \"cost\": %.17g, \"waypoints\": %zu, "
@@ -103,6 +124,6 @@ int main(int argc, char** argv) {
   for (auto& x : th) x.join();
   const double wall = std::chrono::duration<double>(clk::now() - t0).count();
   printf("{\"summary\": true, \"device\": %d, \"threads\": %d, \"tasks\": %zu, \"solved\": %d, \"failed\": %d, \"wall_s\": %.4f, \"sum_solve_s\": %.4f}\n",
-         device, n_threads, tasks.size(), n_solved.load(), n_failed.load(), wall, solve_ns_total.load() / 1e9);
+         device, n_threads, (size_t)n_done.load(), n_solved.load(), n_failed.load(), wall, solve_ns_total.load() / 1e9);
   return n_failed.load() ? 1 : 0;
 }

@@ -62,24 +62,26 @@ def make_tasks(sp, pkg, n_tasks, pairs_per_scene, seeds_per_pair, tmp, frames=60
 
 def run_gpu_arm(tasks, gpus, threads, max_time, tmp):
     exe = os.path.join(ROOT, "manipulationplanning-si-rrt_b200", "host", "sirrt_mass")
-    # whole scenes to one GPU (the runner reuses a scene across the seeds of a pair)
-    packs = []
-    for p, _, _ in tasks:
-        if p not in packs:
-            packs.append(p)
-    owner = {p: i % gpus for i, p in enumerate(packs)}
-    procs, files = [], []
+    # ONE task list for every per-GPU process, scenes ordered heaviest (most cubes) first; the processes drain it through a
+    # shared counter (--queue), a scene at a time, so no GPU idles while another still has scenes queued
+    order = sorted(range(len(tasks)), key=lambda i: (-tasks[i][2], tasks[i][0], i))
+    lst, queue = os.path.join(tmp, "tasks_all.txt"), os.path.join(tmp, "queue.bin")
+    with open(lst, "w") as f:
+        for i in order:
+            f.write(f"{tasks[i][0]} {tasks[i][1]}\n")
+    with open(queue, "wb") as f:
+        f.write(b"\0" * 8)
     t0 = time.perf_counter()
-    for d in range(gpus):
-        lst = os.path.join(tmp, f"tasks_gpu{d}.txt")
-        idx = [i for i, t in enumerate(tasks) if owner[t[0]] == d]
-        with open(lst, "w") as f:
-            for i in idx:
-                f.write(f"{tasks[i][0]} {tasks[i][1]}\n")
-        files.append(idx)
-        procs.append(subprocess.Popen([exe, lst, str(d), str(threads), "--max-time", str(max_time)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
-    outs = [p.communicate() for p in procs]
+    logs = [(open(os.path.join(tmp, f"gpu{d}.out"), "w+"), open(os.path.join(tmp, f"gpu{d}.err"), "w+")) for d in range(gpus)]
+    procs = [subprocess.Popen([exe, lst, str(d), str(threads), "--max-time", str(max_time), "--queue", queue], stdout=logs[d][0], stderr=logs[d][1])
+             for d in range(gpus)]
+    for p in procs:
+        p.wait()
     wall = time.perf_counter() - t0
+    outs = []
+    for o, e in logs:
+        o.seek(0); e.seek(0)
+        outs.append((o.read(), e.read()))
     rows, summaries = {}, []
     for d, (so, se) in enumerate(outs):
         if procs[d].returncode != 0:
@@ -89,7 +91,8 @@ def run_gpu_arm(tasks, gpus, threads, max_time, tmp):
             if r.get("summary"):
                 summaries.append(r)
             else:
-                rows[files[d][r["task"]]] = r
+                r["device"] = d
+                rows[order[r["task"]]] = r
     return wall, rows, summaries
 
 
@@ -113,10 +116,12 @@ def main():
     ap.add_argument("--tasks", type=int, default=1024)
     ap.add_argument("--pairs-per-scene", type=int, default=8)
     ap.add_argument("--seeds-per-pair", type=int, default=8)
-    ap.add_argument("--threads", type=int, default=16, help="planner threads per GPU process")
+    ap.add_argument("--threads", type=int, default=0, help="planner threads per GPU process (0 = host cores / GPUs, clamped to [4, 32])")
     ap.add_argument("--cpu-sample", type=int, default=128)
     ap.add_argument("--max-time", type=float, default=5.0)
     a = ap.parse_args()
+    if a.threads <= 0:
+        a.threads = max(4, min(32, (os.cpu_count() or 16) // a.gpus))
     g.load_build().build_lib(); g.load_build().build_host()
     sp, pkg = g.load_tools(), g.load_package()
     import importlib.util

@@ -75,6 +75,7 @@ enum {
   SIRRT_OPT_CHUNK_CONFIGS = 1,  /* configurations per launch of the batched path (default 262144) */
   SIRRT_OPT_WORKLIST_CAP = 2,   /* capacity of the FP64 re-check work list, entries (default 4194304) */
   SIRRT_OPT_SWEEP_MIN_CONFIGS = 3, /* batches smaller than this use the generic kernel, which splits rows over warps (default 8192) */
+  SIRRT_OPT_HULL_CELLS = 5,     /* 1 (default): GJK support queries on hulls scan the direction cell's candidate vertices; 0: every vertex (same result) */
   SIRRT_OPT_DEFER_MAX_CONFIGS = 4  /* hull scenes: batches up to this many configurations hand their GJK pair tests to a machine-wide task kernel (default 4096; 0 = never) */
 };
 int sirrt_scene_set_option(sirrt_scene*, int key, long long value);

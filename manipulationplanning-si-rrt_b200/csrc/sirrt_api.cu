@@ -61,6 +61,7 @@ struct sirrt_scene {
   DScene d{};
   const float* d_aabb_f = nullptr;
   const double* d_aabb_d = nullptr;
+  const unsigned int* d_hull_cells = nullptr;  // kept while SIRRT_OPT_HULL_CELLS = 0 hides it from the kernels
   SweepTables sweep{};
   std::vector<void*> owned;  // device allocations of the scene tables
   double band = 0;
@@ -69,7 +70,7 @@ struct sirrt_scene {
   int use_sweep = 1;
   long long sweep_min_configs = 8192;
   long long defer_max_configs = 4096;  // hull scenes: batches up to this size hand their GJK runs to k_gjk_tasks
-  DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2;
+  DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2, xf;
   // Latency path (planner in the loop): one pinned host block that the GPU reads and writes in place
   // (cudaMallocHost memory is device-addressable under UVA).  Small host inputs are memcpy'd into it and read
   // by the kernels over the bus; small results are written into it by the kernels and memcpy'd out after the
@@ -127,7 +128,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
 #define UP(field, vec) if ((rc = upload(s, vec, &field))) return bail(rc)
   UP(d.shapes, tb.shapes); UP(d.slots, tb.slots); UP(d.static_slots, tb.static_slots); UP(d.dynamic_slots, tb.dynamic_slots);
   UP(d.pose_f, tb.pose_f); UP(d.bcw_f, tb.bcw_f); UP(d.tight_f, tb.tight_f); UP(d.pose_d, tb.pose_d); UP(d.tile_bounds, tb.tile_bounds);
-  UP(d.verts_f, tb.verts_f); UP(d.verts_d, tb.verts_d); UP(s->d_aabb_f, tb.aabb_f); UP(s->d_aabb_d, tb.aabb_d);
+  UP(d.verts_f, tb.verts_f); UP(d.verts_d, tb.verts_d); UP(d.hull_cells, tb.hull_cells); UP(d.hull_cand, tb.hull_cand); UP(s->d_aabb_f, tb.aabb_f); UP(s->d_aabb_d, tb.aabb_d);
 #undef UP
   // FP32 uncertainty band: the fast path decides a pair only when |signed distance| exceeds it;
   // everything inside is re-evaluated in FP64 (k_recheck).  Scales with the coordinate magnitudes
@@ -150,7 +151,7 @@ extern "C" void sirrt_scene_destroy(sirrt_scene* s) {
   cudaSetDevice(s->device);
   if (s->own_stream) { cudaStreamSynchronize(s->own_stream); }
   for (void* p : s->owned) cudaFree(p);
-  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->tasks, &s->counts, &s->misc, &s->misc2}) b->release();
+  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->tasks, &s->counts, &s->misc, &s->misc2, &s->xf}) b->release();
   if (s->pinned) cudaFreeHost(s->pinned);
   if (s->lazy_cnt) cudaFree(s->lazy_cnt);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
@@ -190,6 +191,11 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
   if (!s) return fail(SIRRT_E_ARG, "null scene");
   switch (key) {
     case SIRRT_OPT_USE_SWEEP: s->use_sweep = value != 0; break;
+    case SIRRT_OPT_HULL_CELLS:
+      if (value != 0 && !s->d_hull_cells) s->d_hull_cells = s->d.hull_cells;
+      if (value == 0 && s->d.hull_cells) { s->d_hull_cells = s->d.hull_cells; s->d.hull_cells = nullptr; }
+      else if (value != 0) s->d.hull_cells = s->d_hull_cells;
+      break;
     case SIRRT_OPT_CHUNK_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad chunk"); s->chunk_configs = value; break;
     case SIRRT_OPT_SWEEP_MIN_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad threshold"); s->sweep_min_configs = value; break;
     case SIRRT_OPT_DEFER_MAX_CONFIGS: if (value < 0) return fail(SIRRT_E_ARG, "bad threshold"); s->defer_max_configs = value; break;

@@ -45,7 +45,11 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.bits = d_bits; P.n_words = W;
         P.semantics = semantics; P.band = (float)s->band;
         const bool defer = may_defer && qv.cnt <= s->defer_max_configs && nr == 1;  // one task list: one range at a time
-        if (defer) P.tasks = WorkList{s->tasks.as<WorkItem>(), wl.count + 3, s->wl_cap};
+        if (defer) {
+          P.tasks = WorkList{s->tasks.as<WorkItem>(), wl.count + 3, s->wl_cap};
+          if (s->xf.ensure((size_t)qv.cnt * s->tb.robot.n_links * 12 * sizeof(double))) return fail(SIRRT_E_CUDA, "cudaMalloc(link transforms) failed");
+          P.xf = s->xf.as<double>();
+        }
         // small batches: split each row over several warps (tile chunks) to fill the machine
         long long target = (long long)s->n_sm * 32;
         int n_chunks = (int)std::max(1ll, std::min((long long)W, target / std::max(1ll, qv.cnt)));
@@ -57,7 +61,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         launches++;
         if (defer) {
           GjkTaskParams G{};
-          G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl;
+          G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl; G.xf = P.xf;
           G.bits = d_bits; G.n_words = W; G.cells = nullptr; G.band = (float)s->band;
           k_gjk_tasks<<<s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, G);
           launches++;
@@ -227,13 +231,17 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     if (defer) {
       if (s->tasks.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(task list) failed");
       P.tasks = WorkList{s->tasks.as<WorkItem>(), wl.count + 3, s->wl_cap};
+      if (qv.cnt <= (16 << 10)) {  // FP64 link transforms handed to the task kernel (larger batches redo FK per task)
+        if (s->xf.ensure((size_t)qv.cnt * s->tb.robot.n_links * 12 * sizeof(double))) return fail(SIRRT_E_CUDA, "cudaMalloc(link transforms) failed");
+        P.xf = s->xf.as<double>();
+      }
     }
     const int grid = grid_for(qv.cnt, s->n_sm, 8);
     if (s->tb.has_hull) k_check_cells<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
     else k_check_cells<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
     if (defer) {
       GjkTaskParams G{};
-      G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl;
+      G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl; G.xf = P.xf;
       G.bits = nullptr; G.n_words = s->tb.n_tiles; G.cells = d_out; G.band = (float)s->band;
       k_gjk_tasks<<<s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, G);
       s->stats[0]++;

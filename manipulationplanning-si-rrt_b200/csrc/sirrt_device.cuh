@@ -38,7 +38,7 @@ struct DShape {
   int type;            // SH_*
   int vert_off;        // hull: first vertex in the vertex arrays
   int n_verts;
-  int pad;
+  int cell_off;        // hull: first entry of its support-cell offsets in DScene::hull_cells, -1 = none
   float radius, half_len;  // capsule / sphere
   float half[3];           // box half extents
   float bc[3], br;         // bounding sphere (inflated shape), local frame
@@ -72,7 +72,32 @@ struct DScene {
   const float4* tile_bounds; // [tile*n_dynamic + j]    swept bounding sphere of dynamic slot j over the tile
   const float* verts_f;      // xyz interleaved
   const double* verts_d;
+  // support-candidate cells of the hulls (see hull_cell): per hull 6*K*K+1 offsets into hull_cand, which lists for
+  // each cube-map cell of directions every vertex that can be the support vertex for a direction of that cell
+  const unsigned int* hull_cells;
+  const unsigned short* hull_cand;  // vertex indices local to the hull, ascending within a cell
 };
+
+// Cube-map cell of a (non-zero, finite) direction: dominant axis and sign pick the face, the two other components
+// divided by the dominant magnitude pick one of K x K squares.  Host and device may round the ratios differently:
+// the host dilates every cell by SIRRT_HULL_CELL_PAD in (u, v) when it collects the candidates.
+#define SIRRT_HULL_K 16
+#define SIRRT_HULL_CELLS (6 * SIRRT_HULL_K * SIRRT_HULL_K)
+#define SIRRT_HULL_CELL_PAD 1e-3
+template <typename T> __host__ __device__ inline int hull_cell(const T* d) {
+  const T ax = d[0] < T(0) ? -d[0] : d[0], ay = d[1] < T(0) ? -d[1] : d[1], az = d[2] < T(0) ? -d[2] : d[2];
+  int a = 0;
+  T m = ax;
+  if (ay > m) { a = 1; m = ay; }
+  if (az > m) { a = 2; m = az; }
+  if (!(m > T(0)) || !(m < T(3.0e38))) return -1;  // zero / NaN / inf direction: caller scans every vertex
+  const T u = d[(a + 1) % 3] / m, v = d[(a + 2) % 3] / m;
+  int iu = (int)((u + T(1)) * T(0.5 * SIRRT_HULL_K)), iv = (int)((v + T(1)) * T(0.5 * SIRRT_HULL_K));
+  iu = iu < 0 ? 0 : (iu > SIRRT_HULL_K - 1 ? SIRRT_HULL_K - 1 : iu);
+  iv = iv < 0 ? 0 : (iv > SIRRT_HULL_K - 1 ? SIRRT_HULL_K - 1 : iv);
+  const int face = 2 * a + (d[a] < T(0) ? 1 : 0);
+  return (face * SIRRT_HULL_K + iu) * SIRRT_HULL_K + iv;
+}
 
 struct WorkItem {  // one ambiguous pair test for the FP64 re-check
   int config;
@@ -235,6 +260,8 @@ template <typename T> __device__ inline T seg_box_dist2(const T* a, const T* b, 
 template <typename T> struct GShape {
   int type;        // SH_*
   const T* verts;  // hull: xyz interleaved
+  const unsigned int* cells;     // hull: support-candidate cell offsets (null: scan every vertex)
+  const unsigned short* cand;
   int n;
   T half[3];       // box
   T half_len;      // capsule core
@@ -244,10 +271,22 @@ template <typename T>
 __device__ inline int warp_support(const GShape<T>& s, const T* d, T* out, int lane) {
   if (s.type == SH_HULL) {
     T bv = T(-3.0e38);
-    int bi = 0;
-    for (int i = lane; i < s.n; i += 32) {
-      T v = s.verts[3 * i] * d[0] + s.verts[3 * i + 1] * d[1] + s.verts[3 * i + 2] * d[2];
-      if (v > bv) { bv = v; bi = i; }
+    int bi = 0x7fffffff;
+    const int cell = s.cells ? hull_cell(d) : -1;
+    if (cell >= 0) {
+      // every vertex that can win the full scan for a direction of this cell is listed (ascending index), so the
+      // winner -- largest dot product, lowest index on ties -- is the one the full scan finds, bit for bit
+      const unsigned c0 = s.cells[cell], c1 = s.cells[cell + 1];
+      for (unsigned k = c0 + lane; k < c1; k += 32) {
+        const int i = s.cand[k];
+        T v = s.verts[3 * i] * d[0] + s.verts[3 * i + 1] * d[1] + s.verts[3 * i + 2] * d[2];
+        if (v > bv) { bv = v; bi = i; }
+      }
+    } else {
+      for (int i = lane; i < s.n; i += 32) {
+        T v = s.verts[3 * i] * d[0] + s.verts[3 * i + 1] * d[1] + s.verts[3 * i + 2] * d[2];
+        if (v > bv) { bv = v; bi = i; }
+      }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -255,6 +294,7 @@ __device__ inline int warp_support(const GShape<T>& s, const T* d, T* out, int l
       int oi = __shfl_xor_sync(SIRRT_FULL, bi, o);
       if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
     }
+    if (bi == 0x7fffffff) bi = 0;
     out[0] = s.verts[3 * bi]; out[1] = s.verts[3 * bi + 1]; out[2] = s.verts[3 * bi + 2];
     return bi;
   }
@@ -407,7 +447,10 @@ template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v,
 //         *dist_out gets the signed distance (core distance - rsum).
 template <typename T, bool FINAL>
 __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* Rrel, const T* trel, T rsum, T band,
-                               int lane, T* dist_out) {
+                               int lane, T* dist_out, int* enc_ids = nullptr) {
+  // enc_ids (FP32 pass only): when the answer is AMBIGUOUS because the enclosing tetrahedron is too thin to trust in
+  // FP32, the four support-point ids -- the caller can certify the enclosure in FP64 from them (gjk_point / tetra_encloses)
+  if (enc_ids) enc_ids[0] = -1;
   Simplex<T> s;
   T v[3] = {-trel[0], -trel[1], -trel[2]};  // A is centred near its origin, B near trel
   if (dot3(v, v) == T(0)) v[0] = T(1);
@@ -456,7 +499,9 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
       if (dist_out) *dist_out = -rsum;
       if (FINAL) return RES_HIT;  // core distance 0 <= threshold + rsum
       if (rsum > band) return RES_HIT;
-      return min_face > band ? RES_HIT : RES_AMBIG;
+      if (min_face > band) return RES_HIT;
+      if (enc_ids && s.n == 4) { enc_ids[0] = s.id[0]; enc_ids[1] = s.id[1]; enc_ids[2] = s.id[2]; enc_ids[3] = s.id[3]; }
+      return RES_AMBIG;
     }
     T n2 = dot3(nvv, nvv);
     if (!(n2 < vv)) break;
@@ -467,4 +512,43 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
   if (FINAL) return ((double)d - SIRRT_SECURITY_MARGIN <= SIRRT_COLLISION_THRESHOLD) ? RES_HIT : RES_FREE;
   if (d < -band) return RES_HIT;
   return RES_AMBIG;  // |d| <= band, or not converged enough to certify separation
+}
+
+// Point of shape s behind a support id returned by warp_support (hull vertex index, box corner bits, capsule end).
+template <typename T> __device__ __forceinline__ void gjk_point(const GShape<T>& s, int id, T* out) {
+  if (s.type == SH_HULL) { out[0] = s.verts[3 * id]; out[1] = s.verts[3 * id + 1]; out[2] = s.verts[3 * id + 2]; }
+  else if (s.type == SH_BOX) { for (int k = 0; k < 3; k++) out[k] = (id >> k) & 1 ? s.half[k] : -s.half[k]; }
+  else if (s.type == SH_CAPSULE) { out[0] = out[1] = T(0); out[2] = id ? s.half_len : -s.half_len; }
+  else { out[0] = out[1] = out[2] = T(0); }
+}
+
+// FP64 certificate for "the cores intersect": the four points of A - B named by the ids of an FP32 GJK simplex form a
+// tetrahedron with real volume that has the origin strictly inside, at least `margin` from every face.  Four points of
+// the Minkowski difference enclosing the origin prove the intersection whatever GJK run found them.
+__device__ inline bool tetra_encloses(const GShape<double>& A, const GShape<double>& B, const double* Rrel, const double* trel,
+                                      const int* ids, double margin, double* min_face) {
+  double w[4][3];
+  for (int i = 0; i < 4; i++) {
+    double pa[3], u[3], pb[3];
+    gjk_point(A, ids[i] >> 12, pa);
+    gjk_point(B, ids[i] & 4095, u);
+    matvec(pb, Rrel, u);
+    for (int k = 0; k < 3; k++) w[i][k] = pa[k] - (pb[k] + trel[k]);
+  }
+  const int F[4][4] = {{0, 1, 2, 3}, {0, 2, 3, 1}, {0, 3, 1, 2}, {1, 3, 2, 0}};
+  double mf = 3.0e38;
+  for (int f = 0; f < 4; f++) {
+    const double *a = w[F[f][0]], *b = w[F[f][1]], *c = w[F[f][2]], *d = w[F[f][3]];
+    double e1[3], e2[3], fn[3], ed[3];
+    sub3(e1, b, a); sub3(e2, c, a); cross3(fn, e1, e2); sub3(ed, d, a);
+    const double nn = dot3(fn, fn);
+    if (!(nn > 0.0)) return false;
+    const double inv = 1.0 / sqrt(nn);
+    const double so = -dot3(a, fn) * inv, sd = dot3(ed, fn) * inv;  // signed distances of the origin and of d from the face plane
+    if (!(so * sd > 0.0)) return false;                               // origin on d's side
+    if (!(fabs(sd) > 1e-7)) return false;                             // real volume: the apex is clear of the face plane
+    mf = fabs(so) < mf ? fabs(so) : mf;
+  }
+  *min_face = mf;
+  return mf > margin;
 }

@@ -55,7 +55,7 @@ struct WarpCtx {   // per-warp shared memory: the planned robot's links in world
 };
 
 // FK in FP64, then narrow to the FP32 world-space link table.  Executed redundantly by all lanes.
-__device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QView& qv, long long n, WarpCtx& W, int lane) {
+__device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QView& qv, long long n, WarpCtx& W, int lane, double* xf_out = nullptr) {
   double q[SIRRT_MAXJ];
   for (int j = 0; j < rb.n_joints; j++) q[j] = j < qv.dof ? load_q(qv, n, j) : 0.0;
   LinkXfD X[SIRRT_MAXL];
@@ -68,6 +68,11 @@ __device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QVi
       const double* t = X[l].t;
       for (int k = 0; k < 9; k++) W.R[l][k] = (float)R[k];
       for (int k = 0; k < 3; k++) W.t[l][k] = (float)t[k];
+      if (xf_out) {  // FP64 link transforms for the deferred GJK tasks of this configuration (k_gjk_tasks)
+        double* o = xf_out + ((size_t)(n - qv.n0) * rb.n_links + l) * 12;
+        for (int k = 0; k < 9; k++) o[k] = R[k];
+        for (int k = 0; k < 3; k++) o[9 + k] = t[k];
+      }
       W.type[l] = sh.type;
       W.r[l] = sh.radius;
       W.br[l] = sh.br;
@@ -134,20 +139,20 @@ __device__ __forceinline__ void load_pose(const DScene& sc, int slot, int f, flo
 
 // warp-cooperative FP32 test of (link l, shape sh posed at slot/frame): anything involving a hull
 __device__ inline int coop_test(const DScene& sc, const float* RA, const float* tA, const DShape& lsh, const DShape& sh, int slot,
-                                int f, float band, int lane) {
+                                int f, float band, int lane, int* enc_ids = nullptr) {
   float RB[9], tB[3];
   load_pose(sc, slot, f, RB, tB, true);
   GShape<float> A, B;
-  A.type = lsh.type; A.verts = sc.verts_f + 3 * (size_t)lsh.vert_off; A.n = lsh.n_verts; A.half_len = lsh.half_len;
+  A.type = lsh.type; A.verts = sc.verts_f + 3 * (size_t)lsh.vert_off; A.n = lsh.n_verts; A.cells = (sc.hull_cells && lsh.cell_off >= 0) ? sc.hull_cells + lsh.cell_off : nullptr; A.cand = sc.hull_cand; A.half_len = lsh.half_len;
   A.half[0] = lsh.half[0]; A.half[1] = lsh.half[1]; A.half[2] = lsh.half[2];
-  B.type = sh.type; B.verts = sc.verts_f + 3 * (size_t)sh.vert_off; B.n = sh.n_verts; B.half_len = sh.half_len;
+  B.type = sh.type; B.verts = sc.verts_f + 3 * (size_t)sh.vert_off; B.n = sh.n_verts; B.cells = (sc.hull_cells && sh.cell_off >= 0) ? sc.hull_cells + sh.cell_off : nullptr; B.cand = sc.hull_cand; B.half_len = sh.half_len;
   B.half[0] = sh.half[0]; B.half[1] = sh.half[1]; B.half[2] = sh.half[2];
   float Rrel[9], trel[3], dt[3];
   matTmul3(Rrel, RA, RB);
   sub3(dt, tB, tA);
   matTvec(trel, RA, dt);
   float rsum = (lsh.type == SH_HULL ? 0.f : lsh.radius) + ((sh.type == SH_SPHERE || sh.type == SH_CAPSULE) ? sh.radius : 0.f);
-  return warp_gjk<float, false>(A, B, Rrel, trel, rsum, band, lane, (float*)nullptr);
+  return warp_gjk<float, false>(A, B, Rrel, trel, rsum, band, lane, (float*)nullptr, enc_ids);
 }
 
 // Tight-AABB cull: a pair whose world AABBs are further apart than the FP32 uncertainty band on some axis cannot
@@ -184,6 +189,7 @@ struct BitsParams {
   WorkList wl;
   WorkList tasks;       // items != null: hull pair tests are NOT run by the producing warp but appended here for k_gjk_tasks
   const float* aabb_f;  // robot slots: [(slot*6 + k)*Tp + f] coal AABB lo(3) hi(3); may be null
+  double* xf;           // deferred tasks: FP64 link transforms [cnt][n_links][12] written here for k_gjk_tasks; may be null
   uint32_t* bits;       // [N][W]
   int n_words;          // W
   int tiles_per_chunk;
@@ -216,7 +222,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
     const int tile_lo = chunk * P.tiles_per_chunk;
     const int tile_hi = min(tile_lo + P.tiles_per_chunk, sc.n_tiles);
     __syncwarp();
-    setup_links(rb, sc, P.q, n, W, lane);
+    setup_links(rb, sc, P.q, n, W, lane, P.xf);
     const int L = rb.n_links;
 
     // evaluates one candidate for this lane; returns hit bit, pushes ambiguous work
@@ -386,6 +392,7 @@ struct CellParams {
   WorkList wl;
   WorkList tasks;       // items != null: hull pair tests are deferred to k_gjk_tasks
   const float* aabb_f;
+  double* xf;             // as BitsParams::xf
   const int32_t* frames;  // [N]; null: every cell uses frame_one (latency path, single cell)
   int frame_one;
   uint8_t* out;           // [N]
@@ -412,7 +419,7 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
       continue;
     }
     __syncwarp();
-    setup_links(rb, sc, P.q, n, W, lane);
+    setup_links(rb, sc, P.q, n, W, lane, P.xf);
     const int L = rb.n_links, n_pairs = L * sc.n_slots;
     bool hit = false;
     for (int p0 = 0; p0 < n_pairs && !hit; p0 += 32) {
@@ -508,7 +515,7 @@ struct RecheckParams {
 };
 
 __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const LinkXfD& X, int l, const DShape& sh,
-                                      const double* pose, int lane, int* res) {
+                                      const double* pose, int lane, int* res, const int* enc_ids = nullptr, bool* near = nullptr) {
   const DShape& lsh = sc.shapes[rb.link_shape[l]];
   const double *RB = pose, *tB = pose + 9;
   double d;
@@ -528,20 +535,52 @@ __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const 
       d = sqrt(seg_seg_dist2(a, b, p2, q2)) - lsh.d_radius - sh.d_radius;
     }
     *res = (d - SIRRT_SECURITY_MARGIN <= SIRRT_COLLISION_THRESHOLD) ? RES_HIT : RES_FREE;
+    if (near) *near = fabs(d) < 1e-6;
     return d;
   }
   GShape<double> A, B;
-  A.type = lsh.type; A.verts = sc.verts_d + 3 * (size_t)lsh.vert_off; A.n = lsh.n_verts; A.half_len = lsh.d_half_len;
+  A.type = lsh.type; A.verts = sc.verts_d + 3 * (size_t)lsh.vert_off; A.n = lsh.n_verts; A.cells = (sc.hull_cells && lsh.cell_off >= 0) ? sc.hull_cells + lsh.cell_off : nullptr; A.cand = sc.hull_cand; A.half_len = lsh.d_half_len;
   A.half[0] = lsh.d_half[0]; A.half[1] = lsh.d_half[1]; A.half[2] = lsh.d_half[2];
-  B.type = sh.type; B.verts = sc.verts_d + 3 * (size_t)sh.vert_off; B.n = sh.n_verts; B.half_len = sh.d_half_len;
+  B.type = sh.type; B.verts = sc.verts_d + 3 * (size_t)sh.vert_off; B.n = sh.n_verts; B.cells = (sc.hull_cells && sh.cell_off >= 0) ? sc.hull_cells + sh.cell_off : nullptr; B.cand = sc.hull_cand; B.half_len = sh.d_half_len;
   B.half[0] = sh.d_half[0]; B.half[1] = sh.d_half[1]; B.half[2] = sh.d_half[2];
   double Rrel[9], trel[3], dt[3];
   matTmul3(Rrel, X.R, RB);
   sub3(dt, tB, X.t);
   matTvec(trel, X.R, dt);
   double rsum = (lsh.type == SH_HULL ? 0.0 : lsh.d_radius) + ((sh.type == SH_SPHERE || sh.type == SH_CAPSULE) ? sh.d_radius : 0.0);
+  if (enc_ids && enc_ids[0] >= 0) {
+    // the FP32 pass ended with an enclosing but thin tetrahedron: certify the same four points in FP64 instead of
+    // running GJK again (an intersection of the cores is a collision whatever the radii: distance = -rsum <= threshold)
+    double mf;
+    if (tetra_encloses(A, B, Rrel, trel, enc_ids, 1e-9, &mf)) {
+      *res = RES_HIT;
+      if (near) *near = rsum < 1e-6 && mf < 1e-6;
+      return -rsum;
+    }
+  }
   *res = warp_gjk<double, true>(A, B, Rrel, trel, rsum, 0.0, lane, &d);
+  if (near) *near = fabs(d) < 1e-6;
   return d;
+}
+
+// FP64 certificate of an FP32 "enclosed, but thin" GJK verdict (see tetra_encloses); kept out of line so that the task
+// kernel's register budget stays that of the FP32 GJK
+__device__ __noinline__ bool certify_enclosure(const DRobot& rb, const DScene& sc, const LinkXfD& X, int l, const DShape& sh,
+                                               const double* pose, const int* enc_ids, bool* near) {
+  const DShape& lsh = sc.shapes[rb.link_shape[l]];
+  GShape<double> A, B;
+  A.type = lsh.type; A.verts = sc.verts_d + 3 * (size_t)lsh.vert_off; A.n = lsh.n_verts; A.cells = nullptr; A.cand = nullptr; A.half_len = lsh.d_half_len;
+  A.half[0] = lsh.d_half[0]; A.half[1] = lsh.d_half[1]; A.half[2] = lsh.d_half[2];
+  B.type = sh.type; B.verts = sc.verts_d + 3 * (size_t)sh.vert_off; B.n = sh.n_verts; B.cells = nullptr; B.cand = nullptr; B.half_len = sh.d_half_len;
+  B.half[0] = sh.d_half[0]; B.half[1] = sh.d_half[1]; B.half[2] = sh.d_half[2];
+  double Rrel[9], trel[3], dt[3], mf;
+  matTmul3(Rrel, X.R, pose);
+  sub3(dt, pose + 9, X.t);
+  matTvec(trel, X.R, dt);
+  if (!tetra_encloses(A, B, Rrel, trel, enc_ids, 1e-9, &mf)) return false;
+  const double rsum = (lsh.type == SH_HULL ? 0.0 : lsh.d_radius) + ((sh.type == SH_SPHERE || sh.type == SH_CAPSULE) ? sh.d_radius : 0.0);
+  *near = rsum < 1e-6 && mf < 1e-6;
+  return true;
 }
 
 __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
@@ -622,6 +661,7 @@ struct GjkTaskParams {
   const unsigned int* count;  // tasks pushed (clamped to cap here; an overflow is detected by the host)
   unsigned int cap;
   WorkList wl;                // FP64 re-check list
+  const double* xf;           // FP64 link transforms [cnt][n_links][12] left by the producing kernel, or null (FK is redone here)
   uint32_t* bits;             // bits mode: [N][W]
   int n_words;
   uint8_t* cells;             // cell mode: [N]
@@ -635,20 +675,42 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
   const unsigned int n_items = min(*P.count, P.cap);
   for (unsigned int w = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5); w < n_items; w += gridDim.x * SIRRT_WARPS_PER_BLOCK) {
     const WorkItem it = P.items[w];
-    double q[SIRRT_MAXJ];
-    for (int j = 0; j < rb.n_joints; j++) q[j] = j < P.q.dof ? load_q(P.q, it.config, j) : 0.0;
-    LinkXfD X[SIRRT_MAXL];
-    fk_links(rb, q, X);
     const int l = it.link, f = it.frame < 0 ? 0 : it.frame;
+    LinkXfD Xl;
+    if (P.xf) {
+      const double* x = P.xf + ((size_t)(it.config - P.q.n0) * rb.n_links + l) * 12;
+#pragma unroll
+      for (int k = 0; k < 9; k++) Xl.R[k] = x[k];
+#pragma unroll
+      for (int k = 0; k < 3; k++) Xl.t[k] = x[9 + k];
+    } else {
+      double q[SIRRT_MAXJ];
+      for (int j = 0; j < rb.n_joints; j++) q[j] = j < P.q.dof ? load_q(P.q, it.config, j) : 0.0;
+      LinkXfD X[SIRRT_MAXL];
+      fk_links(rb, q, X);
+      Xl = X[l];
+    }
     float RA[9], tA[3];
 #pragma unroll
-    for (int k = 0; k < 9; k++) RA[k] = (float)X[l].R[k];  // the same narrowing as setup_links
+    for (int k = 0; k < 9; k++) RA[k] = (float)Xl.R[k];  // the same narrowing as setup_links
 #pragma unroll
-    for (int k = 0; k < 3; k++) tA[k] = (float)X[l].t[k];
+    for (int k = 0; k < 3; k++) tA[k] = (float)Xl.t[k];
     const DSlot S = sc.slots[it.slot];
     const DShape& sh = sc.shapes[it.shifted ? S.shape_shift : S.shape];
-    const int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane);
-    if (r == RES_AMBIG) { if (lane == 0) push_work(P.wl, it.config, it.frame, l, it.slot, it.shifted); continue; }
+    int enc_ids[4];
+    int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids);
+    if (r == RES_AMBIG) {
+      // a thin enclosing tetrahedron is certified here in FP64 by the warp that found it (it holds the FP64 link
+      // transform); anything else goes to the FP64 re-check list
+      bool near = false;
+      if (enc_ids[0] >= 0 && certify_enclosure(rb, sc, Xl, l, sh, sc.pose_d + ((size_t)it.slot * sc.Tp + f) * 12, enc_ids, &near)) {
+        r = RES_HIT;
+        if (lane == 0 && near) atomicAdd(P.wl.count + 2, 1u);
+      } else {
+        if (lane == 0) push_work(P.wl, it.config, it.frame, l, it.slot, it.shifted);
+        continue;
+      }
+    }
     if (r != RES_HIT) continue;
     if (P.cells) { if (lane == 0) P.cells[it.config] = 1; continue; }
     uint32_t* row = P.bits + (size_t)it.config * P.n_words;

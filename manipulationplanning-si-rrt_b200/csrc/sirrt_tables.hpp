@@ -15,16 +15,76 @@ struct HostTables {
   std::vector<float> pose_f, bcw_f, aabb_f, tight_f, verts_f;
   std::vector<double> pose_d, aabb_d, verts_d;
   std::vector<float4> tile_bounds;
+  std::vector<unsigned int> hull_cells;     // per hull SIRRT_HULL_CELLS + 1 offsets into hull_cand
+  std::vector<unsigned short> hull_cand;
   double extent = 0;  // largest |coordinate| the FP32 path can meet near the arm (band scaling)
 };
 
-inline void to_dshape(const HShape& h, DShape& d, std::vector<float>& vf, std::vector<double>& vd) {
+// Support-candidate cells of one hull.  For a cube-map cell with unit centre direction c and chord radius eps
+// (|d/|d| - c| <= eps for every direction d of the dilated cell), a vertex v can only be the support vertex for such a d
+// if  v.c >= h(c) - |v - w*| eps  (w* = a support vertex for c, h(c) = w*.c): from v.d >= w*.d with d = c + (d - c).
+// `slack` covers the rounding of the dot products the device compares (FP32: ~2e-7 |v| per unit direction), so the
+// winner of the device's full FP32 / FP64 scan is always listed.
+inline void build_hull_cells(const std::vector<float>& verts, std::vector<unsigned int>& cells, std::vector<unsigned short>& cand) {
+  const int n = (int)(verts.size() / 3), K = SIRRT_HULL_K;
+  double rmax = 0;
+  for (int i = 0; i < n; i++) rmax = std::max(rmax, std::sqrt((double)verts[3 * i] * verts[3 * i] + (double)verts[3 * i + 1] * verts[3 * i + 1] + (double)verts[3 * i + 2] * verts[3 * i + 2]));
+  const double slack = 1e-5 * std::max(rmax, 1e-3);
+  for (int face = 0; face < 6; face++) {
+    const int a = face >> 1;
+    const double sgn = (face & 1) ? -1.0 : 1.0;
+    for (int iu = 0; iu < K; iu++)
+      for (int iv = 0; iv < K; iv++) {
+        cells.push_back((unsigned int)cand.size());
+        const double u0 = -1.0 + 2.0 * iu / K - SIRRT_HULL_CELL_PAD, u1 = -1.0 + 2.0 * (iu + 1) / K + SIRRT_HULL_CELL_PAD;
+        const double v0 = -1.0 + 2.0 * iv / K - SIRRT_HULL_CELL_PAD, v1 = -1.0 + 2.0 * (iv + 1) / K + SIRRT_HULL_CELL_PAD;
+        auto dir = [&](double u, double v, double* o) {
+          o[a] = sgn; o[(a + 1) % 3] = u; o[(a + 2) % 3] = v;
+          const double nn = std::sqrt(o[0] * o[0] + o[1] * o[1] + o[2] * o[2]);
+          o[0] /= nn; o[1] /= nn; o[2] /= nn;
+        };
+        double c[3], k4[4][3];
+        dir(0.5 * (u0 + u1), 0.5 * (v0 + v1), c);
+        dir(u0, v0, k4[0]); dir(u0, v1, k4[1]); dir(u1, v0, k4[2]); dir(u1, v1, k4[3]);
+        double eps = 0;
+        for (auto& k : k4) eps = std::max(eps, std::sqrt((k[0] - c[0]) * (k[0] - c[0]) + (k[1] - c[1]) * (k[1] - c[1]) + (k[2] - c[2]) * (k[2] - c[2])));
+        eps *= 1.001;
+        double h = -1e300;
+        int w = 0;
+        for (int i = 0; i < n; i++) {
+          const double dv = verts[3 * i] * c[0] + verts[3 * i + 1] * c[1] + verts[3 * i + 2] * c[2];
+          if (dv > h) { h = dv; w = i; }
+        }
+        for (int i = 0; i < n; i++) {
+          const double dv = verts[3 * i] * c[0] + verts[3 * i + 1] * c[1] + verts[3 * i + 2] * c[2];
+          const double ex = (double)verts[3 * i] - verts[3 * w], ey = (double)verts[3 * i + 1] - verts[3 * w + 1], ez = (double)verts[3 * i + 2] - verts[3 * w + 2];
+          if (dv >= h - std::sqrt(ex * ex + ey * ey + ez * ez) * eps - slack) cand.push_back((unsigned short)i);
+        }
+      }
+  }
+  cells.push_back((unsigned int)cand.size());
+  if (getenv("SIRRT_DEBUG_CELLS")) {
+    unsigned mx = 0;
+    const size_t c0 = cells.size() - 1 - SIRRT_HULL_CELLS;
+    for (size_t i = c0; i + 1 < cells.size(); i++) mx = std::max(mx, cells[i + 1] - cells[i]);
+    fprintf(stderr, "hull cells: %d vertices, mean %.1f candidates per cell, max %u\n", n, (double)(cells.back() - cells[c0]) / SIRRT_HULL_CELLS, mx);
+  }
+}
+
+inline void to_dshape(const HShape& h, DShape& d, std::vector<float>& vf, std::vector<double>& vd, std::vector<unsigned int>& cells,
+                      std::vector<unsigned short>& cand) {
   memset(&d, 0, sizeof d);
   d.type = h.type;
   d.vert_off = (int)(vf.size() / 3);
   d.n_verts = h.type == SH_HULL ? (int)(h.verts.size() / 3) : 0;
-  if (h.type == SH_HULL)
+  d.cell_off = -1;
+  if (h.type == SH_HULL) {
     for (float v : h.verts) { vf.push_back(v); vd.push_back((double)v); }
+    if (d.n_verts > 64 && d.n_verts < 65536) {  // small hulls: the full scan is two steps anyway
+      d.cell_off = (int)cells.size();
+      build_hull_cells(h.verts, cells, cand);
+    }
+  }
   d.radius = (float)h.radius; d.half_len = (float)h.half_len;
   d.d_radius = h.radius; d.d_half_len = h.half_len;
   for (int k = 0; k < 3; k++) {
@@ -76,7 +136,7 @@ inline int build_tables(const HScene& sc, int parity_mode, HostTables& tb, std::
     const HShape& s = rb.shapes[l + rb.n_strip];
     dr.link_jb[l] = s.joints_before; dr.link_shape[l] = l;
     memcpy(dr.lo_t[l], s.lo_t, 24); memcpy(dr.lo_R[l], s.lo_R, 72);
-    DShape d; to_dshape(s, d, tb.verts_f, tb.verts_d);
+    DShape d; to_dshape(s, d, tb.verts_f, tb.verts_d, tb.hull_cells, tb.hull_cand);
     tb.shapes.push_back(d);
     if (s.type == SH_HULL) tb.has_hull = 1;
   }
@@ -88,19 +148,21 @@ inline int build_tables(const HScene& sc, int parity_mode, HostTables& tb, std::
   tb.extent = sqrt(rb.base_t[0] * rb.base_t[0] + rb.base_t[1] * rb.base_t[1] + rb.base_t[2] * rb.base_t[2]) + reach + lmax;
 
   // ---- obstacle shapes, then ALL shapes of every robot obstacle (QUIRK 7 needs the stripped ones too)
-  for (const HObst& o : sc.obst) { DShape d; to_dshape(o.shape, d, tb.verts_f, tb.verts_d); tb.shapes.push_back(d); }
+  for (const HObst& o : sc.obst) { DShape d; to_dshape(o.shape, d, tb.verts_f, tb.verts_d, tb.hull_cells, tb.hull_cand); tb.shapes.push_back(d); }
   const int rob_shape_base = (int)tb.shapes.size();
   int n_rob_shapes_all = 0, n_rob_links = 0;
   std::vector<int> rob_off;
   for (const HRobObst& ro : sc.robs) {
     rob_off.push_back(n_rob_shapes_all);
     for (const HShape& s : ro.robot.shapes) {
-      DShape d; to_dshape(s, d, tb.verts_f, tb.verts_d); tb.shapes.push_back(d);
+      DShape d; to_dshape(s, d, tb.verts_f, tb.verts_d, tb.hull_cells, tb.hull_cand); tb.shapes.push_back(d);
       if (s.type == SH_HULL) tb.has_hull = 1;
     }
     n_rob_shapes_all += ro.robot.n_shapes; n_rob_links += ro.robot.n_links;
   }
   if (tb.verts_f.empty()) { tb.verts_f.assign(3, 0.f); tb.verts_d.assign(3, 0.0); }
+  if (tb.hull_cells.empty()) tb.hull_cells.assign(1, 0u);
+  if (tb.hull_cand.empty()) tb.hull_cand.assign(1, 0);
 
   const int n_slots = sc.C + n_rob_links;
   tb.n_slots = n_slots; tb.n_robot_slots = n_rob_links;

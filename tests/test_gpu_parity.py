@@ -375,3 +375,28 @@ def test_validator_classes_program(pkg, orc, sp, packs, tmp_path):
         col, d = ref.get_distances(q0[e], fr)
         assert abs(float(clr) - (0.0 if col else float(np.float32(d.min())))) < 1e-6
     assert lines[n + 1].split() == ["counters", str(tested), str(3 * n)]
+
+
+@pytest.mark.parametrize("name", ["flying_boxes", "mass_test", "multiple_robots"])
+def test_hull_support_cells_equal_full_scan(pkg, orc, sp, packs, name):
+    """GJK support queries through the cube-map candidate cells (csrc/sirrt_tables.hpp: build_hull_cells) pick the
+    vertex the full scan picks: rows, cells and per-link distances are identical with the cells switched off, and
+    both equal the oracle."""
+    pk = packs(name)
+    a, b = pkg.Scene(pk), pkg.Scene(pk)
+    b.set_option(pkg.OPT_HULL_CELLS, 0)
+    q = random_q(sp, pk, 96, 53)
+    ta, ba, _ = a.safe_intervals_batch(q, 8)
+    tb, bb, _ = b.safe_intervals_batch(q, 8)
+    assert np.array_equal(ba, bb) and np.array_equal(ta, tb) and ba.any()
+    rt, rb = orc.Oracle(pk).safe_intervals_batch(q, 8)
+    assert np.array_equal(ba, rb) and np.array_equal(ta, rt)
+    q64 = q.T.astype(np.float64)
+    for i in range(0, 96, 8):
+        f = (61 * i) % a.n_frames
+        ca, da = a.get_distances(q64[i], f)
+        cb, db = b.get_distances(q64[i], f)
+        assert ca == cb and np.array_equal(da, db)
+    b.set_option(pkg.OPT_HULL_CELLS, 1)
+    tc, bc, _ = b.safe_intervals_batch(q, 8)
+    assert np.array_equal(bc, ba)

@@ -2,6 +2,9 @@
 // collision / safe-interval / edge entry points and the single-call drop-ins.  Everything that
 // computes runs in the hand-written sm_100a kernels of sirrt_kernels.cuh / sirrt_sweep.cuh /
 // sirrt_knn.cuh; there is no CPU fallback: without a CUDA device every compute call fails.
+#include <sched.h>
+#include <stdlib.h>
+#include <string.h>
 #include <stdio.h>
 
 #include <algorithm>
@@ -25,6 +28,20 @@ static int fail(int code, const char* fmt, const char* a = "") {
     cudaError_t e_ = (x);                                                                              \
     if (e_ != cudaSuccess) { cudaGetLastError(); return fail(SIRRT_E_CUDA, "CUDA: %s (" #x ")", cudaGetErrorString(e_)); } \
   } while (0)
+
+// Every host wait of the library goes through here.  Default: cudaStreamSynchronize (spins: lowest latency when each
+// planner thread has a core).  SIRRT_SYNC=yield in the environment: poll the stream and give the core away between
+// polls -- for boxes that run more planner threads than cores (the mass test shares 32 cores between 8 GPUs' workers;
+// a planner thread spends most of its time waiting for its GPU).
+static cudaError_t sirrt_sync(cudaStream_t st) {
+  static const int mode = [] { const char* e = getenv("SIRRT_SYNC"); return (e && !strcmp(e, "yield")) ? 1 : 0; }();
+  if (!mode) return cudaStreamSynchronize(st);
+  for (;;) {
+    const cudaError_t e = cudaStreamQuery(st);
+    if (e != cudaErrorNotReady) return e;
+    sched_yield();
+  }
+}
 
 extern "C" const char* sirrt_last_error(void) { return g_err; }
 extern "C" int sirrt_version(void) { return 100; }

@@ -83,7 +83,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
     }
     std::vector<unsigned> host(nr * 4);
     CU(cudaMemcpyAsync(host.data(), s->counts.p, nr * 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
+    CU(sirrt_sync(st));
     for (size_t i = 0; i < nr && i < s->ev.size() / 2; i++) {
       float ms = 0;
       if (cudaEventElapsedTime(&ms, s->ev[2 * i], s->ev[2 * i + 1]) == cudaSuccess) sweep_ns += (uint64_t)(ms * 1e6);
@@ -177,7 +177,7 @@ static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, i
       if (small) { b_host = (uint32_t*)(s->pinned + PIN_OUT + PIN_OUT_CAP / 2); CU(cudaMemcpyAsync(b_host, d_bits, bbytes, cudaMemcpyDeviceToHost, s->stream)); }
       else CU(cudaMemcpyAsync(bits, d_bits, bbytes, cudaMemcpyDeviceToHost, s->stream));
     }
-    CU(cudaStreamSynchronize(s->stream));
+    CU(sirrt_sync(s->stream));
     if (lazy && finish_lazy(s)) continue;  // FP64 work list overflowed: repeat with the checked, splitting loop
     if (t_host) memcpy(table, t_host, tbytes);
     if (b_host) memcpy(bits, b_host, bbytes);
@@ -277,7 +277,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
     for (int j = 0; j < s->hs.dof; j++) q1.inl[j] = q_aos[j];
     uint8_t* d_out1 = (uint8_t*)(s->pinned + PIN_OUT);
     if ((rc = run_cells(s, q1, 1, nullptr, d_out1, SIRRT_SEM_FRAME, frames[0]))) return rc;
-    CU(cudaStreamSynchronize(s->stream));
+    CU(sirrt_sync(s->stream));
     collided[0] = d_out1[0];
     return SIRRT_OK;
   }
@@ -296,7 +296,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   QView q{q_soa ? (const float*)dq : nullptr, q_soa ? nullptr : (const double*)dq, N, 0, N, s->hs.dof};
   if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME))) return rc;
   if (!odev && !opin) CU(cudaMemcpyAsync(collided, d_out, (size_t)N, cudaMemcpyDeviceToHost, s->stream));
-  CU(cudaStreamSynchronize(s->stream));
+  CU(sirrt_sync(s->stream));
   if (opin) memcpy(collided, d_out, (size_t)N);
   return SIRRT_OK;
 }
@@ -325,7 +325,7 @@ extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo
   if (s->misc.ensure((size_t)W * 4 + 64)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
   // latency path: q is read from, and the interval table written to, the pinned block in place; one synchronisation
   double* dq = (double*)(s->pinned + PIN_Q);
-  if (is_device_ptr(q)) { CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyDeviceToHost, s->stream)); CU(cudaStreamSynchronize(s->stream)); }
+  if (is_device_ptr(q)) { CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyDeviceToHost, s->stream)); CU(sirrt_sync(s->stream)); }
   else memcpy(dq, q, sizeof(double) * dof);
   uint32_t* d_bits = s->misc.as<uint32_t>();
   const int32_t* host_table = (const int32_t*)(s->pinned + PIN_OUT);
@@ -335,7 +335,7 @@ extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo
     int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits, attempt == 0);
     if (rc) return rc;
     if ((rc = run_intervals(s, d_bits, 1, (int32_t*)host_table, Kmax))) return rc;
-    CU(cudaStreamSynchronize(s->stream));
+    CU(sirrt_sync(s->stream));
     if (attempt == 0 && finish_lazy(s)) continue;
     break;
   }
@@ -470,7 +470,7 @@ extern "C" int sirrt_edge_check_batch(sirrt_scene* s, const double* q0, const do
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(first, d_first, n_edges * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   if (coord) CU(cudaMemcpyAsync(coord, d_coord, eb, cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
+  CU(sirrt_sync(st));
   return SIRRT_OK;
 }
 
@@ -563,7 +563,7 @@ extern "C" int sirrt_motion_check_batch(sirrt_scene* s, const double* q0, const 
   s->stats[0] += 2;
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(result, d_first, n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
-  CU(cudaStreamSynchronize(st));
+  CU(sirrt_sync(st));
   for (int64_t e = 0; e < n; e++) {
     const int32_t raw = result[e];  // index of the first colliding cell of this motion, -1 = none
     const long long steps = offs[e + 1] - offs[e] - 1;

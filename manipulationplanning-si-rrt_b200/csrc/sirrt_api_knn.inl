@@ -78,7 +78,7 @@ extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
     // Tree::add_vertex once per planner iteration: the point goes into a pinned ring slot that the append kernel
     // reads in place; nothing is synchronised (queries are ordered behind it on the same stream) except when the
     // ring wraps
-    if (k->ring_next == (int)KPIN_RING_SLOTS) { CU(cudaStreamSynchronize(k->stream)); k->ring_next = 0; }
+    if (k->ring_next == (int)KPIN_RING_SLOTS) { CU(sirrt_sync(k->stream)); k->ring_next = 0; }
     double* slot = (double*)(k->pinned + KPIN_RING) + (size_t)k->ring_next++ * SIRRT_KNN_MAXDIM;
     memcpy(slot, pts, bytes);
     k_knn_append<<<1, 32, 0, k->stream>>>(slot, 1, k->dim, k->pts, k->cap, k->n);
@@ -94,7 +94,7 @@ extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
   const long long tot = (long long)n * k->dim;
   k_knn_append<<<(unsigned)((tot + 255) / 256), 256, 0, k->stream>>>(src, n, k->dim, k->pts, k->cap, k->n);
   CU(cudaGetLastError());
-  CU(cudaStreamSynchronize(k->stream));
+  CU(sirrt_sync(k->stream));
   k->n += n;
   return SIRRT_OK;
 }
@@ -134,7 +134,7 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
     for (int j = 0; j < k->dim; j++) Q.v[j] = queries[j];
     k_knn_nearest1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S1, Q, k->part_d.as<double>(), k->part_i.as<long long>(), k->ticket, o_i, o_d);
     CU(cudaGetLastError());
-    CU(cudaStreamSynchronize(k->stream));
+    CU(sirrt_sync(k->stream));
     idx[0] = o_i[0];
     if (dist2) dist2[0] = o_d[0];
     return SIRRT_OK;
@@ -156,7 +156,7 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
   CU(cudaGetLastError());
   if (!idev && !opin) CU(cudaMemcpyAsync(idx, o_i, sizeof(long long) * nq, cudaMemcpyDeviceToHost, k->stream));
   if (dist2 && !ddev && !opin) CU(cudaMemcpyAsync(dist2, o_d, sizeof(double) * nq, cudaMemcpyDeviceToHost, k->stream));
-  CU(cudaStreamSynchronize(k->stream));
+  CU(sirrt_sync(k->stream));
   if (!idev && opin) memcpy(idx, o_i, sizeof(long long) * nq);
   if (dist2 && !ddev && opin) memcpy(dist2, o_d, sizeof(double) * nq);
   return SIRRT_OK;
@@ -181,7 +181,7 @@ extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, in
   int* ph = (int*)(k->pinned + KPIN_OUT);
   k_knn_radius1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, Q, r2, k->hits.as<int>(), k->ticket + 1, ph, (int)first);
   CU(cudaGetLastError());
-  CU(cudaStreamSynchronize(k->stream));
+  CU(sirrt_sync(k->stream));
   const unsigned cnt = (unsigned)ph[0];
   *n_out = cnt;
   if (cnt == 0) return SIRRT_OK;
@@ -206,7 +206,7 @@ extern "C" int sirrt_knn_topk(sirrt_knn* k, const double* queries, int64_t nq, i
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(idx, k->out_i.p, sizeof(long long) * nq * kk, cudaMemcpyDefault, k->stream));  // host or device result buffers
   if (dist2) CU(cudaMemcpyAsync(dist2, k->out_d.p, sizeof(double) * nq * kk, cudaMemcpyDefault, k->stream));
-  CU(cudaStreamSynchronize(k->stream));
+  CU(sirrt_sync(k->stream));
   return SIRRT_OK;
 }
 
@@ -292,7 +292,7 @@ extern "C" int sirrt_get_distances(sirrt_scene* s, const double* q, int frame, d
   CU(cudaGetLastError());
   std::vector<double> h((size_t)L * C);
   CU(cudaMemcpyAsync(h.data(), dout, sizeof(double) * h.size(), cudaMemcpyDeviceToHost, s->stream));
-  CU(cudaStreamSynchronize(s->stream));
+  CU(sirrt_sync(s->stream));
   for (int l = 0; l < L; l++) {
     double m = 1e300;
     for (int c = 0; c < C; c++) m = std::min(m, h[(size_t)l * C + c]);
@@ -325,7 +325,7 @@ extern "C" int sirrt_scene_fk(sirrt_scene* s, const double* q, double* out) {
   k_fk_dump<<<1, 32, 0, s->stream>>>(s->tb.robot, dq, dof, dq + dof);
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(out, dq + dof, sizeof(double) * 12 * L, cudaMemcpyDeviceToHost, s->stream));
-  CU(cudaStreamSynchronize(s->stream));
+  CU(sirrt_sync(s->stream));
   return SIRRT_OK;
 }
 

@@ -60,7 +60,7 @@ def make_tasks(sp, pkg, n_tasks, pairs_per_scene, seeds_per_pair, tmp, frames=60
     return tasks[:n_tasks]
 
 
-def run_gpu_arm(tasks, gpus, threads, max_time, tmp):
+def run_gpu_arm(tasks, gpus, threads, max_time, tmp, sync="spin"):
     exe = os.path.join(ROOT, "manipulationplanning-si-rrt_b200", "host", "sirrt_mass")
     # ONE task list for every per-GPU process, scenes ordered heaviest (most cubes) first; the processes drain it through a
     # shared counter (--queue), a scene at a time, so no GPU idles while another still has scenes queued
@@ -73,7 +73,8 @@ def run_gpu_arm(tasks, gpus, threads, max_time, tmp):
         f.write(b"\0" * 8)
     t0 = time.perf_counter()
     logs = [(open(os.path.join(tmp, f"gpu{d}.out"), "w+"), open(os.path.join(tmp, f"gpu{d}.err"), "w+")) for d in range(gpus)]
-    procs = [subprocess.Popen([exe, lst, str(d), str(threads), "--max-time", str(max_time), "--queue", queue], stdout=logs[d][0], stderr=logs[d][1])
+    env = dict(os.environ, SIRRT_SYNC=sync)
+    procs = [subprocess.Popen([exe, lst, str(d), str(threads), "--max-time", str(max_time), "--queue", queue], stdout=logs[d][0], stderr=logs[d][1], env=env)
              for d in range(gpus)]
     for p in procs:
         p.wait()
@@ -119,6 +120,8 @@ def main():
     ap.add_argument("--threads", type=int, default=0, help="planner threads per GPU process (0 = host cores / GPUs, clamped to [4, 32])")
     ap.add_argument("--cpu-sample", type=int, default=128)
     ap.add_argument("--max-time", type=float, default=5.0)
+    ap.add_argument("--sync", default="spin", help="spin | yield (SIRRT_SYNC of the planner processes; yield when threads exceed cores)")
+    ap.add_argument("--also", default="", help="extra GPU arms to time on the same tasks, e.g. '8:yield,16:yield' (threads per GPU : sync)")
     a = ap.parse_args()
     if a.threads <= 0:
         a.threads = max(4, min(32, (os.cpu_count() or 16) // a.gpus))
@@ -132,7 +135,16 @@ def main():
     t0 = time.perf_counter()
     tasks = make_tasks(sp, pkg, a.tasks, a.pairs_per_scene, a.seeds_per_pair, tmp)
     gen_s = time.perf_counter() - t0
-    wall, rows, summaries = run_gpu_arm(tasks, a.gpus, a.threads, a.max_time, tmp)
+    wall, rows, summaries = run_gpu_arm(tasks, a.gpus, a.threads, a.max_time, tmp, a.sync)
+    extra = []
+    for spec in [x for x in a.also.split(",") if x]:
+        th, sy = spec.split(":")
+        w2, r2, _ = run_gpu_arm(tasks, a.gpus, int(th), a.max_time, tmp, sy)
+        ms = [r["solve_ms"] for r in r2.values()]
+        same_out = sum(1 for i in r2 if i in rows and r2[i]["solved"] and rows[i]["solved"] and r2[i]["path_hash"] == rows[i]["path_hash"])
+        extra.append({"threads_per_gpu": int(th), "sync": sy, "wall_s": w2, "tasks_per_s": len(r2) / w2, "solved": sum(1 for r in r2.values() if r["solved"]),
+                      "p50_solve_ms": float(np.median(ms)), "solved_by_both_with_identical_path": same_out,
+                      "solved_by_both": sum(1 for i in r2 if i in rows and r2[i]["solved"] and rows[i]["solved"])})
     ncpu = os.cpu_count() or 1
     step = max(1, len(tasks) // max(1, a.cpu_sample))
     sample = list(range(0, len(tasks), step))[: a.cpu_sample]
@@ -158,7 +170,8 @@ def main():
     out = {
         "metric": "mass test: independent SI-RRT planning tasks per second", "n_gpus": a.gpus, "tasks": len(tasks), "task_generation_s": gen_s,
         "recipe": "xArm6 (visual-mesh hulls), 600 frames @ 30 fps, k in {1,20,...,300} bouncing cubes, |dq|_1 > pi, check_scene rule, seed 42",
-        "gpu_arm": {"processes": a.gpus, "threads_per_gpu": a.threads, "wall_s": wall, "tasks_per_s": len(rows) / wall if wall > 0 else None,
+        "gpu_arm_variants": extra,
+        "gpu_arm": {"processes": a.gpus, "threads_per_gpu": a.threads, "sync": a.sync, "wall_s": wall, "tasks_per_s": len(rows) / wall if wall > 0 else None,
                     "solved": sum(1 for r in rows.values() if r["solved"]), "finished": len(rows), "p50_solve_ms": float(np.median(gms)) if gms else None,
                     "mean_solve_ms": float(np.mean(gms)) if gms else None, "per_process": summaries},
         "cpu_arm": {"kind": "port (oracle baseline mode), one process per task", "workers": ncpu, "sample": len(sample), "wall_s": cpu_wall,

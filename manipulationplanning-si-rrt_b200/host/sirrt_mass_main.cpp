@@ -4,16 +4,18 @@
 // box shards them across GPUs by launching one of these per device (scripts/mass_test.py); no inter-GPU traffic.
 //   sirrt_mass <tasks.txt> <device> <threads> [--max-time s] [--max-iters n] [--fixed] [--queue counter.bin]
 // tasks.txt: one "<scene.pack> <seed>" per line.  Output: one JSON line per task (task index = line number), then a
-// summary line.  A scene (pack) is the unit of work: a thread claims the next unclaimed pack from a counter, builds the
-// scene once and runs all seeds of that pack on it.  With --queue the counter lives in a shared file (8 bytes, mmap'ed,
-// atomic fetch-add), so the per-GPU processes of one box, all given the SAME task list, drain one queue: a GPU whose
-// tasks finish early takes the next scene instead of idling (the list is ordered heaviest first by the driver).
+// summary line.  A task is the unit of work: a thread claims the next unclaimed line from a counter and keeps the scene
+// it built for its previous task when the pack is the same (the list keeps the seeds of a pack together).  With --queue
+// the counter lives in a shared file (8 bytes, mmap'ed, atomic fetch-add), so the per-GPU processes of one box, all
+// given the SAME task list, drain one queue: a GPU whose tasks finish early takes the next task instead of idling (the
+// list is ordered heaviest first by the driver).
 #include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <sstream>
 #include <thread>
@@ -65,13 +67,6 @@ int main(int argc, char** argv) {
       if (is >> t.pack >> t.seed) { t.index = (int)tasks.size(); tasks.push_back(t); }
     }
   }
-  // packs in order of first appearance; threads (of every process on the queue) claim them one at a time
-  std::vector<std::string> packs;
-  std::map<std::string, std::vector<int>> by_pack;
-  for (const Task& t : tasks) {
-    if (!by_pack.count(t.pack)) packs.push_back(t.pack);
-    by_pack[t.pack].push_back(t.index);
-  }
   using clk = std::chrono::steady_clock;
   std::mutex out_mu;
   std::atomic<int> n_solved{0}, n_failed{0}, n_done{0};
@@ -79,43 +74,48 @@ int main(int argc, char** argv) {
   const auto t0 = clk::now();
   auto worker = [&](int tid) {
     (void)tid;
+    std::unique_ptr<MDP::CollisionManager> cm;
+    std::string cm_pack;
     for (;;) {
-      const size_t p = (size_t)__atomic_fetch_add(counter, 1ull, __ATOMIC_RELAXED);
-      if (p >= packs.size()) break;
+      const size_t ti = (size_t)__atomic_fetch_add(counter, 1ull, __ATOMIC_RELAXED);
+      if (ti >= tasks.size()) break;
+      const Task& t = tasks[ti];
       try {
-        MDP::CollisionManager cm = MDP::CollisionManager::from_pack_file(packs[p], device, parity);
-        for (int ti : by_pack[packs[p]]) {
-          const Task& t = tasks[ti];
-          MDP::B200Backend be(cm, device, true);
-          MDP::MSIRRT::PlannerConnect<MDP::B200Backend> planner(be, t.seed);
-          if (!planner.valid()) throw std::runtime_error(planner.error());
-          if (max_iters) planner.set_max_iterations(max_iters);
-          if (max_time > 0) planner.set_max_planning_time(max_time);
-          const auto a = clk::now();
-          const bool ok = planner.solve();
-          const uint64_t ns = (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - a).count();
-          uint64_t h = 1469598103934665603ull;
-          double cost = -1;
-          size_t n_way = 0;
-          if (ok) {
-            const auto path = planner.get_result_path(0.0);
-            for (const auto& s : path) { h = fnv(s.q.data(), s.q.size() * sizeof(double), h); h = fnv(&s.time, sizeof(double), h); }
-            cost = path.back().time; n_way = path.size();
-            n_solved++;
-          }
-          solve_ns_total += ns;
-          n_done++;
-          const MDP::MSIRRT::PlannerStats& st = planner.stats();
-          std::lock_guard<std::mutex> lk(out_mu);
-          printf("{\"task\": %d, \"pack\": \"%s\", \"seed\": %d, \"solved\": %s, \"solve_ms\": %.4f, \"cost\": %.17g, \"waypoints\": %zu, "
-                 "\"path_hash\": \"%016llx\", \"iterations\": %llu, \"safe_interval_calls\": %llu, \"state_checks\": %llu}\n",
-                 t.index, t.pack.c_str(), t.seed, ok ? "true" : "false", ns / 1e6, cost, n_way, (unsigned long long)h,
-                 (unsigned long long)st.iterations, (unsigned long long)st.n_safe_interval_calls, (unsigned long long)st.n_state_checks);
+        if (!cm || cm_pack != t.pack) {
+          cm.reset();
+          cm.reset(new MDP::CollisionManager(MDP::CollisionManager::from_pack_file(t.pack, device, parity)));
+          cm_pack = t.pack;
         }
-      } catch (const std::exception& e) {
-        n_failed += (int)by_pack[packs[p]].size();
+        MDP::B200Backend be(*cm, device, true);
+        MDP::MSIRRT::PlannerConnect<MDP::B200Backend> planner(be, t.seed);
+        if (!planner.valid()) throw std::runtime_error(planner.error());
+        if (max_iters) planner.set_max_iterations(max_iters);
+        if (max_time > 0) planner.set_max_planning_time(max_time);
+        const auto a = clk::now();
+        const bool ok = planner.solve();
+        const uint64_t ns = (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(clk::now() - a).count();
+        uint64_t h = 1469598103934665603ull;
+        double cost = -1;
+        size_t n_way = 0;
+        if (ok) {
+          const auto path = planner.get_result_path(0.0);
+          for (const auto& s : path) { h = fnv(s.q.data(), s.q.size() * sizeof(double), h); h = fnv(&s.time, sizeof(double), h); }
+          cost = path.back().time; n_way = path.size();
+          n_solved++;
+        }
+        solve_ns_total += ns;
+        n_done++;
+        const MDP::MSIRRT::PlannerStats& st = planner.stats();
         std::lock_guard<std::mutex> lk(out_mu);
-        fprintf(stderr, "sirrt_mass: %s: %s\n", packs[p].c_str(), e.what());
+        printf("{\"task\": %d, \"pack\": \"%s\", \"seed\": %d, \"solved\": %s, \"solve_ms\": %.4f, \"cost\": %.17g, \"waypoints\": %zu, "
+               "\"path_hash\": \"%016llx\", \"iterations\": %llu, \"safe_interval_calls\": %llu, \"state_checks\": %llu}\n",
+               t.index, t.pack.c_str(), t.seed, ok ? "true" : "false", ns / 1e6, cost, n_way, (unsigned long long)h,
+               (unsigned long long)st.iterations, (unsigned long long)st.n_safe_interval_calls, (unsigned long long)st.n_state_checks);
+      } catch (const std::exception& e) {
+        n_failed++;
+        cm.reset();
+        std::lock_guard<std::mutex> lk(out_mu);
+        fprintf(stderr, "sirrt_mass: %s seed %d: %s\n", t.pack.c_str(), t.seed, e.what());
       }
     }
   };

@@ -153,12 +153,20 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   s->band = 2e-5 * std::max(1.0, tb.extent / 1.5);
   if ((rc = sweep_build(s->hs, tb, s->d, &s->sweep, s->owned))) return bail(fail(rc, "sweep table build failed"));
   if (cudaMallocHost((void**)&s->pinned, PIN_BYTES) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMallocHost failed")); }
-  if (cudaMalloc((void**)&s->lazy_cnt, 64) != cudaSuccess || cudaMemset(s->lazy_cnt, 0, 64) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMalloc failed")); }
+  // cleared ON THE SCENE'S STREAM and waited for: a plain cudaMemset runs on the legacy default stream, is asynchronous
+  // to the host for device memory, and is not ordered against this non-blocking stream -- under load it could land after
+  // the first kernels had started counting
+  if (cudaMalloc((void**)&s->lazy_cnt, 64) != cudaSuccess || cudaMemsetAsync(s->lazy_cnt, 0, 64, s->own_stream) != cudaSuccess ||
+      cudaStreamSynchronize(s->own_stream) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMalloc failed")); }
   for (int i = 0; i < 64; i++) {
     cudaEvent_t e;
     if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); break; }
     s->ev.push_back(e);
   }
+  // the table uploads above are plain cudaMemcpy calls from pageable memory: for small copies the call may return once
+  // the data sits in the driver's staging buffer, with the DMA still queued on the legacy default stream -- which this
+  // scene's non-blocking stream is not ordered against.  Wait for it before the first kernel can be launched.
+  if (cudaStreamSynchronize(cudaStreamLegacy) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "scene upload failed")); }
   *out = s;
   return SIRRT_OK;
 }

@@ -32,7 +32,7 @@ extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn
   cudaDeviceGetAttribute(&k->n_sm, cudaDevAttrMultiProcessorCount, device);
   if (cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&k->pts, sizeof(double) * dim * (size_t)capacity) != cudaSuccess ||
       cudaMallocHost((void**)&k->pinned, KPIN_BYTES) != cudaSuccess || cudaMalloc((void**)&k->ticket, 64) != cudaSuccess ||
-      cudaMemset(k->ticket, 0, 64) != cudaSuccess) {
+      cudaMemsetAsync(k->ticket, 0, 64, k->stream) != cudaSuccess || cudaStreamSynchronize(k->stream) != cudaSuccess) {  // on the store's own stream, see sirrt_scene_create_from_pack
     cudaGetLastError();
     if (k->pts) cudaFree(k->pts);
     if (k->stream) cudaStreamDestroy(k->stream);

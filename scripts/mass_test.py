@@ -144,7 +144,10 @@ def main():
         same_out = sum(1 for i in r2 if i in rows and r2[i]["solved"] and rows[i]["solved"] and r2[i]["path_hash"] == rows[i]["path_hash"])
         extra.append({"threads_per_gpu": int(th), "sync": sy, "wall_s": w2, "tasks_per_s": len(r2) / w2, "solved": sum(1 for r in r2.values() if r["solved"]),
                       "p50_solve_ms": float(np.median(ms)), "solved_by_both_with_identical_path": same_out,
-                      "solved_by_both": sum(1 for i in r2 if i in rows and r2[i]["solved"] and rows[i]["solved"])})
+                      "solved_by_both": sum(1 for i in r2 if i in rows and r2[i]["solved"] and rows[i]["solved"]),
+                      "mismatches": [{"task": i, "pack": os.path.basename(tasks[i][0]), "seed": tasks[i][1], "iters": [rows[i]["iterations"], r2[i]["iterations"]],
+                                      "cost": [rows[i]["cost"], r2[i]["cost"]], "device": [rows[i]["device"], r2[i]["device"]]}
+                                     for i in r2 if i in rows and r2[i]["solved"] and rows[i]["solved"] and r2[i]["path_hash"] != rows[i]["path_hash"]]})
     ncpu = os.cpu_count() or 1
     step = max(1, len(tasks) // max(1, a.cpu_sample))
     sample = list(range(0, len(tasks), step))[: a.cpu_sample]

@@ -400,3 +400,18 @@ def test_hull_support_cells_equal_full_scan(pkg, orc, sp, packs, name):
     b.set_option(pkg.OPT_HULL_CELLS, 1)
     tc, bc, _ = b.safe_intervals_batch(q, 8)
     assert np.array_equal(bc, ba)
+
+
+def test_concurrent_scenes_are_deterministic(pkg, packs, tmp_path):
+    """host/sirrt_stress: 8 host threads, each with its own scene and kNN stores on the same GPU, issue the planner's
+    call mix (safe intervals, cell batches, edge tables, kNN add / nearest / radius, stores created and destroyed) on
+    identical inputs, in both wait modes; every answer must equal the single-thread answer."""
+    import json, os, subprocess
+    exe = os.path.join(os.path.dirname(pkg.__file__), "host", "sirrt_stress")
+    assert os.path.exists(exe), "host/sirrt_stress not built (python __graft_entry__.py)"
+    (tmp_path / "s.pack").write_bytes(packs("mass_test"))
+    for mode in ("spin", "yield"):
+        r = subprocess.run([exe, str(tmp_path / "s.pack"), "8", "6"], capture_output=True, text=True, timeout=300, env=dict(os.environ, SIRRT_SYNC=mode))
+        assert r.returncode == 0, (mode, r.stdout, r.stderr)
+        out = json.loads(r.stdout.strip().splitlines()[-1])
+        assert out["failed_threads"] == 0 and not any(out["mismatch"].values()), out

@@ -15,7 +15,11 @@ struct Range { long long n0, cnt; };
 // lazy = true (single-launch batches of the latency path): nothing is synchronised here; the launch counters
 // travel to PIN_CNT behind the kernels and the caller settles them with finish_lazy() after its one
 // synchronisation (a work-list overflow then repeats the call on the checked path).
-static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits, bool lazy = false) {
+// fuse_table (latency path, at most 64 rows): k_recheck's last block also reduces the rows to intervals; *fused tells the
+// caller that no k_bits_to_intervals launch is needed.
+static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits, bool lazy = false, int32_t* fuse_table = nullptr,
+                    int fuse_kmax = 0, bool* fused = nullptr) {
+  if (fused) *fused = false;
   const int W = s->tb.n_tiles;
   cudaStream_t st = s->stream;
   if (s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(work list) failed");
@@ -72,7 +76,12 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
       R.aabb_d = s->d_aabb_d; R.bits = d_bits; R.n_words = W; R.cells = nullptr; R.counters = wl.count;
       if (self_clearing) { R.ticket = s->lazy_cnt + 4; R.publish = (unsigned int*)(s->pinned + PIN_CNT); }
-      k_recheck<<<s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
+      if (self_clearing && fuse_table && N <= 64) {
+        R.iv = IvParams{d_bits, N, W, s->tb.T, fuse_kmax, fuse_table};
+        if (fused) *fused = true;
+      }
+      // a handful of rows leaves a handful of ambiguous pair tests: a small grid shortens the last-block hand-over
+      k_recheck<<<(self_clearing && N <= 64) ? 16 : s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
       launches++;
       CU(cudaGetLastError());
     }
@@ -250,7 +259,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
     R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
     if (self_clearing) R.ticket = s->lazy_cnt + 4;
-    k_recheck<<<s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
+    k_recheck<<<(self_clearing && qv.cnt <= 256) ? 16 : s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
     s->stats[0] += 2;
     CU(cudaGetLastError());
   }
@@ -332,9 +341,10 @@ extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo
   QView qv{nullptr, dq, 1, 0, 1, dof, 0, {}};
   if (dof <= SIRRT_MAXJ) { qv.inl_on = 1; for (int j = 0; j < dof; j++) qv.inl[j] = dq[j]; }  // angles travel in the kernel parameters
   for (int attempt = 0; attempt < 2; attempt++) {
-    int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits, attempt == 0);
+    bool fused = false;
+    int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits, attempt == 0, (int32_t*)host_table, Kmax, &fused);
     if (rc) return rc;
-    if ((rc = run_intervals(s, d_bits, 1, (int32_t*)host_table, Kmax))) return rc;
+    if (!fused && (rc = run_intervals(s, d_bits, 1, (int32_t*)host_table, Kmax))) return rc;
     CU(sirrt_sync(s->stream));
     if (attempt == 0 && finish_lazy(s)) continue;
     break;

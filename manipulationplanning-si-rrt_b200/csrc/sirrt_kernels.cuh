@@ -497,6 +497,67 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
 // ------------------------------------------------------------------------------------------------
 // FP64 re-check: one warp per ambiguous pair test; formulas identical to the CPU oracle
 // ------------------------------------------------------------------------------------------------
+struct IvParams {
+  const uint32_t* bits;
+  long long N;
+  int n_words, T, Kmax;
+  int32_t* table;  // [N][1+2*Kmax]
+};
+
+__device__ __forceinline__ int warp_excl_scan(int v, int lane, int& total) {
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    int u = __shfl_up_sync(SIRRT_FULL, incl, o);
+    if (lane >= o) incl += u;
+  }
+  total = __shfl_sync(SIRRT_FULL, incl, 31);
+  return incl - v;
+}
+
+// one warp: collision row n -> its line of the interval table.  Rows are read past L1 (__ldcg): on the fused latency path
+// the bits were OR-ed in by other blocks of the same launch.
+__device__ inline void row_to_intervals(const IvParams& P, long long n, int lane) {
+  const uint32_t* row = P.bits + (size_t)n * P.n_words;
+  int32_t* out = P.table + (size_t)n * (1 + 2 * P.Kmax);
+  int n_starts = 0, n_ends = 0;
+  uint32_t prev_safe = 0;  // safe bit of the last frame of the previous group (frame -1: "collision")
+  for (int w0 = 0; w0 < P.n_words; w0 += 32) {
+    const int w = w0 + lane;
+    uint32_t s = 0;
+    if (w < P.n_words) {
+      const int left = P.T - w * 32;
+      s = ~__ldcg(row + w) & (left >= 32 ? 0xffffffffu : ((1u << left) - 1u));
+    }
+    uint32_t prev_msb = __shfl_up_sync(SIRRT_FULL, s >> 31, 1);
+    if (lane == 0) prev_msb = prev_safe;
+    uint32_t next_lsb = __shfl_down_sync(SIRRT_FULL, s & 1u, 1);
+    if (lane == 31) {
+      next_lsb = 0;
+      if (w + 1 < P.n_words) next_lsb = (~__ldcg(row + w + 1)) & 1u;  // frame (w+1)*32 < T, so the bit is valid
+    }
+    uint32_t starts = s & ~((s << 1) | prev_msb);
+    uint32_t ends = s & ~((s >> 1) | (next_lsb << 31));
+    int ts, te;
+    int rs = n_starts + warp_excl_scan(__popc(starts), lane, ts);
+    int re = n_ends + warp_excl_scan(__popc(ends), lane, te);
+    while (starts) { const int b = __ffs(starts) - 1; starts &= starts - 1; if (rs < P.Kmax) out[1 + 2 * rs] = w * 32 + b; rs++; }
+    while (ends) { const int b = __ffs(ends) - 1; ends &= ends - 1; if (re < P.Kmax) out[2 + 2 * re] = w * 32 + b; re++; }
+    n_starts += ts; n_ends += te;
+    prev_safe = __shfl_sync(SIRRT_FULL, s >> 31, 31);
+  }
+  // unused pairs = -1; the count is the true number of intervals even when it exceeds Kmax
+  for (int k = 2 * min(n_starts, P.Kmax) + lane; k < 2 * P.Kmax; k += 32) out[1 + k] = -1;
+  if (lane == 0) out[0] = n_starts;
+}
+
+__global__ void __launch_bounds__(256) k_bits_to_intervals(const __grid_constant__ IvParams P) {
+  const int lane = threadIdx.x & 31;
+  const long long n = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (n >= P.N) return;
+  row_to_intervals(P, n, lane);
+}
+
 struct RecheckParams {
   DScene sc;
   QView q;
@@ -512,6 +573,7 @@ struct RecheckParams {
   // and the ticket, so that a call needs neither a memset before nor a copy after its kernels
   unsigned int* ticket;
   unsigned int* publish;
+  IvParams iv;              // latency path with a small table: iv.table != null -> the last block also turns the rows into intervals
 };
 
 __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const LinkXfD& X, int l, const DShape& sh,
@@ -633,16 +695,22 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
     }
   }
   }
-  if (P.ticket) {  // latency path: last block out publishes and clears the launch counters
+  if (P.ticket) {  // latency path: last block out (fuses the interval reduction,) publishes and clears the launch counters
+    __shared__ bool last;
+    __threadfence();
     __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(P.ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    if (P.iv.table) {
+      for (long long n = threadIdx.x >> 5; n < P.iv.N; n += SIRRT_WARPS_PER_BLOCK) row_to_intervals(P.iv, n, lane);
+      __syncthreads();
+    }
     if (threadIdx.x == 0) {
-      __threadfence();
-      if (atomicAdd(P.ticket, 1u) == gridDim.x - 1) {
-        __threadfence();
-        volatile unsigned int* c = P.counters;
-        for (int i = 0; i < 4; i++) { const unsigned int v = c[i]; if (P.publish) P.publish[i] = v; c[i] = 0u; }
-        *P.ticket = 0u;
-      }
+      volatile unsigned int* c = P.counters;
+      for (int i = 0; i < 4; i++) { const unsigned int v = c[i]; if (P.publish) P.publish[i] = v; c[i] = 0u; }
+      *P.ticket = 0u;
     }
   }
 }
@@ -732,57 +800,3 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
 // ascending, so the k-th start pairs with the k-th end; each is ranked with a warp prefix sum of
 // popcounts on top of a running count carried across groups of 32 words.
 // ------------------------------------------------------------------------------------------------
-struct IvParams {
-  const uint32_t* bits;
-  long long N;
-  int n_words, T, Kmax;
-  int32_t* table;  // [N][1+2*Kmax]
-};
-
-__device__ __forceinline__ int warp_excl_scan(int v, int lane, int& total) {
-  int incl = v;
-#pragma unroll
-  for (int o = 1; o < 32; o <<= 1) {
-    int u = __shfl_up_sync(SIRRT_FULL, incl, o);
-    if (lane >= o) incl += u;
-  }
-  total = __shfl_sync(SIRRT_FULL, incl, 31);
-  return incl - v;
-}
-
-__global__ void __launch_bounds__(256) k_bits_to_intervals(const __grid_constant__ IvParams P) {
-  const int lane = threadIdx.x & 31;
-  const long long n = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (n >= P.N) return;
-  const uint32_t* row = P.bits + (size_t)n * P.n_words;
-  int32_t* out = P.table + (size_t)n * (1 + 2 * P.Kmax);
-  int n_starts = 0, n_ends = 0;
-  uint32_t prev_safe = 0;  // safe bit of the last frame of the previous group (frame -1: "collision")
-  for (int w0 = 0; w0 < P.n_words; w0 += 32) {
-    const int w = w0 + lane;
-    uint32_t s = 0;
-    if (w < P.n_words) {
-      const int left = P.T - w * 32;
-      s = ~row[w] & (left >= 32 ? 0xffffffffu : ((1u << left) - 1u));
-    }
-    uint32_t prev_msb = __shfl_up_sync(SIRRT_FULL, s >> 31, 1);
-    if (lane == 0) prev_msb = prev_safe;
-    uint32_t next_lsb = __shfl_down_sync(SIRRT_FULL, s & 1u, 1);
-    if (lane == 31) {
-      next_lsb = 0;
-      if (w + 1 < P.n_words) next_lsb = (~row[w + 1]) & 1u;  // frame (w+1)*32 < T, so the bit is valid
-    }
-    uint32_t starts = s & ~((s << 1) | prev_msb);
-    uint32_t ends = s & ~((s >> 1) | (next_lsb << 31));
-    int ts, te;
-    int rs = n_starts + warp_excl_scan(__popc(starts), lane, ts);
-    int re = n_ends + warp_excl_scan(__popc(ends), lane, te);
-    while (starts) { const int b = __ffs(starts) - 1; starts &= starts - 1; if (rs < P.Kmax) out[1 + 2 * rs] = w * 32 + b; rs++; }
-    while (ends) { const int b = __ffs(ends) - 1; ends &= ends - 1; if (re < P.Kmax) out[2 + 2 * re] = w * 32 + b; re++; }
-    n_starts += ts; n_ends += te;
-    prev_safe = __shfl_sync(SIRRT_FULL, s >> 31, 31);
-  }
-  // unused pairs = -1; the count is the true number of intervals even when it exceeds Kmax
-  for (int k = 2 * min(n_starts, P.Kmax) + lane; k < 2 * P.Kmax; k += 32) out[1 + k] = -1;
-  if (lane == 0) out[0] = n_starts;
-}

@@ -1,0 +1,33 @@
+"""CPU-run check of the GJK support-candidate cells (csrc/sirrt_tables.hpp: build_hull_cells, csrc/sirrt_device.cuh:
+hull_cell): tests/hull_cells_host_main.cu is compiled with nvcc and run on the HOST -- for every hull of the shipped
+xArm6 scene and ~1.4 million directions (random over seven decades of magnitude, cell corners / edges with a hair of
+jitter, cube edges, hull vertices, edge and cross-product directions) the candidate scan must pick the vertex the full
+scan picks, in FP32 and in FP64."""
+import json
+import os
+import shutil
+import subprocess
+
+import pytest
+
+from conftest import ROOT
+
+
+def test_support_cells_pick_the_full_scan_winner(packs, tmp_path):
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available")
+    exe = os.path.join(ROOT, "tests", "_build", "hull_cells_host")
+    src = os.path.join(ROOT, "tests", "hull_cells_host_main.cu")
+    csrc = os.path.join(ROOT, "manipulationplanning-si-rrt_b200", "csrc")
+    os.makedirs(os.path.dirname(exe), exist_ok=True)
+    deps = [src] + [os.path.join(csrc, f) for f in ("sirrt_device.cuh", "sirrt_tables.hpp", "sirrt_host.hpp")]
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(d) for d in deps):
+        subprocess.check_call([nvcc, "-O2", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-I", csrc, "-I", os.path.join(ROOT, "include"),
+                               "-o", exe, src])
+    (tmp_path / "s.pack").write_bytes(packs("flying_boxes"))
+    r = subprocess.run([exe, str(tmp_path / "s.pack"), "100000"], capture_output=True, text=True, timeout=600)
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert r.returncode == 0 and out["hulls"] >= 5 and out["directions"] > 700000, (out, r.stderr)
+    assert out["mismatch_fp32"] == 0 and out["mismatch_fp64"] == 0, out
+    assert out["mean_candidates_per_cell"] < 32, out   # the point of the cells: one lane-step per support query on average

@@ -20,8 +20,19 @@ namespace MDP {
 
 class B200Backend {
  public:
-  explicit B200Backend(CollisionManager& cm, int device = 0, bool use_edge_table = true) : cm_(cm), device_(device), use_table_(use_edge_table) {}
-  ~B200Backend() { for (sirrt_knn* k : knn_) if (k) sirrt_knn_destroy(k); }
+  // knn_pool (optional, owned by the caller, one per host thread and device): vertex stores are taken from / returned to it
+  // instead of being allocated and freed per planner -- a 2 x 50 MB cudaMalloc / cudaFree pair per task, the latter a
+  // device-wide synchronisation that stalls every other planner thread sharing the GPU (mass test)
+  explicit B200Backend(CollisionManager& cm, int device = 0, bool use_edge_table = true, std::vector<sirrt_knn*>* knn_pool = nullptr)
+      : cm_(cm), device_(device), use_table_(use_edge_table), pool_(knn_pool) {}
+  ~B200Backend() {
+    for (sirrt_knn* k : knn_) {
+      if (!k) continue;
+      if (pool_ && sirrt_knn_clear(k) == SIRRT_OK) pool_->push_back(k);
+      else sirrt_knn_destroy(k);
+    }
+  }
+  static void destroy_pool(std::vector<sirrt_knn*>& pool) { for (sirrt_knn* k : pool) sirrt_knn_destroy(k); pool.clear(); }
   B200Backend(const B200Backend&) = delete;
   B200Backend& operator=(const B200Backend&) = delete;
 
@@ -71,6 +82,11 @@ class B200Backend {
 
   int knn_new() {
     sirrt_knn* k = nullptr;
+    if (pool_ && !pool_->empty()) {
+      k = pool_->back(); pool_->pop_back();
+      knn_.push_back(k);
+      return (int)knn_.size() - 1;
+    }
     if (sirrt_knn_create(dof(), 1 << 20, device_, &k)  /* the reference reserves 1e6 vertices per tree (PlannerConnect.cpp:16-18) */ != SIRRT_OK) throw std::runtime_error(std::string("libsirrt_b200: ") + sirrt_last_error());
     knn_.push_back(k);
     return (int)knn_.size() - 1;
@@ -103,6 +119,7 @@ class B200Backend {
   CollisionManager& cm_;
   int device_;
   bool use_table_;
+  std::vector<sirrt_knn*>* pool_ = nullptr;
   std::vector<sirrt_knn*> knn_;
   std::vector<int64_t> rad_;
   std::vector<double> e_q0_, e_dir_, e_states_;

@@ -76,6 +76,7 @@ int main(int argc, char** argv) {
     (void)tid;
     std::unique_ptr<MDP::CollisionManager> cm;
     std::string cm_pack;
+    std::vector<sirrt_knn*> knn_pool;  // this thread's vertex stores, reused by its consecutive tasks
     for (;;) {
       const size_t ti = (size_t)__atomic_fetch_add(counter, 1ull, __ATOMIC_RELAXED);
       if (ti >= tasks.size()) break;
@@ -86,7 +87,7 @@ int main(int argc, char** argv) {
           cm.reset(new MDP::CollisionManager(MDP::CollisionManager::from_pack_file(t.pack, device, parity)));
           cm_pack = t.pack;
         }
-        MDP::B200Backend be(*cm, device, true);
+        MDP::B200Backend be(*cm, device, true, &knn_pool);
         MDP::MSIRRT::PlannerConnect<MDP::B200Backend> planner(be, t.seed);
         if (!planner.valid()) throw std::runtime_error(planner.error());
         if (max_iters) planner.set_max_iterations(max_iters);
@@ -118,6 +119,7 @@ int main(int argc, char** argv) {
         fprintf(stderr, "sirrt_mass: %s seed %d: %s\n", t.pack.c_str(), t.seed, e.what());
       }
     }
+    MDP::B200Backend::destroy_pool(knn_pool);
   };
   std::vector<std::thread> th;
   for (int t = 0; t < n_threads; t++) th.emplace_back(worker, t);

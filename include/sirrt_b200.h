@@ -108,6 +108,11 @@ int sirrt_safe_intervals_batch(sirrt_scene*, const float* q_soa, int64_t N, int3
 /* same, double-precision configurations as array of structures [N][dof] (edge tables, §7.3) with
  * explicit semantics (SIRRT_SEM_*) */
 int sirrt_collision_bits_f64(sirrt_scene*, const double* q_aos, int64_t N, int semantics, uint32_t* bits);
+/* windowed form of the edge table: row i is only computed for the n_tiles 32-frame tiles starting at tile first_tile[i]
+ * (host array [N], clamped to the scene); bits keeps the full-row layout [N][ceil(T/32)], words outside a row's window carry
+ * no information (zero, or all ones when the configuration hits a static obstacle) */
+int sirrt_collision_bits_window_f64(sirrt_scene*, const double* q_aos, int64_t N, int semantics, const int32_t* first_tile, int n_tiles,
+                                    uint32_t* bits);
 /* N independent (configuration, frame) cells: check_collision_frame semantics */
 int sirrt_check_frames_batch(sirrt_scene*, const float* q_soa, const int32_t* frames, int64_t N, uint8_t* collided);
 int sirrt_check_frames_batch_f64(sirrt_scene*, const double* q_aos, const int32_t* frames, int64_t N, uint8_t* collided);

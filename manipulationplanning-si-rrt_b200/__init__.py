@@ -49,6 +49,7 @@ EXPORTS = {
     "sirrt_get_distances": (_i32, [_vp, _vp, _i32, _vp, _vp]),
     "sirrt_safe_intervals_batch": (_i32, [_vp, _vp, _i64, _vp, _i32, _vp, _vp]),
     "sirrt_collision_bits_f64": (_i32, [_vp, _vp, _i64, _i32, _vp]),
+    "sirrt_collision_bits_window_f64": (_i32, [_vp, _vp, _i64, _i32, _vp, _i32, _vp]),
     "sirrt_check_frames_batch": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "sirrt_check_frames_batch_f64": (_i32, [_vp, _vp, _vp, _i64, _vp]),
     "sirrt_edge_check_batch": (_i32, [_vp, _vp, _vp, _vp, _vp, _i64, _f64, _vp, _vp]),
@@ -200,6 +201,15 @@ class Scene:
         q = np.ascontiguousarray(q_aos, np.float64).reshape(-1, self.dof)
         bits = np.zeros((q.shape[0], self.words), np.uint32)
         _ck(_lib.sirrt_collision_bits_f64(self._h, q.ctypes.data, q.shape[0], semantics, bits.ctypes.data))
+        return bits
+
+    def collision_bits_window_f64(self, q_aos, first_tile, n_tiles: int, semantics: int = SEM_FRAME):
+        """Edge-table rows restricted to n_tiles 32-frame tiles from first_tile[i]; words outside the window carry no information."""
+        q = np.ascontiguousarray(q_aos, np.float64).reshape(-1, self.dof)
+        ft = np.ascontiguousarray(first_tile, np.int32).reshape(-1)
+        assert ft.size == q.shape[0]
+        bits = np.zeros((q.shape[0], self.words), np.uint32)
+        _ck(_lib.sirrt_collision_bits_window_f64(self._h, q.ctypes.data, q.shape[0], semantics, ft.ctypes.data, int(n_tiles), bits.ctypes.data))
         return bits
 
     def check_frames_batch(self, q_soa, frames):

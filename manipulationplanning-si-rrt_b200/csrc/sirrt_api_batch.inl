@@ -17,8 +17,9 @@ struct Range { long long n0, cnt; };
 // synchronisation (a work-list overflow then repeats the call on the checked path).
 // fuse_table (latency path, at most 64 rows): k_recheck's last block also reduces the rows to intervals; *fused tells the
 // caller that no k_bits_to_intervals launch is needed.
+// row_tiles / win_tiles: every row only needs the win_tiles tiles starting at row_tiles[i].x (windowed edge tables).
 static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits, bool lazy = false, int32_t* fuse_table = nullptr,
-                    int fuse_kmax = 0, bool* fused = nullptr) {
+                    int fuse_kmax = 0, bool* fused = nullptr, const int2* row_tiles = nullptr, int win_tiles = 0) {
   if (fused) *fused = false;
   const int W = s->tb.n_tiles;
   cudaStream_t st = s->stream;
@@ -26,7 +27,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
   std::vector<Range> todo;
   for (long long n0 = 0; n0 < N; n0 += s->chunk_configs) todo.push_back({n0, std::min(s->chunk_configs, N - n0)});
   uint64_t launches = 0, rechecked = 0, near = 0, exact = 0, sweep_ns = 0;
-  const bool sweep = s->use_sweep && s->sweep.supported && N >= s->sweep_min_configs;
+  const bool sweep = !row_tiles && s->use_sweep && s->sweep.supported && N >= s->sweep_min_configs;
   const bool may_defer = !sweep && s->tb.has_hull && s->defer_max_configs > 0;
   if (may_defer && s->tasks.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(task list) failed");
   while (!todo.empty()) {
@@ -48,6 +49,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         BitsParams P{};
         P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.bits = d_bits; P.n_words = W;
         P.semantics = semantics; P.band = (float)s->band;
+        P.row_tiles = row_tiles ? row_tiles + qv.n0 : nullptr;
         const bool defer = may_defer && qv.cnt <= s->defer_max_configs && nr == 1;  // one task list: one range at a time
         if (defer) {
           P.tasks = WorkList{s->tasks.as<WorkItem>(), wl.count + 3, s->wl_cap};
@@ -56,9 +58,10 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         }
         // small batches: split each row over several warps (tile chunks) to fill the machine
         long long target = (long long)s->n_sm * 32;
-        int n_chunks = (int)std::max(1ll, std::min((long long)W, target / std::max(1ll, qv.cnt)));
-        P.tiles_per_chunk = (W + n_chunks - 1) / n_chunks;
-        P.n_chunks = (W + P.tiles_per_chunk - 1) / P.tiles_per_chunk;
+        const int Wr = row_tiles ? std::max(1, std::min(win_tiles, W)) : W;  // tiles a row needs
+        int n_chunks = (int)std::max(1ll, std::min((long long)Wr, target / std::max(1ll, qv.cnt)));
+        P.tiles_per_chunk = (Wr + n_chunks - 1) / n_chunks;
+        P.n_chunks = (Wr + P.tiles_per_chunk - 1) / P.tiles_per_chunk;
         const int grid = grid_for(qv.cnt * P.n_chunks, s->n_sm, 8);
         if (s->tb.has_hull) k_collide_bits<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         else k_collide_bits<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
@@ -149,7 +152,7 @@ static int stage_in(sirrt_scene* s, DevBuf& buf, const void* src, size_t bytes, 
 }
 
 static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, int32_t* table, int Kmax, uint32_t* bits,
-                          uint64_t* near_contact_count) {
+                          uint64_t* near_contact_count, const int2* row_tiles = nullptr, int win_tiles = 0) {
   const int W = s->tb.n_tiles;
   CU(cudaSetDevice(s->device));
   memset(s->stats, 0, sizeof s->stats);
@@ -166,7 +169,8 @@ static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, i
   const bool small = N <= s->chunk_configs && (!table || tdev || tbytes <= PIN_OUT_CAP / 2) && (!bits || bits_dev || bbytes <= PIN_OUT_CAP / 2);
   for (int attempt = 0; attempt < 2; attempt++) {
     const bool lazy = small && attempt == 0;
-    int rc = run_bits(s, q, N, semantics, d_bits, lazy);
+    if (row_tiles) CU(cudaMemsetAsync(d_bits, 0, bbytes, s->stream));  // defined content outside the rows' windows (callers only look inside)
+    int rc = run_bits(s, q, N, semantics, d_bits, lazy, nullptr, 0, nullptr, row_tiles, win_tiles);
     if (rc) return rc;
     int32_t* t_host = nullptr;
     uint32_t* b_host = nullptr;
@@ -218,6 +222,37 @@ extern "C" int sirrt_collision_bits_f64(sirrt_scene* s, const double* q_aos, int
   if (rc) return rc;
   QView q{nullptr, (const double*)dq, N, 0, N, s->hs.dof};
   return bits_and_table(s, q, N, semantics, nullptr, 0, bits, nullptr);
+}
+
+// §7.3 edge table, windowed: the departure-time scan of one edge (PlannerConnect.cpp:494-537) moves every state's frame
+// by one per step, so the table only needs, per state, the frames around the current query.
+extern "C" int sirrt_collision_bits_window_f64(sirrt_scene* s, const double* q_aos, int64_t N, int semantics, const int32_t* first_tile, int n_tiles,
+                                               uint32_t* bits) {
+  if (!s || !q_aos || !bits || !first_tile || N < 0 || n_tiles < 1 || (semantics != SIRRT_SEM_INTERVAL && semantics != SIRRT_SEM_FRAME))
+    return fail(SIRRT_E_ARG, "sirrt_collision_bits_window_f64: bad argument");
+  if (N == 0) return SIRRT_OK;
+  if (is_device_ptr(first_tile)) return fail(SIRRT_E_ARG, "sirrt_collision_bits_window_f64: first_tile is a host array");
+  CU(cudaSetDevice(s->device));
+  const void* dq = nullptr;
+  int rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq, PIN_Q, 64 << 10);
+  if (rc) return rc;
+  const int W = s->tb.n_tiles;
+  std::vector<int2> rt((size_t)N);
+  for (int64_t i = 0; i < N; i++) {
+    const int lo = std::max(0, std::min(first_tile[i], W));
+    rt[i] = make_int2(lo, std::min(W, lo + n_tiles));
+  }
+  const int2* d_rt = nullptr;
+  const size_t rb = (size_t)N * sizeof(int2);
+  if (rb <= PIN_FR_CAP) { memcpy(s->pinned + PIN_FR, rt.data(), rb); d_rt = (const int2*)(s->pinned + PIN_FR); }  // read in place
+  else {
+    if (s->frames.ensure(rb)) return fail(SIRRT_E_CUDA, "cudaMalloc(row windows) failed");
+    CU(cudaMemcpyAsync(s->frames.p, rt.data(), rb, cudaMemcpyHostToDevice, s->stream));
+    CU(sirrt_sync(s->stream));  // rt is a local
+    d_rt = s->frames.as<int2>();
+  }
+  QView q{nullptr, (const double*)dq, N, 0, N, s->hs.dof};
+  return bits_and_table(s, q, N, semantics, nullptr, 0, bits, nullptr, d_rt, n_tiles);
 }
 
 // ---- a4: independent (configuration, frame) cells ------------------------------------------------

@@ -189,6 +189,7 @@ struct BitsParams {
   WorkList wl;
   WorkList tasks;       // items != null: hull pair tests are NOT run by the producing warp but appended here for k_gjk_tasks
   const float* aabb_f;  // robot slots: [(slot*6 + k)*Tp + f] coal AABB lo(3) hi(3); may be null
+  const int2* row_tiles; // windowed rows (edge tables around a departure time): configuration i only needs tiles [x, y); null = every tile
   double* xf;           // deferred tasks: FP64 link transforms [cnt][n_links][12] written here for k_gjk_tasks; may be null
   uint32_t* bits;       // [N][W]
   int n_words;          // W
@@ -219,8 +220,10 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   for (long long item = warp0; item < n_items; item += n_warps) {
     const long long n = P.q.n0 + item / P.n_chunks;
     const int chunk = (int)(item % P.n_chunks);
-    const int tile_lo = chunk * P.tiles_per_chunk;
-    const int tile_hi = min(tile_lo + P.tiles_per_chunk, sc.n_tiles);
+    int tile_lo = chunk * P.tiles_per_chunk, tile_end = sc.n_tiles;
+    if (P.row_tiles) { const int2 rt = P.row_tiles[n - P.q.n0]; tile_lo += rt.x; tile_end = min(rt.y, sc.n_tiles); }
+    const int tile_hi = min(tile_lo + P.tiles_per_chunk, tile_end);
+    if (P.row_tiles && tile_lo >= tile_hi) continue;  // this chunk lies past the row's window
     __syncwarp();
     setup_links(rb, sc, P.q, n, W, lane, P.xf);
     const int L = rb.n_links;

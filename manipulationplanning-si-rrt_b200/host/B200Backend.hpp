@@ -49,6 +49,7 @@ class B200Backend {
     const bool same = steps == e_steps_ && e_q0_.size() == (size_t)d && !memcmp(e_q0_.data(), q0, d * sizeof(double)) &&
                       !memcmp(e_dir_.data(), dir, d * sizeof(double));
     if (!same) {
+      note_edge_done();
       e_q0_.assign(q0, q0 + d); e_dir_.assign(dir, dir + d); e_steps_ = steps; e_uses_ = 0; e_have_table_ = false;
       e_states_.resize((size_t)n * d);
       for (int s = 0; s < n; s++)
@@ -57,13 +58,35 @@ class B200Backend {
     e_uses_++;
     frames_.resize(n);
     for (int s = 0; s < n; s++) frames_[s] = (int32_t)(t0 + (t1 - t0) * (double)s / (double)steps);  // :886
-    if (use_table_ && e_uses_ >= 2 && !e_have_table_) {
-      cm_.collision_bits(e_states_, SIRRT_SEM_FRAME, e_bits_);
-      e_have_table_ = true;
-      n_tables_++;
-    }
-    if (e_have_table_) {
+    if (use_table_ && e_uses_ >= 2) {
+      // windowed table: the scan moves every state's frame by about one per departure time, so the rows are only
+      // computed for kWinTiles 32-frame tiles from the current frames on, in the direction the scan moves; the window
+      // is rebuilt when a query leaves it
       const int W = cm_.words();
+      bool covered = e_have_table_;
+      for (int s = 0; s < n && covered; s++) {
+        const int f = frames_[s];
+        if (f >= 0 && f < T && (f < 32 * e_tlo_[s] || f >= 32 * e_thi_[s])) covered = false;
+      }
+      if (!covered) {
+        const bool forward = frames_[0] >= e_prev_f0_;
+        e_tlo_.resize(n); e_thi_.resize(n);
+        for (int s = 0; s < n; s++) {
+          const int tile = std::min(std::max(frames_[s], 0), T - 1) >> 5;
+          const int lo = std::max(0, forward ? tile : tile - (kWinTiles - 1));
+          e_tlo_[s] = lo; e_thi_[s] = std::min(W, lo + kWinTiles);
+        }
+        e_bits_.assign((size_t)n * W, 0u);
+        if (W <= kWinTiles + 1) {
+          cm_.collision_bits(e_states_, SIRRT_SEM_FRAME, e_bits_);
+          for (int s = 0; s < n; s++) { e_tlo_[s] = 0; e_thi_[s] = W; }
+        } else if (sirrt_collision_bits_window_f64(cm_.handle(), e_states_.data(), n, SIRRT_SEM_FRAME, e_tlo_.data(), kWinTiles, e_bits_.data()) != SIRRT_OK) {
+          throw std::runtime_error(std::string("libsirrt_b200: ") + sirrt_last_error());
+        }
+        e_have_table_ = true;
+        n_tables_++;
+      }
+      e_prev_f0_ = frames_[0];
       for (int s = 0; s < n; s++) {
         const int f = frames_[s];
         if (f < 0 || f >= T) return s;  // the reference indexes unchecked (CollisionManager.cpp:369); we answer "collided"
@@ -72,6 +95,7 @@ class B200Backend {
       n_lookups_++;
       return -1;
     }
+    e_prev_f0_ = frames_[0];
     cells_.assign(n, 0);
     if (sirrt_check_frames_batch_f64(cm_.handle(), e_states_.data(), frames_.data(), n, cells_.data()) != SIRRT_OK)
       throw std::runtime_error(std::string("libsirrt_b200: ") + sirrt_last_error());
@@ -110,11 +134,18 @@ class B200Backend {
     out.assign(rad_.begin(), rad_.begin() + n);
   }
 
+  // histogram of queries per distinct edge: 1, 2, 3, 4-7, 8-15, 16+ (what the "table on the 2nd use" rule is judged by)
+  const uint64_t* uses_histogram() { note_edge_done(); e_uses_ = 0; return uses_hist_; }
   uint64_t n_tables() const { return n_tables_; }
   uint64_t n_cell_batches() const { return n_cell_batches_; }
   uint64_t n_lookups() const { return n_lookups_; }
 
  private:
+  void note_edge_done() {
+    if (e_uses_ <= 0) return;
+    const int b = e_uses_ == 1 ? 0 : e_uses_ == 2 ? 1 : e_uses_ == 3 ? 2 : e_uses_ < 8 ? 3 : e_uses_ < 16 ? 4 : 5;
+    uses_hist_[b]++;
+  }
   void ck(int rc) const { if (rc != SIRRT_OK) throw std::runtime_error(std::string("libsirrt_b200: ") + sirrt_last_error()); }
   CollisionManager& cm_;
   int device_;
@@ -126,9 +157,11 @@ class B200Backend {
   int e_steps_ = -1, e_uses_ = 0;
   bool e_have_table_ = false;
   std::vector<uint32_t> e_bits_;
-  std::vector<int32_t> frames_;
+  std::vector<int32_t> frames_, e_tlo_, e_thi_;  // e_tlo_/e_thi_: tiles [lo, hi) each state's table row is valid for
+  int e_prev_f0_ = 0;
+  static constexpr int kWinTiles = 3;            // >= 64 frames ahead of the query that built the window
   std::vector<uint8_t> cells_;
-  uint64_t n_tables_ = 0, n_cell_batches_ = 0, n_lookups_ = 0;
+  uint64_t n_tables_ = 0, n_cell_batches_ = 0, n_lookups_ = 0, uses_hist_[6] = {0, 0, 0, 0, 0, 0};
 };
 
 }  // namespace MDP

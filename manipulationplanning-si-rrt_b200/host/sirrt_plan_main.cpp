@@ -63,6 +63,11 @@ int main(int argc, char** argv) {
     }
     log.extra = {{"iterations", (double)st.iterations}, {"motion_checks", (double)st.n_motion_checks}, {"edge_tables", (double)be.n_tables()},
                  {"edge_cell_batches", (double)be.n_cell_batches()}, {"edge_table_lookups", (double)be.n_lookups()}};
+    {
+      const uint64_t* h = be.uses_histogram();
+      const char* names[6] = {"edges_used_1", "edges_used_2", "edges_used_3", "edges_used_4_7", "edges_used_8_15", "edges_used_16_up"};
+      for (int i = 0; i < 6; i++) log.extra.push_back({names[i], (double)h[i]});
+    }
     if (to_stdout) std::cout << log.to_json() << std::endl;
     else {
       const std::string fn = log.save(std::to_string(std::chrono::system_clock::to_time_t(std::chrono::system_clock::now())), seed);

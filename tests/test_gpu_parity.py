@@ -415,3 +415,25 @@ def test_concurrent_scenes_are_deterministic(pkg, packs, tmp_path):
         assert r.returncode == 0, (mode, r.stdout, r.stderr)
         out = json.loads(r.stdout.strip().splitlines()[-1])
         assert out["failed_threads"] == 0 and not any(out["mismatch"].values()), out
+
+
+@pytest.mark.parametrize("name", ["flying_boxes", "mass_test", "synB_32_200", "multiple_robots"])
+def test_windowed_edge_table_equals_full_rows(pkg, sp, packs, name):
+    """sirrt_collision_bits_window_f64: inside each row's window (n_tiles 32-frame tiles from first_tile[i]) the words equal
+    the full edge-table rows of sirrt_collision_bits_f64 (words outside carry no information).  Windows at the start, in the middle,
+    hanging over the end of the scene and entirely past it."""
+    pk = packs(name)
+    dev = pkg.Scene(pk)
+    W = dev.words
+    q = random_q(sp, pk, 40, 67).T.astype(np.float64)
+    full = dev.collision_bits_f64(q, pkg.SEM_FRAME)
+    rng = np.random.default_rng(68)
+    for n_tiles in (1, 3):
+        ft = rng.integers(-2, W + 2, 40).astype(np.int32)
+        ft[:4] = [0, W - 1, W, -5]
+        win = dev.collision_bits_window_f64(q, ft, n_tiles, pkg.SEM_FRAME)
+        for i in range(40):
+            lo = min(max(int(ft[i]), 0), W)
+            hi = min(W, lo + n_tiles)
+            assert np.array_equal(win[i, lo:hi], full[i, lo:hi]), (name, n_tiles, i, lo, hi)
+    assert full.any()

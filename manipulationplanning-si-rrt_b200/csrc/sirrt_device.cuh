@@ -109,12 +109,12 @@ struct WorkItem {  // one ambiguous pair test for the FP64 re-check
 // ---------------------------------------------------------------------------------------------
 // small algebra
 // ---------------------------------------------------------------------------------------------
-template <typename T> __device__ __forceinline__ T dot3(const T* a, const T* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
-template <typename T> __device__ __forceinline__ void sub3(T* o, const T* a, const T* b) { o[0] = a[0] - b[0]; o[1] = a[1] - b[1]; o[2] = a[2] - b[2]; }
-template <typename T> __device__ __forceinline__ void cross3(T* o, const T* a, const T* b) {
+template <typename T> __host__ __device__ __forceinline__ T dot3(const T* a, const T* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+template <typename T> __host__ __device__ __forceinline__ void sub3(T* o, const T* a, const T* b) { o[0] = a[0] - b[0]; o[1] = a[1] - b[1]; o[2] = a[2] - b[2]; }
+template <typename T> __host__ __device__ __forceinline__ void cross3(T* o, const T* a, const T* b) {
   o[0] = a[1] * b[2] - a[2] * b[1]; o[1] = a[2] * b[0] - a[0] * b[2]; o[2] = a[0] * b[1] - a[1] * b[0];
 }
-template <typename T> __device__ __forceinline__ void matvec(T* o, const T* R, const T* v) {
+template <typename T> __host__ __device__ __forceinline__ void matvec(T* o, const T* R, const T* v) {
   o[0] = R[0] * v[0] + R[1] * v[1] + R[2] * v[2];
   o[1] = R[3] * v[0] + R[4] * v[1] + R[5] * v[2];
   o[2] = R[6] * v[0] + R[7] * v[1] + R[8] * v[2];
@@ -515,7 +515,7 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
 }
 
 // Point of shape s behind a support id returned by warp_support (hull vertex index, box corner bits, capsule end).
-template <typename T> __device__ __forceinline__ void gjk_point(const GShape<T>& s, int id, T* out) {
+template <typename T> __host__ __device__ __forceinline__ void gjk_point(const GShape<T>& s, int id, T* out) {
   if (s.type == SH_HULL) { out[0] = s.verts[3 * id]; out[1] = s.verts[3 * id + 1]; out[2] = s.verts[3 * id + 2]; }
   else if (s.type == SH_BOX) { for (int k = 0; k < 3; k++) out[k] = (id >> k) & 1 ? s.half[k] : -s.half[k]; }
   else if (s.type == SH_CAPSULE) { out[0] = out[1] = T(0); out[2] = id ? s.half_len : -s.half_len; }
@@ -525,7 +525,7 @@ template <typename T> __device__ __forceinline__ void gjk_point(const GShape<T>&
 // FP64 certificate for "the cores intersect": the four points of A - B named by the ids of an FP32 GJK simplex form a
 // tetrahedron with real volume that has the origin strictly inside, at least `margin` from every face.  Four points of
 // the Minkowski difference enclosing the origin prove the intersection whatever GJK run found them.
-__device__ inline bool tetra_encloses(const GShape<double>& A, const GShape<double>& B, const double* Rrel, const double* trel,
+__host__ __device__ inline bool tetra_encloses(const GShape<double>& A, const GShape<double>& B, const double* Rrel, const double* trel,
                                       const int* ids, double margin, double* min_face) {
   double w[4][3];
   for (int i = 0; i < 4; i++) {

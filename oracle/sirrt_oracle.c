@@ -927,7 +927,10 @@ int oracle_state_valid(const Oracle* o, const double* q, double time_s) {
 /* f4 -- SpaceTimeMotionValidator::checkMotion, SpaceTimeMotionValidator.cpp:22-74 (variant 0: 2*delta_t*fps, :51)
  * and :76-127 (variant 1: delta_t*fps, :108; reports lastValid.second).  Times in seconds.
  * returns -1 valid, -4 s2 invalid (:25/:82), -2 delta_t <= 0 (:41/:98), -3 speed gate (:46/:103),
- * >= 0 index of the first invalid interpolated state (:54-64 / :111-123). */
+ * >= 0 index of the first invalid interpolated state (:54-64 / :111-123).
+ * The reference takes `abs(...)` (unqualified) of the double joint differences (:33, :90); with <cmath> in scope that is
+ * the double overload, and the differences are squared right after, so only an integer-truncating abs could matter --
+ * the reference's logged ST-RRT* solutions are valid motions under the double reading (tests/test_oracle.py). */
 int oracle_motion_check(const Oracle* o, const double* q0, const double* q1, double t0, double t1, double vmax,
                         int variant, double* last_valid_fraction) {
   int dof = o->dof;

@@ -648,45 +648,130 @@ __device__ __noinline__ bool certify_enclosure(const DRobot& rb, const DScene& s
   return true;
 }
 
+// FK of one link only (what a re-check item needs): the chain is walked up to link `want` and no further
+__device__ inline void fk_one_link(const DRobot& rb, const double* q, int want, LinkXfD& out) {
+  double t[3] = {rb.base_t[0], rb.base_t[1], rb.base_t[2]}, R[9];
+#pragma unroll
+  for (int i = 0; i < 9; i++) R[i] = rb.base_R[i];
+  int l = 0;
+  for (int k = 0; k <= rb.n_joints; k++) {
+    while (l < rb.n_links && rb.link_jb[l] == k) {
+      if (l == want) {
+        double w[3];
+        matvec(w, R, rb.lo_t[l]);  // :335
+        out.t[0] = t[0] + w[0]; out.t[1] = t[1] + w[1]; out.t[2] = t[2] + w[2];  // :336
+        matmul3(out.R, R, rb.lo_R[l]);  // :347
+        return;
+      }
+      l++;
+    }
+    if (k == rb.n_joints) break;
+    double w[3];
+    matvec(w, R, rb.jt[k]);  // :319,361
+    t[0] += w[0]; t[1] += w[1]; t[2] += w[2];
+    matmul3(R, R, rb.jR[k]);  // :320,362
+    double sn, cs;
+    sincos(q[k], &sn, &cs);
+    const double Rz[9] = {cs, -sn, 0, sn, cs, 0, 0, 0, (1.0 - cs) * 1.0 + cs};  // :321,363
+    matmul3(R, R, Rz);
+  }
+}
+
+// QUIRK 7 broadphase gate of a `shifted == 1` item in FP64: do the coal AABBs of the true geometries overlap?
+__device__ inline bool recheck_gate(const DScene& sc, const DShape& lsh, const LinkXfD& X, const double* ab) {
+  double alo[3], ahi[3];
+  bool ident = true;
+  for (int k = 0; k < 9; k++) ident &= fabs(X.R[k] - ((k % 4) == 0 ? 1.0 : 0.0)) <= 1e-12;
+  if (ident) { for (int k = 0; k < 3; k++) { alo[k] = lsh.d_amin[k] + X.t[k]; ahi[k] = lsh.d_amax[k] + X.t[k]; } }
+  else {
+    double c[3]; matvec(c, X.R, lsh.d_ac);
+    for (int k = 0; k < 3; k++) { alo[k] = c[k] + X.t[k] - lsh.d_ar; ahi[k] = c[k] + X.t[k] + lsh.d_ar; }
+  }
+  bool overlap = true;
+  for (int k = 0; k < 3; k++) if (alo[k] > ab[3 + k] || ahi[k] < ab[k]) overlap = false;
+  return overlap;
+}
+
+// publish one decided HIT of the re-check: the bit of (config, frame), the whole row for a static slot, or the cell flag
+__device__ __forceinline__ void recheck_set(const RecheckParams& P, const WorkItem& it) {
+  if (P.cells) { P.cells[it.config] = 1; return; }
+  uint32_t* row = P.bits + (size_t)it.config * P.n_words;
+  if (it.frame >= 0) { atomicOr(row + (it.frame >> 5), 1u << (it.frame & 31)); return; }
+  for (int wd = 0; wd < P.n_words; wd++) {
+    uint32_t m = 0xffffffffu;
+    if (P.sc.T - wd * 32 < 32) m = (1u << (P.sc.T - wd * 32)) - 1u;
+    atomicOr(row + wd, m);
+  }
+}
+
+// closed-form item (capsule link vs box / sphere / capsule): is this item one?  (everything else needs the warp GJK)
+__device__ __forceinline__ bool recheck_is_closed(const DRobot& rb, const DScene& sc, const WorkItem& it) {
+  const DSlot S = sc.slots[it.slot];
+  const int lt = sc.shapes[rb.link_shape[it.link]].type;
+  if (lt != SH_CAPSULE) return false;
+  if (it.shifted == 1) return S.shape_shift >= 0 && sc.shapes[S.shape_shift].type != SH_HULL;
+  return sc.shapes[it.shifted ? S.shape_shift : S.shape].type != SH_HULL;
+}
+
+// Two passes over the work list.  Pass 1: one LANE per closed-form item (the synthetic sweep leaves ~4e5 of them per
+// 2^20 configurations; a warp per item idled 31 lanes through an FP64 FK of the whole chain).  Pass 2: one WARP per
+// item that needs the warp-cooperative FP64 GJK (hull links / hull obstacles), spread over the machine because a
+// planner-sized call has a handful of them and each is a long dependent chain.
 __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
 k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckParams P) {
   const int lane = threadIdx.x & 31;
   const DScene& sc = P.sc;
   const unsigned int n_items = min(*P.count, P.cap);
-  for (unsigned int w = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5); w < n_items;
-       w += gridDim.x * SIRRT_WARPS_PER_BLOCK) {
+  const unsigned int warp0 = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5), n_warps = gridDim.x * SIRRT_WARPS_PER_BLOCK;
+  unsigned int n_near = 0;
+  for (unsigned int base = warp0 * 32; base < n_items; base += n_warps * 32) {
+    const unsigned int w = base + lane;
+    if (w >= n_items) continue;
+    const WorkItem it = P.items[w];
+    if (!recheck_is_closed(rb, sc, it)) continue;
+    double q[SIRRT_MAXJ];
+    for (int j = 0; j < rb.n_joints; j++) q[j] = j < P.q.dof ? load_q(P.q, it.config, j) : 0.0;
+    LinkXfD X;
+    fk_one_link(rb, q, it.link, X);
+    const int l = it.link, f = it.frame < 0 ? 0 : it.frame;
+    const DSlot S = sc.slots[it.slot];
+    const double* pose = sc.pose_d + ((size_t)it.slot * sc.Tp + f) * 12;
+    int shifted = it.shifted;
+    if (shifted == 1) {
+      if (!recheck_gate(sc, sc.shapes[rb.link_shape[l]], X, P.aabb_d + ((size_t)it.slot * sc.Tp + f) * 6)) continue;
+      shifted = 2;
+    }
+    int res;
+    const double d = recheck_pair(rb, sc, X, l, sc.shapes[shifted ? S.shape_shift : S.shape], pose, 0, &res);  // closed form: no warp primitive inside
+    if (fabs(d) < 1e-6) n_near++;
+    if (res == RES_HIT) recheck_set(P, it);
+  }
+  if (__any_sync(SIRRT_FULL, n_near != 0)) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n_near += __shfl_xor_sync(SIRRT_FULL, n_near, o);
+    if (lane == 0) atomicAdd(P.counters + 2, n_near);
+  }
+  if (sc.has_hull)  // a scene without a hull (links, obstacles, robot-obstacle links) has closed-form items only
+  for (unsigned int w = warp0; w < n_items; w += n_warps) {
   const WorkItem it = P.items[w];
+  if (recheck_is_closed(rb, sc, it)) continue;
   double q[SIRRT_MAXJ];
   for (int j = 0; j < rb.n_joints; j++) q[j] = j < P.q.dof ? load_q(P.q, it.config, j) : 0.0;
-  LinkXfD X[SIRRT_MAXL];
-  fk_links(rb, q, X);
+  LinkXfD X;
+  fk_one_link(rb, q, it.link, X);
   const int l = it.link, f = it.frame < 0 ? 0 : it.frame;
   const DSlot S = sc.slots[it.slot];
   const double* pose = sc.pose_d + ((size_t)it.slot * sc.Tp + f) * 12;
-  bool hit = false;
   int shifted = it.shifted;
   if (shifted == 1) {  // undecided broadphase gate: coal AABB overlap of the true geometries, FP64
-    const DShape& lsh = sc.shapes[rb.link_shape[l]];
-    double alo[3], ahi[3];
-    bool ident = true;
-    for (int k = 0; k < 9; k++) ident &= fabs(X[l].R[k] - ((k % 4) == 0 ? 1.0 : 0.0)) <= 1e-12;
-    if (ident) { for (int k = 0; k < 3; k++) { alo[k] = lsh.d_amin[k] + X[l].t[k]; ahi[k] = lsh.d_amax[k] + X[l].t[k]; } }
-    else {
-      double c[3]; matvec(c, X[l].R, lsh.d_ac);
-      for (int k = 0; k < 3; k++) { alo[k] = c[k] + X[l].t[k] - lsh.d_ar; ahi[k] = c[k] + X[l].t[k] + lsh.d_ar; }
-    }
-    const double* ab = P.aabb_d + ((size_t)it.slot * sc.Tp + f) * 6;
-    bool overlap = true;
-    for (int k = 0; k < 3; k++) if (alo[k] > ab[3 + k] || ahi[k] < ab[k]) overlap = false;
-    if (!overlap) continue;
+    if (!recheck_gate(sc, sc.shapes[rb.link_shape[l]], X, P.aabb_d + ((size_t)it.slot * sc.Tp + f) * 6)) continue;
     shifted = 2;
   }
   const DShape& sh = sc.shapes[shifted ? S.shape_shift : S.shape];
   int res;
-  double d = recheck_pair(rb, sc, X[l], l, sh, pose, lane, &res);
-  hit = res == RES_HIT;
+  double d = recheck_pair(rb, sc, X, l, sh, pose, lane, &res);
   if (lane == 0 && fabs(d) < 1e-6) atomicAdd(P.counters + 2, 1u);
-  if (!hit) continue;
+  if (res != RES_HIT) continue;
   if (P.cells) { if (lane == 0) P.cells[it.config] = 1; continue; }
   uint32_t* row = P.bits + (size_t)it.config * P.n_words;
   if (it.frame >= 0) { if (lane == 0) atomicOr(row + (it.frame >> 5), 1u << (it.frame & 31)); }

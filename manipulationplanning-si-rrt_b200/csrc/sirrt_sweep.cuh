@@ -13,34 +13,48 @@
 //                               (32-frame tile, dynamic slot) pair (uniform float4 loads)      -> Q0
 //   A1   lane = Q0 entry        the 7 link bounding spheres vs that swept sphere; one Q1 entry per
 //                               surviving link (warp prefix sum of popcounts)                   -> Q1
-//   B1   lane = Q1 entry        link axis vs the slot's swept capsule over the tile (segment-segment)
-//   B2   lane = frame of tile   per B1 survivor: point-segment distance from the obstacle centre to
-//                               the link axis decides FREE / HIT (inscribed sphere) / UNDECIDED per
-//                               frame; __ballot_sync of the hits is one word of the collision row -> Q3
+//   B1   lane = Q1 entry        link axis vs the slot's swept capsule over the tile (segment-segment)   -> QW
+//   W    lane = QW entry        analytic frame windows (sirrt_sweep_window.cuh): the obstacle centre moves piecewise
+//                               linearly inside a tile, so its squared distance to the link axis is a quadratic in
+//                               the frame; one root solve yields the frames that are certainly HIT (OR-ed into the
+//                               row as a mask, no per-frame work) and the frames that can be neither decided FREE nor
+//                               HIT from the model; only those are enumerated, one (configuration, link, slot, frame)
+//                               entry each                                                                -> Q2
+//   B2   lane = Q2 entry        point-segment distance from the TRUE obstacle centre to the link axis; axis-aligned
+//                               boxes: separating-plane lower bound / closest-point upper bound of the segment-box
+//                               distance decide FREE / HIT, the rest is UNDECIDED                       -> Q3
 //   C    lane = Q3 entry        exact segment-box distance for the UNDECIDED (config, link, slot, frame)
 // Pairs inside the FP32 uncertainty band go to the FP64 re-check work list exactly as in the
 // generic kernel.  Collision rows accumulate in shared memory and leave as coalesced 128-byte rows.
 #pragma once
+#include <mutex>
 #include <vector>
 
 #include "sirrt_kernels.cuh"
+#include "sirrt_sweep_window.cuh"
 #include "sirrt_tables.hpp"
 
 #define SWEEP_MAXL 8
 #define SWEEP_WARPS 4
 #define SWEEP_G 16       // configurations per warp (16 keeps the per-warp tables at ~7 KB -> 28 resident warps per SM)
 #define SWEEP_Q0CAP 160   // 31 left over + 32 x 4 pushed per A0 round
-#define SWEEP_Q1CAP 256   // 31 left over + 32 x 7 pushed per A1 batch
-#define SWEEP_Q3CAP 64    // 31 left over + 32 pushed per B2 entry
+#define SWEEP_LMAX 7      // links the queue capacities are sized for (sweep_build rejects robots with more)
+#define SWEEP_Q1CAP 256   // 31 left over + 32 x SWEEP_LMAX pushed per A1 batch
+#define SWEEP_QWCAP 64    // 31 left over + 32 pushed per B1 batch
+#define SWEEP_Q2CAP 64    // 31 left over + 32 pushed per enumeration round of stage W
+#define SWEEP_Q3CAP 64    // 31 left over + 32 pushed per B2 batch
 #define SWEEP_ROWS 7      // per link: centre xyz, axis xyz (b - a), 1 / |axis|^2
 #define SWEEP_LDC (SWEEP_G + 1)  // row stride of the per-warp link table (odd: rows of one configuration fall into different banks)
-#define SWEEP_PER_WARP(L, Wp) ((size_t)(L) * SWEEP_ROWS * SWEEP_LDC + (size_t)SWEEP_G * (Wp) + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_Q3CAP)
+#define SWEEP_PER_WARP(L, Wp) ((size_t)(L) * SWEEP_ROWS * SWEEP_LDC + (size_t)SWEEP_G * (Wp) + SWEEP_Q0CAP + SWEEP_Q1CAP + SWEEP_QWCAP + SWEEP_Q2CAP + SWEEP_Q3CAP)
 
 struct SweepTables {
   int supported = 0;
   const float4* bounds = nullptr;  // [pair]: swept bounding sphere of (tile, slot j), pair = tile*ndp + j (ndp = n_dynamic padded to x8)
   const float4* seg = nullptr;     // [pair*2]: (p0, r) and (p1, 0): swept capsule of the slot over the tile
   const float4* dyn = nullptr;     // [j]: inscribed radius, bounding radius, sphere radius or -1, offset of the slot's translation rows in pose_f (int bits)
+  const float4* dyn2 = nullptr;    // [j]: box half extents, w = 1 when every pose of the slot has R == I exactly
+  const float4* mdl = nullptr;     // [pair*4]: two-piece linear model of the slot's centre over the tile (sirrt_sweep_window.cuh)
+  const float4* ctr = nullptr;     // [j*Tp + f]: the slot's centre at frame f (xyz)
   int ndp = 0;
   int n_links = 0;
   float link_r[SWEEP_MAXL], link_br[SWEEP_MAXL];
@@ -57,6 +71,9 @@ struct SweepParams {
   const float4* bounds;
   const float4* seg;
   const float4* dyn;
+  const float4* dyn2;
+  const float4* mdl;
+  const float4* ctr;
   int ndp, n_words, Wp, n_links;
   float band;
   float link_r[SWEEP_MAXL], link_br[SWEEP_MAXL];
@@ -154,7 +171,9 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
   uint32_t* sbits = (uint32_t*)(lk + (size_t)L * SWEEP_ROWS * SWEEP_LDC);  // [cfg][Wp]
   uint32_t* q0 = sbits + (size_t)SWEEP_G * Wp;
   uint32_t* q1 = q0 + SWEEP_Q0CAP;
-  uint32_t* q3 = q1 + SWEEP_Q1CAP;
+  uint32_t* qw = q1 + SWEEP_Q1CAP;
+  uint32_t* q2 = qw + SWEEP_QWCAP;
+  uint32_t* q3 = q2 + SWEEP_Q2CAP;
   if (threadIdx.x < SWEEP_MAXL) s_lr[threadIdx.x] = P.link_r[threadIdx.x];
   __syncthreads();
   const float band = P.band;
@@ -236,148 +255,208 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
     }
     const unsigned shm = __ballot_sync(SIRRT_FULL, static_hit);  // bit c: configuration c of the group hits a static slot
     const bool active = have && !((shm >> cl) & 1u);
-    int q0n = 0, q1n = 0, q3n = 0;
+    int q0n = 0, q1n = 0, qwn = 0, q2n = 0, q3n = 0;
+
+    // ---- B2: lane = Q2 entry (configuration, link, slot, frame): the frames stage W could not decide from the model
+    auto run_b2 = [&](const uint32_t* qp, int count) {
+      __syncwarp();
+      bool want = false;
+      unsigned u = 0;
+      if (lane < count) {
+        u = qp[lane];
+        const int cfg = u & 31, l = (u >> 5) & 7, fr = (u >> 8) & 31, tile = u >> 24, j = (u >> 13) & 2047;
+        if (!((sbits[cfg * Wp + tile] >> fr) & 1u)) {  // another pair may have decided this frame already
+          const int f = tile * 32 + fr;
+          const float4 c4 = __ldg(P.ctr + (size_t)j * Tp + f);
+          const float4 dj = __ldg(P.dyn + j);
+          const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + cfg;
+          const float apx = c4.x - lkp[0], apy = c4.y - lkp[SWEEP_LDC], apz = c4.z - lkp[2 * SWEEP_LDC];
+          const float abx = lkp[3 * SWEEP_LDC], aby = lkp[4 * SWEEP_LDC], abz = lkp[5 * SWEEP_LDC];
+          float tt = (apx * abx + apy * aby + apz * abz) * lkp[6 * SWEEP_LDC];
+          tt = fminf(fmaxf(tt, -0.5f), 0.5f);
+          const float ex = apx - tt * abx, ey = apy - tt * aby, ez = apz - tt * abz;  // closest axis point -> obstacle centre
+          const float d2 = ex * ex + ey * ey + ez * ez;
+          const float rl = s_lr[l];
+          bool hit = false;
+          if (dj.z >= 0.f) {  // sphere obstacle: the point-segment distance IS the narrowphase
+            const int r = classify(sqrtf(d2) - rl - dj.z, band);
+            n_exact++;
+            if (r == RES_HIT) hit = true;
+            else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), f, l, sc.dynamic_slots[j], 0);
+          } else {
+            const float4 h4 = __ldg(P.dyn2 + j);
+            bool fre;
+            if (h4.w != 0.f) {
+              // axis-aligned box (world frame == box frame up to the translation).  With p* the closest axis point:
+              //   dist(segment, box) <= dist(p*, box)                              -> HIT  when dist(p*, box) < rl - band
+              //   dist(segment, box) >= |e| - h.|e|/|e|  (plane through p* normal to e separates: the segment lies
+              //   on or behind it, the box reaches at most its support h.|n| towards it) -> FREE when that > rl + band
+              const float ax = fabsf(ex), ay = fabsf(ey), az = fabsf(ez);
+              const float qx = fmaxf(ax - h4.x, 0.f), qy = fmaxf(ay - h4.y, 0.f), qz = fmaxf(az - h4.z, 0.f);
+              const float rlo = rl - band, rhi = rl + band;
+              hit = qx * qx + qy * qy + qz * qz < rlo * rlo;
+              fre = d2 - (h4.x * ax + h4.y * ay + h4.z * az) > rhi * sqrtf(d2);
+            } else {
+              const float hi = rl + dj.y + band;  // beyond the circumscribed sphere: free
+              const float lo = rl + dj.x - band;  // inside the inscribed sphere: hit
+              fre = d2 > hi * hi;
+              hit = d2 < lo * lo;
+            }
+            want = !hit && !fre;
+          }
+          if (hit) atomicOr(&sbits[cfg * Wp + tile], 1u << fr);
+        }
+      }
+      const unsigned mq = __ballot_sync(SIRRT_FULL, want);
+      if (mq) {
+        if (want) q3[q3n + __popc(mq & lt_mask)] = u;
+        q3n += __popc(mq);
+      }
+      __syncwarp();
+      if (q3n >= 32) {
+        q3n -= 32;
+        n_exact += sweep_exact_batch(P, lk, sbits, s_lr, q3 + q3n, 32, lane, cfg0);
+      }
+    };
+
+    // ---- W: lane = QW entry (configuration, link, tile, slot): analytic HIT / IN frame windows, then the undecided
+    // frames are enumerated into Q2, at most one per lane and round
+    auto run_w = [&](const uint32_t* qp, int count) {
+      __syncwarp();
+      unsigned tm = 0, code = 0;
+      if (lane < count) {
+        const unsigned e = qp[lane];
+        const int cfg = e & 31, l = (e >> 5) & 7, tile = e >> 19, j = (e >> 8) & 2047;
+        const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + cfg;
+        const float4* mp = P.mdl + 4 * (size_t)SWEEP_PAIR(e >> 8, ndp);
+        const float4 m0 = __ldg(mp), m1 = __ldg(mp + 1), m2 = __ldg(mp + 2), m3 = __ldg(mp + 3);
+        const float4 dj = __ldg(P.dyn + j);
+        const float rl = s_lr[l];
+        unsigned in, hit;
+        sweep_windows(m0, m1, m2, m3, lkp[0], lkp[SWEEP_LDC], lkp[2 * SWEEP_LDC], lkp[3 * SWEEP_LDC], lkp[4 * SWEEP_LDC], lkp[5 * SWEEP_LDC],
+                      lkp[6 * SWEEP_LDC], rl + dj.y + band, rl + dj.x - band, in, hit);
+        const uint32_t cur = sbits[cfg * Wp + tile];
+        if (hit & ~cur) atomicOr(&sbits[cfg * Wp + tile], hit);
+        tm = in & ~hit & ~cur;
+        code = (e & 0xffu) | ((e >> 8) << 13);
+      }
+      for (;;) {
+        const unsigned b = __ballot_sync(SIRRT_FULL, tm != 0u);
+        if (!b) break;
+        if (tm) {
+          const unsigned fr = __ffs(tm) - 1;
+          tm &= tm - 1;
+          q2[q2n + __popc(b & lt_mask)] = code | (fr << 8);
+        }
+        q2n += __popc(b);
+        if (q2n >= 32) {
+          q2n -= 32;
+          run_b2(q2 + q2n, 32);
+        }
+      }
+    };
+
+    // ---- B1: lane = Q1 entry; link axis vs the slot's swept capsule over the tile
+    auto run_b1 = [&](const uint32_t* qp, int count) {
+      bool kp = false;
+      unsigned e = 0;
+      if (lane < count) {
+        e = qp[lane];
+        const int l = (e >> 5) & 7;
+        const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + (e & 31);
+        float a[3], b[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) { const float cc = lkp[k * SWEEP_LDC], h = 0.5f * lkp[(3 + k) * SWEEP_LDC]; a[k] = cc - h; b[k] = cc + h; }
+        const float4* sp = P.seg + 2 * SWEEP_PAIR(e >> 8, ndp);
+        const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
+        const float p0[3] = {s0.x, s0.y, s0.z}, p1[3] = {s1.x, s1.y, s1.z};
+        const float rr = s_lr[l] + s0.w + band;
+        kp = seg_seg_dist2(a, b, p0, p1) <= rr * rr;
+      }
+      const unsigned keep = __ballot_sync(SIRRT_FULL, kp);
+      if (keep) {
+        if (kp) qw[qwn + __popc(keep & lt_mask)] = e;
+        qwn += __popc(keep);
+        if (qwn >= 32) {
+          qwn -= 32;
+          run_w(qw + qwn, 32);
+        }
+      }
+    };
+
+    // ---- A1: lane = Q0 entry; link bounding spheres vs the swept sphere of the pair
+    auto run_a1 = [&](const uint32_t* qp, int count) {
+      __syncwarp();
+      unsigned lm = 0, e = 0;
+      if (lane < count) {
+        e = qp[lane];
+        const float* lkp = lk + (e & 31);
+        const float4 b4 = __ldg(P.bounds + SWEEP_PAIR(e >> 5, ndp));
+        const float rb4 = b4.w + band;
+#pragma unroll
+        for (int l = 0; l < SWEEP_MAXL; l++)
+          if (l < L) {
+            const float dx = lkp[(l * SWEEP_ROWS + 0) * SWEEP_LDC] - b4.x, dy = lkp[(l * SWEEP_ROWS + 1) * SWEEP_LDC] - b4.y,
+                        dz = lkp[(l * SWEEP_ROWS + 2) * SWEEP_LDC] - b4.z;
+            const float rr = P.link_br[l] + rb4;
+            if (dx * dx + dy * dy + dz * dz <= rr * rr) lm |= 1u << l;
+          }
+      }
+      int total;
+      int w = q1n + warp_excl_scan(__popc(lm), lane, total);
+      const unsigned ebase = (e & 31u) | ((e >> 5) << 8);
+      while (lm) {
+        const int l = __ffs(lm) - 1;
+        lm &= lm - 1;
+        q1[w++] = ebase | ((unsigned)l << 5);
+      }
+      q1n += total;
+      __syncwarp();
+      while (q1n >= 32) {
+        q1n -= 32;
+        run_b1(q1 + q1n, 32);
+      }
+    };
 
     // ---- dynamic slots: A0 rounds of 8 (tile, slot) pairs, stages drained whenever a batch of 32 is ready
-    int tile0 = 0, j0 = 0;
-    for (;;) {
-      const bool flush = tile0 >= n_tiles;
-      if (!flush) {
-        // ---- A0: lane = (configuration, half of the round); arm sphere vs 4 of the round's 8 swept
-        // spheres -> per-lane pass mask
-        const int u0 = (lane >> 4) * 4;
-        const float4* bp = P.bounds + (size_t)tile0 * ndp + j0 + u0;
-        unsigned mask = 0;
+    for (int tile0 = 0, j0 = 0; tile0 < n_tiles;) {
+      // ---- A0: lane = (configuration, half of the round); arm sphere vs 4 of the round's 8 swept
+      // spheres -> per-lane pass mask
+      const int u0 = (lane >> 4) * 4;
+      const float4* bp = P.bounds + (size_t)tile0 * ndp + j0 + u0;
+      unsigned mask = 0;
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-          const float4 tb = __ldg(bp + u);
-          const float dx = acx - tb.x, dy = acy - tb.y, dz = acz - tb.z;
-          const float rr = ar + tb.w;
-          if (dx * dx + dy * dy + dz * dz <= rr * rr) mask |= 1u << u;
-        }
-        mask <<= u0;
-        if (!active) mask = 0;
-        if (__any_sync(SIRRT_FULL, mask != 0)) {
-          int total;
-          int w = q0n + warp_excl_scan(__popc(mask), lane, total);
-          const unsigned base = (unsigned)cl | ((((unsigned)tile0 << 11) | (unsigned)j0) << 5);
-          while (mask) {
-            const int u = __ffs(mask) - 1;
-            mask &= mask - 1;
-            q0[w++] = base + ((unsigned)u << 5);
-          }
-          q0n += total;
-        }
-        j0 += 8;
-        if (j0 >= ndp) { j0 = 0; tile0++; }
+      for (int u = 0; u < 4; u++) {
+        const float4 tb = __ldg(bp + u);
+        const float dx = acx - tb.x, dy = acy - tb.y, dz = acz - tb.z;
+        const float rr = ar + tb.w;
+        if (dx * dx + dy * dy + dz * dz <= rr * rr) mask |= 1u << u;
       }
-      if (q0n >= 32 || flush) {
-        do {
-          if (q0n > 0) {
-            // ---- A1: lane = Q0 entry; link bounding spheres vs the swept sphere of the pair
-            const int cnt = min(32, q0n);
-            q0n -= cnt;
-            __syncwarp();
-            unsigned lm = 0, e = 0;
-            if (lane < cnt) {
-              e = q0[q0n + lane];
-              const float* lkp = lk + (e & 31);
-              const float4 b4 = __ldg(P.bounds + SWEEP_PAIR(e >> 5, ndp));
-              const float rb4 = b4.w + band;
-#pragma unroll
-              for (int l = 0; l < SWEEP_MAXL; l++)
-                if (l < L) {
-                  const float dx = lkp[(l * SWEEP_ROWS + 0) * SWEEP_LDC] - b4.x, dy = lkp[(l * SWEEP_ROWS + 1) * SWEEP_LDC] - b4.y,
-                              dz = lkp[(l * SWEEP_ROWS + 2) * SWEEP_LDC] - b4.z;
-                  const float rr = P.link_br[l] + rb4;
-                  if (dx * dx + dy * dy + dz * dz <= rr * rr) lm |= 1u << l;
-                }
-            }
-            int total;
-            int w = q1n + warp_excl_scan(__popc(lm), lane, total);
-            const unsigned ebase = (e & 31u) | ((e >> 5) << 8);
-            while (lm) {
-              const int l = __ffs(lm) - 1;
-              lm &= lm - 1;
-              q1[w++] = ebase | ((unsigned)l << 5);
-            }
-            q1n += total;
-            __syncwarp();
-          }
-          while (q1n >= 32 || (flush && q0n == 0 && q1n > 0)) {
-            // ---- B1: lane = Q1 entry; link axis vs the slot's swept capsule over the tile
-            const int cnt = min(32, q1n);
-            q1n -= cnt;
-            bool kp = false;
-            unsigned e = 0;
-            if (lane < cnt) {
-              e = q1[q1n + lane];
-              const int l = (e >> 5) & 7;
-              const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + (e & 31);
-              float a[3], b[3];
-#pragma unroll
-              for (int k = 0; k < 3; k++) { const float cc = lkp[k * SWEEP_LDC], h = 0.5f * lkp[(3 + k) * SWEEP_LDC]; a[k] = cc - h; b[k] = cc + h; }
-              const float4* sp = P.seg + 2 * SWEEP_PAIR(e >> 8, ndp);
-              const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
-              const float p0[3] = {s0.x, s0.y, s0.z}, p1[3] = {s1.x, s1.y, s1.z};
-              const float rr = s_lr[l] + s0.w + band;
-              kp = seg_seg_dist2(a, b, p0, p1) <= rr * rr;
-            }
-            unsigned keep = __ballot_sync(SIRRT_FULL, kp);
-            while (keep) {
-              // ---- B2: lane = frame of the tile, one B1 survivor at a time
-              const int src = __ffs(keep) - 1;
-              keep &= keep - 1;
-              const unsigned ee = __shfl_sync(SIRRT_FULL, e, src);
-              const int cfg = ee & 31, l = (ee >> 5) & 7, tile = ee >> 19, j = (ee >> 8) & 2047;
-              const int f = tile * 32 + lane;
-              const bool valid = f < T;
-              const uint32_t cur = sbits[cfg * Wp + tile];
-              const bool done = !valid || ((cur >> lane) & 1u);
-              if (__all_sync(SIRRT_FULL, done)) continue;  // every frame of this tile is already decided
-              const float4 dj = __ldg(P.dyn + j);
-              const float* pp = posef + (__float_as_int(dj.w) + (valid ? f : T - 1));
-              const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + cfg;
-              const float apx = pp[0] - lkp[0], apy = pp[Tp] - lkp[SWEEP_LDC], apz = pp[2 * Tp] - lkp[2 * SWEEP_LDC];
-              const float abx = lkp[3 * SWEEP_LDC], aby = lkp[4 * SWEEP_LDC], abz = lkp[5 * SWEEP_LDC];
-              float tt = (apx * abx + apy * aby + apz * abz) * lkp[6 * SWEEP_LDC];
-              tt = fminf(fmaxf(tt, -0.5f), 0.5f);
-              const float ex = apx - tt * abx, ey = apy - tt * aby, ez = apz - tt * abz;
-              const float d2 = ex * ex + ey * ey + ez * ez;
-              const float rl = s_lr[l];
-              bool hit = false, want = false;
-              if (dj.z >= 0.f) {  // sphere obstacle: the point-segment distance IS the narrowphase
-                if (!done) {
-                  const int r = classify(sqrtf(d2) - rl - dj.z, band);
-                  n_exact++;
-                  if (r == RES_HIT) hit = true;
-                  else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), f, l, sc.dynamic_slots[j], 0);
-                }
-              } else {
-                const float hi = rl + dj.y + band;  // beyond the circumscribed sphere: free
-                const float lo = rl + dj.x - band;  // inside the inscribed sphere: hit (lo > 0: link radii exceed the band)
-                const bool in = !done && d2 <= hi * hi;
-                hit = in && d2 < lo * lo;
-                want = in && !hit;
-              }
-              const unsigned word = __ballot_sync(SIRRT_FULL, hit);
-              if (word && lane == 0) sbits[cfg * Wp + tile] = cur | word;
-              const unsigned mq = __ballot_sync(SIRRT_FULL, want);
-              if (mq) {
-                if (want) q3[q3n + __popc(mq & lt_mask)] = (ee & 0xffu) | ((unsigned)lane << 8) | ((ee >> 8) << 13);
-                q3n += __popc(mq);
-              }
-              __syncwarp();
-              if (q3n >= 32) {
-                q3n -= 32;
-                n_exact += sweep_exact_batch(P, lk, sbits, s_lr, q3 + q3n, 32, lane, cfg0);
-              }
-            }
-          }
-        } while (q0n >= 32 || (flush && q0n > 0));
+      mask <<= u0;
+      if (!active) mask = 0;
+      if (__any_sync(SIRRT_FULL, mask != 0)) {
+        int total;
+        int w = q0n + warp_excl_scan(__popc(mask), lane, total);
+        const unsigned base = (unsigned)cl | ((((unsigned)tile0 << 11) | (unsigned)j0) << 5);
+        while (mask) {
+          const int u = __ffs(mask) - 1;
+          mask &= mask - 1;
+          q0[w++] = base + ((unsigned)u << 5);
+        }
+        q0n += total;
+        while (q0n >= 32) {
+          q0n -= 32;
+          run_a1(q0 + q0n, 32);
+        }
       }
-      if (flush) break;
+      j0 += 8;
+      if (j0 >= ndp) { j0 = 0; tile0++; }
     }
+    // ---- flush: every queue is drained front to back (a stage only pushes into the queues behind it)
+    while (q0n > 0) { const int c = min(32, q0n); q0n -= c; run_a1(q0 + q0n, c); }
+    while (q1n > 0) { const int c = min(32, q1n); q1n -= c; run_b1(q1 + q1n, c); }
+    while (qwn > 0) { const int c = min(32, qwn); qwn -= c; run_w(qw + qwn, c); }
+    while (q2n > 0) { const int c = min(32, q2n); q2n -= c; run_b2(q2 + q2n, c); }
     if (q3n > 0) n_exact += sweep_exact_batch(P, lk, sbits, s_lr, q3, q3n, lane, cfg0);
 
     // ---- rows out: lane = word, coalesced ------------------------------------------------------------
@@ -411,7 +490,7 @@ static inline int sweep_upload(const void* src, size_t bytes, std::vector<void*>
 static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& tb, const DScene& d, SweepTables* st, std::vector<void*>& owned) {
   st->supported = 0;
   const int L = hs.robot.n_links, nd = tb.n_dynamic;
-  if (tb.has_hull || tb.n_robot_slots > 0 || L > SWEEP_MAXL || nd > 2047 || tb.n_tiles > 255) return 0;
+  if (tb.has_hull || tb.n_robot_slots > 0 || L > SWEEP_LMAX || nd > 2047 || tb.n_tiles > 255) return 0;  // Q1 is sized for SWEEP_LMAX links
   for (int l = 0; l < L; l++) {
     const sirrt::HShape& s = hs.robot.shapes[l + hs.robot.n_strip];
     if (s.type != SH_CAPSULE || s.bc[0] != 0 || s.bc[1] != 0 || s.bc[2] != 0) return 0;
@@ -470,6 +549,29 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
     memcpy(&v.w, &toff32, 4);
     dyn[j] = v;
   }
+  // per dynamic slot: box half extents + "every pose has R == I" flag; the centre per frame as one float4; the two-piece
+  // linear model of the centre per (tile, slot) for the analytic frame windows of stage W
+  std::vector<float4> dyn2((size_t)std::max(nd, 1), make_float4(0, 0, 0, 0));
+  std::vector<float4> ctr((size_t)std::max(nd, 1) * Tp, make_float4(0, 0, 0, 0));
+  std::vector<float4> mdl((size_t)std::max(n_pairs, 8) * 4, make_float4(1e18f, 1e18f, 1e18f, 0.f));
+  for (int j = 0; j < nd; j++) {
+    const int s = tb.dynamic_slots[j];
+    const DShape& sh = tb.shapes[tb.slots[s].shape];
+    dyn2[j] = make_float4(sh.half[0], sh.half[1], sh.half[2], tb.slots[s].rot_identity ? 1.f : 0.f);
+    for (int f = 0; f < Tp; f++) {
+      const int ff = std::min(f, T - 1);
+      ctr[(size_t)j * Tp + f] = make_float4(tb.bcw_f[((size_t)s * 3 + 0) * Tp + ff], tb.bcw_f[((size_t)s * 3 + 1) * Tp + ff], tb.bcw_f[((size_t)s * 3 + 2) * Tp + ff], 0.f);
+    }
+    for (int tile = 0; tile < tb.n_tiles; tile++) {
+      const int f0 = tile * 32, nf = std::min(32, T - f0);
+      double c[32][3];
+      for (int f = 0; f < nf; f++)
+        for (int k = 0; k < 3; k++) c[f][k] = (double)tb.bcw_f[((size_t)s * 3 + k) * Tp + f0 + f];
+      sweep_fit_model(c, nf, &mdl[((size_t)tile * ndp + j) * 4]);
+    }
+  }
+  for (size_t it = 0; it < mdl.size() / 4; it++)  // padding pairs (never survivors of A0): an empty model
+    if (mdl[it * 4].x > 1e17f) { mdl[it * 4 + 1] = make_float4(0, 0, 0, 0); mdl[it * 4 + 2] = make_float4(1e18f, 1e18f, 1e18f, 0); mdl[it * 4 + 3] = make_float4(0, 0, 0, 0); }
   const void* p = nullptr;
   if (sweep_upload(bounds.data(), bounds.size() * sizeof(float4), owned, &p)) return -3;
   st->bounds = (const float4*)p;
@@ -477,11 +579,29 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
   st->seg = (const float4*)p;
   if (sweep_upload(dyn.data(), dyn.size() * sizeof(float4), owned, &p)) return -3;
   st->dyn = (const float4*)p;
+  if (sweep_upload(dyn2.data(), dyn2.size() * sizeof(float4), owned, &p)) return -3;
+  st->dyn2 = (const float4*)p;
+  if (sweep_upload(mdl.data(), mdl.size() * sizeof(float4), owned, &p)) return -3;
+  st->mdl = (const float4*)p;
+  if (sweep_upload(ctr.data(), ctr.size() * sizeof(float4), owned, &p)) return -3;
+  st->ctr = (const float4*)p;
   st->ndp = ndp;
   st->Wp = tb.n_tiles | 1;
   st->smem = (size_t)SWEEP_WARPS * SWEEP_PER_WARP(L, st->Wp) * 4;
   if (st->smem > 200 * 1024) return 0;
-  if (cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+  // the dynamic shared-memory limit of a kernel is a per-device, process-wide attribute: only ever raise it (a later,
+  // smaller scene must not lower the limit of an earlier, larger one)
+  {
+    static std::mutex mu;
+    static size_t granted[64] = {0};
+    std::lock_guard<std::mutex> lk(mu);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && st->smem > granted[dev]) {
+      if (cudaFuncSetAttribute(k_sweep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)st->smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+      granted[dev] = st->smem;
+    }
+  }
   int bps = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_sweep, SWEEP_WARPS * 32, st->smem) != cudaSuccess || bps < 1) { cudaGetLastError(); return 0; }
   st->blocks_per_sm = bps;
@@ -493,7 +613,7 @@ static inline int sweep_build(const sirrt::HScene& hs, const sirrt::HostTables& 
 static inline int sweep_launch(const SweepTables& st, const DRobot& rb, const DScene& sc, const QView& q, const WorkList& wl, uint32_t* bits,
                                int n_words, float band, int n_sm, cudaStream_t stream) {
   SweepParams P{};
-  P.sc = sc; P.q = q; P.wl = wl; P.bits = bits; P.bounds = st.bounds; P.seg = st.seg; P.dyn = st.dyn;
+  P.sc = sc; P.q = q; P.wl = wl; P.bits = bits; P.bounds = st.bounds; P.seg = st.seg; P.dyn = st.dyn; P.dyn2 = st.dyn2; P.mdl = st.mdl; P.ctr = st.ctr;
   P.ndp = st.ndp; P.n_words = n_words; P.Wp = st.Wp; P.n_links = st.n_links; P.band = band;
   for (int l = 0; l < SWEEP_MAXL; l++) { P.link_r[l] = l < st.n_links ? st.link_r[l] : 0.f; P.link_br[l] = l < st.n_links ? st.link_br[l] : 0.f; }
   const long long groups = (q.cnt + SWEEP_G - 1) / SWEEP_G;

@@ -76,6 +76,7 @@ enum {
   SIRRT_OPT_WORKLIST_CAP = 2,   /* capacity of the FP64 re-check work list, entries (default 4194304) */
   SIRRT_OPT_SWEEP_MIN_CONFIGS = 3, /* batches smaller than this use the generic kernel, which splits rows over warps (default 8192) */
   SIRRT_OPT_HULL_CELLS = 5,     /* 1 (default): GJK support queries on hulls scan the direction cell's candidate vertices; 0: every vertex (same result) */
+  SIRRT_OPT_PIPELINE = 6,       /* 1 (default): batches of more than 131072 configurations in HOST buffers run as a 3-stream pipeline (H2D || kernels || D2H) */
   SIRRT_OPT_DEFER_MAX_CONFIGS = 4  /* hull scenes: batches up to this many configurations hand their GJK pair tests to a machine-wide task kernel (default 4096; 0 = never) */
 };
 int sirrt_scene_set_option(sirrt_scene*, int key, long long value);
@@ -105,6 +106,9 @@ int sirrt_get_distances(sirrt_scene*, const double* q, int frame, double* min_di
  *   near_contact_count : pair tests within 1e-6 m of contact (after FP64 re-evaluation); or NULL */
 int sirrt_safe_intervals_batch(sirrt_scene*, const float* q_soa, int64_t N, int32_t* table, int Kmax,
                                uint32_t* bits, uint64_t* near_contact_count);
+/* compact interval table for host callers: int16 entries, same row layout {count, lo0, hi0, ...}, unused = -1 (halves the
+ * bytes read back over the bus); host buffers only, scenes with at most 32767 frames (SIRRT_E_LIMIT otherwise) */
+int sirrt_safe_intervals_batch_i16(sirrt_scene*, const float* q_soa_host, int64_t N, int16_t* table16, int Kmax, uint64_t* near_contact_count);
 /* same, double-precision configurations as array of structures [N][dof] (edge tables, §7.3) with
  * explicit semantics (SIRRT_SEM_*) */
 int sirrt_collision_bits_f64(sirrt_scene*, const double* q_aos, int64_t N, int semantics, uint32_t* bits);

@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_DIR, "libsirrt_b200.so")
 
 PARITY_REFERENCE_EXACT, PARITY_FIXED = 0, 1
 SEM_INTERVAL, SEM_FRAME = 0, 1
-OPT_USE_SWEEP, OPT_CHUNK_CONFIGS, OPT_WORKLIST_CAP, OPT_SWEEP_MIN_CONFIGS, OPT_DEFER_MAX_CONFIGS, OPT_HULL_CELLS = 0, 1, 2, 3, 4, 5
+OPT_USE_SWEEP, OPT_CHUNK_CONFIGS, OPT_WORKLIST_CAP, OPT_SWEEP_MIN_CONFIGS, OPT_DEFER_MAX_CONFIGS, OPT_HULL_CELLS, OPT_PIPELINE = 0, 1, 2, 3, 4, 5, 6
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -48,6 +48,7 @@ EXPORTS = {
     "sirrt_check_frame": (_i32, [_vp, _vp, _i32, _vp]),
     "sirrt_get_distances": (_i32, [_vp, _vp, _i32, _vp, _vp]),
     "sirrt_safe_intervals_batch": (_i32, [_vp, _vp, _i64, _vp, _i32, _vp, _vp]),
+    "sirrt_safe_intervals_batch_i16": (_i32, [_vp, _vp, _i64, _vp, _i32, _vp]),
     "sirrt_collision_bits_f64": (_i32, [_vp, _vp, _i64, _i32, _vp]),
     "sirrt_collision_bits_window_f64": (_i32, [_vp, _vp, _i64, _i32, _vp, _i32, _vp]),
     "sirrt_check_frames_batch": (_i32, [_vp, _vp, _vp, _i64, _vp]),
@@ -190,6 +191,20 @@ class Scene:
         near = C.c_uint64()
         _ck(_lib.sirrt_safe_intervals_batch(self._h, q.ctypes.data, N, _ptr(table), kmax, _ptr(bits), C.byref(near)))
         return table, bits, near.value
+
+    def safe_intervals_batch_i16(self, q_soa, kmax: int = 8):
+        """compact (int16) interval table, host buffers"""
+        q = np.ascontiguousarray(q_soa, np.float32)
+        assert q.ndim == 2 and q.shape[0] == self.dof
+        table = np.zeros((q.shape[1], 1 + 2 * kmax), np.int16)
+        near = C.c_uint64()
+        _ck(_lib.sirrt_safe_intervals_batch_i16(self._h, q.ctypes.data, q.shape[1], table.ctypes.data, kmax, C.byref(near)))
+        return table, near.value
+
+    def safe_intervals_batch_i16_raw(self, q_ptr, N: int, table_ptr, kmax: int):
+        near = C.c_uint64()
+        _ck(_lib.sirrt_safe_intervals_batch_i16(self._h, q_ptr, N, table_ptr, kmax, C.byref(near)))
+        return near.value
 
     def safe_intervals_batch_raw(self, q_ptr, N: int, table_ptr, kmax: int, bits_ptr):
         """Pointer-level call (device or pinned host memory): no allocation, no conversion."""

@@ -73,6 +73,9 @@ struct DevBuf {
 struct sirrt_scene {
   int device = 0, parity_mode = 0, n_sm = 148;
   cudaStream_t own_stream = nullptr, stream = nullptr;
+  cudaStream_t copy_in = nullptr, copy_out = nullptr;  // pipelined host-buffer batches: H2D / D2H beside the compute stream
+  std::vector<cudaEvent_t> pipe_ev;                     // per block: upload done, results ready
+  int pipeline = 1;
   HScene hs;
   HostTables tb;
   DScene d{};
@@ -180,6 +183,9 @@ extern "C" void sirrt_scene_destroy(sirrt_scene* s) {
   if (s->pinned) cudaFreeHost(s->pinned);
   if (s->lazy_cnt) cudaFree(s->lazy_cnt);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
+  for (cudaEvent_t e : s->pipe_ev) cudaEventDestroy(e);
+  if (s->copy_in) cudaStreamDestroy(s->copy_in);
+  if (s->copy_out) cudaStreamDestroy(s->copy_out);
   if (s->own_stream) cudaStreamDestroy(s->own_stream);
   cudaGetLastError();
   delete s;
@@ -224,6 +230,7 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
     case SIRRT_OPT_CHUNK_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad chunk"); s->chunk_configs = value; break;
     case SIRRT_OPT_SWEEP_MIN_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad threshold"); s->sweep_min_configs = value; break;
     case SIRRT_OPT_DEFER_MAX_CONFIGS: if (value < 0) return fail(SIRRT_E_ARG, "bad threshold"); s->defer_max_configs = value; break;
+    case SIRRT_OPT_PIPELINE: s->pipeline = value != 0; break;
     case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
     default: return fail(SIRRT_E_ARG, "unknown option");
   }

@@ -200,17 +200,134 @@ static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, i
   return SIRRT_OK;
 }
 
+// Pipelined form of the batched path for HOST buffers (the end-to-end path of a caller that keeps its configurations and
+// tables in host memory): the batch is cut into blocks of at most SIRRT_PIPE_CONFIGS configurations and three streams run
+//   copy-in: H2D of block k+1   ||   compute: sweep + FP64 re-check + intervals of block k   ||   copy-out: D2H of block k-1
+// so that only the first block's upload and the last block's download are exposed.  Results are those of the plain path
+// (same kernels, same per-block work lists); a block whose FP64 work list overflowed sends the call to the plain path.
+#define SIRRT_PIPE_CONFIGS (128 << 10)
+static int bits_and_table_pipelined(sirrt_scene* s, const float* hq, long long N, int32_t* table, int Kmax, uint32_t* bits, uint64_t* near_contact_count,
+                                    bool* fell_back, int16_t* table16 = nullptr) {
+  *fell_back = false;
+  const int W = s->tb.n_tiles, dof = s->hs.dof, cols = 1 + 2 * Kmax;
+  const size_t esz = table16 ? sizeof(int16_t) : sizeof(int32_t);  // compact rows: int16 entries
+  if (table16) table = (int32_t*)table16;
+  CU(cudaSetDevice(s->device));
+  memset(s->stats, 0, sizeof s->stats);
+  if (!s->copy_in) {
+    CU(cudaStreamCreateWithFlags(&s->copy_in, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&s->copy_out, cudaStreamNonBlocking));
+  }
+  const long long per = std::min<long long>(SIRRT_PIPE_CONFIGS, s->chunk_configs);
+  const size_t nb = (size_t)((N + per - 1) / per);
+  while (s->pipe_ev.size() < 2 * nb) {
+    cudaEvent_t e;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    s->pipe_ev.push_back(e);
+  }
+  if (s->q.ensure((size_t)N * dof * sizeof(float)) || s->bits.ensure((size_t)N * W * sizeof(uint32_t)) || (table && s->table.ensure((size_t)N * cols * esz)) ||
+      s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem)) || s->counts.ensure(nb * 4 * sizeof(unsigned)))
+    return fail(SIRRT_E_CUDA, "cudaMalloc(pipeline buffers) failed");
+  cudaStream_t st = s->stream;
+  float* dq = s->q.as<float>();
+  uint32_t* d_bits = s->bits.as<uint32_t>();
+  int32_t* d_table = table ? s->table.as<int32_t>() : nullptr;
+  const bool sweep = s->use_sweep && s->sweep.supported && N >= s->sweep_min_configs;
+  CU(cudaMemsetAsync(s->counts.p, 0, nb * 4 * sizeof(unsigned), st));
+  uint64_t launches = 0;
+  for (size_t i = 0; i < nb; i++) {
+    const long long n0 = (long long)i * per, cnt = std::min(per, N - n0);
+    // joint rows of the SoA batch are N floats apart on both sides: one strided copy per block
+    CU(cudaMemcpy2DAsync(dq + n0, (size_t)N * sizeof(float), hq + n0, (size_t)N * sizeof(float), (size_t)cnt * sizeof(float), dof, cudaMemcpyHostToDevice, s->copy_in));
+    CU(cudaEventRecord(s->pipe_ev[2 * i], s->copy_in));
+    CU(cudaStreamWaitEvent(st, s->pipe_ev[2 * i], 0));
+    QView qv{dq, nullptr, N, n0, cnt, dof};
+    WorkList wl{s->work.as<WorkItem>(), s->counts.as<unsigned>() + 4 * i, s->wl_cap};
+    const bool timed = i < s->ev.size() / 2;
+    if (timed) cudaEventRecord(s->ev[2 * i], st);
+    if (sweep) launches += sweep_launch(s->sweep, s->tb.robot, s->d, qv, wl, d_bits, W, (float)s->band, s->n_sm, st);
+    else {
+      BitsParams P{};
+      P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.bits = d_bits; P.n_words = W; P.semantics = SIRRT_SEM_INTERVAL; P.band = (float)s->band;
+      const long long target = (long long)s->n_sm * 32;
+      int n_chunks = (int)std::max(1ll, std::min((long long)W, target / std::max(1ll, cnt)));
+      P.tiles_per_chunk = (W + n_chunks - 1) / n_chunks;
+      P.n_chunks = (W + P.tiles_per_chunk - 1) / P.tiles_per_chunk;
+      const int grid = grid_for(cnt * P.n_chunks, s->n_sm, 8);
+      if (s->tb.has_hull) k_collide_bits<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
+      else k_collide_bits<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
+      launches++;
+    }
+    if (timed) cudaEventRecord(s->ev[2 * i + 1], st);
+    RecheckParams R{};
+    R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
+    R.aabb_d = s->d_aabb_d; R.bits = d_bits; R.n_words = W; R.cells = nullptr; R.counters = wl.count;
+    k_recheck<<<s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
+    launches++;
+    if (table) {
+      IvParams I{d_bits + (size_t)n0 * W, cnt, W, s->tb.T, Kmax, table16 ? nullptr : d_table + (size_t)n0 * cols};
+      if (table16) I.table16 = (int16_t*)d_table + (size_t)n0 * cols;
+      k_bits_to_intervals<<<(unsigned)((cnt + 7) / 8), 256, 0, st>>>(I);
+      launches++;
+    }
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(s->pipe_ev[2 * i + 1], st));
+    CU(cudaStreamWaitEvent(s->copy_out, s->pipe_ev[2 * i + 1], 0));
+    if (table) CU(cudaMemcpyAsync((char*)table + (size_t)n0 * cols * esz, (char*)d_table + (size_t)n0 * cols * esz, (size_t)cnt * cols * esz, cudaMemcpyDeviceToHost, s->copy_out));
+    if (bits) CU(cudaMemcpyAsync(bits + (size_t)n0 * W, d_bits + (size_t)n0 * W, (size_t)cnt * W * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->copy_out));
+  }
+  std::vector<unsigned> host(nb * 4);
+  CU(cudaMemcpyAsync(host.data(), s->counts.p, nb * 4 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+  CU(sirrt_sync(st));
+  CU(sirrt_sync(s->copy_out));
+  uint64_t rechecked = 0, near = 0, exact = 0, sweep_ns = 0;
+  for (size_t i = 0; i < nb; i++) {
+    if (host[4 * i] > s->wl_cap || host[4 * i + 3] > s->wl_cap) { *fell_back = true; return SIRRT_OK; }  // repeat on the plain (splitting) path
+    rechecked += host[4 * i]; exact += host[4 * i + 1] + host[4 * i + 3]; near += host[4 * i + 2];
+    float ms = 0;
+    if (i < s->ev.size() / 2 && cudaEventElapsedTime(&ms, s->ev[2 * i], s->ev[2 * i + 1]) == cudaSuccess) sweep_ns += (uint64_t)(ms * 1e6);
+    else cudaGetLastError();
+  }
+  s->stats[0] = launches; s->stats[1] = rechecked; s->stats[2] = near; s->stats[3] = exact; s->stats[4] = sweep_ns;
+  if (near_contact_count) *near_contact_count = near;
+  return SIRRT_OK;
+}
+
 extern "C" int sirrt_safe_intervals_batch(sirrt_scene* s, const float* q_soa, int64_t N, int32_t* table, int Kmax,
                                           uint32_t* bits, uint64_t* near_contact_count) {
   if (!s || !q_soa || N < 0 || (table && Kmax < 1) || (!table && !bits)) return fail(SIRRT_E_ARG, "sirrt_safe_intervals_batch: bad argument");
   if (N == 0) { if (near_contact_count) *near_contact_count = 0; return SIRRT_OK; }
   if (N > 0x7fffffffll) return fail(SIRRT_E_ARG, "N exceeds 2^31-1 configurations per call");
   CU(cudaSetDevice(s->device));
+  int rc;
+  if (s->pipeline && N > SIRRT_PIPE_CONFIGS && !is_device_ptr(q_soa) && !(table && is_device_ptr(table)) && !(bits && is_device_ptr(bits))) {
+    bool fell_back = false;  // host buffers, more than one block: copies overlap the kernels
+    rc = bits_and_table_pipelined(s, q_soa, N, table, Kmax, bits, near_contact_count, &fell_back);
+    if (rc || !fell_back) return rc;
+  }
   const void* dq = nullptr;
-  int rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq, PIN_Q, 64 << 10);
+  rc = stage_in(s, s->q, q_soa, (size_t)N * s->hs.dof * sizeof(float), &dq, PIN_Q, 64 << 10);
   if (rc) return rc;
   QView q{(const float*)dq, nullptr, N, 0, N, s->hs.dof};
   return bits_and_table(s, q, N, SIRRT_SEM_INTERVAL, table, Kmax, bits, near_contact_count);
+}
+
+// Compact form of the interval table: int16 entries (row = {count, lo0, hi0, ...}, unused = -1), half the bytes of the
+// default int32 table on the way back to the host.  Host buffers; scenes with at most 32767 frames.
+extern "C" int sirrt_safe_intervals_batch_i16(sirrt_scene* s, const float* q_soa, int64_t N, int16_t* table16, int Kmax, uint64_t* near_contact_count) {
+  if (!s || !q_soa || !table16 || N < 0 || Kmax < 1) return fail(SIRRT_E_ARG, "sirrt_safe_intervals_batch_i16: bad argument");
+  if (s->tb.T > 32767) return fail(SIRRT_E_LIMIT, "sirrt_safe_intervals_batch_i16: more than 32767 frames; use the int32 table");
+  if (is_device_ptr(q_soa) || is_device_ptr(table16)) return fail(SIRRT_E_ARG, "sirrt_safe_intervals_batch_i16 takes host buffers");
+  if (N == 0) { if (near_contact_count) *near_contact_count = 0; return SIRRT_OK; }
+  if (N > 0x7fffffffll) return fail(SIRRT_E_ARG, "N exceeds 2^31-1 configurations per call");
+  bool fell_back = false;
+  int rc = bits_and_table_pipelined(s, q_soa, N, nullptr, Kmax, nullptr, near_contact_count, &fell_back, table16);
+  if (rc || !fell_back) return rc;
+  // a block's FP64 work list overflowed: the plain path (which splits such blocks), then narrow on the host
+  std::vector<int32_t> wide((size_t)N * (1 + 2 * Kmax));
+  if ((rc = sirrt_safe_intervals_batch(s, q_soa, N, wide.data(), Kmax, nullptr, near_contact_count))) return rc;
+  for (size_t i = 0; i < wide.size(); i++) table16[i] = (int16_t)wide[i];
+  return SIRRT_OK;
 }
 
 extern "C" int sirrt_collision_bits_f64(sirrt_scene* s, const double* q_aos, int64_t N, int semantics, uint32_t* bits) {

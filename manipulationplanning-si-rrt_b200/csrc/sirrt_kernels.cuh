@@ -505,6 +505,7 @@ struct IvParams {
   long long N;
   int n_words, T, Kmax;
   int32_t* table;  // [N][1+2*Kmax]
+  int16_t* table16 = nullptr;  // compact form of the same rows (frames < 32768); used instead of `table` when set
 };
 
 __device__ __forceinline__ int warp_excl_scan(int v, int lane, int& total) {
@@ -520,9 +521,8 @@ __device__ __forceinline__ int warp_excl_scan(int v, int lane, int& total) {
 
 // one warp: collision row n -> its line of the interval table.  Rows are read past L1 (__ldcg): on the fused latency path
 // the bits were OR-ed in by other blocks of the same launch.
-__device__ inline void row_to_intervals(const IvParams& P, long long n, int lane) {
+template <typename OutT> __device__ inline void row_to_intervals_t(const IvParams& P, OutT* out, long long n, int lane) {
   const uint32_t* row = P.bits + (size_t)n * P.n_words;
-  int32_t* out = P.table + (size_t)n * (1 + 2 * P.Kmax);
   int n_starts = 0, n_ends = 0;
   uint32_t prev_safe = 0;  // safe bit of the last frame of the previous group (frame -1: "collision")
   for (int w0 = 0; w0 < P.n_words; w0 += 32) {
@@ -544,14 +544,18 @@ __device__ inline void row_to_intervals(const IvParams& P, long long n, int lane
     int ts, te;
     int rs = n_starts + warp_excl_scan(__popc(starts), lane, ts);
     int re = n_ends + warp_excl_scan(__popc(ends), lane, te);
-    while (starts) { const int b = __ffs(starts) - 1; starts &= starts - 1; if (rs < P.Kmax) out[1 + 2 * rs] = w * 32 + b; rs++; }
-    while (ends) { const int b = __ffs(ends) - 1; ends &= ends - 1; if (re < P.Kmax) out[2 + 2 * re] = w * 32 + b; re++; }
+    while (starts) { const int b = __ffs(starts) - 1; starts &= starts - 1; if (rs < P.Kmax) out[1 + 2 * rs] = (OutT)(w * 32 + b); rs++; }
+    while (ends) { const int b = __ffs(ends) - 1; ends &= ends - 1; if (re < P.Kmax) out[2 + 2 * re] = (OutT)(w * 32 + b); re++; }
     n_starts += ts; n_ends += te;
     prev_safe = __shfl_sync(SIRRT_FULL, s >> 31, 31);
   }
   // unused pairs = -1; the count is the true number of intervals even when it exceeds Kmax
-  for (int k = 2 * min(n_starts, P.Kmax) + lane; k < 2 * P.Kmax; k += 32) out[1 + k] = -1;
-  if (lane == 0) out[0] = n_starts;
+  for (int k = 2 * min(n_starts, P.Kmax) + lane; k < 2 * P.Kmax; k += 32) out[1 + k] = (OutT)-1;
+  if (lane == 0) out[0] = (OutT)n_starts;
+}
+__device__ inline void row_to_intervals(const IvParams& P, long long n, int lane) {
+  if (P.table16) row_to_intervals_t<int16_t>(P, P.table16 + (size_t)n * (1 + 2 * P.Kmax), n, lane);
+  else row_to_intervals_t<int32_t>(P, P.table + (size_t)n * (1 + 2 * P.Kmax), n, lane);
 }
 
 __global__ void __launch_bounds__(256) k_bits_to_intervals(const __grid_constant__ IvParams P) {

@@ -257,207 +257,209 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
     const bool active = have && !((shm >> cl) & 1u);
     int q0n = 0, q1n = 0, qwn = 0, q2n = 0, q3n = 0;
 
-    // ---- B2: lane = Q2 entry (configuration, link, slot, frame): the frames stage W could not decide from the model
-    auto run_b2 = [&](const uint32_t* qp, int count) {
-      __syncwarp();
-      bool want = false;
-      unsigned u = 0;
-      if (lane < count) {
-        u = qp[lane];
-        const int cfg = u & 31, l = (u >> 5) & 7, fr = (u >> 8) & 31, tile = u >> 24, j = (u >> 13) & 2047;
-        if (!((sbits[cfg * Wp + tile] >> fr) & 1u)) {  // another pair may have decided this frame already
-          const int f = tile * 32 + fr;
-          const float4 c4 = __ldg(P.ctr + (size_t)j * Tp + f);
-          const float4 dj = __ldg(P.dyn + j);
-          const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + cfg;
-          const float apx = c4.x - lkp[0], apy = c4.y - lkp[SWEEP_LDC], apz = c4.z - lkp[2 * SWEEP_LDC];
-          const float abx = lkp[3 * SWEEP_LDC], aby = lkp[4 * SWEEP_LDC], abz = lkp[5 * SWEEP_LDC];
-          float tt = (apx * abx + apy * aby + apz * abz) * lkp[6 * SWEEP_LDC];
-          tt = fminf(fmaxf(tt, -0.5f), 0.5f);
-          const float ex = apx - tt * abx, ey = apy - tt * aby, ez = apz - tt * abz;  // closest axis point -> obstacle centre
-          const float d2 = ex * ex + ey * ey + ez * ez;
-          const float rl = s_lr[l];
-          bool hit = false;
-          if (dj.z >= 0.f) {  // sphere obstacle: the point-segment distance IS the narrowphase
-            const int r = classify(sqrtf(d2) - rl - dj.z, band);
-            n_exact++;
-            if (r == RES_HIT) hit = true;
-            else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), f, l, sc.dynamic_slots[j], 0);
-          } else {
-            const float4 h4 = __ldg(P.dyn2 + j);
-            bool fre;
-            if (h4.w != 0.f) {
-              // axis-aligned box (world frame == box frame up to the translation).  With p* the closest axis point:
-              //   dist(segment, box) <= dist(p*, box)                              -> HIT  when dist(p*, box) < rl - band
-              //   dist(segment, box) >= |e| - h.|e|/|e|  (plane through p* normal to e separates: the segment lies
-              //   on or behind it, the box reaches at most its support h.|n| towards it) -> FREE when that > rl + band
-              const float ax = fabsf(ex), ay = fabsf(ey), az = fabsf(ez);
-              const float qx = fmaxf(ax - h4.x, 0.f), qy = fmaxf(ay - h4.y, 0.f), qz = fmaxf(az - h4.z, 0.f);
-              const float rlo = rl - band, rhi = rl + band;
-              hit = qx * qx + qy * qy + qz * qz < rlo * rlo;
-              fre = d2 - (h4.x * ax + h4.y * ay + h4.z * az) > rhi * sqrtf(d2);
-            } else {
-              const float hi = rl + dj.y + band;  // beyond the circumscribed sphere: free
-              const float lo = rl + dj.x - band;  // inside the inscribed sphere: hit
-              fre = d2 > hi * hi;
-              hit = d2 < lo * lo;
+    // ---- dynamic slots.  Every stage has exactly ONE call site (the kernel's instruction footprint decides how often the
+    // 28 resident warps, each in a different stage, miss the instruction cache): nested loops, a stage runs when a full
+    // batch of 32 is queued or, once everything in front of it has drained (fN), on what is left.
+    for (int tile0 = 0, j0 = 0;;) {
+      const bool flush = tile0 >= n_tiles;
+      if (!flush) {
+        // ---- A0: lane = (configuration, half of the round); arm sphere vs 4 of the round's 8 swept spheres
+        const int u0 = (lane >> 4) * 4;
+        const float4* bp = P.bounds + (size_t)tile0 * ndp + j0 + u0;
+        unsigned mask = 0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const float4 tb = __ldg(bp + u);
+          const float dx = acx - tb.x, dy = acy - tb.y, dz = acz - tb.z;
+          const float rr = ar + tb.w;
+          if (dx * dx + dy * dy + dz * dz <= rr * rr) mask |= 1u << u;
+        }
+        mask <<= u0;
+        if (!active) mask = 0;
+        if (__any_sync(SIRRT_FULL, mask != 0)) {
+          int total;
+          int w = q0n + warp_excl_scan(__popc(mask), lane, total);
+          const unsigned base = (unsigned)cl | ((((unsigned)tile0 << 11) | (unsigned)j0) << 5);
+          while (mask) {
+            const int u = __ffs(mask) - 1;
+            mask &= mask - 1;
+            q0[w++] = base + ((unsigned)u << 5);
+          }
+          q0n += total;
+        }
+        j0 += 8;
+        if (j0 >= ndp) { j0 = 0; tile0++; }
+      }
+      if (q0n >= 32 || flush) do {
+        if (q0n > 0) {
+          // ---- A1: lane = Q0 entry; link bounding spheres vs the swept sphere of the pair
+          const int cnt = min(32, q0n);
+          q0n -= cnt;
+          __syncwarp();
+          unsigned lm = 0, e = 0;
+          if (lane < cnt) {
+            e = q0[q0n + lane];
+            const float* lkp = lk + (e & 31);
+            const float4 b4 = __ldg(P.bounds + SWEEP_PAIR(e >> 5, ndp));
+            const float rb4 = b4.w + band;
+#pragma unroll
+            for (int l = 0; l < SWEEP_MAXL; l++)
+              if (l < L) {
+                const float dx = lkp[(l * SWEEP_ROWS + 0) * SWEEP_LDC] - b4.x, dy = lkp[(l * SWEEP_ROWS + 1) * SWEEP_LDC] - b4.y,
+                            dz = lkp[(l * SWEEP_ROWS + 2) * SWEEP_LDC] - b4.z;
+                const float rr = P.link_br[l] + rb4;
+                if (dx * dx + dy * dy + dz * dz <= rr * rr) lm |= 1u << l;
+              }
+          }
+          int total;
+          int w = q1n + warp_excl_scan(__popc(lm), lane, total);
+          const unsigned ebase = (e & 31u) | ((e >> 5) << 8);
+          while (lm) {
+            const int l = __ffs(lm) - 1;
+            lm &= lm - 1;
+            q1[w++] = ebase | ((unsigned)l << 5);
+          }
+          q1n += total;
+          __syncwarp();
+        }
+        const bool f1 = flush && q0n == 0;
+        if (q1n >= 32 || f1) do {
+          if (q1n > 0) {
+            // ---- B1: lane = Q1 entry; link axis vs the slot's swept capsule over the tile
+            const int cnt = min(32, q1n);
+            q1n -= cnt;
+            bool kp = false;
+            unsigned e = 0;
+            if (lane < cnt) {
+              e = q1[q1n + lane];
+              const int l = (e >> 5) & 7;
+              const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + (e & 31);
+              float a[3], b[3];
+#pragma unroll
+              for (int k = 0; k < 3; k++) { const float cc = lkp[k * SWEEP_LDC], h = 0.5f * lkp[(3 + k) * SWEEP_LDC]; a[k] = cc - h; b[k] = cc + h; }
+              const float4* sp = P.seg + 2 * SWEEP_PAIR(e >> 8, ndp);
+              const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
+              const float p0[3] = {s0.x, s0.y, s0.z}, p1[3] = {s1.x, s1.y, s1.z};
+              const float rr = s_lr[l] + s0.w + band;
+              kp = seg_seg_dist2(a, b, p0, p1) <= rr * rr;
             }
-            want = !hit && !fre;
+            const unsigned keep = __ballot_sync(SIRRT_FULL, kp);
+            if (keep) {
+              if (kp) qw[qwn + __popc(keep & lt_mask)] = e;
+              qwn += __popc(keep);
+            }
           }
-          if (hit) atomicOr(&sbits[cfg * Wp + tile], 1u << fr);
-        }
-      }
-      const unsigned mq = __ballot_sync(SIRRT_FULL, want);
-      if (mq) {
-        if (want) q3[q3n + __popc(mq & lt_mask)] = u;
-        q3n += __popc(mq);
-      }
-      __syncwarp();
-      if (q3n >= 32) {
-        q3n -= 32;
-        n_exact += sweep_exact_batch(P, lk, sbits, s_lr, q3 + q3n, 32, lane, cfg0);
-      }
-    };
-
-    // ---- W: lane = QW entry (configuration, link, tile, slot): analytic HIT / IN frame windows, then the undecided
-    // frames are enumerated into Q2, at most one per lane and round
-    auto run_w = [&](const uint32_t* qp, int count) {
-      __syncwarp();
-      unsigned tm = 0, code = 0;
-      if (lane < count) {
-        const unsigned e = qp[lane];
-        const int cfg = e & 31, l = (e >> 5) & 7, tile = e >> 19, j = (e >> 8) & 2047;
-        const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + cfg;
-        const float4* mp = P.mdl + 4 * (size_t)SWEEP_PAIR(e >> 8, ndp);
-        const float4 m0 = __ldg(mp), m1 = __ldg(mp + 1), m2 = __ldg(mp + 2), m3 = __ldg(mp + 3);
-        const float4 dj = __ldg(P.dyn + j);
-        const float rl = s_lr[l];
-        unsigned in, hit;
-        sweep_windows(m0, m1, m2, m3, lkp[0], lkp[SWEEP_LDC], lkp[2 * SWEEP_LDC], lkp[3 * SWEEP_LDC], lkp[4 * SWEEP_LDC], lkp[5 * SWEEP_LDC],
-                      lkp[6 * SWEEP_LDC], rl + dj.y + band, rl + dj.x - band, in, hit);
-        const uint32_t cur = sbits[cfg * Wp + tile];
-        if (hit & ~cur) atomicOr(&sbits[cfg * Wp + tile], hit);
-        tm = in & ~hit & ~cur;
-        code = (e & 0xffu) | ((e >> 8) << 13);
-      }
-      for (;;) {
-        const unsigned b = __ballot_sync(SIRRT_FULL, tm != 0u);
-        if (!b) break;
-        if (tm) {
-          const unsigned fr = __ffs(tm) - 1;
-          tm &= tm - 1;
-          q2[q2n + __popc(b & lt_mask)] = code | (fr << 8);
-        }
-        q2n += __popc(b);
-        if (q2n >= 32) {
-          q2n -= 32;
-          run_b2(q2 + q2n, 32);
-        }
-      }
-    };
-
-    // ---- B1: lane = Q1 entry; link axis vs the slot's swept capsule over the tile
-    auto run_b1 = [&](const uint32_t* qp, int count) {
-      bool kp = false;
-      unsigned e = 0;
-      if (lane < count) {
-        e = qp[lane];
-        const int l = (e >> 5) & 7;
-        const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + (e & 31);
-        float a[3], b[3];
-#pragma unroll
-        for (int k = 0; k < 3; k++) { const float cc = lkp[k * SWEEP_LDC], h = 0.5f * lkp[(3 + k) * SWEEP_LDC]; a[k] = cc - h; b[k] = cc + h; }
-        const float4* sp = P.seg + 2 * SWEEP_PAIR(e >> 8, ndp);
-        const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
-        const float p0[3] = {s0.x, s0.y, s0.z}, p1[3] = {s1.x, s1.y, s1.z};
-        const float rr = s_lr[l] + s0.w + band;
-        kp = seg_seg_dist2(a, b, p0, p1) <= rr * rr;
-      }
-      const unsigned keep = __ballot_sync(SIRRT_FULL, kp);
-      if (keep) {
-        if (kp) qw[qwn + __popc(keep & lt_mask)] = e;
-        qwn += __popc(keep);
-        if (qwn >= 32) {
-          qwn -= 32;
-          run_w(qw + qwn, 32);
-        }
-      }
-    };
-
-    // ---- A1: lane = Q0 entry; link bounding spheres vs the swept sphere of the pair
-    auto run_a1 = [&](const uint32_t* qp, int count) {
-      __syncwarp();
-      unsigned lm = 0, e = 0;
-      if (lane < count) {
-        e = qp[lane];
-        const float* lkp = lk + (e & 31);
-        const float4 b4 = __ldg(P.bounds + SWEEP_PAIR(e >> 5, ndp));
-        const float rb4 = b4.w + band;
-#pragma unroll
-        for (int l = 0; l < SWEEP_MAXL; l++)
-          if (l < L) {
-            const float dx = lkp[(l * SWEEP_ROWS + 0) * SWEEP_LDC] - b4.x, dy = lkp[(l * SWEEP_ROWS + 1) * SWEEP_LDC] - b4.y,
-                        dz = lkp[(l * SWEEP_ROWS + 2) * SWEEP_LDC] - b4.z;
-            const float rr = P.link_br[l] + rb4;
-            if (dx * dx + dy * dy + dz * dz <= rr * rr) lm |= 1u << l;
-          }
-      }
-      int total;
-      int w = q1n + warp_excl_scan(__popc(lm), lane, total);
-      const unsigned ebase = (e & 31u) | ((e >> 5) << 8);
-      while (lm) {
-        const int l = __ffs(lm) - 1;
-        lm &= lm - 1;
-        q1[w++] = ebase | ((unsigned)l << 5);
-      }
-      q1n += total;
-      __syncwarp();
-      while (q1n >= 32) {
-        q1n -= 32;
-        run_b1(q1 + q1n, 32);
-      }
-    };
-
-    // ---- dynamic slots: A0 rounds of 8 (tile, slot) pairs, stages drained whenever a batch of 32 is ready
-    for (int tile0 = 0, j0 = 0; tile0 < n_tiles;) {
-      // ---- A0: lane = (configuration, half of the round); arm sphere vs 4 of the round's 8 swept
-      // spheres -> per-lane pass mask
-      const int u0 = (lane >> 4) * 4;
-      const float4* bp = P.bounds + (size_t)tile0 * ndp + j0 + u0;
-      unsigned mask = 0;
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const float4 tb = __ldg(bp + u);
-        const float dx = acx - tb.x, dy = acy - tb.y, dz = acz - tb.z;
-        const float rr = ar + tb.w;
-        if (dx * dx + dy * dy + dz * dz <= rr * rr) mask |= 1u << u;
-      }
-      mask <<= u0;
-      if (!active) mask = 0;
-      if (__any_sync(SIRRT_FULL, mask != 0)) {
-        int total;
-        int w = q0n + warp_excl_scan(__popc(mask), lane, total);
-        const unsigned base = (unsigned)cl | ((((unsigned)tile0 << 11) | (unsigned)j0) << 5);
-        while (mask) {
-          const int u = __ffs(mask) - 1;
-          mask &= mask - 1;
-          q0[w++] = base + ((unsigned)u << 5);
-        }
-        q0n += total;
-        while (q0n >= 32) {
-          q0n -= 32;
-          run_a1(q0 + q0n, 32);
-        }
-      }
-      j0 += 8;
-      if (j0 >= ndp) { j0 = 0; tile0++; }
+          const bool f2 = f1 && q1n == 0;
+          if (qwn >= 32 || f2) do {
+            // ---- W: lane = QW entry (configuration, link, tile, slot): analytic HIT / IN frame windows
+            unsigned tm = 0, code = 0;
+            if (qwn > 0) {
+              const int cnt = min(32, qwn);
+              qwn -= cnt;
+              __syncwarp();
+              if (lane < cnt) {
+                const unsigned e = qw[qwn + lane];
+                const int cfg = e & 31, l = (e >> 5) & 7, tile = e >> 19, j = (e >> 8) & 2047;
+                const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + cfg;
+                const float4* mp = P.mdl + 4 * (size_t)SWEEP_PAIR(e >> 8, ndp);
+                const float4 m0 = __ldg(mp), m1 = __ldg(mp + 1), m2 = __ldg(mp + 2), m3 = __ldg(mp + 3);
+                const float4 dj = __ldg(P.dyn + j);
+                const float rl = s_lr[l];
+                unsigned in, hit;
+                sweep_windows(m0, m1, m2, m3, lkp[0], lkp[SWEEP_LDC], lkp[2 * SWEEP_LDC], lkp[3 * SWEEP_LDC], lkp[4 * SWEEP_LDC],
+                              lkp[5 * SWEEP_LDC], lkp[6 * SWEEP_LDC], rl + dj.y + band, rl + dj.x - band, in, hit);
+                const uint32_t cur = sbits[cfg * Wp + tile];
+                if (hit & ~cur) atomicOr(&sbits[cfg * Wp + tile], hit);
+                tm = in & ~hit & ~cur;
+                code = (e & 0xffu) | ((e >> 8) << 13);
+              }
+            }
+            const bool f3 = f2 && qwn == 0;
+            // the frames the model could not decide are enumerated into Q2, at most one per lane and round
+            for (;;) {
+              const unsigned b = __ballot_sync(SIRRT_FULL, tm != 0u);
+              if (b) {
+                if (tm) {
+                  const unsigned fr = __ffs(tm) - 1;
+                  tm &= tm - 1;
+                  q2[q2n + __popc(b & lt_mask)] = code | (fr << 8);
+                }
+                q2n += __popc(b);
+              }
+              const bool f4 = f3 && !b;
+              if (q2n >= 32 || f4) do {
+                // ---- B2: lane = Q2 entry (configuration, link, slot, frame), tested against the TRUE centre
+                const int cnt = min(32, q2n);  // 0 only on the final drain (f4) with an empty Q2: Q3 may still hold entries
+                q2n -= cnt;
+                __syncwarp();
+                bool want = false;
+                unsigned u = 0;
+                if (lane < cnt) {
+                  u = q2[q2n + lane];
+                  const int cfg = u & 31, l = (u >> 5) & 7, fr = (u >> 8) & 31, tile = u >> 24, j = (u >> 13) & 2047;
+                  if (!((sbits[cfg * Wp + tile] >> fr) & 1u)) {  // another pair may have decided this frame already
+                    const int f = tile * 32 + fr;
+                    const float4 c4 = __ldg(P.ctr + (size_t)j * Tp + f);
+                    const float4 dj = __ldg(P.dyn + j);
+                    const float* lkp = lk + l * (SWEEP_ROWS * SWEEP_LDC) + cfg;
+                    const float apx = c4.x - lkp[0], apy = c4.y - lkp[SWEEP_LDC], apz = c4.z - lkp[2 * SWEEP_LDC];
+                    const float abx = lkp[3 * SWEEP_LDC], aby = lkp[4 * SWEEP_LDC], abz = lkp[5 * SWEEP_LDC];
+                    float tt = (apx * abx + apy * aby + apz * abz) * lkp[6 * SWEEP_LDC];
+                    tt = fminf(fmaxf(tt, -0.5f), 0.5f);
+                    const float ex = apx - tt * abx, ey = apy - tt * aby, ez = apz - tt * abz;  // closest axis point -> obstacle centre
+                    const float d2 = ex * ex + ey * ey + ez * ez;
+                    const float rl = s_lr[l];
+                    bool hit = false;
+                    if (dj.z >= 0.f) {  // sphere obstacle: the point-segment distance IS the narrowphase
+                      const int r = classify(sqrtf(d2) - rl - dj.z, band);
+                      n_exact++;
+                      if (r == RES_HIT) hit = true;
+                      else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), f, l, sc.dynamic_slots[j], 0);
+                    } else {
+                      const float4 h4 = __ldg(P.dyn2 + j);
+                      bool fre;
+                      if (h4.w != 0.f) {
+                        // axis-aligned box (world frame == box frame up to the translation).  With p* the closest axis point:
+                        //   dist(segment, box) <= dist(p*, box)                      -> HIT  when dist(p*, box) < rl - band
+                        //   dist(segment, box) >= |e| - h.|e| / |e|  (the plane through p* normal to e separates: the
+                        //   segment lies on or behind it, the box reaches at most its support h.|n| towards it)
+                        //                                                            -> FREE when that > rl + band
+                        const float ax = fabsf(ex), ay = fabsf(ey), az = fabsf(ez);
+                        const float qx = fmaxf(ax - h4.x, 0.f), qy = fmaxf(ay - h4.y, 0.f), qz = fmaxf(az - h4.z, 0.f);
+                        const float rlo = rl - band, rhi = rl + band;
+                        hit = qx * qx + qy * qy + qz * qz < rlo * rlo;
+                        fre = d2 - (h4.x * ax + h4.y * ay + h4.z * az) > rhi * sqrtf(d2);
+                      } else {
+                        const float hi = rl + dj.y + band;  // beyond the circumscribed sphere: free
+                        const float lo = rl + dj.x - band;  // inside the inscribed sphere: hit
+                        fre = d2 > hi * hi;
+                        hit = d2 < lo * lo;
+                      }
+                      want = !hit && !fre;
+                    }
+                    if (hit) atomicOr(&sbits[cfg * Wp + tile], 1u << fr);
+                  }
+                }
+                const unsigned mq = __ballot_sync(SIRRT_FULL, want);
+                if (mq) {
+                  if (want) q3[q3n + __popc(mq & lt_mask)] = u;
+                  q3n += __popc(mq);
+                }
+                const bool f5 = f4 && q2n == 0;
+                while (q3n >= 32 || (f5 && q3n > 0)) {
+                  // ---- C: lane = Q3 entry: exact segment-box narrowphase
+                  const int c3 = min(32, q3n);
+                  q3n -= c3;
+                  n_exact += sweep_exact_batch(P, lk, sbits, s_lr, q3 + q3n, c3, lane, cfg0);
+                }
+              } while (q2n >= 32 || (f4 && q2n > 0));
+              if (!b) break;
+            }
+          } while (qwn >= 32 || (f2 && qwn > 0));
+        } while (q1n >= 32 || (f1 && q1n > 0));
+      } while (q0n >= 32 || (flush && q0n > 0));
+      if (flush) break;
     }
-    // ---- flush: every queue is drained front to back (a stage only pushes into the queues behind it)
-    while (q0n > 0) { const int c = min(32, q0n); q0n -= c; run_a1(q0 + q0n, c); }
-    while (q1n > 0) { const int c = min(32, q1n); q1n -= c; run_b1(q1 + q1n, c); }
-    while (qwn > 0) { const int c = min(32, qwn); qwn -= c; run_w(qw + qwn, c); }
-    while (q2n > 0) { const int c = min(32, q2n); q2n -= c; run_b2(q2 + q2n, c); }
-    if (q3n > 0) n_exact += sweep_exact_batch(P, lk, sbits, s_lr, q3, q3n, lane, cfg0);
 
     // ---- rows out: lane = word, coalesced ------------------------------------------------------------
     __syncwarp();

@@ -37,7 +37,12 @@ SWEEP_HD unsigned sweep_quad_mask(float A, float B, float C, int deg, bool super
   } else {
     const float disc = B * B - A * C;
     if (!(disc >= 0.f)) return 0u;
+#ifdef __CUDA_ARCH__
+    // MUFU approximations (2 ulp): a root may move by 1e-5 frames, far inside what the radius margins absorb
+    const float sq = disc * rsqrtf(fmaxf(disc, 1e-37f)), ia = __fdividef(1.f, A);
+#else
     const float sq = sqrtf(disc), ia = 1.f / A;
+#endif
     const float r1 = (-B - sq) * ia, r2 = (-B + sq) * ia;
     if (!(r1 <= r2)) return 0u;
     lo = fmaxf(lo, ceilf(r1));
@@ -55,7 +60,11 @@ SWEEP_HD unsigned sweep_lin_mask(float wa, float va, float h, int g0, int len) {
   if (fabsf(va) < 1e-12f) {
     if (!(fabsf(wa) <= h)) return 0u;
   } else {
+#ifdef __CUDA_ARCH__
+    const float iv = __fdividef(1.f, va);
+#else
     const float iv = 1.f / va;
+#endif
     const float r1 = (-h - wa) * iv, r2 = (h - wa) * iv;
     lo = fmaxf(lo, ceilf(fminf(r1, r2)));
     hi = fminf(hi, floorf(fmaxf(r1, r2)));

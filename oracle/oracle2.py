@@ -342,24 +342,31 @@ def segment_segment_distance(a1, b1, a2, b2) -> float:
 
 def hull_intersect_lp(A: np.ndarray, B: np.ndarray) -> bool:
     """conv(A) and conv(B) share a point  <=>  the LP {lambda, mu >= 0, sum lambda = sum mu = 1, A^T lambda = B^T mu} is
-    feasible (world-frame vertex arrays [n,3]).  Coordinates are centred on the mean of B to keep the rows well scaled."""
+    feasible (world-frame vertex arrays [n,3]).  Coordinates are centred on the mean of B and scaled to unit size.  A
+    grazing contact can leave the simplex runs undecided ("unknown" status); then the phase-1 form of the same LP
+    (always feasible: minimise the L1 norm of the slack s in A^T lambda - B^T mu = s) decides: intersecting iff its
+    optimum is zero to the solver's 1e-9."""
     c = B.mean(0)
-    A, B = A - c, B - c
+    sc = max(float(np.abs(A - c).max()), float(np.abs(B - c).max()), 1e-9)
+    A, B = (A - c) / sc, (B - c) / sc
     na, nb = len(A), len(B)
     Aeq = np.zeros((5, na + nb))
     Aeq[:3, :na], Aeq[:3, na:] = A.T, -B.T
     Aeq[3, :na] = 1.0
     Aeq[4, na:] = 1.0
     beq = np.array([0, 0, 0, 1.0, 1.0])
-    res = None
-    for method, opts in (("highs", {"primal_feasibility_tolerance": 1e-10, "dual_feasibility_tolerance": 1e-10, "presolve": False}),
-                         ("highs-ds", {}), ("highs-ipm", {})):  # grazing contacts can leave one simplex run undecided
+    for method, opts in (("highs", {"primal_feasibility_tolerance": 1e-10, "dual_feasibility_tolerance": 1e-10, "presolve": False}), ("highs-ds", {})):
         res = linprog(np.zeros(na + nb), A_eq=Aeq, b_eq=beq, bounds=(0, None), method=method, options=opts)
         if res.status == 0:
             return True
         if res.status == 2:
             return False
-    raise RuntimeError(f"linprog: {res.message}")
+    A1 = np.hstack([Aeq, np.vstack([np.eye(3), np.zeros((2, 3))]), np.vstack([-np.eye(3), np.zeros((2, 3))])])
+    cost = np.concatenate([np.zeros(na + nb), np.ones(6)])
+    res = linprog(cost, A_eq=A1, b_eq=beq, bounds=(0, None), method="highs")
+    if res.status != 0:
+        raise RuntimeError(f"linprog (phase 1): {res.message}")
+    return bool(res.fun <= 1e-9)
 
 
 def hull_distance_qp(A: np.ndarray, B: np.ndarray, w: float = 1e4) -> Tuple[float, np.ndarray, np.ndarray]:

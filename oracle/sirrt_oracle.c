@@ -1,5 +1,6 @@
 /*
- * sirrt_oracle.c -- TEST INFRASTRUCTURE ONLY (see sirrt_oracle.h).  PARITY PINNED ON THE FREE SIDE ONLY (see header).
+ * sirrt_oracle.c -- TEST INFRASTRUCTURE ONLY (see sirrt_oracle.h).  PARITY UNPINNED against the reference (see header);
+ * cross-checked cell by cell against the independent oracle/oracle2.py (tests/test_oracle2.py).
  *
  * FP64 CPU restatement of the reference's hot path.  Each function cites the reference lines it
  * follows (paths relative to the reference root).  The collision arithmetic itself lives in the

@@ -2,14 +2,18 @@
  * sirrt_oracle.h -- TEST INFRASTRUCTURE ONLY.  CPU (FP64) restatement of the reference's
  * collision-checker / safe-interval / edge-validation / kNN algorithm.
  *
- * PARITY PINNED ON THE FREE SIDE ONLY: the reference ships no unit tests or golden vectors for
- * this path and cannot be compiled in this image (coal, Eigen, nanoflann, urdfdom, orocos-kdl are
- * absent).  The one set of real reference OUTPUTS at this boundary are the trajectories its
- * planners logged (the JSON logs under "Blender/scenes with animation"; tests/golden/make_logged_paths.py):
- * 8 700 (q, frame) cells its own checker accepted, which pass 2-31 mm from obstacles, all FREE
- * here (tests/test_oracle.py).  The colliding side is UNPINNED: it rests on the reference's call
- * sites and soft fixtures (check_scene invariants, FK sanity values, closed-form vs GJK).
- *
+ * PARITY UNPINNED against the reference: it ships no unit tests or golden vectors for this path and cannot be
+ * compiled in this image (coal, Eigen, nanoflann, urdfdom, orocos-kdl are absent), so no output of the shipped
+ * C++ checker (CollisionManager.cpp:330-380) exists to compare with.  What stands in for it:
+ *   - a second, code-independent oracle (oracle/oracle2.py: NumPy/SciPy, LP feasibility + NNLS-QP for hulls, scalar
+ *     minimisation for capsule/box, matrix FK, own pack parser, no GJK) agrees with this file on >= 10 000 stratified
+ *     (configuration, frame) cells per scene, >= 1 000 colliding and >= 200 within 1e-4 m of contact
+ *     (tests/test_oracle2.py) -- this pins the arithmetic on BOTH sides of the decision, not the reference's semantics;
+ *   - a centimetre-level sanity check: trajectories logged by an OLDER pipeline of the same project (the JSON logs
+ *     under "Blender/scenes with animation" carry the keys of STRRT/STRRT_eval/evaluate_blender_scene.py:414-422, whose
+ *     checker was pybullet, not the shipped ResultsWriter.cpp:69-99) stay collision-free here, passing 2-31 mm from
+ *     the obstacles (tests/test_oracle.py);
+ *   - the reference's call sites (every function cites them), check_scene invariants, FK sanity values.
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
  * load this library.  The product (libsirrt_b200.so) never links or calls it.
  */

@@ -1,9 +1,31 @@
 #!/usr/bin/env python
 """Summarise an .ncu-rep (run here, no GPU needed): headline counters + hottest source lines.
-usage: python scripts/ncu_summary.py gpurun_out/x.ncu-rep [top_n]"""
-import csv, subprocess, sys, io
+usage: python scripts/ncu_summary.py gpurun_out/x.ncu-rep [top_n]
+       python scripts/ncu_summary.py gpurun_out/x.ncu-rep --emit-constants HASHES.json CONFIGS FRAMES SUMMARY.txt > profiles/ksweep_constants.json
+--emit-constants writes the per-launch counters bench.py's roofline uses (executed FP32 FLOP, warp instructions, DRAM bytes of
+ONE k_sweep launch) together with the SHA-256 of the kernel sources the capture was taken from (HASHES.json = the output of
+`python bench.py --print-source-hash` ON THE GPU BOX in the same gpurun call as the capture); bench.py refuses the constants
+when the working tree's sources hash differently."""
+import csv, json, subprocess, sys, io
 
 rep = sys.argv[1]
+if len(sys.argv) > 2 and sys.argv[2] == "--emit-constants":
+    hashes = json.load(open(sys.argv[3]))
+    configs, frames, summary = int(sys.argv[4]), int(sys.argv[5]), sys.argv[6]
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(raw)))
+    hdr, units, data = rows[0], rows[1], rows[2]
+    def val(k, scale={"Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0, "Gbyte": 1e9, "ms": 1.0, "us": 1e-3, "inst": 1.0, "": 1.0}):
+        i = hdr.index(k)
+        return float(data[i].replace(",", "")) * scale.get(units[i], 1.0)
+    out = {"kernel": data[hdr.index("Kernel Name")] if "Kernel Name" in hdr else "k_sweep", "configs_per_launch": configs, "frames": frames,
+           "warp_inst": val("smsp__inst_executed.sum"),
+           "flop": val("smsp__sass_thread_inst_executed_op_fadd_pred_on.sum") + val("smsp__sass_thread_inst_executed_op_fmul_pred_on.sum")
+                   + 2 * val("smsp__sass_thread_inst_executed_op_ffma_pred_on.sum"),
+           "dram_read_bytes": val("dram__bytes_read.sum"), "dram_write_bytes": val("dram__bytes_write.sum"),
+           "gpu_time_ms_under_ncu": val("gpu__time_duration.sum"), "source_sha256": hashes, "ncu_report": rep, "summary": summary}
+    print(json.dumps(out, indent=1))
+    sys.exit(0)
 top = int(sys.argv[2]) if len(sys.argv) > 2 else 30
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))

@@ -49,8 +49,9 @@ def golden_vectors():
 
 @pytest.fixture(scope="session")
 def logged_cells(sp):
-    """(q [n][dof] float64, frames [n] int32) cells that the REFERENCE's own checker accepted as collision-free,
-    from the planner trajectories it logged (tests/golden/make_logged_paths.py).  ST-RRT* solutions are expanded
+    """(q [n][dof] float64, frames [n] int32) cells of trajectories logged by an OLDER pipeline of the reference project
+    (its checker was pybullet, not the shipped CollisionManager -- tests/golden/make_logged_paths.py): a centimetre-level
+    sanity check, not a pin.  ST-RRT* solutions are expanded
     edge by edge exactly as SpaceTimeMotionValidator::checkMotion interpolates them
     (SpaceTimeMotionValidator.cpp:48-55: steps = max(int(|dq|/0.1), int(2*dt*fps+0.5)) + 2, states i/steps, plus
     the end state checked first at :25); DRGBT logs are executed states.  Frame = (int)(float32 time * fps)

@@ -1,16 +1,16 @@
-"""Extracts the planner trajectories the REFERENCE itself logged (Blender/scenes with animation/*.json:
-outputs of the reference's ST-RRT* and DRGBT executables on its shipped scenes) into
+"""Extracts planner trajectories logged by the reference PROJECT (Blender/scenes with animation/*.json) into
 tests/golden/reference_logged_paths.json.gz.
 
 Run in the build container (needs /root/reference):  python tests/golden/make_logged_paths.py
 
-Why these pin the oracle (one-sided, at the a4 boundary): every state of an ST-RRT* solution was accepted by
-the reference's own checker -- SpaceTimeMotionValidator::checkMotion (SpaceTimeMotionValidator.cpp:22-74)
-interpolates each tree edge into max(int(|dq|/0.1), int(2*dt*fps+0.5)) + 2 states and calls
-StateValidityCheckerFunctor::isValid -> CollisionManager::check_collision(q, float time)
-(StateValidityCheckerFunctor.cpp:29-47, CollisionManager.cpp:330-336) on each; the DRGBT logs are executed
-trajectories sampled every 10 ms.  The oracle must therefore report every one of these (q, frame) cells FREE.
-Only data is extracted (time stamps and joint vectors); no reference source is copied."""
+What these are, and are not: the files carry the keys `path_to_strrt_config_json`, `execution_time_ms`,
+`number_of_state_validations`, `path: [[t, [q...]], ...]` -- the writer of the legacy Python prototype
+(STRRT/STRRT_eval/evaluate_blender_scene.py:414-422, collision checker: pybullet), NOT the keys of the shipped C++
+writer (ResultsWriter.cpp:69-99: `path_to_config_json`, `full_execution_time_ns`, `final_planner_data`).  They are
+therefore outputs of an OLDER pipeline with a DIFFERENT checker, on the same scenes and robot model.  They do not pin
+the shipped checker (CollisionManager.cpp:330-380); they are a centimetre-level sanity check of FK, hulls, box extents
+and pose tables: a plausible collision-free trajectory that passes 2-31 mm from the obstacles must stay collision-free
+in our oracle and on the GPU.  Only data is extracted (time stamps and joint vectors); no reference source is copied."""
 import gzip
 import json
 import os

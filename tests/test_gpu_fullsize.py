@@ -99,3 +99,23 @@ def test_full_size_near_contact_is_reported(full):
     assert near >= 0 and st["exact_tests"] > 0
     # the FP64 re-check is a thin band, not a second pass over everything
     assert st["rechecked"] < 0.01 * st["exact_tests"] + 1000
+
+
+def test_pipelined_host_path_equals_plain_path_and_compact_table(full, pkg):
+    """The 3-stream pipeline of the host-buffer path (H2D || kernels || D2H, blocks of 131 072 configurations) gives the
+    plain single-stream path's table, bits and near-contact count at full size; the int16 table is the int32 table narrowed."""
+    pk, q, dev, table, bits, near = full   # computed with the pipeline on (the default for host buffers)
+    plain = pkg.Scene(pk)
+    plain.set_option(pkg.OPT_PIPELINE, 0)
+    n = 400_003  # a ragged number of blocks
+    qs = np.ascontiguousarray(q[:, :n])
+    t0, b0, near0 = plain.safe_intervals_batch(qs, KMAX)
+    assert np.array_equal(t0, table[:n]) and np.array_equal(b0, bits[:n])
+    t1, b1, near1 = dev.safe_intervals_batch(qs, KMAX)
+    assert np.array_equal(t1, t0) and np.array_equal(b1, b0) and near1 == near0
+    t2, _, _ = dev.safe_intervals_batch(qs, KMAX, want_bits=False)
+    assert np.array_equal(t2, t0)
+    t16, near16 = dev.safe_intervals_batch_i16(qs, KMAX)
+    assert t16.dtype == np.int16 and np.array_equal(t16.astype(np.int32), t0) and near16 == near0
+    small16, _ = dev.safe_intervals_batch_i16(np.ascontiguousarray(q[:, :1000]), KMAX)   # a single block
+    assert np.array_equal(small16.astype(np.int32), table[:1000])

@@ -136,3 +136,27 @@ def test_sharded_knn_and_table_gather_over_nccl(pkg, orc, sp, packs, tmp_path):
         assert np.array_equal(got["ni"], bi[:, 0]) and np.array_equal(got["nd"], bd[:, 0])
         assert np.array_equal(got["rad"], np.nonzero(d0 < 4.0)[0])
         assert np.array_equal(got["table"], rtable)
+
+
+@pytest.mark.parametrize("name,n,devices", [("synA_32_200", 20011, [0, 0]), ("synA_32_200", 10007, [0, 0, 0]), ("synB_16_100", 5, [0, 0, 0]),
+                                            ("flying_boxes", 101, [0, 0, 0]), ("multiple_robots_cyl", 333, [0, 0])])
+def test_multi_scene_splits_one_batch_like_a_single_scene(pkg, sp, packs, name, n, devices):
+    """sirrt_multi_create / sirrt_multi_safe_intervals_batch (the in-process form of the §8e partition): one batch cut into
+    G contiguous blocks, one scene replica and host thread per block -- G = 2 and 3, N not divisible by G, N < G blocks
+    with empty shards, sweep and generic kernels.  Replicas on the SAME device exercise the slicing, the table / bits
+    offsets and the summed near-contact count without needing a multi-GPU box; with more GPUs the replicas spread out."""
+    import torch
+
+    nd = torch.cuda.device_count()
+    devs = [d % max(1, nd) for d in range(len(devices))] if nd >= len(devices) else devices
+    pk = packs(name)
+    q = sp.random_configs(sp.read_pack(pk).robot, n, 61)
+    one = pkg.Scene(pk, 0)
+    table, bits, near = one.safe_intervals_batch(q, 8)
+    multi = pkg.MultiScene(pk, devs)
+    mtable, mbits, mnear = multi.safe_intervals_batch(q, one.words, 8)
+    assert np.array_equal(mtable, table)
+    assert np.array_equal(mbits, bits)
+    assert mnear == near
+    mtable2, none_bits, _ = multi.safe_intervals_batch(q, one.words, 8, want_bits=False)
+    assert none_bits is None and np.array_equal(mtable2, table)

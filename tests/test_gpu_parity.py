@@ -43,13 +43,15 @@ def test_generic_kernel_equals_sweep_kernel(pkg, orc, sp, packs):
     assert np.array_equal(ba, bb) and np.array_equal(ta, tb)
 
 
-@pytest.mark.parametrize("name,n", [("mass_test_cyl", 256), ("mass_test", 48), ("flying_boxes", 48), ("scene_task", 16)])
+@pytest.mark.parametrize("name,n", [("mass_test_cyl", 2048), ("mass_test", 2048), ("flying_boxes", 2048), ("scene_task", 16)])
 def test_reference_scenes_bit_exact(pkg, orc, sp, packs, name, n):
+    """>= 2 000 configurations per hull scene (1.2e6 - 3.7e6 cells each): the FP32 GJK + FP64 certificate + support-cell
+    path is the riskiest code of the library"""
     pk = packs(name)
     _compare(pkg, orc, pk, random_q(sp, pk, n, 17))
 
 
-@pytest.mark.parametrize("name,n", [("multiple_robots_cyl", 128), ("multiple_robots", 24)])
+@pytest.mark.parametrize("name,n", [("multiple_robots_cyl", 2048), ("multiple_robots", 2048)])
 @pytest.mark.parametrize("mode", [0, 1])
 def test_robot_obstacles_both_parity_modes(pkg, orc, sp, packs, name, n, mode):
     """QUIRK 7: REFERENCE_EXACT reproduces the functor mis-indexing, FIXED tests true geometry."""
@@ -107,14 +109,18 @@ def test_check_frames_batch(pkg, orc, sp, packs):
         assert np.array_equal(got64, exp)
 
 
-def test_edge_check_batch(pkg, orc, sp, packs):
-    pk = packs("synA_32_200")
-    dev, ref = pkg.Scene(pk), orc.Oracle(pk)
+@pytest.mark.parametrize("name,mode", [("synA_32_200", 0), ("flying_boxes", 0), ("mass_test", 0), ("multiple_robots", 0), ("multiple_robots", 1)])
+def test_edge_check_batch(pkg, orc, sp, packs, name, mode):
+    """PlannerConnect::is_collision_motion (PlannerConnect.cpp:862-897) through sirrt_edge_check_batch on the capsule
+    scene AND on the hull / robot-obstacle scenes (per-frame semantics: the QUIRK-7 functor in REFERENCE_EXACT)"""
+    pk = packs(name)
+    dev, ref = pkg.Scene(pk, 0, mode), orc.Oracle(pk, mode)
     rng = np.random.default_rng(31)
     n = 200
+    T = ref.n_frames
     q0 = random_q(sp, pk, n, 37).T.astype(np.float64)
     q1 = q0 + rng.normal(0, 0.4, q0.shape)
-    t0 = rng.uniform(0, 150, n)
+    t0 = rng.uniform(0, 0.75 * T, n)
     t1 = t0 + rng.uniform(-5, 60, n)
     first, coord = dev.edge_check_batch(q0, q1, t0, t1, vmax=3.1415)
     kinds = set()
@@ -124,7 +130,7 @@ def test_edge_check_batch(pkg, orc, sp, packs):
         if s >= 0:
             assert np.array_equal(coord[e], cc)
         kinds.add(min(s, 0) if s < 0 else 1)
-    assert kinds == {-3, -2, -1, 1}, kinds
+    assert {-3, -2, -1} <= kinds and (1 in kinds or name == "mass_test"), kinds
 
 
 def test_get_distances(pkg, orc, sp, packs):
@@ -221,8 +227,8 @@ def test_collision_manager_mirror(pkg, orc, packs, sp):
 @pytest.mark.parametrize("key", ["strrt_mass_test", "strrt_flying_boxes", "drgbt_mass_test", "rgbtstar_mass_test", "drgbt_flying_boxes",
                                  "drgbt_multiple_robots", "strrt_multiple_robots"])
 def test_reference_logged_trajectories_free_on_gpu(pkg, orc, packs, logged_cells, key):
-    """Cells the REFERENCE's own checker accepted (trajectories its planners logged, tests/golden/make_logged_paths.py)
-    must be FREE through the C ABI too, and equal to the oracle cell by cell (robot scene: FIXED mode, see
+    """Sanity check (not a pin): cells of trajectories logged by the project's older pipeline (different checker, see
+    tests/golden/make_logged_paths.py) must be FREE through the C ABI too, and equal to the oracle cell by cell (robot scene: FIXED mode, see
     tests/test_oracle.py::test_reference_logged_trajectories_are_free)."""
     scene, q, frames = logged_cells(key)
     mode = pkg.PARITY_FIXED if scene == "multiple_robots" else pkg.PARITY_REFERENCE_EXACT

@@ -184,12 +184,13 @@ LOGGED = ["strrt_mass_test", "strrt_flying_boxes", "drgbt_mass_test", "rgbtstar_
 
 @pytest.mark.parametrize("key", LOGGED)
 def test_reference_logged_trajectories_are_free(orc, packs, logged_cells, key):
-    """REFERENCE OUTPUTS pin the oracle (free side, a4 boundary): every (q, frame) cell of a trajectory the
-    reference's planners logged was accepted by the reference's checker, so the oracle must call it free.
-    The robot-obstacle scene is pinned in FIXED mode only: its logs pre-date the pair mis-indexing of the
-    shipped source (QUIRK 7) -- under REFERENCE_EXACT the shifted base-link hull rejects 15 of the 918 ST-RRT*
-    states, which the reference as shipped would have rejected too (it cannot even read that scene file's
-    legacy trajectory format, config_read.cpp:156-168)."""
+    """Centimetre-level SANITY CHECK, not a pin: the logged trajectories come from an OLDER pipeline of the project (keys
+    of STRRT/STRRT_eval/evaluate_blender_scene.py:414-422, checker pybullet; the shipped ResultsWriter.cpp:69-99 writes
+    different keys), so they were accepted by *a* checker on the same scenes and robot, not by the shipped
+    CollisionManager.cpp:330-380.  A collision-free trajectory of that pipeline must stay collision-free here.
+    The robot-obstacle scene only holds in FIXED mode: under REFERENCE_EXACT the QUIRK-7 mis-indexed base-link hull
+    rejects 15 of the 918 ST-RRT* states -- consistent with logs that pre-date the shipped checker (whose reader
+    cannot even parse that scene file's legacy trajectory format, config_read.cpp:156-168)."""
     scene, q, frames = logged_cells(key)
     o = orc.Oracle(packs(scene), orc.FIXED if scene == "multiple_robots" else orc.REFERENCE_EXACT)
     hit = [int(f) for qq, f in zip(q, frames) if o.check_frame(qq, int(f))]
@@ -198,7 +199,7 @@ def test_reference_logged_trajectories_are_free(orc, packs, logged_cells, key):
 
 @pytest.mark.parametrize("key", ["drgbt_mass_test", "rgbtstar_mass_test", "drgbt_flying_boxes", "drgbt_multiple_robots"])
 def test_logged_trajectories_discriminate(orc, packs, logged_cells, key):
-    """The pin above is not vacuous: the executed trajectories pass within millimetres to centimetres of the
+    """The sanity check above is not vacuous: the executed trajectories pass within millimetres to centimetres of the
     obstacles (oracle clearances 1.9 mm flying boxes, 22 mm robots on the table, 24-31 mm mass test), so an
     oracle whose FK, hulls, box sizes or pose tables were off by a few centimetres would report collisions."""
     scene, q, frames = logged_cells(key)
@@ -229,9 +230,10 @@ def test_fast_mode_is_bit_identical(orc, packs, sp, name):
 
 @pytest.mark.parametrize("key", ["strrt_mass_test", "strrt_flying_boxes", "strrt_multiple_robots"])
 def test_reference_strrt_solutions_are_valid_motions(orc, packs, sp, key):
-    """REFERENCE OUTPUTS pin the restated SpaceTimeMotionValidator::checkMotion (f4): every edge of a solution the
-    reference's ST-RRT* logged passed its own checkMotion (s2 valid, delta_t > 0, speed gate, all interpolated
-    states valid), so the oracle must answer -1 for it in both forms."""
+    """Sanity check of the restated SpaceTimeMotionValidator::checkMotion (f4) on ST-RRT* solutions logged by the
+    project's older pipeline (see test_reference_logged_trajectories_are_free: not the shipped checker): every edge of
+    such a solution is a plausible valid motion (s2 valid, delta_t > 0, speed gate, all interpolated states valid),
+    so the oracle answers -1 for it in both forms."""
     import gzip, json, os
     from conftest import GOLDEN
     with gzip.open(os.path.join(GOLDEN, "reference_logged_paths.json.gz"), "rb") as f:

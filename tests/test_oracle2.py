@@ -111,6 +111,12 @@ _W = {}
 
 
 def _init_worker(pack, mode):
+    try:  # one BLAS thread per worker process: the pool already uses every core
+        from threadpoolctl import threadpool_limits
+
+        _W["limit"] = threadpool_limits(1)
+    except Exception:
+        pass
     _W["o"] = load_oracle2().Oracle2(pack, mode)
 
 

@@ -5,6 +5,7 @@ import os
 import sys
 
 import numpy as np
+import pytest
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
@@ -19,28 +20,30 @@ def _worker(rank, world, port, pack, q, out_path):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     bench = g._load("sirrt_bench", os.path.join(ROOT, "bench.py"))
-    n0, n1 = bench.shard_range(q.shape[1], rank, world)
+    N = q.shape[1]
+    n0, n1 = bench.shard_range(N, rank, world)          # bench.py's own partition of ONE batch ...
     o = g.load_oracle().Oracle(pack)  # stands in for the per-rank GPU scene on this CPU-only box
     table, _ = o.safe_intervals_batch(np.ascontiguousarray(q[:, n0:n1]), 8)
-    t = torch.from_numpy(table)
-    parts = [torch.zeros_like(t) for _ in range(world)] if (n1 - n0) * world == q.shape[1] else None
-    assert parts is not None
-    dist.all_gather(parts, t)
+    full = bench.gather_table_shards(torch.from_numpy(table), N, rank, world, dist)   # ... and its all-gather of the table shards
+    assert full.shape == (N, 17)
     total = torch.tensor([n1 - n0], dtype=torch.int64)
     dist.all_reduce(total)
-    if rank == 0:
-        np.save(out_path, torch.cat(parts).numpy())
-        assert int(total) == q.shape[1]
+    assert int(total) == N
+    np.save(out_path + f".{rank}.npy", full.numpy())   # EVERY rank must hold all rows
     dist.destroy_process_group()
 
 
-def test_two_rank_shards_reassemble(tmp_path, sp, orc, packs):
+@pytest.mark.parametrize("n,world,port", [(64, 2, 29531), (65, 2, 29535), (67, 3, 29537)])
+def test_bench_partition_reassembles_on_every_rank(tmp_path, sp, orc, packs, n, world, port):
+    """bench.py's N>1 data path on CPU (gloo): contiguous blocks of ONE batch, interval-table shards all-gathered; equal
+    blocks, blocks that differ by one row (padding path), three ranks"""
     pk = packs("synA_8_50")
-    q = sp.random_configs(sp.read_pack(pk).robot, 64, 3)
-    out = str(tmp_path / "gathered.npy")
-    mp.spawn(_worker, args=(2, 29531, pk, q, out), nprocs=2, join=True)
+    q = sp.random_configs(sp.read_pack(pk).robot, n, 3)
+    out = str(tmp_path / "gathered")
+    mp.spawn(_worker, args=(world, port, pk, q, out), nprocs=world, join=True)
     full, _ = orc.Oracle(pk).safe_intervals_batch(q, 8)
-    assert np.array_equal(np.load(out), full)
+    for r in range(world):
+        assert np.array_equal(np.load(out + f".{r}.npy"), full), r
 
 
 def test_shard_range_covers_everything():

@@ -96,6 +96,14 @@ int sirrt_check_frame(sirrt_scene*, const double* q, int frame, int* collided);
  * per planned-robot link the minimum distance to the box/sphere obstacles at `frame`.
  * Links after the first colliding one are left at +inf (the reference returns early). */
 int sirrt_get_distances(sirrt_scene*, const double* q, int frame, double* min_dist, int* is_collision);
+/* the same, plus what DistanceCallback::distance collects per visited pair (CollisionManager.cpp:568-598,
+ * robot_link_distance_to_obj at CollisionManager.hpp:91-99): for EVERY (link, box/sphere obstacle) pair of the frame its signed
+ * distance pair_dist [n_links][C] and the closest point pair points [n_links][C][6] = point on the link surface (xyz), point on
+ * the obstacle surface (xyz), world frame (coal DistanceResult::nearest_points[0], [1]).  The reference's vectors hold the
+ * pairs its AABB-tree traversal happened to visit, in traversal order; here all C pairs are returned in obstacle order. */
+int sirrt_get_distances_ex(sirrt_scene*, const double* q, int frame, double* min_dist, int* is_collision, double* pair_dist, double* points);
+/* number of box / sphere obstacles (C) and of robot obstacles of the scene */
+int sirrt_scene_counts(const sirrt_scene*, int* n_obstacles, int* n_robot_obstacles);
 
 /* ---- batched throughput path ------------------------------------------------------------- */
 /* N configurations -> collision bit rows and/or fixed-width interval table.

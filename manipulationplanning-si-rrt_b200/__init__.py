@@ -47,6 +47,8 @@ EXPORTS = {
     "sirrt_safe_intervals": (_i32, [_vp, _vp, _vp, _i32, _vp]),
     "sirrt_check_frame": (_i32, [_vp, _vp, _i32, _vp]),
     "sirrt_get_distances": (_i32, [_vp, _vp, _i32, _vp, _vp]),
+    "sirrt_get_distances_ex": (_i32, [_vp, _vp, _i32, _vp, _vp, _vp, _vp]),
+    "sirrt_scene_counts": (_i32, [_vp, _vp, _vp]),
     "sirrt_safe_intervals_batch": (_i32, [_vp, _vp, _i64, _vp, _i32, _vp, _vp]),
     "sirrt_safe_intervals_batch_i16": (_i32, [_vp, _vp, _i64, _vp, _i32, _vp]),
     "sirrt_collision_bits_f64": (_i32, [_vp, _vp, _i64, _i32, _vp]),
@@ -180,6 +182,22 @@ class Scene:
         col = C.c_int()
         _ck(_lib.sirrt_get_distances(self._h, q.ctypes.data, int(frame), d.ctypes.data, C.byref(col)))
         return bool(col.value), d
+
+    def counts(self):
+        c, r = C.c_int(), C.c_int()
+        _ck(_lib.sirrt_scene_counts(self._h, C.byref(c), C.byref(r)))
+        return c.value, r.value
+
+    def get_distances_ex(self, q, frame: int):
+        """(is_collision, min_dist [L], pair_dist [L][C], link points [L][C][3], obstacle points [L][C][3])"""
+        q = np.ascontiguousarray(q, np.float64)
+        n_obs = self.counts()[0]
+        d = np.zeros(self.n_links)
+        pd = np.zeros((self.n_links, n_obs))
+        pts = np.zeros((self.n_links, n_obs, 6))
+        col = C.c_int()
+        _ck(_lib.sirrt_get_distances_ex(self._h, q.ctypes.data, int(frame), d.ctypes.data, C.byref(col), pd.ctypes.data, pts.ctypes.data))
+        return bool(col.value), d, pd, pts[:, :, :3].copy(), pts[:, :, 3:].copy()
 
     # -- batched path (numpy host arrays or torch cuda tensors)
     def safe_intervals_batch(self, q_soa, kmax: int = 8, want_bits: bool = True, want_table: bool = True):

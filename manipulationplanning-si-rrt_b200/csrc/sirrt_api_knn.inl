@@ -258,6 +258,7 @@ struct DistParams {
   const double* q;  // [dof]
   int dof, frame, n_obst;
   double* out;      // [n_links][n_obst]
+  double* pts;      // [n_links][n_obst][6] closest point on the link, closest point on the obstacle (world); may be null
 };
 __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32) k_pair_distances(const __grid_constant__ DRobot rb, const __grid_constant__ DistParams P) {
   const int lane = threadIdx.x & 31;
@@ -273,9 +274,16 @@ __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32) k_pair_distances(c
   int res;
   const double d = recheck_pair(rb, P.sc, X[l], l, P.sc.shapes[S.shape], pose, lane, &res);
   if (lane == 0) P.out[pair] = d;
+  if (P.pts) {  // witness points: the distance itself stays the one every other entry point reports
+    double pl[3], po[3];
+    pair_distance_witness(rb, P.sc, X[l], l, P.sc.shapes[S.shape], pose, lane, pl, po);
+    if (lane == 0)
+      for (int k = 0; k < 3; k++) { P.pts[(size_t)pair * 6 + k] = pl[k]; P.pts[(size_t)pair * 6 + 3 + k] = po[k]; }
+  }
 }
 
-extern "C" int sirrt_get_distances(sirrt_scene* s, const double* q, int frame, double* min_dist, int* is_collision) {
+// min_dist [n_links]; optional: pair_dist [n_links][C], points [n_links][C][6] (closest point on the link, on the obstacle)
+static int get_distances_impl(sirrt_scene* s, const double* q, int frame, double* min_dist, int* is_collision, double* pair_dist, double* points) {
   if (!s || !q || !min_dist || !is_collision) return fail(SIRRT_E_ARG, "sirrt_get_distances: bad argument");
   if (frame < 0 || frame >= s->hs.T) return fail(SIRRT_E_ARG, "sirrt_get_distances: frame out of range");
   CU(cudaSetDevice(s->device));
@@ -283,22 +291,39 @@ extern "C" int sirrt_get_distances(sirrt_scene* s, const double* q, int frame, d
   *is_collision = 0;
   for (int l = 0; l < L; l++) min_dist[l] = 1.0 / 0.0;
   if (C == 0) { for (int l = 0; l < L; l++) min_dist[l] = 1e300; return SIRRT_OK; }
-  if (s->misc.ensure(sizeof(double) * (dof + (size_t)L * C))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  const size_t np = (size_t)L * C;
+  if (s->misc.ensure(sizeof(double) * (dof + np * (points ? 7 : 1)))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
   double* dq = s->misc.as<double>();
   double* dout = dq + dof;
+  double* dpts = points ? dout + np : nullptr;
   CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyHostToDevice, s->stream));
-  DistParams P{s->d, dq, dof, frame, C, dout};
+  DistParams P{s->d, dq, dof, frame, C, dout, dpts};
   k_pair_distances<<<(L * C + SIRRT_WARPS_PER_BLOCK - 1) / SIRRT_WARPS_PER_BLOCK, SIRRT_WARPS_PER_BLOCK * 32, 0, s->stream>>>(s->tb.robot, P);
   CU(cudaGetLastError());
-  std::vector<double> h((size_t)L * C);
-  CU(cudaMemcpyAsync(h.data(), dout, sizeof(double) * h.size(), cudaMemcpyDeviceToHost, s->stream));
+  std::vector<double> h(np);
+  CU(cudaMemcpyAsync(h.data(), dout, sizeof(double) * np, cudaMemcpyDeviceToHost, s->stream));
+  if (points) CU(cudaMemcpyAsync(points, dpts, sizeof(double) * np * 6, cudaMemcpyDeviceToHost, s->stream));
   CU(sirrt_sync(s->stream));
+  if (pair_dist) memcpy(pair_dist, h.data(), sizeof(double) * np);
   for (int l = 0; l < L; l++) {
     double m = 1e300;
     for (int c = 0; c < C; c++) m = std::min(m, h[(size_t)l * C + c]);
     min_dist[l] = m;
     if (m - SIRRT_SECURITY_MARGIN <= SIRRT_COLLISION_THRESHOLD) { *is_collision = 1; break; }  // reference returns at the first colliding link
   }
+  return SIRRT_OK;
+}
+extern "C" int sirrt_get_distances(sirrt_scene* s, const double* q, int frame, double* min_dist, int* is_collision) {
+  return get_distances_impl(s, q, frame, min_dist, is_collision, nullptr, nullptr);
+}
+extern "C" int sirrt_get_distances_ex(sirrt_scene* s, const double* q, int frame, double* min_dist, int* is_collision, double* pair_dist, double* points) {
+  if (!pair_dist || !points) return fail(SIRRT_E_ARG, "sirrt_get_distances_ex: bad argument");
+  return get_distances_impl(s, q, frame, min_dist, is_collision, pair_dist, points);
+}
+extern "C" int sirrt_scene_counts(const sirrt_scene* s, int* n_obstacles, int* n_robot_obstacles) {
+  if (!s) return fail(SIRRT_E_ARG, "null scene");
+  if (n_obstacles) *n_obstacles = s->hs.C;
+  if (n_robot_obstacles) *n_robot_obstacles = (int)s->hs.robs.size();
   return SIRRT_OK;
 }
 

@@ -215,6 +215,23 @@ template <typename T> __device__ inline T seg_seg_dist2(const T* p1, const T* q1
   return dot3(d, d);
 }
 
+// parameters (s on p1q1, t on p2q2) of the closest points of two segments (same case analysis as seg_seg_dist2)
+template <typename T> __device__ inline void seg_seg_params(const T* p1, const T* q1, const T* p2, const T* q2, T& s, T& t) {
+  T d1[3], d2[3], r[3];
+  sub3(d1, q1, p1); sub3(d2, q2, p2); sub3(r, p1, p2);
+  T a = dot3(d1, d1), e = dot3(d2, d2), f = dot3(d2, r);
+  const T EPS = T(1e-30);
+  if (a <= EPS && e <= EPS) { s = t = T(0); return; }
+  if (a <= EPS) { s = T(0); t = clamp01(f / e); return; }
+  T c = dot3(d1, r);
+  if (e <= EPS) { t = T(0); s = clamp01(-c / a); return; }
+  T b = dot3(d1, d2), denom = a * e - b * b;
+  s = denom > T(0) ? clamp01((b * f - c * e) / denom) : T(0);
+  t = (b * s + f) / e;
+  if (t < T(0)) { t = T(0); s = clamp01(-c / a); }
+  else if (t > T(1)) { t = T(1); s = clamp01((b - c) / a); }
+}
+
 // segment a + t*d (t in [0,1]) vs box [-h,h]: g(t) = sum max(|p_i|-h_i,0)^2 is convex, g' is
 // continuous piecewise linear with breakpoints at the slab crossings -> bracket and solve.
 template <typename T> __device__ __forceinline__ T sb_g(const T* a, const T* d, const T* h, T t, T& gp) {
@@ -227,11 +244,11 @@ template <typename T> __device__ __forceinline__ T sb_g(const T* a, const T* d, 
   gp = T(2) * s;
   return g;
 }
-template <typename T> __device__ inline T seg_box_dist2(const T* a, const T* b, const T* h) {
+template <typename T> __device__ inline T seg_box_dist2(const T* a, const T* b, const T* h, T* t_out = nullptr) {
   T d[3]; sub3(d, b, a);
   T gp0, gp1, g0 = sb_g(a, d, h, T(0), gp0), g1 = sb_g(a, d, h, T(1), gp1);
-  if (gp0 >= T(0)) return g0;
-  if (gp1 <= T(0)) return g1;
+  if (gp0 >= T(0)) { if (t_out) *t_out = T(0); return g0; }
+  if (gp1 <= T(0)) { if (t_out) *t_out = T(1); return g1; }
   T lo = T(0), hi = T(1), glo = gp0, ghi = gp1;
 #pragma unroll
   for (int i = 0; i < 3; i++) {
@@ -247,6 +264,7 @@ template <typename T> __device__ inline T seg_box_dist2(const T* a, const T* b, 
   T t = lo;
   if (ghi > glo) t = lo - glo * (hi - lo) / (ghi - glo);
   t = t < lo ? lo : (t > hi ? hi : t);
+  if (t_out) *t_out = t;
   T gp;
   return sb_g(a, d, h, t, gp);
 }
@@ -447,7 +465,7 @@ template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v,
 //         *dist_out gets the signed distance (core distance - rsum).
 template <typename T, bool FINAL>
 __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* Rrel, const T* trel, T rsum, T band,
-                               int lane, T* dist_out, int* enc_ids = nullptr) {
+                               int lane, T* dist_out, int* enc_ids = nullptr, Simplex<T>* final_simplex = nullptr, T* final_v = nullptr) {
   // enc_ids (FP32 pass only): when the answer is AMBIGUOUS because the enclosing tetrahedron is too thin to trust in
   // FP32, the four support-point ids -- the caller can certify the enclosure in FP64 from them (gjk_point / tetra_encloses)
   if (enc_ids) enc_ids[0] = -1;
@@ -509,6 +527,7 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
   }
   T d = tsqrt(vv) - rsum;
   if (dist_out) *dist_out = d;
+  if (final_simplex) { *final_simplex = s; final_v[0] = v[0]; final_v[1] = v[1]; final_v[2] = v[2]; }  // witness points (get_distances)
   if (FINAL) return ((double)d - SIRRT_SECURITY_MARGIN <= SIRRT_COLLISION_THRESHOLD) ? RES_HIT : RES_FREE;
   if (d < -band) return RES_HIT;
   return RES_AMBIG;  // |d| <= band, or not converged enough to certify separation

@@ -632,6 +632,92 @@ __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const 
   return d;
 }
 
+// a9: signed distance of (link l, shape sh at pose) WITH the closest point pair in world coordinates
+// (coal::DistanceResult::nearest_points as the reference's DistanceCallback collects them, CollisionManager.cpp:549-600):
+// pl on the planned-robot link's surface, po on the obstacle's surface.  Closed forms give the feet directly; hull pairs
+// take them from the barycentric coordinates of GJK's final simplex.  For a penetrating pair the points are the cores'
+// closest points (meaningless, as in coal without EPA; the reference returns before reading them).
+__device__ inline double pair_distance_witness(const DRobot& rb, const DScene& sc, const LinkXfD& X, int l, const DShape& sh,
+                                               const double* pose, int lane, double* pl, double* po) {
+  const DShape& lsh = sc.shapes[rb.link_shape[l]];
+  const double *RB = pose, *tB = pose + 9;
+  double ca[3], cb[3];  // closest points of the two CORES, world frame
+  double ra = lsh.type == SH_HULL ? 0.0 : lsh.d_radius, rbb = (sh.type == SH_SPHERE || sh.type == SH_CAPSULE) ? sh.d_radius : 0.0;
+  if (lsh.type == SH_CAPSULE && sh.type != SH_HULL) {
+    double a[3], b[3];
+    for (int k = 0; k < 3; k++) { a[k] = X.t[k] - X.R[3 * k + 2] * lsh.d_half_len; b[k] = X.t[k] + X.R[3 * k + 2] * lsh.d_half_len; }
+    if (sh.type == SH_SPHERE) {
+      double ab[3], ap[3];
+      sub3(ab, b, a); sub3(ap, tB, a);
+      const double den = dot3(ab, ab), t = den > 0.0 ? clamp01(dot3(ap, ab) / den) : 0.0;
+      for (int k = 0; k < 3; k++) { ca[k] = a[k] + t * ab[k]; cb[k] = tB[k]; }
+    } else if (sh.type == SH_BOX) {
+      double da[3], db[3], la[3], lb[3], t;
+      sub3(da, a, tB); sub3(db, b, tB);
+      matTvec(la, RB, da); matTvec(lb, RB, db);
+      seg_box_dist2(la, lb, sh.d_half, &t);
+      double ps[3], pb[3], w[3];
+      for (int k = 0; k < 3; k++) {
+        ps[k] = la[k] + t * (lb[k] - la[k]);
+        pb[k] = ps[k] < -sh.d_half[k] ? -sh.d_half[k] : (ps[k] > sh.d_half[k] ? sh.d_half[k] : ps[k]);
+        ca[k] = a[k] + t * (b[k] - a[k]);
+      }
+      matvec(w, RB, pb);
+      for (int k = 0; k < 3; k++) cb[k] = w[k] + tB[k];
+    } else {
+      double p2[3], q2[3], s, t;
+      for (int k = 0; k < 3; k++) { p2[k] = tB[k] - RB[3 * k + 2] * sh.d_half_len; q2[k] = tB[k] + RB[3 * k + 2] * sh.d_half_len; }
+      seg_seg_params(a, b, p2, q2, s, t);
+      for (int k = 0; k < 3; k++) { ca[k] = a[k] + s * (b[k] - a[k]); cb[k] = p2[k] + t * (q2[k] - p2[k]); }
+    }
+  } else {
+    GShape<double> A, B;
+    A.type = lsh.type; A.verts = sc.verts_d + 3 * (size_t)lsh.vert_off; A.n = lsh.n_verts; A.cells = (sc.hull_cells && lsh.cell_off >= 0) ? sc.hull_cells + lsh.cell_off : nullptr; A.cand = sc.hull_cand; A.half_len = lsh.d_half_len;
+    A.half[0] = lsh.d_half[0]; A.half[1] = lsh.d_half[1]; A.half[2] = lsh.d_half[2];
+    B.type = sh.type; B.verts = sc.verts_d + 3 * (size_t)sh.vert_off; B.n = sh.n_verts; B.cells = (sc.hull_cells && sh.cell_off >= 0) ? sc.hull_cells + sh.cell_off : nullptr; B.cand = sc.hull_cand; B.half_len = sh.d_half_len;
+    B.half[0] = sh.d_half[0]; B.half[1] = sh.d_half[1]; B.half[2] = sh.d_half[2];
+    double Rrel[9], trel[3], dt[3], d, v[3] = {0, 0, 0};
+    matTmul3(Rrel, X.R, RB);
+    sub3(dt, tB, X.t);
+    matTvec(trel, X.R, dt);
+    Simplex<double> S;
+    S.n = 0;
+    warp_gjk<double, true>(A, B, Rrel, trel, ra + rbb, 0.0, lane, &d, nullptr, &S, v);
+    // barycentric coordinates of v (the point of the final simplex closest to the origin) by least squares on its vertices
+    double lam[4] = {1, 0, 0, 0};
+    if (S.n == 2) {
+      double e[3], r[3];
+      sub3(e, S.w[1], S.w[0]); sub3(r, v, S.w[0]);
+      const double den = dot3(e, e);
+      lam[1] = den > 0.0 ? clamp01(dot3(r, e) / den) : 0.0; lam[0] = 1.0 - lam[1];
+    } else if (S.n >= 3) {
+      double e1[3], e2[3], r[3];
+      sub3(e1, S.w[1], S.w[0]); sub3(e2, S.w[2], S.w[0]); sub3(r, v, S.w[0]);
+      const double a11 = dot3(e1, e1), a12 = dot3(e1, e2), a22 = dot3(e2, e2), b1 = dot3(r, e1), b2 = dot3(r, e2), det = a11 * a22 - a12 * a12;
+      if (det > 0.0) { lam[1] = (b1 * a22 - b2 * a12) / det; lam[2] = (b2 * a11 - b1 * a12) / det; }
+      lam[0] = 1.0 - lam[1] - lam[2];
+    }
+    double pa[3] = {0, 0, 0}, pb[3] = {0, 0, 0};
+    const int ns = S.n < 1 ? 0 : (S.n > 3 ? 3 : S.n);
+    for (int i = 0; i < ns; i++) {
+      double xa[3], xb[3], w[3];
+      gjk_point(A, S.id[i] >> 12, xa);
+      gjk_point(B, S.id[i] & 4095, xb);
+      matvec(w, Rrel, xb);
+      for (int k = 0; k < 3; k++) { pa[k] += lam[i] * xa[k]; pb[k] += lam[i] * (w[k] + trel[k]); }
+    }
+    double wa[3], wb[3];
+    matvec(wa, X.R, pa); matvec(wb, X.R, pb);
+    for (int k = 0; k < 3; k++) { ca[k] = wa[k] + X.t[k]; cb[k] = wb[k] + X.t[k]; }
+  }
+  double n[3];
+  sub3(n, cb, ca);
+  const double len = sqrt(dot3(n, n));
+  if (len > 0.0) { n[0] /= len; n[1] /= len; n[2] /= len; } else { n[0] = n[1] = n[2] = 0.0; }
+  for (int k = 0; k < 3; k++) { pl[k] = ca[k] + ra * n[k]; po[k] = cb[k] - rbb * n[k]; }
+  return len - ra - rbb;
+}
+
 // FP64 certificate of an FP32 "enclosed, but thin" GJK verdict (see tetra_encloses); kept out of line so that the task
 // kernel's register budget stays that of the FP32 GJK
 __device__ __noinline__ bool certify_enclosure(const DRobot& rb, const DScene& sc, const LinkXfD& X, int l, const DShape& sh,

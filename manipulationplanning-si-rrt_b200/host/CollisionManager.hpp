@@ -87,17 +87,31 @@ class CollisionManager {
     ck(sirrt_check_frame(scene_, robot_angles.data(), frame, &collided));
     return collided != 0;
   }
-  // CollisionManager.cpp:382-420.  min_distance per link is the true minimum over the box/sphere
-  // obstacles of the frame; nearest points are not produced by this backend (vectors left empty).
+  // CollisionManager.cpp:382-420 + DistanceCallback :549-600.  Per link: min_distance and the closest point pairs
+  // (neares_point_robot / neares_point_obj, coal nearest_points[0] / [1]).  Two documented deviations:
+  // the reference's callback overwrites `dist` with the LAST pair its AABB-tree traversal visited and pushes one point pair per
+  // visited leaf in traversal order; this backend reports the true minimum over all box / sphere obstacles of the frame
+  // and returns the point pairs of ALL of them in obstacle order (the visited ones are a subset).
   std::vector<robot_link_distance_to_obj> get_distances(std::vector<double> robot_angles, float time, bool& is_collision) {
     need_dof(robot_angles);
-    std::vector<double> d(n_links_);
+    int n_obs = 0;
+    ck(sirrt_scene_counts(scene_, &n_obs, nullptr));
+    std::vector<double> d(n_links_), pd((size_t)n_links_ * n_obs), pts((size_t)n_links_ * n_obs * 6);
     int col = 0;
-    ck(sirrt_get_distances(scene_, robot_angles.data(), (int)(time * fps_), d.data(), &col));
+    if (n_obs > 0) ck(sirrt_get_distances_ex(scene_, robot_angles.data(), (int)(time * fps_), d.data(), &col, pd.data(), pts.data()));
+    else ck(sirrt_get_distances(scene_, robot_angles.data(), (int)(time * fps_), d.data(), &col));
     is_collision = col != 0;
     std::vector<robot_link_distance_to_obj> out;
-    if (is_collision) return out;  // the reference returns the (partial) vector it had; callers only read is_collision then
-    for (int l = 0; l < n_links_; l++) out.push_back({(float)d[l], {}, {}});
+    for (int l = 0; l < n_links_; l++) {
+      if (d[l] - 1e-21 <= 1e-12) break;  // the reference returns what it had collected when a link collides (:409-413)
+      robot_link_distance_to_obj r{(float)d[l], {}, {}};
+      for (int c = 0; c < n_obs; c++) {
+        const double* p = &pts[((size_t)l * n_obs + c) * 6];
+        r.neares_point_robot.push_back(Vector3d{p[0], p[1], p[2]});
+        r.neares_point_obj.push_back(Vector3d{p[3], p[4], p[5]});
+      }
+      out.push_back(std::move(r));
+    }
     return out;
   }
   bool check_robot_selfcollision(std::vector<double>) { return false; }     // CollisionManager.cpp:445-447

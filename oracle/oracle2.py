@@ -464,6 +464,38 @@ def signed_distance(a: Posed, b: Posed) -> float:
     return d - rsum
 
 
+def closest_points(a: Posed, b: Posed) -> Tuple[float, np.ndarray, np.ndarray]:
+    """(signed distance, closest point on a's surface, closest point on b's surface) for SEPARATED shapes -- coal's
+    DistanceResult::nearest_points, collected per pair by the reference's DistanceCallback (CollisionManager.cpp:568-598).
+    Core closest points: projection / scalar minimisation for capsule pairs, the NNLS-QP for polytopes; radii are then
+    stepped off along the line between them."""
+    ka, kb = a.geom.kind, b.geom.kind
+    ra, rb = a.geom.core_radius(), b.geom.core_radius()
+    if ka == CAPSULE and kb == SPHERE:
+        p = a.world_core()
+        _, ca = point_segment_distance(b.T[:3, 3], p[0], p[1])
+        cb = b.T[:3, 3].copy()
+    elif ka == CAPSULE and kb == BOX:
+        p = a.world_core()
+        Rb, tb = b.T[:3, :3], b.T[:3, 3]
+        la, lb = Rb.T @ (p[0] - tb), Rb.T @ (p[1] - tb)
+        t, _ = _golden(lambda u: point_box_dist(la + u * (lb - la), b.geom.half), 120)
+        ps = la + t * (lb - la)
+        ca = p[0] + t * (p[1] - p[0])
+        cb = Rb @ np.clip(ps, -b.geom.half, b.geom.half) + tb
+    elif ka == CAPSULE and kb == CAPSULE:
+        p, q = a.world_core(), b.world_core()
+        s, _ = _golden(lambda u: point_segment_distance(p[0] + u * (p[1] - p[0]), q[0], q[1])[0], 120)
+        ca = p[0] + s * (p[1] - p[0])
+        _, cb = point_segment_distance(ca, q[0], q[1])
+    else:
+        _, ca, cb = hull_distance_qp(a.world_core(), b.world_core())
+    n = cb - ca
+    ln = float(np.linalg.norm(n))
+    n = n / ln if ln > 0 else n
+    return ln - ra - rb, ca + ra * n, cb - rb * n
+
+
 def collides(a: Posed, b: Posed) -> Tuple[bool, float]:
     """(collision boolean, signed distance).  Polytope-polytope pairs without radii are decided by LP feasibility alone."""
     d = signed_distance(a, b)

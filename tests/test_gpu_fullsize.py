@@ -112,10 +112,15 @@ def test_pipelined_host_path_equals_plain_path_and_compact_table(full, pkg):
     t0, b0, near0 = plain.safe_intervals_batch(qs, KMAX)
     assert np.array_equal(t0, table[:n]) and np.array_equal(b0, bits[:n])
     t1, b1, near1 = dev.safe_intervals_batch(qs, KMAX)
-    assert np.array_equal(t1, t0) and np.array_equal(b1, b0) and near1 == near0
+    assert np.array_equal(t1, t0) and np.array_equal(b1, b0)
+    # near_contact_count counts the EVALUATED pair tests within 1e-6 m of contact; a pair whose frame another pair has
+    # already decided is never evaluated, so the count depends (slightly) on how work is batched, never the bits
+    assert abs(near1 - near0) <= max(16, near0 // 20), (near1, near0)
+    t1b, b1b, near1b = dev.safe_intervals_batch(qs, KMAX)
+    assert near1b == near1 and np.array_equal(b1b, b1), "the same call twice must give the same count"
     t2, _, _ = dev.safe_intervals_batch(qs, KMAX, want_bits=False)
     assert np.array_equal(t2, t0)
     t16, near16 = dev.safe_intervals_batch_i16(qs, KMAX)
-    assert t16.dtype == np.int16 and np.array_equal(t16.astype(np.int32), t0) and near16 == near0
+    assert t16.dtype == np.int16 and np.array_equal(t16.astype(np.int32), t0) and near16 == near1
     small16, _ = dev.safe_intervals_batch_i16(np.ascontiguousarray(q[:, :1000]), KMAX)   # a single block
     assert np.array_equal(small16.astype(np.int32), table[:1000])

@@ -147,6 +147,45 @@ def test_get_distances(pkg, orc, sp, packs):
             assert np.allclose(d[k], rd[k], atol=1e-9), (d, rd)
 
 
+@pytest.mark.parametrize("name", ["synB_32_200", "synC_32_200", "flying_boxes", "mass_test"])
+def test_get_distances_nearest_points(pkg, orc, sp, packs, name):
+    """a9: sirrt_get_distances_ex -- per (link, obstacle) the signed distance and the closest point pair (what
+    DistanceCallback collects, CollisionManager.cpp:568-598).  Against the C oracle: pair distances.  Against the
+    independent oracle2 (projection / scalar minimisation / NNLS-QP witness points): the points span the distance, each
+    lies on its own shape, and where the closest pair is unique they coincide."""
+    import os
+    import __graft_entry__ as g
+
+    o2 = g._load("sirrt_oracle2", os.path.join(g.ROOT, "oracle", "oracle2.py"))
+    pk = packs(name)
+    dev, ref, O2 = pkg.Scene(pk), orc.Oracle(pk), o2.Oracle2(pk)
+    q = random_q(sp, pk, 6, 43).T.astype(np.float64)
+    n_unique = 0
+    for i, qq in enumerate(q):
+        f = (53 * i + 7) % ref.n_frames
+        col, d, pd, pl, po = dev.get_distances_ex(qq, f)
+        col0, d0 = dev.get_distances(qq, f)
+        assert col == col0 and np.array_equal(d, d0)
+        links = O2.links(qq)
+        for l in range(dev.n_links):
+            for c in range(O2.C):
+                dref = ref.pair_distance(qq, l, c, f)
+                if dref > 1e-6:  # separated pairs: penetrating ones have no meaningful witness (the reference returns before reading them)
+                    assert abs(pd[l, c] - dref) < 1e-9, (name, l, c, pd[l, c], dref)
+                    if dref > 0.5:
+                        continue  # far pairs add nothing; keep the solver count down
+                    ob = O2.obstacle(c, f)
+                    assert abs(np.linalg.norm(pl[l, c] - po[l, c]) - dref) < 1e-8
+                    pt = lambda x: o2.Posed(o2.Geom(o2.SPHERE, radius=0.0), np.block([[np.eye(3), x[:, None]], [np.zeros((1, 3)), np.ones((1, 1))]]))
+                    assert abs(o2.signed_distance(pt(pl[l, c]), links[l])) < 1e-7, "link point is not on the link surface"
+                    assert abs(o2.signed_distance(pt(po[l, c]), ob)) < 1e-7, "obstacle point is not on the obstacle surface"
+                    d2, a2, b2 = o2.closest_points(links[l], ob)
+                    assert abs(d2 - dref) < 1e-7
+                    if np.linalg.norm(a2 - pl[l, c]) < 1e-6 and np.linalg.norm(b2 - po[l, c]) < 1e-6:
+                        n_unique += 1
+    assert n_unique > 0, "no pair whose witness points agree with the second oracle"
+
+
 def test_edge_cases(pkg, orc, sp, packs):
     pk = packs("synA_32_200")
     dev, ref = pkg.Scene(pk), orc.Oracle(pk)

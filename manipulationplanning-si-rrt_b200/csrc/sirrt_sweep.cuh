@@ -131,8 +131,6 @@ __device__ __noinline__ unsigned sweep_exact_batch(const SweepParams& P, const f
                                                    const uint32_t* q, int count, int lane, long long cfg0) {
   __syncwarp();
   unsigned n_exact = 0;
-  uint32_t* hit_word = nullptr;
-  uint32_t hit_bit = 0;
   if (lane < count) {
     const DScene& sc = P.sc;
     const uint32_t u = q[lane];
@@ -152,14 +150,10 @@ __device__ __noinline__ unsigned sweep_exact_batch(const SweepParams& P, const f
       load_pose(sc, slot, f, R, t, !S.rot_identity);
       const int r = capsule_exact(a, b, s_lr[l], sh, R, t, S.rot_identity != 0, P.band);
       n_exact = 1;
-      if (r == RES_HIT) { hit_word = &sbits[cfg * P.Wp + tile]; hit_bit = 1u << fr; }
+      if (r == RES_HIT) atomicOr(&sbits[cfg * P.Wp + tile], 1u << fr);
       else if (r == RES_AMBIG) push_work(P.wl, (int)(cfg0 + cfg), f, l, slot, 0);
     }
   }
-  // every lane has read the row state of this batch before any lane publishes a hit: which entries are skipped as
-  // "already decided" (and therefore which near-contact pairs are ever evaluated) does not depend on lane timing
-  __syncwarp();
-  if (hit_word) atomicOr(hit_word, hit_bit);
   __syncwarp();
   return n_exact;
 }
@@ -358,8 +352,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
           const bool f2 = f1 && q1n == 0;
           if (qwn >= 32 || f2) do {
             // ---- W: lane = QW entry (configuration, link, tile, slot): analytic HIT / IN frame windows
-            unsigned tm = 0, code = 0, w_hit = 0;
-            uint32_t* w_word = nullptr;
+            unsigned tm = 0, code = 0;
             if (qwn > 0) {
               const int cnt = min(32, qwn);
               qwn -= cnt;
@@ -376,13 +369,10 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
                 sweep_windows(m0, m1, m2, m3, lkp[0], lkp[SWEEP_LDC], lkp[2 * SWEEP_LDC], lkp[3 * SWEEP_LDC], lkp[4 * SWEEP_LDC],
                               lkp[5 * SWEEP_LDC], lkp[6 * SWEEP_LDC], rl + dj.y + band, rl + dj.x - band, in, hit);
                 const uint32_t cur = sbits[cfg * Wp + tile];
+                if (hit & ~cur) atomicOr(&sbits[cfg * Wp + tile], hit);
                 tm = in & ~hit & ~cur;
                 code = (e & 0xffu) | ((e >> 8) << 13);
-                w_word = &sbits[cfg * Wp + tile];
-                w_hit = hit & ~cur;
               }
-              __syncwarp();  // all lanes have read their row words before any publishes its HIT window (deterministic skipping)
-              if (w_hit) atomicOr(w_word, w_hit);
             }
             const bool f3 = f2 && qwn == 0;
             // the frames the model could not decide are enumerated into Q2, at most one per lane and round
@@ -403,8 +393,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
                 q2n -= cnt;
                 __syncwarp();
                 bool want = false;
-                unsigned u = 0, b_bit = 0;
-                uint32_t* b_word = nullptr;
+                unsigned u = 0;
                 if (lane < cnt) {
                   u = q2[q2n + lane];
                   const int cfg = u & 31, l = (u >> 5) & 7, fr = (u >> 8) & 31, tile = u >> 24, j = (u >> 13) & 2047;
@@ -448,11 +437,10 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
                       }
                       want = !hit && !fre;
                     }
-                    if (hit) { b_word = &sbits[cfg * Wp + tile]; b_bit = 1u << fr; }
+                    if (hit) atomicOr(&sbits[cfg * Wp + tile], 1u << fr);
                   }
                 }
-                const unsigned mq = __ballot_sync(SIRRT_FULL, want);  // also: every lane has read the row state before hits are published
-                if (b_word) atomicOr(b_word, b_bit);
+                const unsigned mq = __ballot_sync(SIRRT_FULL, want);
                 if (mq) {
                   if (want) q3[q3n + __popc(mq & lt_mask)] = u;
                   q3n += __popc(mq);

@@ -158,6 +158,7 @@ class CollisionManager {
   }
 
   int dof() const { return dof_; }
+  int link_count() const { return n_links_; }  // collision links of the planned robot (collision_robot_links_count)
   int frame_count() const { return frame_count_; }
   int fps() const { return fps_; }
   int words() const { return (frame_count_ + 31) / 32; }

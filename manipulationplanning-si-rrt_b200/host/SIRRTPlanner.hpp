@@ -60,6 +60,8 @@ struct PathState { Coord q; double time; };  // RobotObstacleJsonInfo.hpp:17-22
 
 struct PlannerStats {
   uint64_t n_safe_interval_calls = 0, n_motion_checks = 0, n_state_checks = 0, iterations = 0;
+  // ResultsWriter counters the planner can reproduce exactly (CollisionManager.cpp:374, :511-545)
+  uint64_t n_detected_collisions = 0, n_safe_intervals = 0, sum_safe_interval_frames = 0;
   uint64_t safe_interval_ns = 0, motion_ns = 0, solve_ns = 0;
 };
 
@@ -163,6 +165,8 @@ class PlannerConnect {
     auto r = be_.get_safe_intervals(q);
     stats_.safe_interval_ns += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
     stats_.n_safe_interval_calls++;
+    stats_.n_safe_intervals += r.size();
+    for (const auto& iv : r) stats_.sum_safe_interval_frames += (uint64_t)(iv.second - iv.first + 1);
     return r;
   }
 
@@ -300,6 +304,7 @@ class PlannerConnect {
         };
         if (hit >= 0) {
           res = true;
+          stats_.n_detected_collisions++;  // the one state check that returned true (CollisionManager.cpp:372-376)
           if (collision_coord) { state(hit, *collision_coord); if (hit > 0) state(hit - 1, last_valid_coord_); }
         } else if (collision_coord) state(steps, last_valid_coord_);
       }

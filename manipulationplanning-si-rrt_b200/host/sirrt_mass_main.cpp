@@ -109,9 +109,11 @@ int main(int argc, char** argv) {
         const MDP::MSIRRT::PlannerStats& st = planner.stats();
         std::lock_guard<std::mutex> lk(out_mu);
         printf("{\"task\": %d, \"pack\": \"%s\", \"seed\": %d, \"solved\": %s, \"solve_ms\": %.4f, \"cost\": %.17g, \"waypoints\": %zu, "
-               "\"path_hash\": \"%016llx\", \"iterations\": %llu, \"safe_interval_calls\": %llu, \"state_checks\": %llu}\n",
+               "\"path_hash\": \"%016llx\", \"iterations\": %llu, \"safe_interval_calls\": %llu, \"state_checks\": %llu, "
+               "\"detected_collisions\": %llu, \"safe_intervals\": %llu, \"safe_interval_frames\": %llu}\n",
                t.index, t.pack.c_str(), t.seed, ok ? "true" : "false", ns / 1e6, cost, n_way, (unsigned long long)h,
-               (unsigned long long)st.iterations, (unsigned long long)st.n_safe_interval_calls, (unsigned long long)st.n_state_checks);
+               (unsigned long long)st.iterations, (unsigned long long)st.n_safe_interval_calls, (unsigned long long)st.n_state_checks,
+               (unsigned long long)st.n_detected_collisions, (unsigned long long)st.n_safe_intervals, (unsigned long long)st.sum_safe_interval_frames);
       } catch (const std::exception& e) {
         n_failed++;
         cm.reset();

@@ -48,10 +48,10 @@ int main(int argc, char** argv) {
     MDP::ResultsLog log;
     log.path_to_scene_json = pack_path; log.path_to_result_folder = out_dir;
     log.full_execution_time_ns = ns(t_start, t_end); log.planner_config_time_ns = ns(t_start, t_cfg);
-    log.algorithm_solving_time_ns = ns(t_cfg, t_end); log.scene_init_time_ns = ns(t_start, t_scene);
+    log.scene_init_time_ns = ns(t_start, t_scene);
     const MDP::MSIRRT::PlannerStats& st = planner.stats();
-    log.collision_check_time_ns = st.motion_ns; log.get_safe_interval_time_ns = st.safe_interval_ns;
-    log.number_of_collision_checks = st.n_state_checks; log.number_of_get_safe_interval = st.n_safe_interval_calls;
+    log.set_counters(st, cm.link_count());
+    log.algorithm_solving_time_ns = ns(t_cfg, t_end);
     log.has_result = result;
     log.start_tree_vertices = planner.get_start_tree_vertices_count();
     log.goal_tree_vertices = planner.get_goal_tree_vertices_count();

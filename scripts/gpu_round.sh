@@ -4,7 +4,7 @@
 TAG=${1:-x}; shift
 OUT=gpurun_out
 mkdir -p $OUT
-timeout 600 python -m pytest tests -m gpu -x -q "$@" > $OUT/${TAG}_gpu_tests.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/${TAG}_gpu_tests.log
+timeout 1500 python -m pytest tests -m gpu -q "$@" > $OUT/${TAG}_gpu_tests.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/${TAG}_gpu_tests.log
 tail -5 $OUT/${TAG}_gpu_tests.log
 timeout 300 python bench.py --steps 5 --warmup 3 > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err; echo "bench rc=$?"
 python - <<PY

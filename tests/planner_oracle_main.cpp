@@ -102,8 +102,7 @@ int main(int argc, char** argv) {
     MDP::ResultsLog log;
     log.path_to_scene_json = argv[1];
     const auto& st = planner.stats();
-    log.algorithm_solving_time_ns = st.solve_ns; log.collision_check_time_ns = st.motion_ns; log.get_safe_interval_time_ns = st.safe_interval_ns;
-    log.number_of_collision_checks = st.n_state_checks; log.number_of_get_safe_interval = st.n_safe_interval_calls;
+    log.set_counters(st, be.n_links);
     log.has_result = result;
     log.start_tree_vertices = planner.get_start_tree_vertices_count();
     log.goal_tree_vertices = planner.get_goal_tree_vertices_count();

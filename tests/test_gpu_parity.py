@@ -175,7 +175,9 @@ def test_get_distances_nearest_points(pkg, orc, sp, packs, name):
                     if dref > 0.5:
                         continue  # far pairs add nothing; keep the solver count down
                     ob = O2.obstacle(c, f)
-                    assert abs(np.linalg.norm(pl[l, c] - po[l, c]) - dref) < 1e-8
+                    # the packs carry FP32 obstacle rotations (orthonormal to ~1e-7): a distance evaluated in the obstacle's
+                    # frame and the world-frame span of the two points differ by that much
+                    assert abs(np.linalg.norm(pl[l, c] - po[l, c]) - dref) < 3e-7 * max(1.0, dref)
                     pt = lambda x: o2.Posed(o2.Geom(o2.SPHERE, radius=0.0), np.block([[np.eye(3), x[:, None]], [np.zeros((1, 3)), np.ones((1, 1))]]))
                     assert abs(o2.signed_distance(pt(pl[l, c]), links[l])) < 1e-7, "link point is not on the link surface"
                     assert abs(o2.signed_distance(pt(po[l, c]), ob)) < 1e-7, "obstacle point is not on the obstacle surface"

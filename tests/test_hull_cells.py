@@ -54,3 +54,25 @@ def test_enclosure_certificate_is_sound(tmp_path):
     assert r.returncode == 0, (out, r.stderr)
     assert out["wrong_certificates"] == 0 and out["flat_certified"] == 0 and out["speck_certified"] == 0
     assert out["certified"] > 50000 and out["speck_inside"] > 10000   # the sample exercises both sides
+
+
+def test_sweep_frame_windows_are_rigorous(tmp_path):
+    """tests/sweep_window_host_main.cu, run on the HOST: the analytic frame windows of k_sweep's stage W
+    (csrc/sirrt_sweep_window.cuh) on random capsule links against bouncing-box tiles (reflections, slow, static,
+    axis-parallel and far-coordinate motion), checked against an FP64 point-segment distance of the true FP32 centres:
+    no frame that can touch is missing from the IN window, no frame of the HIT window is farther than r_hit."""
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("nvcc not available")
+    exe = os.path.join(ROOT, "tests", "_build", "sweep_window_host")
+    src = os.path.join(ROOT, "tests", "sweep_window_host_main.cu")
+    csrc = os.path.join(ROOT, "manipulationplanning-si-rrt_b200", "csrc")
+    os.makedirs(os.path.dirname(exe), exist_ok=True)
+    deps = [src, os.path.join(csrc, "sirrt_sweep_window.cuh")]
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(d) for d in deps):
+        subprocess.check_call([nvcc, "-O2", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-I", csrc, "-o", exe, src])
+    r = subprocess.run([exe, "400000"], capture_output=True, text=True, timeout=600)
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert r.returncode == 0, (out, r.stderr)
+    assert out["missed_in"] == 0 and out["false_hit"] == 0, out
+    assert out["true_in"] > 100000 and out["true_hit"] > 10000, out   # both windows are exercised

@@ -119,6 +119,29 @@ def test_planner_is_deterministic_per_seed_and_log_schema(planner_oracle, scenes
         assert set(st) == {"time", "robot_angles"}
 
 
+EXACT_COUNTERS = ["number_of_collision_checks", "number_of_get_safe_interval", "number_of_detected_collisions", "number_of_safe_intervals",
+                  "number_of_sum_of_safe_interval_frames", "number_of_forward_kinematics", "number_of_broadphase_get_safe_interval",
+                  "number_of_broadphase_collision_checks"]
+
+
+def test_log_counters_follow_the_reference_definitions(planner_oracle, scenes, orc):
+    """ResultsWriter counters the planner can reproduce (CollisionManager.cpp:350-377, :492-545): one FK per state
+    check and per interval query, `links` broad-phase queries per interval query, one detected collision per colliding
+    motion check, and interval counts / frame sums consistent with the scene's frame count."""
+    with open(scenes["dyn1"], "rb") as f:
+        o = orc.Oracle(f.read())
+    d = run_json([planner_oracle, scenes["dyn1"], "3", "--max-time", "20"])
+    n_si, n_cc = d["number_of_get_safe_interval"], d["number_of_collision_checks"]
+    assert n_si > 0 and n_cc > 0
+    assert d["number_of_forward_kinematics"] == n_si + n_cc
+    assert d["number_of_broadphase_get_safe_interval"] == o.n_links * n_si
+    assert d["number_of_broadphase_collision_checks"] == o.n_links * n_cc
+    assert 0 < d["number_of_detected_collisions"] <= d["b200"]["motion_checks"]
+    assert 0 < d["number_of_safe_intervals"] and 0 < d["number_of_sum_of_safe_interval_frames"] <= o.n_frames * n_si
+    # every interval holds at least one frame and two intervals of one query are separated by a colliding frame
+    assert d["number_of_sum_of_safe_interval_frames"] >= d["number_of_safe_intervals"]
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", ["scene_task", "mass_test", "dyn0", "dyn1"])
 def test_b200_planner_gives_identical_plans(planner_oracle, scenes, pkg, name):
@@ -132,3 +155,5 @@ def test_b200_planner_gives_identical_plans(planner_oracle, scenes, pkg, name):
             assert got["final_planner_data"] == ref["final_planner_data"], f"{name} seed {seed} {extra}: plans differ"
             for k in REFERENCE_LOG_KEYS:
                 assert k in got
+            for k in EXACT_COUNTERS:  # same tree growth, same queries, same answers -> the same counters
+                assert got[k] == ref[k], f"{name} seed {seed} {extra}: {k} {got[k]} != {ref[k]}"

@@ -248,6 +248,85 @@ def plan_time_leg(seeds: int, max_time: float, device: int):
     return out
 
 
+def knn_leg(pkg, device: int, hbm_gbs: float, fp32_tflops: float):
+    """C-space nearest-neighbour throughput (MSIRRT/src/Tree.cpp:18-36, PlannerConnect.cpp:382-412): queries/s through
+    the C ABI with device-resident queries and results (1-NN: tiled multi-query kernel; top-8: single-pass per-warp lists) and
+    with host buffers one query at a time (radius: what the planner calls once per iteration), D = 6.  Every figure is the wall
+    time of the synchronous API call, averaged over repetitions; 64 answers per size are checked against a NumPy brute force."""
+    import time
+
+    import torch
+    from scipy.spatial import cKDTree
+
+    oracle = g.load_oracle()
+    D = 6
+    rng = np.random.default_rng(3)
+    out = {"dim": D, "unit": "queries/s", "sizes": {},
+           "roofline_note": "1-NN: each 256-query tile streams the FP32 row copy once (32 B per point) and executes 18 FLOP per (query, point) pair; "
+                            "hbm_frac = tiles * 32 N / time / hbm peak, fp32_frac = 18 * pairs / time / measured FFMA peak. The kernel is bound by FP32 issue slots, "
+                            "not by HBM: the store (32 MB at N = 1e6) stays in the 126 MB L2."}
+    for n in (1000, 10000, 100000, 1000000):
+        pts = rng.uniform(-3.2, 3.2, (n, D))
+        idx = pkg.KnnIndex(D, n, device)
+        idx.add(pts)
+        nq = 65536 if n <= 100000 else 16384
+        qh = rng.uniform(-3.2, 3.2, (nq, D))
+        q = torch.from_numpy(qh).cuda()
+        oi = torch.empty(nq, dtype=torch.int64, device="cuda")
+        od = torch.empty(nq, dtype=torch.float64, device="cuda")
+
+        def timed(fn, reps):
+            fn()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                fn()
+            return (time.perf_counter() - t0) / reps
+
+        t_nn = timed(lambda: pkg._ck(pkg._lib.sirrt_knn_nearest(idx._h, q.data_ptr(), nq, oi.data_ptr(), od.data_ptr())), 5)
+        ref = np.empty(64, np.int64)
+        for j in range(64):   # NumPy brute force, dimension-order accumulation (no oracle on this path)
+            acc = np.zeros(n)
+            for c in range(D):
+                e = qh[j, c] - pts[:, c]
+                acc = acc + e * e
+            ref[j] = int(np.argmin(acc))
+        ok = bool(np.array_equal(oi[:64].cpu().numpy(), ref))
+        k = 8
+        nqk = 4096 if n <= 100000 else 1024
+        ti = torch.empty((nqk, k), dtype=torch.int64, device="cuda")
+        td = torch.empty((nqk, k), dtype=torch.float64, device="cuda")
+        t_k = timed(lambda: pkg._ck(pkg._lib.sirrt_knn_topk(idx._h, q.data_ptr(), nqk, k, ti.data_ptr(), td.data_ptr())), 3)
+        ok = ok and bool(np.array_equal(ti[:64, 0].cpu().numpy(), oi[:64].cpu().numpy()))
+        hits = []
+        t0 = time.perf_counter()
+        for j in range(200):
+            hits.append(idx.radius(qh[j], 1.0, 4096)[1])
+        t_r = (time.perf_counter() - t0) / 200
+        t0 = time.perf_counter()
+        for j in range(200):
+            idx.nearest(qh[j : j + 1])
+        t_1 = (time.perf_counter() - t0) / 200
+        idx.close()
+        # cpu baseline of this leg: the oracle's brute force (one thread) on a bounded sample, and a kd-tree (SciPy cKDTree, one thread: the data structure nanoflann implements)
+        nq_cpu = int(max(8, min(nq, 2e8 // n)))
+        t0 = time.perf_counter()
+        oracle.knn_nearest(pts, qh[:nq_cpu])
+        t_cpu = (time.perf_counter() - t0) / nq_cpu
+        tree = cKDTree(pts)
+        t0 = time.perf_counter()
+        tree.query(qh[:4096], k=1, workers=1)
+        t_kd = (time.perf_counter() - t0) / 4096
+        pairs = float(nq) * n
+        out["sizes"][str(n)] = {
+            "nearest_batch_qps": nq / t_nn, "nearest_batch_queries": nq, "pairs_per_s": pairs / t_nn,
+            "hbm_frac": ((nq + 255) // 256) * 32.0 * n / t_nn / 1e9 / hbm_gbs, "fp32_frac": 18.0 * pairs / t_nn / 1e12 / fp32_tflops if fp32_tflops else None,
+            "top8_batch_qps": nqk / t_k, "top8_batch_queries": nqk,
+            "radius_single_qps": 1.0 / t_r, "radius_mean_hits": float(np.mean(hits)), "nearest_single_qps": 1.0 / t_1,
+            "single_query_hbm_frac": 48.0 * n / t_1 / 1e9 / hbm_gbs,
+            "cpu_bruteforce_qps_1thread": 1.0 / t_cpu, "cpu_kdtree_qps_1thread": 1.0 / t_kd, "self_check_64_answers": ok}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -263,6 +342,7 @@ def main():
     ap.add_argument("--ref-budget", type=float, default=60.0, help="seconds of CPU work for --impl reference")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-plan-time", action="store_true")
+    ap.add_argument("--no-knn", action="store_true", help="skip the nearest-neighbour throughput leg (results.knn)")
     ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the weak-scaling side figure")
     ap.add_argument("--plan-seeds", type=int, default=3)
     ap.add_argument("--generic", action="store_true", help="force the generic kernel instead of the sweep kernel")
@@ -464,6 +544,8 @@ def main():
             out["results"]["weak_scaling"] = weak
         if not a.no_plan_time and world == 1:
             out["results"]["plan_time"] = plan_time_leg(a.plan_seeds, 5.0, local)
+        if not a.no_knn and world == 1:
+            out["results"]["knn"] = knn_leg(pkg, local, hbm_peak, roofline["peak"])
         if not a.no_cpu_baseline:
             threads = os.cpu_count() or 1
             v, n, dt = cpu_baseline(pack, q, a.cpu_budget, threads)

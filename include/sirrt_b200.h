@@ -151,11 +151,15 @@ int sirrt_motion_check_batch(sirrt_scene*, const double* q0, const double* q1, c
 
 /* ---- kNN: replaces nanoflann KDTreeSingleIndexDynamicAdaptor<L2_Simple> as used by
  * MSIRRT/src/Tree.cpp:5,18-36 and PlannerConnect.cpp:382-412 (exact, FP64, squared L2) ------- */
+/* `capacity` is the initial reservation: the store doubles when an insertion does not fit (up to 2^31 - 1 points) */
 int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn** out);
 int sirrt_knn_destroy(sirrt_knn*);
 int sirrt_knn_size(const sirrt_knn*, int64_t* n);
+int sirrt_knn_info(const sirrt_knn*, int* dim, int64_t* capacity, int* device); /* any pointer may be NULL */
 int sirrt_knn_clear(sirrt_knn*);
 int sirrt_knn_add(sirrt_knn*, const double* pts /*[n][dim]*/, int64_t n);
+/* nq == 1 with host buffers: single-launch latency path; nq > 1: tiled multi-query kernel (FP32 filter with a rigorous
+ * bound + FP64 verification; same answers bit for bit).  queries / idx / dist2 may be host or device pointers. */
 int sirrt_knn_nearest(sirrt_knn*, const double* queries /*[nq][dim]*/, int64_t nq, int64_t* idx, double* dist2);
 /* strict dist2 < r2 (nanoflann RadiusResultSet); indices ascending; *n_out = true count */
 int sirrt_knn_radius(sirrt_knn*, const double* query, double r2, int64_t* idx, int64_t cap, int64_t* n_out);

@@ -61,6 +61,7 @@ EXPORTS = {
     "sirrt_knn_create": (_i32, [_i32, _i64, _i32, _vp]),
     "sirrt_knn_destroy": (_i32, [_vp]),
     "sirrt_knn_size": (_i32, [_vp, _vp]),
+    "sirrt_knn_info": (_i32, [_vp, _vp, _vp, _vp]),
     "sirrt_knn_clear": (_i32, [_vp]),
     "sirrt_knn_add": (_i32, [_vp, _vp, _i64]),
     "sirrt_knn_nearest": (_i32, [_vp, _vp, _i64, _vp, _vp]),
@@ -315,6 +316,12 @@ class KnnIndex:
 
     def clear(self):
         _ck(_lib.sirrt_knn_clear(self._h))
+
+    @property
+    def capacity(self) -> int:
+        cap = C.c_int64()
+        _ck(_lib.sirrt_knn_info(self._h, None, C.byref(cap), None))
+        return cap.value
 
     def add(self, pts):
         pts = np.ascontiguousarray(pts, np.float64).reshape(-1, self.dim)

@@ -8,12 +8,14 @@ struct sirrt_knn {
   int device = 0, dim = 0, n_sm = 148;
   long long cap = 0, n = 0;
   cudaStream_t stream = nullptr;
-  double* pts = nullptr;
+  double* pts = nullptr;   // [dim][cap] FP64, the store every answer is computed from
+  float* pf = nullptr;     // [cap][row] FP32 rows (zero padded): the filter of the tiled multi-query kernel
+  int row = 8;
   DevBuf stage, qbuf, part_d, part_i, out_i, out_d, hits, count;
   // latency path (one query per planner iteration): pinned block read / written in place by the kernels
   char* pinned = nullptr;   // [KPIN_Q | KPIN_OUT | KPIN_RING]
   int ring_next = 0;        // next slot of the asynchronous single-point insertion ring
-  unsigned int* ticket = nullptr;  // last-block-done counter of the single-launch queries (zero between launches)
+  unsigned int* ticket = nullptr;  // [0], [1]: last-block-done counters of the single-launch queries (zero between launches); [2]: largest |coordinate| (float bits)
   size_t hits_cap_zeroed = 0;      // capacity of `hits` whose counter word has been cleared
 };
 enum : size_t { KPIN_Q = 0, KPIN_Q_CAP = 16 << 10, KPIN_OUT = KPIN_Q_CAP, KPIN_OUT_CAP = 32 << 10, KPIN_RING = KPIN_OUT + KPIN_OUT_CAP,
@@ -28,13 +30,16 @@ extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn
   CU(cudaSetDevice(device));
   sirrt_knn* k = new (std::nothrow) sirrt_knn;
   if (!k) return fail(SIRRT_E_ARG, "out of memory");
-  k->device = device; k->dim = dim; k->cap = capacity;
+  k->device = device; k->dim = dim; k->cap = capacity; k->row = dim <= 8 ? 8 : 16;
   cudaDeviceGetAttribute(&k->n_sm, cudaDevAttrMultiProcessorCount, device);
   if (cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking) != cudaSuccess || cudaMalloc(&k->pts, sizeof(double) * dim * (size_t)capacity) != cudaSuccess ||
-      cudaMallocHost((void**)&k->pinned, KPIN_BYTES) != cudaSuccess || cudaMalloc((void**)&k->ticket, 64) != cudaSuccess ||
+      cudaMalloc(&k->pf, sizeof(float) * k->row * (size_t)capacity) != cudaSuccess || cudaMallocHost((void**)&k->pinned, KPIN_BYTES) != cudaSuccess || cudaMalloc((void**)&k->ticket, 64) != cudaSuccess ||
       cudaMemsetAsync(k->ticket, 0, 64, k->stream) != cudaSuccess || cudaStreamSynchronize(k->stream) != cudaSuccess) {  // on the store's own stream, see sirrt_scene_create_from_pack
     cudaGetLastError();
     if (k->pts) cudaFree(k->pts);
+    if (k->pf) cudaFree(k->pf);
+    if (k->pinned) cudaFreeHost(k->pinned);
+    if (k->ticket) cudaFree(k->ticket);
     if (k->stream) cudaStreamDestroy(k->stream);
     delete k;
     return fail(SIRRT_E_CUDA, "sirrt_knn_create: allocation failed");
@@ -47,6 +52,7 @@ extern "C" int sirrt_knn_destroy(sirrt_knn* k) {
   cudaSetDevice(k->device);
   cudaStreamSynchronize(k->stream);
   cudaFree(k->pts);
+  cudaFree(k->pf);
   if (k->pinned) cudaFreeHost(k->pinned);
   if (k->ticket) cudaFree(k->ticket);
   for (DevBuf* b : {&k->stage, &k->qbuf, &k->part_d, &k->part_i, &k->out_i, &k->out_d, &k->hits, &k->count}) b->release();
@@ -60,9 +66,40 @@ extern "C" int sirrt_knn_size(const sirrt_knn* k, int64_t* n) {
   *n = k->n;
   return SIRRT_OK;
 }
+extern "C" int sirrt_knn_info(const sirrt_knn* k, int* dim, int64_t* capacity, int* device) {
+  if (!k) return fail(SIRRT_E_ARG, "null argument");
+  if (dim) *dim = k->dim;
+  if (capacity) *capacity = k->cap;
+  if (device) *device = k->device;
+  return SIRRT_OK;
+}
 extern "C" int sirrt_knn_clear(sirrt_knn* k) {
   if (!k) return fail(SIRRT_E_ARG, "null argument");
   k->n = 0;
+  return SIRRT_OK;
+}
+
+// The capacity given to sirrt_knn_create is the initial reservation; the store doubles when an insertion does not fit
+// (the reference reserves 1e6 vertices per tree up front, PlannerConnect.cpp:16-18, which here would pin 80 MB of HBM per
+// tree of every planner instance).
+static int knn_grow(sirrt_knn* k, long long need) {
+  if (need <= k->cap) return SIRRT_OK;
+  if (need > 0x7fffffffll) return fail(SIRRT_E_OVERFLOW, "sirrt_knn_add: more than 2^31 - 1 points");
+  const long long cap = std::min(0x7fffffffll, std::max(need, 2 * k->cap));
+  double* np = nullptr;
+  float* nf = nullptr;
+  if (cudaMalloc(&np, sizeof(double) * k->dim * (size_t)cap) != cudaSuccess || cudaMalloc(&nf, sizeof(float) * k->row * (size_t)cap) != cudaSuccess) {
+    cudaGetLastError();
+    if (np) cudaFree(np);
+    return fail(SIRRT_E_CUDA, "sirrt_knn_add: cudaMalloc failed while growing the store");
+  }
+  if (k->n) {
+    CU(cudaMemcpy2DAsync(np, sizeof(double) * (size_t)cap, k->pts, sizeof(double) * (size_t)k->cap, sizeof(double) * (size_t)k->n, k->dim, cudaMemcpyDeviceToDevice, k->stream));
+    CU(cudaMemcpyAsync(nf, k->pf, sizeof(float) * k->row * (size_t)k->n, cudaMemcpyDeviceToDevice, k->stream));
+  }
+  CU(sirrt_sync(k->stream));
+  cudaFree(k->pts); cudaFree(k->pf);
+  k->pts = np; k->pf = nf; k->cap = cap;
   return SIRRT_OK;
 }
 
@@ -70,8 +107,8 @@ extern "C" int sirrt_knn_clear(sirrt_knn* k) {
 extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
   if (!k || !pts || n < 0) return fail(SIRRT_E_ARG, "sirrt_knn_add: bad argument");
   if (n == 0) return SIRRT_OK;
-  if (k->n + n > k->cap) return fail(SIRRT_E_OVERFLOW, "sirrt_knn_add: capacity exceeded");
   CU(cudaSetDevice(k->device));
+  { int rc = knn_grow(k, k->n + n); if (rc) return rc; }
   const size_t bytes = sizeof(double) * k->dim * (size_t)n;
   const double* src = pts;
   if (n == 1 && !is_device_ptr(pts)) {
@@ -81,7 +118,7 @@ extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
     if (k->ring_next == (int)KPIN_RING_SLOTS) { CU(sirrt_sync(k->stream)); k->ring_next = 0; }
     double* slot = (double*)(k->pinned + KPIN_RING) + (size_t)k->ring_next++ * SIRRT_KNN_MAXDIM;
     memcpy(slot, pts, bytes);
-    k_knn_append<<<1, 32, 0, k->stream>>>(slot, 1, k->dim, k->pts, k->cap, k->n);
+    k_knn_append<<<1, 32, 0, k->stream>>>(slot, 1, k->dim, k->pts, k->cap, k->n, k->pf, k->row, k->ticket + 2);
     CU(cudaGetLastError());
     k->n += 1;
     return SIRRT_OK;
@@ -91,8 +128,8 @@ extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
     CU(cudaMemcpyAsync(k->stage.p, pts, bytes, cudaMemcpyHostToDevice, k->stream));
     src = k->stage.as<double>();
   }
-  const long long tot = (long long)n * k->dim;
-  k_knn_append<<<(unsigned)((tot + 255) / 256), 256, 0, k->stream>>>(src, n, k->dim, k->pts, k->cap, k->n);
+  const long long tot = (long long)n * k->row;
+  k_knn_append<<<(unsigned)((tot + 255) / 256), 256, 0, k->stream>>>(src, n, k->dim, k->pts, k->cap, k->n, k->pf, k->row, k->ticket + 2);
   CU(cudaGetLastError());
   CU(sirrt_sync(k->stream));
   k->n += n;
@@ -109,13 +146,32 @@ static int knn_queries_in(sirrt_knn* k, const double* queries, int64_t nq, const
   return 0;
 }
 
+// launch of the tiled multi-query 1-NN kernel: grid (n_split, query tiles of 32 G)
+template <int ROW, int DU>
+static void knn_launch_tiled(sirrt_knn* k, const KnnStore& S, const double* dq, long long nq, int G, int n_split, double* pd, long long* pi) {
+  const unsigned tiles = (unsigned)((nq + 32 * G - 1) / (32 * G));
+  k_knn_nearest_tiled<ROW, DU><<<dim3((unsigned)n_split, tiles), SIRRT_KNN_THREADS, 0, k->stream>>>(S, k->pf, k->ticket + 2, dq, nq, G, pd, pi);
+}
+static void knn_nearest_tiled(sirrt_knn* k, const KnnStore& S, const double* dq, long long nq, int G, int n_split, double* pd, long long* pi) {
+  switch (k->dim) {
+    case 1: case 2: knn_launch_tiled<8, 2>(k, S, dq, nq, G, n_split, pd, pi); break;
+    case 3: knn_launch_tiled<8, 3>(k, S, dq, nq, G, n_split, pd, pi); break;
+    case 4: knn_launch_tiled<8, 4>(k, S, dq, nq, G, n_split, pd, pi); break;
+    case 5: knn_launch_tiled<8, 5>(k, S, dq, nq, G, n_split, pd, pi); break;
+    case 6: knn_launch_tiled<8, 6>(k, S, dq, nq, G, n_split, pd, pi); break;
+    case 7: knn_launch_tiled<8, 7>(k, S, dq, nq, G, n_split, pd, pi); break;
+    case 8: knn_launch_tiled<8, 8>(k, S, dq, nq, G, n_split, pd, pi); break;
+    default: knn_launch_tiled<16, 16>(k, S, dq, nq, G, n_split, pd, pi); break;
+  }
+}
+
 // PlannerConnect::get_nearest_node (PlannerConnect.cpp:382-392): exact 1-NN
 extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq, int64_t* idx, double* dist2) {
   if (!k || !queries || !idx || nq < 0) return fail(SIRRT_E_ARG, "sirrt_knn_nearest: bad argument");
   if (nq == 0) return SIRRT_OK;
-  if (nq > 65535) {  // grid.y limit: recurse over slabs
-    for (int64_t o = 0; o < nq; o += 65535) {
-      int rc = sirrt_knn_nearest(k, queries + o * k->dim, std::min<int64_t>(65535, nq - o), idx + o, dist2 ? dist2 + o : nullptr);
+  if (nq > (1 << 20)) {  // grid.y limit (65535 tiles of 32 queries): recurse over slabs
+    for (int64_t o = 0; o < nq; o += 1 << 20) {
+      int rc = sirrt_knn_nearest(k, queries + o * k->dim, std::min<int64_t>(1 << 20, nq - o), idx + o, dist2 ? dist2 + o : nullptr);
       if (rc) return rc;
     }
     return SIRRT_OK;
@@ -140,9 +196,13 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
     return SIRRT_OK;
   }
   if ((rc = knn_queries_in(k, queries, nq, &dq))) return rc;
-  // enough blocks to fill the machine, at least ~4 points per thread per split
-  long long want = std::max(1ll, (long long)k->n_sm * 4 / nq);
-  int n_split = (int)std::max(1ll, std::min(want, (k->n + 4 * SIRRT_KNN_THREADS - 1) / (4 * SIRRT_KNN_THREADS)));
+  // query tiles of 32 G (G = 1, 2, 4, 8 groups of 32 queries per block); the store is split so that about 8 blocks
+  // per SM are in flight, a split being at least one tile of points
+  int G = 1;
+  while (G < 8 && 32 * G < nq) G *= 2;
+  const long long tiles = (nq + 32 * G - 1) / (32 * G);
+  const long long want = std::max(1ll, ((long long)k->n_sm * 8 + tiles - 1) / tiles);
+  const int n_split = (int)std::max(1ll, std::min(want, (k->n + KNN_TILE - 1) / KNN_TILE));
   if (k->part_d.ensure(sizeof(double) * nq * n_split) || k->part_i.ensure(sizeof(long long) * nq * n_split) ||
       k->out_i.ensure(sizeof(long long) * nq) || k->out_d.ensure(sizeof(double) * nq))
     return fail(SIRRT_E_CUDA, "cudaMalloc failed");
@@ -151,7 +211,7 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
   const bool opin = (size_t)nq * 16 <= KPIN_OUT_CAP;  // results written into the pinned block in place
   long long* o_i = idev ? (long long*)idx : (opin ? (long long*)(k->pinned + KPIN_OUT) : k->out_i.as<long long>());
   double* o_d = dist2 ? (ddev ? dist2 : (opin ? (double*)(k->pinned + KPIN_OUT + KPIN_OUT_CAP / 2) : k->out_d.as<double>())) : nullptr;
-  k_knn_partial<<<dim3(n_split, (unsigned)nq), SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, k->part_d.as<double>(), k->part_i.as<long long>());
+  knn_nearest_tiled(k, S, dq, nq, G, n_split, k->part_d.as<double>(), k->part_i.as<long long>());
   k_knn_final<<<(unsigned)((nq + 7) / 8), 256, 0, k->stream>>>(k->part_d.as<double>(), k->part_i.as<long long>(), n_split, nq, o_i, o_d);
   CU(cudaGetLastError());
   if (!idev && !opin) CU(cudaMemcpyAsync(idx, o_i, sizeof(long long) * nq, cudaMemcpyDeviceToHost, k->stream));
@@ -202,7 +262,20 @@ extern "C" int sirrt_knn_topk(sirrt_knn* k, const double* queries, int64_t nq, i
   if (rc) return rc;
   if (k->out_i.ensure(sizeof(long long) * nq * kk) || k->out_d.ensure(sizeof(double) * nq * kk)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
   KnnStore S{k->pts, k->cap, k->n, k->dim};
-  k_knn_topk<<<(unsigned)nq, SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, kk, k->out_i.as<long long>(), k->out_d.as<double>());
+  if (kk <= 32 && k->n > 0) {
+    // one pass: per-warp sorted lists, merged per block, then across the splits of the store
+    for (int64_t o = 0; o < nq; o += 65535) {
+      const long long nqs = std::min<int64_t>(65535, nq - o);
+      const long long want = std::max(1ll, (long long)k->n_sm * 8 / nqs);
+      const int n_split = (int)std::max(1ll, std::min(want, (k->n + 4 * SIRRT_KNN_THREADS - 1) / (4 * SIRRT_KNN_THREADS)));
+      if (k->part_d.ensure(sizeof(double) * nqs * n_split * kk) || k->part_i.ensure(sizeof(long long) * nqs * n_split * kk)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+      k_knn_topk_pass<<<dim3((unsigned)n_split, (unsigned)nqs), SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq + o * k->dim, kk, k->part_d.as<double>(), k->part_i.as<long long>());
+      k_knn_topk_merge<<<(unsigned)((nqs + 7) / 8), 256, 0, k->stream>>>(k->part_d.as<double>(), k->part_i.as<long long>(), n_split, nqs, kk,
+                                                                         k->out_i.as<long long>() + o * kk, k->out_d.as<double>() + o * kk);
+    }
+  } else {
+    k_knn_topk<<<(unsigned)nq, SIRRT_KNN_THREADS, 0, k->stream>>>(S, dq, kk, k->out_i.as<long long>(), k->out_d.as<double>());
+  }
   CU(cudaGetLastError());
   CU(cudaMemcpyAsync(idx, k->out_i.p, sizeof(long long) * nq * kk, cudaMemcpyDefault, k->stream));  // host or device result buffers
   if (dist2) CU(cudaMemcpyAsync(dist2, k->out_d.p, sizeof(double) * nq * kk, cudaMemcpyDefault, k->stream));

@@ -106,12 +106,18 @@ class B200Backend {
 
   int knn_new() {
     sirrt_knn* k = nullptr;
-    if (pool_ && !pool_->empty()) {
+    while (pool_ && !pool_->empty()) {
       k = pool_->back(); pool_->pop_back();
-      knn_.push_back(k);
-      return (int)knn_.size() - 1;
+      int dim = 0, dev = -1;
+      if (sirrt_knn_info(k, &dim, nullptr, &dev) == SIRRT_OK && dim == dof() && dev == device_) {  // a pooled store of another robot / device is of no use
+        knn_.push_back(k);
+        return (int)knn_.size() - 1;
+      }
+      sirrt_knn_destroy(k);
+      k = nullptr;
     }
-    if (sirrt_knn_create(dof(), 1 << 20, device_, &k)  /* the reference reserves 1e6 vertices per tree (PlannerConnect.cpp:16-18) */ != SIRRT_OK) throw std::runtime_error(std::string("libsirrt_b200: ") + sirrt_last_error());
+    // the reference reserves 1e6 vertices per tree (PlannerConnect.cpp:16-18); the store grows on demand instead
+    if (sirrt_knn_create(dof(), 1 << 14, device_, &k) != SIRRT_OK) throw std::runtime_error(std::string("libsirrt_b200: ") + sirrt_last_error());
     knn_.push_back(k);
     return (int)knn_.size() - 1;
   }

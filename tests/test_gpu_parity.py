@@ -248,6 +248,71 @@ def test_knn(pkg, orc):
     assert (i0 == -1).all() and e.radius(qs[0], 1.0)[1] == 0
 
 
+def _topk_ref(pts, q, k):
+    """ascending (distance, index), distance accumulated in dimension order without FMA (float64 numpy does exactly that)"""
+    d2 = np.zeros(len(pts))
+    for j in range(pts.shape[1]):
+        e = q[j] - pts[:, j]
+        d2 = d2 + e * e
+    order = np.lexsort((np.arange(len(pts)), d2))[:k]
+    return order, d2[order]
+
+
+@pytest.mark.parametrize("dim", [1, 2, 3, 6, 7, 8, 9, 16])
+def test_knn_tiled_multi_query_is_exact(pkg, orc, dim):
+    """The throughput path (k_knn_nearest_tiled: FP32 filter with a rigorous error bound + FP64 verification) returns the
+    oracle's index and distance bit for bit -- random data, exact duplicates, clusters whose members differ far below FP32
+    resolution, large offsets -- for store sizes around the tile size and query counts around the warp size; the store grows
+    from a tiny initial capacity.  PlannerConnect.cpp:382-392 (ties -> lowest index)."""
+    rng = np.random.default_rng(100 + dim)
+    for n, kind in [(1, "u"), (255, "u"), (256, "dup"), (257, "cluster"), (5000, "u"), (5003, "cluster"), (3000, "offset"), (4100, "dup")]:
+        pts = rng.uniform(-3.2, 3.2, (n, dim))
+        if kind == "dup" and n > 8:
+            pts[n // 2:] = pts[: n - n // 2]              # every point twice: the lower index must win
+        elif kind == "cluster":
+            c = rng.uniform(-3, 3, (8, dim))
+            pts = c[rng.integers(0, 8, n)] + 1e-9 * rng.standard_normal((n, dim))   # FP32 cannot tell the members apart
+        elif kind == "offset":
+            pts = pts * 1e-3 + 1000.0
+        idx = pkg.KnnIndex(dim, 4)
+        for a in range(0, n, 1777):
+            idx.add(pts[a : a + 1777])
+        assert len(idx) == n
+        for nq in (2, 31, 33, 300):
+            qs = rng.uniform(-3.2, 3.2, (nq, dim)) if kind != "offset" else 1000.0 + 1e-3 * rng.uniform(-3.2, 3.2, (nq, dim))
+            qs[0] = pts[rng.integers(0, n)]               # a query on a stored point: distance 0, duplicates tie
+            if kind == "cluster":
+                qs[1:] = pts[rng.integers(0, n, nq - 1)] + 1e-9 * rng.standard_normal((nq - 1, dim))
+            gi, gd = idx.nearest(qs)
+            ri, rd = orc.knn_nearest(pts, qs)
+            assert np.array_equal(gi, ri), (dim, n, kind, nq, np.flatnonzero(gi != ri)[:5])
+            assert np.array_equal(gd, rd)
+        idx.close()
+
+
+def test_knn_single_pass_topk_is_exact(pkg):
+    """k <= 32: per-warp sorted lists merged across warps and splits give the lexicographic (distance, index) order exactly
+    -- also with duplicates, with fewer points than k (missing entries: index -1, distance inf), and for k > 32 (the k-pass
+    kernel)."""
+    rng = np.random.default_rng(9)
+    for n, dim in [(5, 6), (31, 3), (1000, 6), (20011, 6), (70000, 7)]:
+        pts = rng.uniform(-3.2, 3.2, (n, dim))
+        if n > 100:
+            pts[n // 3 : n // 3 + 50] = pts[:50]
+        idx = pkg.KnnIndex(dim, 16)
+        idx.add(pts)
+        qs = np.vstack([pts[:3], rng.uniform(-3.2, 3.2, (21, dim))])
+        for k in (1, 8, 32, 40):
+            ti, td = idx.topk(qs, k)
+            for j in range(len(qs)):
+                o, d = _topk_ref(pts, qs[j], k)
+                m = len(o)
+                assert np.array_equal(ti[j, :m], o), (n, dim, k, j)
+                assert np.array_equal(td[j, :m], d)
+                assert (ti[j, m:] == -1).all() and np.isinf(td[j, m:]).all()
+        idx.close()
+
+
 def test_collision_manager_mirror(pkg, orc, packs, sp):
     """The reference-facing operator interface (MDP::CollisionManager method names)."""
     pk = packs("flying_boxes")

@@ -43,6 +43,25 @@ static cudaError_t sirrt_sync(cudaStream_t st) {
   }
 }
 
+// Completion through a flag in the object's pinned host block (latency path): the last block of the call's last kernel
+// writes `seq` behind everything the call produced (RecheckParams::done, k_knn_nearest1, k_knn_radius1), and the host polls
+// its own memory -- no driver call, so 16 planner threads waiting on one GPU do not queue on the driver's lock, and the
+// wake-up does not pay cudaStreamSynchronize's hand-shake.  The stream is queried now and then only to surface a failed
+// launch (the flag would never arrive).
+static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int* flag, unsigned int seq) {
+  static const int mode = [] { const char* e = getenv("SIRRT_SYNC"); return (e && !strcmp(e, "yield")) ? 1 : 0; }();
+  for (unsigned spin = 1;; spin++) {
+    if (*flag == seq) return cudaSuccess;
+    if ((spin & (mode ? 0xffu : 0xffffu)) == 0) {
+      const cudaError_t e = cudaStreamQuery(st);
+      if (e == cudaSuccess) return *flag == seq ? cudaSuccess : cudaErrorUnknown;
+      if (e != cudaErrorNotReady) return e;
+    }
+    if (mode) sched_yield();
+    else __builtin_ia32_pause();
+  }
+}
+
 extern "C" const char* sirrt_last_error(void) { return g_err; }
 extern "C" int sirrt_version(void) { return 100; }
 extern "C" int sirrt_device_count(void) {
@@ -99,12 +118,14 @@ struct sirrt_scene {
   char* pinned = nullptr;
   unsigned int* lazy_cnt = nullptr;  // device: 4 launch counters + ticket, zero between calls (k_recheck's last block clears them)
   bool lazy_pending = false;  // counters of the last run_bits launch are in flight to PIN_CNT
+  unsigned int done_seq = 0;  // sequence number of the completion flag (PIN_FLAG) the pending call will write
+  bool done_armed = false;    // the pending call ends with a flag write: wait with sirrt_wait_flag instead of a stream sync
   std::vector<cudaEvent_t> ev;  // start/stop pairs around the sweep launches of one call
   uint64_t stats[5] = {0, 0, 0, 0, 0};
 };
 
 enum : size_t { PIN_Q = 0, PIN_Q_CAP = 256 << 10, PIN_FR = PIN_Q + PIN_Q_CAP, PIN_FR_CAP = 64 << 10, PIN_OUT = PIN_FR + PIN_FR_CAP,
-                PIN_OUT_CAP = 512 << 10, PIN_CNT = PIN_OUT + PIN_OUT_CAP, PIN_CNT_CAP = 4 << 10, PIN_BYTES = PIN_CNT + PIN_CNT_CAP };
+                PIN_OUT_CAP = 512 << 10, PIN_CNT = PIN_OUT + PIN_OUT_CAP, PIN_CNT_CAP = 4 << 10, PIN_FLAG = PIN_CNT + 256, PIN_BYTES = PIN_CNT + PIN_CNT_CAP };
 
 template <typename T> static int upload(sirrt_scene* s, const std::vector<T>& v, const T** out) {
   void* p = nullptr;
@@ -156,6 +177,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   s->band = 2e-5 * std::max(1.0, tb.extent / 1.5);
   if ((rc = sweep_build(s->hs, tb, s->d, &s->sweep, s->owned))) return bail(fail(rc, "sweep table build failed"));
   if (cudaMallocHost((void**)&s->pinned, PIN_BYTES) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaMallocHost failed")); }
+  memset(s->pinned + PIN_CNT, 0, PIN_CNT_CAP);
   // cleared ON THE SCENE'S STREAM and waited for: a plain cudaMemset runs on the legacy default stream, is asynchronous
   // to the host for device memory, and is not ordered against this non-blocking stream -- under load it could land after
   // the first kernels had started counting

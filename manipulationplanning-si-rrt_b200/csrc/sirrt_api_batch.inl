@@ -9,6 +9,19 @@ static int grid_for(long long warps_wanted, int n_sm, int blocks_per_sm) {
 
 struct Range { long long n0, cnt; };
 
+// the call's last kernel (k_recheck on the latency path) will write the next sequence number to PIN_FLAG
+static void arm_done(sirrt_scene* s, RecheckParams& R) {
+  R.done = (unsigned int*)(s->pinned + PIN_FLAG);
+  R.done_seq = ++s->done_seq;
+  s->done_armed = true;
+}
+// wait for the call in flight: by the pinned flag when its last kernel carries one, else by the stream
+static cudaError_t scene_wait(sirrt_scene* s) {
+  if (!s->done_armed) return sirrt_sync(s->stream);
+  s->done_armed = false;
+  return sirrt_wait_flag(s->stream, (const volatile unsigned int*)(s->pinned + PIN_FLAG), s->done_seq);
+}
+
 // Collision bit rows of configurations [0, N) (global indexing into q / d_bits).  Work is cut into
 // launches of at most chunk_configs configurations so that the FP64 re-check work list stays
 // bounded; a launch whose list overflowed is repeated in halves.
@@ -21,6 +34,7 @@ struct Range { long long n0, cnt; };
 static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits, bool lazy = false, int32_t* fuse_table = nullptr,
                     int fuse_kmax = 0, bool* fused = nullptr, const int2* row_tiles = nullptr, int win_tiles = 0) {
   if (fused) *fused = false;
+  s->done_armed = false;
   const int W = s->tb.n_tiles;
   cudaStream_t st = s->stream;
   if (s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(work list) failed");
@@ -82,6 +96,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       if (self_clearing && fuse_table && N <= 64) {
         R.iv = IvParams{d_bits, N, W, s->tb.T, fuse_kmax, fuse_table};
         if (fused) *fused = true;
+        arm_done(s, R);  // the table is the pinned host block and nothing follows this kernel: the caller waits on the flag (scene_wait)
       }
       // a handful of rows leaves a handful of ambiguous pair tests: a small grid shortens the last-block hand-over
       k_recheck<<<(self_clearing && N <= 64) ? 16 : s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
@@ -373,8 +388,12 @@ extern "C" int sirrt_collision_bits_window_f64(sirrt_scene* s, const double* q_a
 }
 
 // ---- a4: independent (configuration, frame) cells ------------------------------------------------
-static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_frames, uint8_t* d_out, int semantics, int frame_one = 0) {
+// flag_when_done: the results land in the pinned host block and nothing follows the last k_recheck, which then writes the
+// completion flag (the caller waits with scene_wait)
+static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_frames, uint8_t* d_out, int semantics, int frame_one = 0,
+                     bool flag_when_done = false) {
   cudaStream_t st = s->stream;
+  s->done_armed = false;
   if (s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(work list) failed");
   if (s->counts.ensure(4 * sizeof(unsigned))) return fail(SIRRT_E_CUDA, "cudaMalloc(counters) failed");
   const bool self_clearing = N <= (long long)(16 << 10);  // latency path: k_recheck's last block clears the counters
@@ -411,6 +430,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
     R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
     if (self_clearing) R.ticket = s->lazy_cnt + 4;
+    if (self_clearing && flag_when_done && n0 + per >= N) arm_done(s, R);
     k_recheck<<<(self_clearing && qv.cnt <= 256) ? 16 : s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
     s->stats[0] += 2;
     CU(cudaGetLastError());
@@ -437,8 +457,8 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
     QView q1{nullptr, nullptr, 1, 0, 1, s->hs.dof, 1, {}};
     for (int j = 0; j < s->hs.dof; j++) q1.inl[j] = q_aos[j];
     uint8_t* d_out1 = (uint8_t*)(s->pinned + PIN_OUT);
-    if ((rc = run_cells(s, q1, 1, nullptr, d_out1, SIRRT_SEM_FRAME, frames[0]))) return rc;
-    CU(sirrt_sync(s->stream));
+    if ((rc = run_cells(s, q1, 1, nullptr, d_out1, SIRRT_SEM_FRAME, frames[0], true))) return rc;
+    CU(scene_wait(s));
     collided[0] = d_out1[0];
     return SIRRT_OK;
   }
@@ -455,9 +475,9 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
     d_out = s->cells.as<uint8_t>();
   }
   QView q{q_soa ? (const float*)dq : nullptr, q_soa ? nullptr : (const double*)dq, N, 0, N, s->hs.dof};
-  if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME))) return rc;
+  if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME, 0, opin))) return rc;
   if (!odev && !opin) CU(cudaMemcpyAsync(collided, d_out, (size_t)N, cudaMemcpyDeviceToHost, s->stream));
-  CU(sirrt_sync(s->stream));
+  CU(scene_wait(s));
   if (opin) memcpy(collided, d_out, (size_t)N);
   return SIRRT_OK;
 }
@@ -497,7 +517,7 @@ extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo
     int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits, attempt == 0, (int32_t*)host_table, Kmax, &fused);
     if (rc) return rc;
     if (!fused && (rc = run_intervals(s, d_bits, 1, (int32_t*)host_table, Kmax))) return rc;
-    CU(sirrt_sync(s->stream));
+    CU(scene_wait(s));
     if (attempt == 0 && finish_lazy(s)) continue;
     break;
   }

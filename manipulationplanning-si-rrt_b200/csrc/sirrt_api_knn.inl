@@ -17,9 +17,10 @@ struct sirrt_knn {
   int ring_next = 0;        // next slot of the asynchronous single-point insertion ring
   unsigned int* ticket = nullptr;  // [0], [1]: last-block-done counters of the single-launch queries (zero between launches); [2]: largest |coordinate| (float bits)
   size_t hits_cap_zeroed = 0;      // capacity of `hits` whose counter word has been cleared
+  unsigned int done_seq = 0;       // completion flag sequence (KPIN_FLAG), see sirrt_wait_flag
 };
 enum : size_t { KPIN_Q = 0, KPIN_Q_CAP = 16 << 10, KPIN_OUT = KPIN_Q_CAP, KPIN_OUT_CAP = 32 << 10, KPIN_RING = KPIN_OUT + KPIN_OUT_CAP,
-                KPIN_RING_SLOTS = 64, KPIN_BYTES = KPIN_RING + KPIN_RING_SLOTS * SIRRT_KNN_MAXDIM * sizeof(double) };
+                KPIN_RING_SLOTS = 64, KPIN_FLAG = KPIN_RING + KPIN_RING_SLOTS * SIRRT_KNN_MAXDIM * sizeof(double), KPIN_BYTES = KPIN_FLAG + 64 };
 
 extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn** out) {
   if (!out || dim < 1 || dim > SIRRT_KNN_MAXDIM || capacity < 1 || capacity > 0x7fffffffll) return fail(SIRRT_E_ARG, "sirrt_knn_create: bad argument");
@@ -44,6 +45,7 @@ extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn
     delete k;
     return fail(SIRRT_E_CUDA, "sirrt_knn_create: allocation failed");
   }
+  memset(k->pinned + KPIN_FLAG, 0, 64);
   *out = k;
   return SIRRT_OK;
 }
@@ -188,9 +190,10 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
     double* o_d = (double*)(k->pinned + KPIN_OUT + 8);
     KnnQuery Q{};
     for (int j = 0; j < k->dim; j++) Q.v[j] = queries[j];
-    k_knn_nearest1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S1, Q, k->part_d.as<double>(), k->part_i.as<long long>(), k->ticket, o_i, o_d);
+    unsigned int* flag = (unsigned int*)(k->pinned + KPIN_FLAG);
+    k_knn_nearest1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S1, Q, k->part_d.as<double>(), k->part_i.as<long long>(), k->ticket, o_i, o_d, flag, ++k->done_seq);
     CU(cudaGetLastError());
-    CU(sirrt_sync(k->stream));
+    CU(sirrt_wait_flag(k->stream, flag, k->done_seq));
     idx[0] = o_i[0];
     if (dist2) dist2[0] = o_d[0];
     return SIRRT_OK;
@@ -239,9 +242,10 @@ extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, in
   const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
   const size_t first = (size_t)std::min<long long>(k->n, 1023ll);
   int* ph = (int*)(k->pinned + KPIN_OUT);
-  k_knn_radius1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, Q, r2, k->hits.as<int>(), k->ticket + 1, ph, (int)first);
+  unsigned int* flag = (unsigned int*)(k->pinned + KPIN_FLAG);
+  k_knn_radius1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, Q, r2, k->hits.as<int>(), k->ticket + 1, ph, (int)first, flag, ++k->done_seq);
   CU(cudaGetLastError());
-  CU(sirrt_sync(k->stream));
+  CU(sirrt_wait_flag(k->stream, flag, k->done_seq));
   const unsigned cnt = (unsigned)ph[0];
   *n_out = cnt;
   if (cnt == 0) return SIRRT_OK;

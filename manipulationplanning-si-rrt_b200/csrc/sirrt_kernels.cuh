@@ -580,6 +580,10 @@ struct RecheckParams {
   // and the ticket, so that a call needs neither a memset before nor a copy after its kernels
   unsigned int* ticket;
   unsigned int* publish;
+  // completion flag in the pinned host block: the last block writes done_seq behind everything the call produced, so the
+  // host can wait by polling its own memory instead of calling into the driver (sirrt_wait_flag)
+  unsigned int* done;
+  unsigned int done_seq;
   IvParams iv;              // latency path with a small table: iv.table != null -> the last block also turns the rows into intervals
 };
 
@@ -875,7 +879,7 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
   }
   if (P.ticket) {  // latency path: last block out (fuses the interval reduction,) publishes and clears the launch counters
     __shared__ bool last;
-    __threadfence();
+    if (P.done) __threadfence_system(); else __threadfence();  // results may live in the pinned host block
     __syncthreads();
     if (threadIdx.x == 0) last = atomicAdd(P.ticket, 1u) == gridDim.x - 1;
     __syncthreads();
@@ -883,12 +887,14 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
     __threadfence();
     if (P.iv.table) {
       for (long long n = threadIdx.x >> 5; n < P.iv.N; n += SIRRT_WARPS_PER_BLOCK) row_to_intervals(P.iv, n, lane);
+      if (P.done) __threadfence_system();
       __syncthreads();
     }
     if (threadIdx.x == 0) {
       volatile unsigned int* c = P.counters;
       for (int i = 0; i < 4; i++) { const unsigned int v = c[i]; if (P.publish) P.publish[i] = v; c[i] = 0u; }
       *P.ticket = 0u;
+      if (P.done) { __threadfence_system(); *(volatile unsigned int*)P.done = P.done_seq; }
     }
   }
 }

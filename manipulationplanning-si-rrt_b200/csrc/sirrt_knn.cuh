@@ -122,7 +122,7 @@ __device__ __forceinline__ double knn_dist2_wide(const KnnStore& S, const double
 
 __global__ void __launch_bounds__(SIRRT_KNN_THREADS)
 k_knn_nearest1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQuery query, double* pd, long long* pi, unsigned int* ticket,
-               long long* out_idx, double* out_d2) {
+               long long* out_idx, double* out_d2, unsigned int* done, unsigned int done_seq) {
   __shared__ double q[SIRRT_KNN_MAXDIM];
   __shared__ double sd[32];
   __shared__ long long si[32];
@@ -155,13 +155,16 @@ k_knn_nearest1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQu
     out_idx[0] = bi == 0x7fffffffffffffffll ? -1 : bi;
     out_d2[0] = best;
     *ticket = 0;  // ready for the next query on this stream
+    __threadfence_system();
+    *(volatile unsigned int*)done = done_seq;  // completion flag in the pinned block: the host polls its own memory
   }
 }
 
 // radius query, single launch: hits appended to hits[1..] with a warp-aggregated atomic on hits[0]; the last
 // block copies the count and the first `first` hits into the pinned block and clears the counter
 __global__ void __launch_bounds__(SIRRT_KNN_THREADS)
-k_knn_radius1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQuery query, double r2, int* hits, unsigned int* ticket, int* out, int first) {
+k_knn_radius1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQuery query, double r2, int* hits, unsigned int* ticket, int* out, int first,
+              unsigned int* done, unsigned int done_seq) {
   __shared__ double q[SIRRT_KNN_MAXDIM];
   __shared__ bool last;
   if (threadIdx.x < S.dim) q[threadIdx.x] = query.v[threadIdx.x];
@@ -188,8 +191,13 @@ k_knn_radius1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQue
   const unsigned cnt = *(volatile unsigned int*)count;
   const int ncopy = (int)min(cnt, (unsigned)first);
   for (int i = threadIdx.x; i < ncopy; i += blockDim.x) out[1 + i] = ((volatile int*)hits)[1 + i];
+  __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) { out[0] = (int)cnt; *count = 0; *ticket = 0; }
+  if (threadIdx.x == 0) {
+    out[0] = (int)cnt; *count = 0; *ticket = 0;
+    __threadfence_system();
+    *(volatile unsigned int*)done = done_seq;
+  }
 }
 
 // k nearest of each query in ascending (distance, index) order: one block per query, k selection

@@ -248,6 +248,23 @@ def plan_time_leg(seeds: int, max_time: float, device: int):
     return out
 
 
+def mass_test_leg(tasks: int, device_count: int):
+    """BASELINE.json config 5 in small: scripts/mass_test.py (host/sirrt_mass: one process per GPU, 16 planner threads each, a
+    shared task queue) on `tasks` synthetic planning tasks with a 5 s budget, next to the reference's execution model (one CPU
+    planner process per task, one worker per core) on a 16-task sample.  Condensed; the full record is the script's own JSON."""
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "mass_test.py"), "--gpus", str(device_count), "--tasks", str(tasks), "--threads", "16",
+                            "--sync", "yield", "--cpu-sample", "16", "--max-time", "5"], capture_output=True, text=True, timeout=600)
+        d = json.loads(r.stdout)
+    except Exception as e:  # the leg is a side figure: never fail the bench line over it
+        return {"unavailable": f"scripts/mass_test.py failed: {e}"}
+    ga, ca = d["gpu_arm"], d["cpu_arm"]
+    return {"metric": d["metric"], "tasks": d["tasks"], "max_time_s": d["max_time_s"], "recipe": d["recipe"],
+            "b200": {"gpus": d["n_gpus"], "threads_per_gpu": ga["threads_per_gpu"], "tasks_per_s": ga["tasks_per_s"], "solved": ga["solved"], "p50_solve_ms": ga["p50_solve_ms"]},
+            "cpu": {"workers": ca["workers"], "sample": ca["sample"], "tasks_per_s": ca["tasks_per_s"], "solved": ca["solved"], "p50_solve_ms": ca["p50_solve_ms"]},
+            "plan_equality_on_sample": d["plan_equality_on_sample"]}
+
+
 def knn_leg(pkg, device: int, hbm_gbs: float, fp32_tflops: float):
     """C-space nearest-neighbour throughput (MSIRRT/src/Tree.cpp:18-36, PlannerConnect.cpp:382-412): queries/s through
     the C ABI with device-resident queries and results (1-NN: tiled multi-query kernel; top-8: single-pass per-warp lists) and
@@ -343,6 +360,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-plan-time", action="store_true")
     ap.add_argument("--no-knn", action="store_true", help="skip the nearest-neighbour throughput leg (results.knn)")
+    ap.add_argument("--mass-tasks", type=int, default=96, help="planning tasks of the mass-test leg (results.mass_test); 0 = skip")
     ap.add_argument("--no-weak", action="store_true", help="N > 1: skip the weak-scaling side figure")
     ap.add_argument("--plan-seeds", type=int, default=3)
     ap.add_argument("--generic", action="store_true", help="force the generic kernel instead of the sweep kernel")
@@ -377,8 +395,14 @@ def main():
     dev = pkg.Scene(pack, local)
     if a.generic:
         dev.set_option(pkg.OPT_USE_SWEEP, 0)
-    stream = torch.cuda.current_stream()
+    # one explicit stream for everything of the step -- the sweep kernels (sirrt_scene_set_stream), the L2 flush, NCCL's
+    # dependency edges and the timing events.  torch's DEFAULT stream is handle 0, which sirrt_scene_set_stream reads as "use
+    # the scene's own stream": events on the default stream would then only see the kernels through the host's blocking
+    # wait, and under N > 1 (the all-gather keeps the stream busy past the host's return) they under-measured the step.
+    stream = torch.cuda.Stream(device=local)
+    torch.cuda.set_stream(stream)
     dev.set_stream(stream.cuda_stream)
+    assert stream.cuda_stream != 0
     q_loc = np.ascontiguousarray(q[:, n0:n1])
     q_dev = torch.from_numpy(q_loc).cuda()
     table_loc = torch.empty((n_loc, 1 + 2 * K), dtype=torch.int32, device="cuda")
@@ -401,6 +425,8 @@ def main():
     def timed(fn, steps):
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
         acc = {"kern_ms": 0.0, "launches": 0, "near": 0, "rechecked": 0, "exact": 0}
+        sync_all()
+        t_wall = time.perf_counter()
         for s0, s1 in ev:
             flush.fill_(1)  # evict L2 (126 MB) between timed steps; outside the event pair
             s0.record(stream)
@@ -409,11 +435,14 @@ def main():
             st = dev.last_stats()
             acc["kern_ms"] += st["sweep_kernel_ms"]; acc["launches"] += st["launches"]; acc["rechecked"] = st["rechecked"]; acc["exact"] = st["exact_tests"]
         sync_all()
-        total_ms = sum(s0.elapsed_time(s1) for s0, s1 in ev)
+        # host wall clock around the same loop (includes the L2 flushes between steps): cross-check of the event times
+        acc["wall_ms_per_step"] = 1e3 * (time.perf_counter() - t_wall) / max(1, steps)
+        acc["step_ms"] = [s0.elapsed_time(s1) for s0, s1 in ev]
+        total_ms = sum(acc["step_ms"])
         if world > 1:
-            t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
+            t = torch.tensor([total_ms, acc["wall_ms_per_step"]], dtype=torch.float64, device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            total_ms = float(t.item())
+            total_ms, acc["wall_ms_per_step"] = float(t[0].item()), float(t[1].item())
         return total_ms / max(1, steps), acc
 
     for _ in range(a.warmup):
@@ -533,6 +562,8 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(q_loc.nbytes) * world, "d2h_bytes_per_step": int(table_pin.numel() * 4) * world,
                     "ms_per_step": e2e_ms, "note": "whole-job bytes; every rank moves its own block" if world > 1 else None},
             "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
+            "timing_check": {"wall_ms_per_step_incl_l2_flush": acc["wall_ms_per_step"], "event_ms_per_step_rank0": acc["step_ms"],
+                             "note": "host wall clock around the timed loop (max over ranks), next to the CUDA-event times the value is computed from"},
             "results": {"colliding_cell_fraction": density, "near_contact_pair_tests_1e-6": int(acc["near"]), "fp64_rechecked_pair_tests": int(acc["rechecked"]),
                         "exact_pair_tests": int(acc["exact"])},
         }
@@ -546,6 +577,8 @@ def main():
             out["results"]["plan_time"] = plan_time_leg(a.plan_seeds, 5.0, local)
         if not a.no_knn and world == 1:
             out["results"]["knn"] = knn_leg(pkg, local, hbm_peak, roofline["peak"])
+        if a.mass_tasks > 0 and world == 1:
+            out["results"]["mass_test"] = mass_test_leg(a.mass_tasks, 1)
         if not a.no_cpu_baseline:
             threads = os.cpu_count() or 1
             v, n, dt = cpu_baseline(pack, q, a.cpu_budget, threads)

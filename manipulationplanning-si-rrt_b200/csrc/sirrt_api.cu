@@ -32,10 +32,29 @@ static int fail(int code, const char* fmt, const char* a = "") {
 // Every host wait of the library goes through here.  Default: cudaStreamSynchronize (spins: lowest latency when each
 // planner thread has a core).  SIRRT_SYNC=yield in the environment: poll the stream and give the core away between
 // polls -- for boxes that run more planner threads than cores (the mass test shares 32 cores between 8 GPUs' workers;
-// a planner thread spends most of its time waiting for its GPU).
+// a planner thread spends most of its time waiting for its GPU).  SIRRT_SYNC=block: cudaStreamSynchronize on a device
+// whose scheduling flag is cudaDeviceScheduleBlockingSync (set at the first scene / store creation): the thread sleeps
+// until the GPU's interrupt -- slower per call, but a waiting thread costs no core at all.
+static int sirrt_sync_mode() {
+  static const int mode = [] { const char* e = getenv("SIRRT_SYNC"); return !e ? 0 : !strcmp(e, "yield") ? 1 : !strcmp(e, "block") ? 2 : 0; }();
+  return mode;
+}
+static void sirrt_apply_sync_mode(int device) {
+  if (sirrt_sync_mode() != 2) return;
+  static std::mutex mu;
+  static bool done[64] = {false};
+  std::lock_guard<std::mutex> lk(mu);
+  if (device < 0 || device >= 64 || done[device]) return;
+  done[device] = true;
+  int cur = 0;
+  cudaGetDevice(&cur);
+  cudaSetDevice(device);
+  if (cudaSetDeviceFlags(cudaDeviceScheduleBlockingSync) != cudaSuccess) cudaGetLastError();  // best effort: plain synchronisation still works
+  cudaSetDevice(cur);
+}
 static cudaError_t sirrt_sync(cudaStream_t st) {
-  static const int mode = [] { const char* e = getenv("SIRRT_SYNC"); return (e && !strcmp(e, "yield")) ? 1 : 0; }();
-  if (!mode) return cudaStreamSynchronize(st);
+  const int mode = sirrt_sync_mode();
+  if (mode != 1) return cudaStreamSynchronize(st);
   for (;;) {
     const cudaError_t e = cudaStreamQuery(st);
     if (e != cudaErrorNotReady) return e;
@@ -49,7 +68,11 @@ static cudaError_t sirrt_sync(cudaStream_t st) {
 // wake-up does not pay cudaStreamSynchronize's hand-shake.  The stream is queried now and then only to surface a failed
 // launch (the flag would never arrive).
 static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int* flag, unsigned int seq) {
-  static const int mode = [] { const char* e = getenv("SIRRT_SYNC"); return (e && !strcmp(e, "yield")) ? 1 : 0; }();
+  const int mode = sirrt_sync_mode();
+  if (mode == 2) {  // sleeping wait: the stream's completion implies the flag
+    const cudaError_t e = cudaStreamSynchronize(st);
+    return e != cudaSuccess ? e : (*flag == seq ? cudaSuccess : cudaErrorUnknown);
+  }
   for (unsigned spin = 1;; spin++) {
     if (*flag == seq) return cudaSuccess;
     if ((spin & (mode ? 0xffu : 0xffffu)) == 0) {
@@ -158,6 +181,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   if (rc) { delete s; return fail(rc, "%s", err.c_str()); }
   s->device = device; s->parity_mode = parity_mode;
   auto bail = [&](int code) { sirrt_scene_destroy(s); return code; };
+  sirrt_apply_sync_mode(device);
   if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaSetDevice failed")); }
   cudaDeviceGetAttribute(&s->n_sm, cudaDevAttrMultiProcessorCount, device);
   if (cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaStreamCreate failed")); }

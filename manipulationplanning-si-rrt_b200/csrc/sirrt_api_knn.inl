@@ -28,6 +28,7 @@ extern "C" int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { cudaGetLastError(); return fail(SIRRT_E_CUDA, "no CUDA device (libsirrt_b200 has no CPU fallback)"); }
   if (device < 0 || device >= ndev) return fail(SIRRT_E_ARG, "device index out of range");
+  sirrt_apply_sync_mode(device);
   CU(cudaSetDevice(device));
   sirrt_knn* k = new (std::nothrow) sirrt_knn;
   if (!k) return fail(SIRRT_E_ARG, "out of memory");

@@ -41,7 +41,7 @@
 #define SWEEP_LMAX 7      // links the queue capacities are sized for (sweep_build rejects robots with more)
 #define SWEEP_Q1CAP 256   // 31 left over + 32 x SWEEP_LMAX pushed per A1 batch
 #define SWEEP_QWCAP 64    // 31 left over + 32 pushed per B1 batch
-#define SWEEP_Q2CAP 64    // 31 left over + 32 pushed per enumeration round of stage W
+#define SWEEP_Q2CAP 96    // 31 left over + 2 x 32 pushed per enumeration round of stage W
 #define SWEEP_Q3CAP 64    // 31 left over + 32 pushed per B2 batch
 #define SWEEP_ROWS 7      // per link: centre xyz, axis xyz (b - a), 1 / |axis|^2
 #define SWEEP_LDC (SWEEP_G + 1)  // row stride of the per-warp link table (odd: rows of one configuration fall into different banks)
@@ -375,7 +375,7 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
               }
             }
             const bool f3 = f2 && qwn == 0;
-            // the frames the model could not decide are enumerated into Q2, at most one per lane and round
+            // the frames the model could not decide are enumerated into Q2, at most two per lane and round
             for (;;) {
               const unsigned b = __ballot_sync(SIRRT_FULL, tm != 0u);
               if (b) {
@@ -385,6 +385,13 @@ k_sweep(const __grid_constant__ DRobot rb, const __grid_constant__ SweepParams P
                   q2[q2n + __popc(b & lt_mask)] = code | (fr << 8);
                 }
                 q2n += __popc(b);
+                const unsigned b2 = __ballot_sync(SIRRT_FULL, tm != 0u);
+                if (tm) {
+                  const unsigned fr = __ffs(tm) - 1;
+                  tm &= tm - 1;
+                  q2[q2n + __popc(b2 & lt_mask)] = code | (fr << 8);
+                }
+                q2n += __popc(b2);
               }
               const bool f4 = f3 && !b;
               if (q2n >= 32 || f4) do {

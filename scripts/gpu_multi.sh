@@ -10,9 +10,9 @@ tail -3 $OUT/${TAG}_multi_tests.log
 for n in 1 2 4 8; do
   if [ $n -gt $N ]; then break; fi
   if [ $n -eq 1 ]; then
-    timeout 600 python bench.py --gpus 1 --steps 5 --warmup 3 --no-plan-time --no-knn > $OUT/${TAG}_bench_1gpu.json 2> $OUT/${TAG}_bench_1gpu.err
+    timeout 600 python bench.py --gpus 1 --steps 5 --warmup 3 --cpu-budget 4 --no-plan-time --no-knn --mass-tasks 0 > $OUT/${TAG}_bench_1gpu.json 2> $OUT/${TAG}_bench_1gpu.err
   else
-    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + n)) bench.py --gpus $n --steps 5 --warmup 3 > $OUT/${TAG}_bench_${n}gpu.json 2> $OUT/${TAG}_bench_${n}gpu.err
+    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + n)) bench.py --gpus $n --steps 5 --warmup 3 --cpu-budget 4 > $OUT/${TAG}_bench_${n}gpu.json 2> $OUT/${TAG}_bench_${n}gpu.err
   fi
   echo "bench $n rc=$?"
   python - <<PY
@@ -25,7 +25,7 @@ except Exception as e:
 PY
 done
 if [ -n "$MASS" ]; then
-  timeout 1200 python scripts/mass_test.py --gpus $N --tasks 1024 --threads 16 --sync yield --cpu-sample 64 --also 16:yield,32:yield > $OUT/${TAG}_mass_test.json 2> $OUT/${TAG}_mass_test.err; echo "mass rc=$?"
+  timeout 1200 python scripts/mass_test.py --gpus $N --tasks 1024 --threads 16 --sync yield --cpu-sample 64 --also 32:yield,48:yield,32:block > $OUT/${TAG}_mass_test.json 2> $OUT/${TAG}_mass_test.err; echo "mass rc=$?"
   python - <<PY
 import json
 try:

@@ -16,7 +16,7 @@ except Exception as e:
     print("bench parse failed", e); print(open("$OUT/${TAG}_bench.err").read()[-2000:])
 PY
 python bench.py --print-source-hash > $OUT/${TAG}_src_hashes.json
-SMALL="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-plan-time --configs 131072"
+SMALL="python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-plan-time --no-knn --mass-tasks 0 --configs 131072"
 $SMALL > $OUT/${TAG}_small_plain.log 2>&1; echo "small plain rc=$?"
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/${TAG}_launches.csv $SMALL > $OUT/${TAG}_ncu_l.log 2>&1; echo "ncu launches rc=$?"
 timeout 600 ncu --set full --metrics smsp__sass_thread_inst_executed_op_fadd_pred_on.sum,smsp__sass_thread_inst_executed_op_fmul_pred_on.sum,smsp__sass_thread_inst_executed_op_ffma_pred_on.sum,smsp__sass_thread_inst_executed_op_dfma_pred_on.sum --clock-control none --import-source on -k regex:k_sweep -c 1 -o $OUT/${TAG}_ksweep -f $SMALL > $OUT/${TAG}_ncu_f.log 2>&1; echo "ncu full rc=$?"

@@ -220,7 +220,15 @@ static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, i
 //   copy-in: H2D of block k+1   ||   compute: sweep + FP64 re-check + intervals of block k   ||   copy-out: D2H of block k-1
 // so that only the first block's upload and the last block's download are exposed.  Results are those of the plain path
 // (same kernels, same per-block work lists); a block whose FP64 work list overflowed sends the call to the plain path.
+// Batches of one to two blocks (a rank's share of a 2^20 batch split over 8 GPUs) are cut in halves of at least
+// SIRRT_PIPE_MIN_CONFIGS (one full wave of k_sweep warps on 148 SMs) so that their copies overlap as well.
 #define SIRRT_PIPE_CONFIGS (128 << 10)
+#define SIRRT_PIPE_MIN_CONFIGS (64 << 10)
+static long long pipe_block_configs(const sirrt_scene* s, long long N) {
+  long long per = std::min<long long>(SIRRT_PIPE_CONFIGS, s->chunk_configs);
+  if (N < 2 * per) per = std::min(per, std::max<long long>(SIRRT_PIPE_MIN_CONFIGS, ((N + 1) / 2 + 1023) / 1024 * 1024));
+  return per;
+}
 static int bits_and_table_pipelined(sirrt_scene* s, const float* hq, long long N, int32_t* table, int Kmax, uint32_t* bits, uint64_t* near_contact_count,
                                     bool* fell_back, int16_t* table16 = nullptr) {
   *fell_back = false;
@@ -233,7 +241,7 @@ static int bits_and_table_pipelined(sirrt_scene* s, const float* hq, long long N
     CU(cudaStreamCreateWithFlags(&s->copy_in, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&s->copy_out, cudaStreamNonBlocking));
   }
-  const long long per = std::min<long long>(SIRRT_PIPE_CONFIGS, s->chunk_configs);
+  const long long per = pipe_block_configs(s, N);
   const size_t nb = (size_t)((N + per - 1) / per);
   while (s->pipe_ev.size() < 2 * nb) {
     cudaEvent_t e;
@@ -315,7 +323,7 @@ extern "C" int sirrt_safe_intervals_batch(sirrt_scene* s, const float* q_soa, in
   if (N > 0x7fffffffll) return fail(SIRRT_E_ARG, "N exceeds 2^31-1 configurations per call");
   CU(cudaSetDevice(s->device));
   int rc;
-  if (s->pipeline && N > SIRRT_PIPE_CONFIGS && !is_device_ptr(q_soa) && !(table && is_device_ptr(table)) && !(bits && is_device_ptr(bits))) {
+  if (s->pipeline && N >= 2 * SIRRT_PIPE_MIN_CONFIGS && !is_device_ptr(q_soa) && !(table && is_device_ptr(table)) && !(bits && is_device_ptr(bits))) {
     bool fell_back = false;  // host buffers, more than one block: copies overlap the kernels
     rc = bits_and_table_pipelined(s, q_soa, N, table, Kmax, bits, near_contact_count, &fell_back);
     if (rc || !fell_back) return rc;

@@ -124,5 +124,9 @@ def test_pipelined_host_path_equals_plain_path_and_compact_table(full, pkg):
     assert np.array_equal(t2, t0)
     t16, near16 = dev.safe_intervals_batch_i16(qs, KMAX)
     assert t16.dtype == np.int16 and np.array_equal(t16.astype(np.int32), t0) and abs(near16 - near1) <= max(16, near1 // 10)
+    # one to two blocks' worth (a rank's share of the batch on 8 GPUs): cut in two halves so that the copies still overlap
+    n2 = 140_001
+    t3, b3, _ = dev.safe_intervals_batch(np.ascontiguousarray(q[:, :n2]), KMAX)
+    assert np.array_equal(t3, table[:n2]) and np.array_equal(b3, bits[:n2])
     small16, _ = dev.safe_intervals_batch_i16(np.ascontiguousarray(q[:, :1000]), KMAX)   # a single block
     assert np.array_equal(small16.astype(np.int32), table[:1000])

@@ -271,10 +271,10 @@ def plan_time_leg(seeds: int, max_time: float, device: int):
 
 def mass_test_leg(tasks: int, device_count: int):
     """BASELINE.json config 5 in small: scripts/mass_test.py (host/sirrt_mass: one process per GPU, 16 planner threads each, a
-    shared task queue) on `tasks` synthetic planning tasks with a 5 s budget, next to the reference's execution model (one CPU
+    shared task queue) on `tasks` synthetic planning tasks (one start / goal pair x 6 planner seeds for each of the 16 cube counts) with a 5 s budget, next to the reference's execution model (one CPU
     planner process per task, one worker per core) on a 16-task sample.  Condensed; the full record is the script's own JSON."""
     try:
-        r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "mass_test.py"), "--gpus", str(device_count), "--tasks", str(tasks), "--threads", "16",
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "mass_test.py"), "--gpus", str(device_count), "--tasks", str(tasks), "--pairs-per-scene", "1", "--seeds-per-pair", "6", "--threads", "16",
                             "--sync", "yield", "--cpu-sample", "16", "--max-time", "5"], capture_output=True, text=True, timeout=600)
         d = json.loads(r.stdout)
     except Exception as e:  # the leg is a side figure: never fail the bench line over it

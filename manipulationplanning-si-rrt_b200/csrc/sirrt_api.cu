@@ -3,6 +3,8 @@
 // computes runs in the hand-written sm_100a kernels of sirrt_kernels.cuh / sirrt_sweep.cuh /
 // sirrt_knn.cuh; there is no CPU fallback: without a CUDA device every compute call fails.
 #include <sched.h>
+#include <sys/prctl.h>
+#include <time.h>
 #include <stdlib.h>
 #include <string.h>
 #include <stdio.h>
@@ -35,9 +37,26 @@ static int fail(int code, const char* fmt, const char* a = "") {
 // a planner thread spends most of its time waiting for its GPU).  SIRRT_SYNC=block: cudaStreamSynchronize on a device
 // whose scheduling flag is cudaDeviceScheduleBlockingSync (set at the first scene / store creation): the thread sleeps
 // until the GPU's interrupt -- slower per call, but a waiting thread costs no core at all.
+// SIRRT_SYNC=nap: like yield, but the thread first SLEEPS for half of what this kind of wait took recently (a running mean
+// kept by the caller's object) -- a planner thread that waits 66 us for its kernels then burns no core for the first 33 us,
+// and boxes with far more planner threads than cores (8 GPUs x 32 threads on 32 cores) keep their cores for the threads
+// that have launches to issue.  The timer slack of the thread is lowered to 1 us once (default 50 us would oversleep).
 static int sirrt_sync_mode() {
-  static const int mode = [] { const char* e = getenv("SIRRT_SYNC"); return !e ? 0 : !strcmp(e, "yield") ? 1 : !strcmp(e, "block") ? 2 : 0; }();
+  static const int mode = [] { const char* e = getenv("SIRRT_SYNC"); return !e ? 0 : !strcmp(e, "yield") ? 1 : !strcmp(e, "block") ? 2 : !strcmp(e, "nap") ? 3 : 0; }();
   return mode;
+}
+static inline double sirrt_now_us() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+}
+static inline void sirrt_nap(float mean_us) {
+  static thread_local bool slack_set = false;
+  if (!slack_set) { prctl(PR_SET_TIMERSLACK, 1000ul, 0ul, 0ul, 0ul); slack_set = true; }
+  const long ns = (long)(mean_us * 500.f);  // half of the recent mean
+  if (ns < 8000) return;                    // short waits (a kNN query): not worth a timer
+  timespec ts{0, ns > 2000000 ? 2000000 : ns};
+  nanosleep(&ts, nullptr);
 }
 static void sirrt_apply_sync_mode(int device) {
   if (sirrt_sync_mode() != 2) return;
@@ -54,10 +73,16 @@ static void sirrt_apply_sync_mode(int device) {
 }
 static cudaError_t sirrt_sync(cudaStream_t st) {
   const int mode = sirrt_sync_mode();
-  if (mode != 1) return cudaStreamSynchronize(st);
+  if (mode != 1 && mode != 3) return cudaStreamSynchronize(st);
+  static thread_local float mean_us = 0.f;  // nap mode: recent duration of this thread's stream waits
+  const double t0 = mode == 3 ? sirrt_now_us() : 0.0;
+  if (mode == 3) sirrt_nap(mean_us);
   for (;;) {
     const cudaError_t e = cudaStreamQuery(st);
-    if (e != cudaErrorNotReady) return e;
+    if (e != cudaErrorNotReady) {
+      if (mode == 3) mean_us += 0.25f * ((float)(sirrt_now_us() - t0) - mean_us);
+      return e;
+    }
     sched_yield();
   }
 }
@@ -67,8 +92,21 @@ static cudaError_t sirrt_sync(cudaStream_t st) {
 // its own memory -- no driver call, so 16 planner threads waiting on one GPU do not queue on the driver's lock, and the
 // wake-up does not pay cudaStreamSynchronize's hand-shake.  The stream is queried now and then only to surface a failed
 // launch (the flag would never arrive).
-static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int* flag, unsigned int seq) {
+static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int* flag, unsigned int seq, float* mean_us = nullptr) {
   const int mode = sirrt_sync_mode();
+  if (mode == 3 && mean_us) {  // sleep through the first half of the expected wait, then poll
+    const double t0 = sirrt_now_us();
+    sirrt_nap(*mean_us);
+    for (unsigned spin = 1;; spin++) {
+      if (*flag == seq) { *mean_us += 0.25f * ((float)(sirrt_now_us() - t0) - *mean_us); return cudaSuccess; }
+      if ((spin & 0xffu) == 0) {
+        const cudaError_t e = cudaStreamQuery(st);
+        if (e == cudaSuccess) return *flag == seq ? cudaSuccess : cudaErrorUnknown;
+        if (e != cudaErrorNotReady) return e;
+      }
+      sched_yield();
+    }
+  }
   if (mode == 2) {  // sleeping wait: the stream's completion implies the flag
     const cudaError_t e = cudaStreamSynchronize(st);
     return e != cudaSuccess ? e : (*flag == seq ? cudaSuccess : cudaErrorUnknown);
@@ -81,7 +119,7 @@ static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int*
       if (e != cudaErrorNotReady) return e;
     }
     if (mode) sched_yield();
-    else __builtin_ia32_pause();
+    else __builtin_ia32_pause();  // mode 3 without a mean falls through here as yield
   }
 }
 
@@ -143,6 +181,7 @@ struct sirrt_scene {
   bool lazy_pending = false;  // counters of the last run_bits launch are in flight to PIN_CNT
   unsigned int done_seq = 0;  // sequence number of the completion flag (PIN_FLAG) the pending call will write
   bool done_armed = false;    // the pending call ends with a flag write: wait with sirrt_wait_flag instead of a stream sync
+  float wait_mean_us = 0.f;   // SIRRT_SYNC=nap: running mean of this scene's flag waits
   std::vector<cudaEvent_t> ev;  // start/stop pairs around the sweep launches of one call
   uint64_t stats[5] = {0, 0, 0, 0, 0};
 };

@@ -19,7 +19,7 @@ static void arm_done(sirrt_scene* s, RecheckParams& R) {
 static cudaError_t scene_wait(sirrt_scene* s) {
   if (!s->done_armed) return sirrt_sync(s->stream);
   s->done_armed = false;
-  return sirrt_wait_flag(s->stream, (const volatile unsigned int*)(s->pinned + PIN_FLAG), s->done_seq);
+  return sirrt_wait_flag(s->stream, (const volatile unsigned int*)(s->pinned + PIN_FLAG), s->done_seq, &s->wait_mean_us);
 }
 
 // Collision bit rows of configurations [0, N) (global indexing into q / d_bits).  Work is cut into

@@ -18,6 +18,7 @@ struct sirrt_knn {
   unsigned int* ticket = nullptr;  // [0], [1]: last-block-done counters of the single-launch queries (zero between launches); [2]: largest |coordinate| (float bits)
   size_t hits_cap_zeroed = 0;      // capacity of `hits` whose counter word has been cleared
   unsigned int done_seq = 0;       // completion flag sequence (KPIN_FLAG), see sirrt_wait_flag
+  float wait_mean_us = 0.f;        // SIRRT_SYNC=nap: running mean of this store's flag waits
 };
 enum : size_t { KPIN_Q = 0, KPIN_Q_CAP = 16 << 10, KPIN_OUT = KPIN_Q_CAP, KPIN_OUT_CAP = 32 << 10, KPIN_RING = KPIN_OUT + KPIN_OUT_CAP,
                 KPIN_RING_SLOTS = 64, KPIN_FLAG = KPIN_RING + KPIN_RING_SLOTS * SIRRT_KNN_MAXDIM * sizeof(double), KPIN_BYTES = KPIN_FLAG + 64 };
@@ -194,7 +195,7 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
     unsigned int* flag = (unsigned int*)(k->pinned + KPIN_FLAG);
     k_knn_nearest1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S1, Q, k->part_d.as<double>(), k->part_i.as<long long>(), k->ticket, o_i, o_d, flag, ++k->done_seq);
     CU(cudaGetLastError());
-    CU(sirrt_wait_flag(k->stream, flag, k->done_seq));
+    CU(sirrt_wait_flag(k->stream, flag, k->done_seq, &k->wait_mean_us));
     idx[0] = o_i[0];
     if (dist2) dist2[0] = o_d[0];
     return SIRRT_OK;
@@ -246,7 +247,7 @@ extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, in
   unsigned int* flag = (unsigned int*)(k->pinned + KPIN_FLAG);
   k_knn_radius1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, Q, r2, k->hits.as<int>(), k->ticket + 1, ph, (int)first, flag, ++k->done_seq);
   CU(cudaGetLastError());
-  CU(sirrt_wait_flag(k->stream, flag, k->done_seq));
+  CU(sirrt_wait_flag(k->stream, flag, k->done_seq, &k->wait_mean_us));
   const unsigned cnt = (unsigned)ph[0];
   *n_out = cnt;
   if (cnt == 0) return SIRRT_OK;

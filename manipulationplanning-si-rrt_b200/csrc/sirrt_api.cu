@@ -170,7 +170,8 @@ struct sirrt_scene {
   int use_sweep = 1;
   long long sweep_min_configs = 8192;
   long long defer_max_configs = 4096;  // hull scenes: batches up to this size hand their GJK runs to k_gjk_tasks
-  DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2, xf;
+  DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2, xf, row1;
+  int slot_split = 1;  // planner-sized batches: dynamic slots of a row split over several warps (SIRRT_OPT_SLOT_SPLIT)
   // Latency path (planner in the loop): one pinned host block that the GPU reads and writes in place
   // (cudaMallocHost memory is device-addressable under UVA).  Small host inputs are memcpy'd into it and read
   // by the kernels over the bus; small results are written into it by the kernels and memcpy'd out after the
@@ -264,7 +265,7 @@ extern "C" void sirrt_scene_destroy(sirrt_scene* s) {
   cudaSetDevice(s->device);
   if (s->own_stream) { cudaStreamSynchronize(s->own_stream); }
   for (void* p : s->owned) cudaFree(p);
-  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->tasks, &s->counts, &s->misc, &s->misc2, &s->xf}) b->release();
+  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->tasks, &s->counts, &s->misc, &s->misc2, &s->xf, &s->row1}) b->release();
   if (s->pinned) cudaFreeHost(s->pinned);
   if (s->lazy_cnt) cudaFree(s->lazy_cnt);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
@@ -316,6 +317,7 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
     case SIRRT_OPT_SWEEP_MIN_CONFIGS: if (value < 1) return fail(SIRRT_E_ARG, "bad threshold"); s->sweep_min_configs = value; break;
     case SIRRT_OPT_DEFER_MAX_CONFIGS: if (value < 0) return fail(SIRRT_E_ARG, "bad threshold"); s->defer_max_configs = value; break;
     case SIRRT_OPT_PIPELINE: s->pipeline = value != 0; break;
+    case SIRRT_OPT_SLOT_SPLIT: s->slot_split = value != 0; break;
     case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
     default: return fail(SIRRT_E_ARG, "unknown option");
   }
@@ -326,6 +328,15 @@ extern "C" int sirrt_scene_last_stats(const sirrt_scene* s, uint64_t st[5]) {
   memcpy(st, s->stats, sizeof s->stats);
   return SIRRT_OK;
 }
+
+#ifdef SIRRT_GJK_STATS
+extern "C" int sirrt_debug_gjk_hist(unsigned int* out, int reset) {  // diagnostics build only (scripts/micro/gjk_hist.cpp)
+  if (cudaDeviceSynchronize() != cudaSuccess) return SIRRT_E_CUDA;
+  if (out && cudaMemcpyFromSymbol(out, g_gjk_hist, sizeof(unsigned int) * 4 * 64) != cudaSuccess) return SIRRT_E_CUDA;
+  if (reset) { static unsigned int z[4 * 64]; if (cudaMemcpyToSymbol(g_gjk_hist, z, sizeof z) != cudaSuccess) return SIRRT_E_CUDA; }
+  return SIRRT_OK;
+}
+#endif
 
 #include "sirrt_api_batch.inl"
 #include "sirrt_api_knn.inl"

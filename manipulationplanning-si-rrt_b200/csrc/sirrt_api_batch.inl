@@ -31,8 +31,11 @@ static cudaError_t scene_wait(sirrt_scene* s) {
 // fuse_table (latency path, at most 64 rows): k_recheck's last block also reduces the rows to intervals; *fused tells the
 // caller that no k_bits_to_intervals launch is needed.
 // row_tiles / win_tiles: every row only needs the win_tiles tiles starting at row_tiles[i].x (windowed edge tables).
+// bits_clean: the caller guarantees that the rows read zero (slot-split launches OR their words in; otherwise the rows are
+// cleared here first).  fuse_clear: the fused interval reduction leaves the rows zeroed again (internal row buffers).
 static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits, bool lazy = false, int32_t* fuse_table = nullptr,
-                    int fuse_kmax = 0, bool* fused = nullptr, const int2* row_tiles = nullptr, int win_tiles = 0) {
+                    int fuse_kmax = 0, bool* fused = nullptr, const int2* row_tiles = nullptr, int win_tiles = 0, bool bits_clean = false,
+                    bool fuse_clear = false) {
   if (fused) *fused = false;
   s->done_armed = false;
   const int W = s->tb.n_tiles;
@@ -76,7 +79,19 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         int n_chunks = (int)std::max(1ll, std::min((long long)Wr, target / std::max(1ll, qv.cnt)));
         P.tiles_per_chunk = (Wr + n_chunks - 1) / n_chunks;
         P.n_chunks = (Wr + P.tiles_per_chunk - 1) / P.tiles_per_chunk;
-        const int grid = grid_for(qv.cnt * P.n_chunks, s->n_sm, 8);
+        // planner-sized batches leave most of the machine idle with one warp per (row, tile): split the dynamic slots of each
+        // over several warps as well (>= 8 slots per warp), words OR-ed into zeroed rows
+        P.n_schunks = 1; P.slots_per_chunk = s->tb.n_dynamic;
+        const long long row_warps = qv.cnt * P.n_chunks;
+        if (s->slot_split && s->tb.n_dynamic >= 16 && row_warps * 2 <= target) {
+          const int want = (int)std::min<long long>((s->tb.n_dynamic + 7) / 8, target / row_warps);
+          if (want > 1) {
+            P.slots_per_chunk = (s->tb.n_dynamic + want - 1) / want;
+            P.n_schunks = (s->tb.n_dynamic + P.slots_per_chunk - 1) / P.slots_per_chunk;
+          }
+        }
+        if (P.n_schunks > 1 && !bits_clean) CU(cudaMemsetAsync(d_bits + (size_t)qv.n0 * W, 0, (size_t)qv.cnt * W * sizeof(uint32_t), st));
+        const int grid = grid_for(row_warps * P.n_schunks, s->n_sm, 8);
         if (s->tb.has_hull) k_collide_bits<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         else k_collide_bits<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         launches++;
@@ -95,6 +110,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       if (self_clearing) { R.ticket = s->lazy_cnt + 4; R.publish = (unsigned int*)(s->pinned + PIN_CNT); }
       if (self_clearing && fuse_table && N <= 64) {
         R.iv = IvParams{d_bits, N, W, s->tb.T, fuse_kmax, fuse_table};
+        R.iv.clear_rows = fuse_clear ? 1 : 0;
         if (fused) *fused = true;
         arm_done(s, R);  // the table is the pinned host block and nothing follows this kernel: the caller waits on the flag (scene_wait)
       }
@@ -185,7 +201,7 @@ static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, i
   for (int attempt = 0; attempt < 2; attempt++) {
     const bool lazy = small && attempt == 0;
     if (row_tiles) CU(cudaMemsetAsync(d_bits, 0, bbytes, s->stream));  // defined content outside the rows' windows (callers only look inside)
-    int rc = run_bits(s, q, N, semantics, d_bits, lazy, nullptr, 0, nullptr, row_tiles, win_tiles);
+    int rc = run_bits(s, q, N, semantics, d_bits, lazy, nullptr, 0, nullptr, row_tiles, win_tiles, row_tiles != nullptr);
     if (rc) return rc;
     int32_t* t_host = nullptr;
     uint32_t* b_host = nullptr;
@@ -398,8 +414,9 @@ extern "C" int sirrt_collision_bits_window_f64(sirrt_scene* s, const double* q_a
 // ---- a4: independent (configuration, frame) cells ------------------------------------------------
 // flag_when_done: the results land in the pinned host block and nothing follows the last k_recheck, which then writes the
 // completion flag (the caller waits with scene_wait)
+// out_zeroed: d_out reads zero (planner-sized batches then split the pairs of a cell over several warps that only write hits)
 static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_frames, uint8_t* d_out, int semantics, int frame_one = 0,
-                     bool flag_when_done = false) {
+                     bool flag_when_done = false, bool out_zeroed = false) {
   cudaStream_t st = s->stream;
   s->done_armed = false;
   if (s->work.ensure((size_t)s->wl_cap * sizeof(WorkItem))) return fail(SIRRT_E_CUDA, "cudaMalloc(work list) failed");
@@ -424,7 +441,16 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
         P.xf = s->xf.as<double>();
       }
     }
-    const int grid = grid_for(qv.cnt, s->n_sm, 8);
+    P.n_pchunks = 1; P.pairs_per_chunk = 0;
+    const long long target = (long long)s->n_sm * 32;
+    const int rounds = (s->tb.robot.n_links * s->tb.n_slots + 31) / 32;
+    if (out_zeroed && s->slot_split && rounds >= 2 && qv.cnt * 2 <= target) {
+      const int want = (int)std::min<long long>(rounds, target / qv.cnt);
+      const int rpc = (rounds + want - 1) / want;  // 32-pair rounds per warp
+      P.pairs_per_chunk = 32 * rpc;
+      P.n_pchunks = (rounds + rpc - 1) / rpc;
+    }
+    const int grid = grid_for(qv.cnt * P.n_pchunks, s->n_sm, 8);
     if (s->tb.has_hull) k_check_cells<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
     else k_check_cells<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
     if (defer) {
@@ -465,7 +491,8 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
     QView q1{nullptr, nullptr, 1, 0, 1, s->hs.dof, 1, {}};
     for (int j = 0; j < s->hs.dof; j++) q1.inl[j] = q_aos[j];
     uint8_t* d_out1 = (uint8_t*)(s->pinned + PIN_OUT);
-    if ((rc = run_cells(s, q1, 1, nullptr, d_out1, SIRRT_SEM_FRAME, frames[0], true))) return rc;
+    d_out1[0] = 0;
+    if ((rc = run_cells(s, q1, 1, nullptr, d_out1, SIRRT_SEM_FRAME, frames[0], true, true))) return rc;
     CU(scene_wait(s));
     collided[0] = d_out1[0];
     return SIRRT_OK;
@@ -477,13 +504,13 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   const bool odev = is_device_ptr(collided);
   const bool opin = !odev && (size_t)N <= (size_t)(16 << 10);  // latency path: the kernels write the pinned block in place
   uint8_t* d_out = collided;
-  if (opin) d_out = (uint8_t*)(s->pinned + PIN_OUT);
+  if (opin) { d_out = (uint8_t*)(s->pinned + PIN_OUT); memset(d_out, 0, (size_t)N); }
   else if (!odev) {
     if (s->cells.ensure((size_t)N)) return fail(SIRRT_E_CUDA, "cudaMalloc(cells) failed");
     d_out = s->cells.as<uint8_t>();
   }
   QView q{q_soa ? (const float*)dq : nullptr, q_soa ? nullptr : (const double*)dq, N, 0, N, s->hs.dof};
-  if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME, 0, opin))) return rc;
+  if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME, 0, opin, opin))) return rc;
   if (!odev && !opin) CU(cudaMemcpyAsync(collided, d_out, (size_t)N, cudaMemcpyDeviceToHost, s->stream));
   CU(scene_wait(s));
   if (opin) memcpy(collided, d_out, (size_t)N);
@@ -511,20 +538,28 @@ extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo
     lo_hi[0] = 0; lo_hi[1] = T - 1;
     return SIRRT_OK;
   }
-  if (s->misc.ensure((size_t)W * 4 + 64)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  // the row of this call lives in an internal buffer that reads zero between calls (slot-split launches OR into it; the
+  // fused interval reduction clears it again)
+  if (!s->row1.p) {
+    if (s->row1.ensure((size_t)W * 4 + 64)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+    CU(cudaMemsetAsync(s->row1.p, 0, (size_t)W * 4 + 64, s->stream));
+  }
   // latency path: q is read from, and the interval table written to, the pinned block in place; one synchronisation
   double* dq = (double*)(s->pinned + PIN_Q);
   if (is_device_ptr(q)) { CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyDeviceToHost, s->stream)); CU(sirrt_sync(s->stream)); }
   else memcpy(dq, q, sizeof(double) * dof);
-  uint32_t* d_bits = s->misc.as<uint32_t>();
+  uint32_t* d_bits = s->row1.as<uint32_t>();
   const int32_t* host_table = (const int32_t*)(s->pinned + PIN_OUT);
   QView qv{nullptr, dq, 1, 0, 1, dof, 0, {}};
   if (dof <= SIRRT_MAXJ) { qv.inl_on = 1; for (int j = 0; j < dof; j++) qv.inl[j] = dq[j]; }  // angles travel in the kernel parameters
   for (int attempt = 0; attempt < 2; attempt++) {
     bool fused = false;
-    int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits, attempt == 0, (int32_t*)host_table, Kmax, &fused);
+    int rc = run_bits(s, qv, 1, SIRRT_SEM_INTERVAL, d_bits, attempt == 0, (int32_t*)host_table, Kmax, &fused, nullptr, 0, true, true);
     if (rc) return rc;
-    if (!fused && (rc = run_intervals(s, d_bits, 1, (int32_t*)host_table, Kmax))) return rc;
+    if (!fused) {
+      if ((rc = run_intervals(s, d_bits, 1, (int32_t*)host_table, Kmax))) return rc;
+      CU(cudaMemsetAsync(d_bits, 0, (size_t)W * 4, s->stream));
+    }
     CU(scene_wait(s));
     if (attempt == 0 && finish_lazy(s)) continue;
     break;

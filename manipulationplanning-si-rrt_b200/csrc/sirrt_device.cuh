@@ -178,6 +178,38 @@ __device__ inline void fk_links(const DRobot& rb, const double* q, LinkXfD* out)
   }
 }
 
+// Warp form of the same chain for the latency kernels (one warp per configuration): lane j evaluates sincos of joint j,
+// so the n_joints dependent sincos expansions of fk_links collapse into one, and lane l keeps only the transform of link l
+// (no per-thread array of every link in local memory).  Same operations in the same order per link: bit-identical to
+// fk_links.  my_q = angle of joint `lane` (0 for lanes without a joint); every lane of the warp must call.
+__device__ inline void fk_link_of_lane(const DRobot& rb, double my_q, int lane, LinkXfD& mine) {
+  double my_sn, my_cs;
+  sincos(my_q, &my_sn, &my_cs);
+  double t[3] = {rb.base_t[0], rb.base_t[1], rb.base_t[2]}, R[9];
+#pragma unroll
+  for (int i = 0; i < 9; i++) R[i] = rb.base_R[i];
+  int l = 0;
+  for (int k = 0; k <= rb.n_joints; k++) {
+    while (l < rb.n_links && rb.link_jb[l] == k) {
+      if (l == lane) {
+        double w[3];
+        matvec(w, R, rb.lo_t[l]);  // :335
+        mine.t[0] = t[0] + w[0]; mine.t[1] = t[1] + w[1]; mine.t[2] = t[2] + w[2];  // :336
+        matmul3(mine.R, R, rb.lo_R[l]);  // :347
+      }
+      l++;
+    }
+    if (k == rb.n_joints) break;
+    double w[3];
+    matvec(w, R, rb.jt[k]);  // :319,361
+    t[0] += w[0]; t[1] += w[1]; t[2] += w[2];
+    matmul3(R, R, rb.jR[k]);  // :320,362
+    const double sn = __shfl_sync(SIRRT_FULL, my_sn, k), cs = __shfl_sync(SIRRT_FULL, my_cs, k);
+    double Rz[9] = {cs, -sn, 0, sn, cs, 0, 0, 0, (1.0 - cs) * 1.0 + cs};
+    matmul3(R, R, Rz);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // closed-form core distances (same formulas as the test-only CPU checker, written independently of
 // precision)
@@ -465,7 +497,8 @@ template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v,
 //         *dist_out gets the signed distance (core distance - rsum).
 template <typename T, bool FINAL>
 __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* Rrel, const T* trel, T rsum, T band,
-                               int lane, T* dist_out, int* enc_ids = nullptr, Simplex<T>* final_simplex = nullptr, T* final_v = nullptr) {
+                               int lane, T* dist_out, int* enc_ids = nullptr, Simplex<T>* final_simplex = nullptr, T* final_v = nullptr,
+                               int* n_iter = nullptr) {
   // enc_ids (FP32 pass only): when the answer is AMBIGUOUS because the enclosing tetrahedron is too thin to trust in
   // FP32, the four support-point ids -- the caller can certify the enclosure in FP64 from them (gjk_point / tetra_encloses)
   if (enc_ids) enc_ids[0] = -1;
@@ -491,6 +524,7 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
   T vv = dot3(v, v);
   const int MAXIT = FINAL ? 256 : 48;
   for (int it = 0; it < MAXIT; it++) {
+    if (n_iter) *n_iter = it + 1;  // diagnostics builds only (SIRRT_GJK_STATS)
     if (vv <= (FINAL ? T(1e-30) : T(1e-20))) {  // cores touch / intersect at a vertex
       if (dist_out) *dist_out = -rsum;
       if (FINAL) return RES_HIT;

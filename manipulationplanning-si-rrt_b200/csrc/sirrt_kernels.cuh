@@ -54,18 +54,18 @@ struct WarpCtx {   // per-warp shared memory: the planned robot's links in world
   unsigned long long q[SIRRT_QCAP];                          // cooperative (hull) task queue
 };
 
-// FK in FP64, then narrow to the FP32 world-space link table.  Executed redundantly by all lanes.
+// FK in FP64 (warp form: lane j takes the sincos of joint j, lane l ends up with link l), then lane l narrows link l to
+// the FP32 world-space link table.
 __device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QView& qv, long long n, WarpCtx& W, int lane, double* xf_out = nullptr) {
-  double q[SIRRT_MAXJ];
-  for (int j = 0; j < rb.n_joints; j++) q[j] = j < qv.dof ? load_q(qv, n, j) : 0.0;
-  LinkXfD X[SIRRT_MAXL];
-  fk_links(rb, q, X);
-  if (lane < rb.n_links) {  // every lane holds the whole chain: lane l narrows link l
+  const double my_q = (lane < rb.n_joints && lane < qv.dof) ? load_q(qv, n, lane) : 0.0;
+  LinkXfD X;
+  fk_link_of_lane(rb, my_q, lane, X);
+  if (lane < rb.n_links) {
     {
       const int l = lane;
       const DShape& sh = sc.shapes[rb.link_shape[l]];
-      const double* R = X[l].R;
-      const double* t = X[l].t;
+      const double* R = X.R;
+      const double* t = X.t;
       for (int k = 0; k < 9; k++) W.R[l][k] = (float)R[k];
       for (int k = 0; k < 3; k++) W.t[l][k] = (float)t[k];
       if (xf_out) {  // FP64 link transforms for the deferred GJK tasks of this configuration (k_gjk_tasks)
@@ -139,7 +139,7 @@ __device__ __forceinline__ void load_pose(const DScene& sc, int slot, int f, flo
 
 // warp-cooperative FP32 test of (link l, shape sh posed at slot/frame): anything involving a hull
 __device__ inline int coop_test(const DScene& sc, const float* RA, const float* tA, const DShape& lsh, const DShape& sh, int slot,
-                                int f, float band, int lane, int* enc_ids = nullptr) {
+                                int f, float band, int lane, int* enc_ids = nullptr, int* n_iter = nullptr) {
   float RB[9], tB[3];
   load_pose(sc, slot, f, RB, tB, true);
   GShape<float> A, B;
@@ -152,7 +152,7 @@ __device__ inline int coop_test(const DScene& sc, const float* RA, const float* 
   sub3(dt, tB, tA);
   matTvec(trel, RA, dt);
   float rsum = (lsh.type == SH_HULL ? 0.f : lsh.radius) + ((sh.type == SH_SPHERE || sh.type == SH_CAPSULE) ? sh.radius : 0.f);
-  return warp_gjk<float, false>(A, B, Rrel, trel, rsum, band, lane, (float*)nullptr, enc_ids);
+  return warp_gjk<float, false>(A, B, Rrel, trel, rsum, band, lane, (float*)nullptr, enc_ids, nullptr, nullptr, n_iter);
 }
 
 // Tight-AABB cull: a pair whose world AABBs are further apart than the FP32 uncertainty band on some axis cannot
@@ -195,6 +195,9 @@ struct BitsParams {
   int n_words;          // W
   int tiles_per_chunk;
   int n_chunks;
+  // small batches: the dynamic slots of a (configuration, tile chunk) are split over n_schunks warps of slots_per_chunk
+  // slots each (static slots go with slot chunk 0) and the words are OR-ed into rows the caller has zeroed
+  int n_schunks, slots_per_chunk;
   int semantics;
   float band;
 };
@@ -209,7 +212,8 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   WarpCtx& W = ctx[wib];
   const DScene& sc = P.sc;
-  const long long n_items = P.q.cnt * P.n_chunks;
+  const int n_sch = P.n_schunks > 1 ? P.n_schunks : 1;
+  const long long n_items = P.q.cnt * P.n_chunks * n_sch;
   const long long warp0 = (long long)blockIdx.x * SIRRT_WARPS_PER_BLOCK + wib;
   const long long n_warps = (long long)gridDim.x * SIRRT_WARPS_PER_BLOCK;
   const bool want_true_rob = (sc.parity_mode == 1) || (P.semantics == 0);
@@ -218,8 +222,10 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   unsigned int n_exact = 0;  // narrowphase pair tests evaluated by this lane (roofline accounting)
 
   for (long long item = warp0; item < n_items; item += n_warps) {
-    const long long n = P.q.n0 + item / P.n_chunks;
-    const int chunk = (int)(item % P.n_chunks);
+    const long long n = P.q.n0 + item / (P.n_chunks * n_sch);
+    const int sub = (int)(item % (P.n_chunks * n_sch));
+    const int chunk = sub / n_sch, sch = sub % n_sch;
+    const int j_lo = n_sch > 1 ? sch * P.slots_per_chunk : 0, j_hi = n_sch > 1 ? min(j_lo + P.slots_per_chunk, sc.n_dynamic) : sc.n_dynamic;
     int tile_lo = chunk * P.tiles_per_chunk, tile_end = sc.n_tiles;
     if (P.row_tiles) { const int2 rt = P.row_tiles[n - P.q.n0]; tile_lo += rt.x; tile_end = min(rt.y, sc.n_tiles); }
     const int tile_hi = min(tile_lo + P.tiles_per_chunk, tile_end);
@@ -303,7 +309,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
 
     // ---- static slots: one test per (link, slot), valid for every frame --------------------
     bool static_hit = false;
-    {
+    if (sch == 0) {
       const int n_pairs = L * sc.n_static;
       for (int p0 = 0; p0 < n_pairs; p0 += 32) {
         int p = p0 + lane;
@@ -334,10 +340,10 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
       const int fc = valid ? f : sc.T - 1;
       bool hit = false;
       if (!static_hit) {
-        for (int j0 = 0; j0 < sc.n_dynamic; j0 += 32) {
+        for (int j0 = j_lo; j0 < j_hi; j0 += 32) {
           const int j = j0 + lane;
           unsigned lm = 0;
-          if (j < sc.n_dynamic) {  // level 0: lanes = slots, swept tile bound vs link bounding spheres
+          if (j < j_hi) {  // level 0: lanes = slots, swept tile bound vs link bounding spheres
             const float4 tb = sc.tile_bounds[(size_t)tile * sc.n_dynamic + j];
             for (int l = 0; l < L; l++) {
               float dx = W.bc[l][0] - tb.x, dy = W.bc[l][1] - tb.y, dz = W.bc[l][2] - tb.z;
@@ -376,7 +382,10 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
       if ((tile & 31) == 31 || tile == tile_hi - 1) {  // flush up to 32 words, coalesced
         const int w0 = tile & ~31;
         const int w = w0 + lane;
-        if (w >= tile_lo && w <= tile) P.bits[(size_t)n * P.n_words + w] = my_word;
+        if (w >= tile_lo && w <= tile) {
+          if (n_sch > 1) { if (my_word) atomicOr(P.bits + (size_t)n * P.n_words + w, my_word); }  // rows zeroed by the caller
+          else P.bits[(size_t)n * P.n_words + w] = my_word;
+        }
         my_word = 0;
       }
     }
@@ -401,6 +410,9 @@ struct CellParams {
   uint8_t* out;           // [N]
   int semantics;
   float band;
+  // planner-sized batches: the (link, slot) pairs of a cell are split over n_pchunks warps of pairs_per_chunk pairs (a
+  // multiple of 32); a warp then only ever WRITES 1 (hit) into flags the caller has zeroed
+  int n_pchunks, pairs_per_chunk;
 };
 
 template <bool HAS_HULL>
@@ -415,17 +427,20 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
   const bool want_true_rob = (sc.parity_mode == 1) || (P.semantics == 0);
   const bool want_shift_rob = (sc.parity_mode == 0);
   const float band = P.band;
-  for (long long n = P.q.n0 + warp0; n < P.q.n0 + P.q.cnt; n += n_warps) {
+  const int n_pch = P.n_pchunks > 1 ? P.n_pchunks : 1;
+  for (long long item = warp0; item < P.q.cnt * n_pch; item += n_warps) {
+    const long long n = P.q.n0 + item / n_pch;
+    const int pch = (int)(item % n_pch);
     const int f = P.frames ? P.frames[n] : P.frame_one;
     if (f < 0 || f >= sc.T) {  // the reference indexes unchecked (CollisionManager.cpp:369); we answer "collided"
-      if (lane == 0) P.out[n] = 1;
+      if (lane == 0 && pch == 0) P.out[n] = 1;
       continue;
     }
     __syncwarp();
     setup_links(rb, sc, P.q, n, W, lane, P.xf);
-    const int L = rb.n_links, n_pairs = L * sc.n_slots;
+    const int L = rb.n_links, n_pairs = n_pch > 1 ? min(L * sc.n_slots, (pch + 1) * P.pairs_per_chunk) : L * sc.n_slots;
     bool hit = false;
-    for (int p0 = 0; p0 < n_pairs && !hit; p0 += 32) {
+    for (int p0 = n_pch > 1 ? pch * P.pairs_per_chunk : 0; p0 < n_pairs && !hit; p0 += 32) {
       const int p = p0 + lane;
       bool h = false;
       bool q_true = false, q_shift = false;
@@ -493,7 +508,7 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
         }
       }
     }
-    if (lane == 0) P.out[n] = hit ? 1 : 0;
+    if (lane == 0 && (hit || n_pch == 1)) P.out[n] = hit ? 1 : 0;
   }
 }
 
@@ -506,6 +521,7 @@ struct IvParams {
   int n_words, T, Kmax;
   int32_t* table;  // [N][1+2*Kmax]
   int16_t* table16 = nullptr;  // compact form of the same rows (frames < 32768); used instead of `table` when set
+  int clear_rows = 0;          // fused latency path: the rows are an internal buffer that must read zero again for the next call
 };
 
 __device__ __forceinline__ int warp_excl_scan(int v, int lane, int& total) {
@@ -889,6 +905,8 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
       for (long long n = threadIdx.x >> 5; n < P.iv.N; n += SIRRT_WARPS_PER_BLOCK) row_to_intervals(P.iv, n, lane);
       if (P.done) __threadfence_system();
       __syncthreads();
+      if (P.iv.clear_rows)
+        for (long long i = threadIdx.x; i < P.iv.N * P.iv.n_words; i += blockDim.x) ((uint32_t*)P.iv.bits)[i] = 0u;
     }
     if (threadIdx.x == 0) {
       volatile unsigned int* c = P.counters;
@@ -906,6 +924,10 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
 // few hundred GJK runs over all SMs instead of serialising them in the <= W warps that own the row.
 // Decisions are the same as in the producing warp: HIT sets the bit / cell, AMBIGUOUS goes to the FP64 list.
 // ------------------------------------------------------------------------------------------------
+#ifdef SIRRT_GJK_STATS
+// diagnostics build: FP32 GJK iterations per task, by verdict (0 FREE, 1 HIT, 2 AMBIGUOUS, 3 AMBIGUOUS with a thin enclosing tetrahedron)
+__device__ unsigned int g_gjk_hist[4][64];
+#endif
 struct GjkTaskParams {
   DScene sc;
   QView q;
@@ -950,7 +972,13 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
     const DSlot S = sc.slots[it.slot];
     const DShape& sh = sc.shapes[it.shifted ? S.shape_shift : S.shape];
     int enc_ids[4];
+#ifdef SIRRT_GJK_STATS
+    int n_iter = 0;
+    int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids, &n_iter);
+    if (lane == 0) atomicAdd(&g_gjk_hist[r == RES_AMBIG ? (enc_ids[0] >= 0 ? 3 : 2) : r][n_iter < 63 ? n_iter : 63], 1u);
+#else
     int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids);
+#endif
     if (r == RES_AMBIG) {
       // a thin enclosing tetrahedron is certified here in FP64 by the warp that found it (it holds the FP64 link
       // transform); anything else goes to the FP64 re-check list

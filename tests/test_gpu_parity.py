@@ -549,3 +549,46 @@ def test_windowed_edge_table_equals_full_rows(pkg, sp, packs, name):
             hi = min(W, lo + n_tiles)
             assert np.array_equal(win[i, lo:hi], full[i, lo:hi]), (name, n_tiles, i, lo, hi)
     assert full.any()
+
+
+@pytest.mark.parametrize("name,mode", [("flying_boxes", 0), ("mass_test", 0), ("synB_32_200", 0), ("synA_64_300", 0), ("multiple_robots", 0),
+                                       ("multiple_robots", 1), ("multiple_robots_cyl", 1)])
+def test_slot_split_equals_whole_rows(pkg, orc, sp, packs, name, mode):
+    """Planner-sized batches split the dynamic obstacles of a row (k_collide_bits) and the (link, slot) pairs of a cell
+    (k_check_cells) over several warps that OR their words / hit flags into zeroed outputs (SIRRT_OPT_SLOT_SPLIT).  Every latency
+    entry point must answer what the unsplit launch and the oracle answer -- including repeated single calls, whose internal
+    row buffer has to read zero again after each call."""
+    pk = packs(name)
+    a, b = pkg.Scene(pk, 0, mode), pkg.Scene(pk, 0, mode)
+    b.set_option(pkg.OPT_SLOT_SPLIT, 0)
+    ref = orc.Oracle(pk, mode)
+    q = random_q(sp, pk, 24, 91)
+    qd = q.T.astype(np.float64).copy()
+    for rep in range(2):  # the second round runs on the buffers the first one left behind
+        for qq in qd[:8]:
+            ia, ib = a.safe_intervals(qq), b.safe_intervals(qq)
+            assert ia == ib == ref.safe_intervals(qq), (name, rep)
+    for sem in (pkg.SEM_FRAME, pkg.SEM_INTERVAL):
+        fa, fb = a.collision_bits_f64(qd, sem), b.collision_bits_f64(qd, sem)
+        assert np.array_equal(fa, fb), (name, sem)
+    ta, ba, _ = a.safe_intervals_batch(q, 8)
+    tb, bb, _ = b.safe_intervals_batch(q, 8)
+    assert np.array_equal(ba, bb) and np.array_equal(ta, tb)
+    assert np.array_equal(ba, a.collision_bits_f64(qd, pkg.SEM_INTERVAL))
+    W = a.words
+    ft = ((np.arange(24) * 5) % max(W, 1)).astype(np.int32)
+    wa, wb = a.collision_bits_window_f64(qd, ft, 3, pkg.SEM_FRAME), b.collision_bits_window_f64(qd, ft, 3, pkg.SEM_FRAME)
+    full = b.collision_bits_f64(qd, pkg.SEM_FRAME)
+    for i in range(24):
+        lo, hi = int(ft[i]), min(W, int(ft[i]) + 3)
+        assert np.array_equal(wa[i, lo:hi], wb[i, lo:hi]) and np.array_equal(wa[i, lo:hi], full[i, lo:hi]), (name, i)
+    fr = ((np.arange(24, dtype=np.int64) * 131) % ref.n_frames).astype(np.int32)
+    fr[3], fr[7] = -1, ref.n_frames  # out-of-range frames answer "collided"
+    ca, cb = a.check_frames_batch_f64(qd, fr), b.check_frames_batch_f64(qd, fr)
+    assert np.array_equal(ca, cb)
+    want = [True if (f < 0 or f >= ref.n_frames) else bool(ref.check_frame(qq, int(f))) for qq, f in zip(qd, fr)]
+    assert [bool(x) for x in ca] == want
+    for rep in range(2):
+        for qq, f in zip(qd[:6], fr[:6]):
+            if 0 <= f < ref.n_frames:
+                assert a.check_frame(qq, int(f)) == b.check_frame(qq, int(f)) == bool(ref.check_frame(qq, int(f)))

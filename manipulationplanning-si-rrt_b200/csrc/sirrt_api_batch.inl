@@ -59,6 +59,20 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       qv.n0 = todo[i].n0; qv.cnt = todo[i].cnt;
       WorkList wl{s->work.as<WorkItem>(), self_clearing ? s->lazy_cnt : s->counts.as<unsigned>() + 4 * i, s->wl_cap};
       const bool timed = !(lazy && nr == 1) && i < s->ev.size() / 2;
+      RecheckParams R{};
+      R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
+      R.aabb_d = s->d_aabb_d; R.bits = d_bits; R.n_words = W; R.cells = nullptr; R.counters = wl.count;
+      if (self_clearing) {
+        R.ticket = s->lazy_cnt + 4; R.publish = (unsigned int*)(s->pinned + PIN_CNT);
+        R.fin = s->lazy_cnt + 7; R.fin_seq = ++s->fin_seq;
+      }
+      if (self_clearing && fuse_table && N <= 64) {
+        R.iv = IvParams{d_bits, N, W, s->tb.T, fuse_kmax, fuse_table};
+        R.iv.clear_rows = fuse_clear ? 1 : 0;
+        R.iv.no_fill = fuse_clear ? 1 : 0;  // sirrt_safe_intervals reads the first `count` pairs only
+        if (fused) *fused = true;
+        arm_done(s, R);  // the table is the pinned host block and nothing follows this kernel: the caller waits on the flag (scene_wait)
+      }
       if (timed) cudaEventRecord(s->ev[2 * i], st);
       if (sweep) {
         launches += sweep_launch(s->sweep, s->tb.robot, s->d, qv, wl, d_bits, W, (float)s->band, s->n_sm, st);
@@ -99,21 +113,14 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
           GjkTaskParams G{};
           G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl; G.xf = P.xf;
           G.bits = d_bits; G.n_words = W; G.cells = nullptr; G.band = (float)s->band;
+          if (self_clearing) {  // the task kernel's last block completes the call when nothing is left for the FP64 re-check
+            G.ticket = s->lazy_cnt + 6; G.publish = R.publish; G.done = R.done; G.done_seq = R.done_seq; G.fin = R.fin; G.fin_seq = R.fin_seq; G.iv = R.iv;
+          }
           k_gjk_tasks<<<s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, G);
           launches++;
         }
       }
       if (timed) cudaEventRecord(s->ev[2 * i + 1], st);
-      RecheckParams R{};
-      R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
-      R.aabb_d = s->d_aabb_d; R.bits = d_bits; R.n_words = W; R.cells = nullptr; R.counters = wl.count;
-      if (self_clearing) { R.ticket = s->lazy_cnt + 4; R.publish = (unsigned int*)(s->pinned + PIN_CNT); }
-      if (self_clearing && fuse_table && N <= 64) {
-        R.iv = IvParams{d_bits, N, W, s->tb.T, fuse_kmax, fuse_table};
-        R.iv.clear_rows = fuse_clear ? 1 : 0;
-        if (fused) *fused = true;
-        arm_done(s, R);  // the table is the pinned host block and nothing follows this kernel: the caller waits on the flag (scene_wait)
-      }
       // a handful of rows leaves a handful of ambiguous pair tests: a small grid shortens the last-block hand-over
       k_recheck<<<(self_clearing && N <= 64) ? 16 : s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
       launches++;
@@ -450,6 +457,11 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
       P.pairs_per_chunk = 32 * rpc;
       P.n_pchunks = (rounds + rpc - 1) / rpc;
     }
+    RecheckParams R{};
+    R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
+    R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
+    if (self_clearing) { R.ticket = s->lazy_cnt + 4; R.fin = s->lazy_cnt + 7; R.fin_seq = ++s->fin_seq; }
+    if (self_clearing && flag_when_done && n0 + per >= N) arm_done(s, R);
     const int grid = grid_for(qv.cnt * P.n_pchunks, s->n_sm, 8);
     if (s->tb.has_hull) k_check_cells<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
     else k_check_cells<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
@@ -457,14 +469,10 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
       GjkTaskParams G{};
       G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl; G.xf = P.xf;
       G.bits = nullptr; G.n_words = s->tb.n_tiles; G.cells = d_out; G.band = (float)s->band;
+      if (self_clearing) { G.ticket = s->lazy_cnt + 6; G.publish = R.publish; G.done = R.done; G.done_seq = R.done_seq; G.fin = R.fin; G.fin_seq = R.fin_seq; }
       k_gjk_tasks<<<s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, G);
       s->stats[0]++;
     }
-    RecheckParams R{};
-    R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
-    R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
-    if (self_clearing) R.ticket = s->lazy_cnt + 4;
-    if (self_clearing && flag_when_done && n0 + per >= N) arm_done(s, R);
     k_recheck<<<(self_clearing && qv.cnt <= 256) ? 16 : s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
     s->stats[0] += 2;
     CU(cudaGetLastError());

@@ -434,13 +434,24 @@ template <typename T> __device__ inline int closest_tri(const T* a, const T* b, 
 // A tetrahedron only counts as enclosing when it has real volume (coplanar support points are the
 // norm between polytopes); otherwise, and whenever the origin is outside, the answer is the best of
 // the four faces.  min_face (enclosing tetrahedron only) is a lower bound of the penetration depth.
-template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v, T& min_face) {
+// Warp form: all 32 lanes hold the same simplex and must call together; for a tetrahedron lane (lane & 3) evaluates
+// face (lane & 3) -- the side test and the closest point of ONE face instead of four per lane -- and the four answers
+// are combined exactly as the sequential loop over the faces would (smallest distance, lowest face on ties).
+template <typename T> __device__ __forceinline__ void simplex_pick(const Simplex<T>& s, int i, T* o) {
+#pragma unroll
+  for (int k = 0; k < 3; k++) o[k] = i == 0 ? s.w[0][k] : (i == 1 ? s.w[1][k] : (i == 2 ? s.w[2][k] : s.w[3][k]));
+}
+template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v, T& min_face, int lane) {
   if (s.n == 1) { v[0] = s.w[0][0]; v[1] = s.w[0][1]; v[2] = s.w[0][2]; return 0; }
   int keep = 0;
   if (s.n == 2) keep = closest_seg(s.w[0], s.w[1], v);
   else if (s.n == 3) keep = closest_tri(s.w[0], s.w[1], s.w[2], v);
   else {
-    const int F[4][4] = {{0, 1, 2, 3}, {0, 2, 3, 1}, {0, 3, 1, 2}, {1, 3, 2, 0}};
+    // faces F[f] = {0,1,2|3}, {0,2,3|1}, {0,3,1|2}, {1,3,2|0}: three vertices of the face, then the opposite one
+    const int f = lane & 3;
+    const int i0 = f == 3 ? 1 : 0, i1 = f == 0 ? 1 : (f == 1 ? 2 : 3), i2 = f == 0 ? 2 : (f == 1 ? 3 : (f == 2 ? 1 : 2)), i3 = f == 0 ? 3 : (f == 1 ? 1 : (f == 2 ? 2 : 0));
+    T a[3], b[3], c[3], d[3];
+    simplex_pick(s, i0, a); simplex_pick(s, i1, b); simplex_pick(s, i2, c); simplex_pick(s, i3, d);
     {
       const T *A = s.w[0], *B = s.w[1], *C = s.w[2], *D = s.w[3];
       T ab[3], ac[3], ad[3], bc[3], bd[3], cd[3], n[3];
@@ -454,31 +465,34 @@ template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v,
       e = dot3(bd, bd); l2 = e > l2 ? e : l2;
       e = dot3(cd, cd); l2 = e > l2 ? e : l2;
       if (tabs(vol6) > GjkEps<T>::tet() * l2 * tsqrt(l2)) {
-        bool inside = true;
-        T mf = T(3.0e38);
-        for (int f = 0; f < 4; f++) {
-          const T *a = s.w[F[f][0]], *b = s.w[F[f][1]], *c = s.w[F[f][2]], *d = s.w[F[f][3]];
-          T e1[3], e2[3], fn[3], ed[3];
-          sub3(e1, b, a); sub3(e2, c, a); cross3(fn, e1, e2); sub3(ed, d, a);
-          const T sp = -dot3(a, fn), sd = dot3(ed, fn);
-          if (!(sp * sd > T(0))) inside = false;  // origin strictly on d's side of every face
-          const T nn = dot3(fn, fn);
-          const T fd = nn > T(0) ? tabs(sp) / tsqrt(nn) : T(0);
-          mf = fd < mf ? fd : mf;
-        }
+        T e1[3], e2[3], fn[3], ed[3];
+        sub3(e1, b, a); sub3(e2, c, a); cross3(fn, e1, e2); sub3(ed, d, a);
+        const T sp = -dot3(a, fn), sd = dot3(ed, fn);
+        const bool inside = __all_sync(SIRRT_FULL, sp * sd > T(0));  // origin strictly on the opposite vertex's side of every face
+        const T nn = dot3(fn, fn);
+        T mf = nn > T(0) ? tabs(sp) / tsqrt(nn) : T(0);
+#pragma unroll
+        for (int o = 1; o < 4; o <<= 1) { const T of = __shfl_xor_sync(SIRRT_FULL, mf, o); mf = of < mf ? of : mf; }
         if (inside) { v[0] = v[1] = v[2] = T(0); min_face = mf; return 1; }
       }
     }
-    T best = T(3.0e38);
-    for (int f = 0; f < 4; f++) {
-      T q[3];
-      const int m = closest_tri(s.w[F[f][0]], s.w[F[f][1]], s.w[F[f][2]], q);
-      const T dd = dot3(q, q);
-      if (dd < best) {
-        best = dd; v[0] = q[0]; v[1] = q[1]; v[2] = q[2];
-        keep = 0;
-        for (int k = 0; k < 3; k++) if (m & (1 << k)) keep |= 1 << F[f][k];
-      }
+    T q[3];
+    int m = closest_tri(a, b, c, q);
+    const T dd = dot3(q, q);
+    T bd = dd < T(3.0e38) ? dd : T(3.0e38);
+    int bf = dd < T(3.0e38) ? f : 4;
+#pragma unroll
+    for (int o = 1; o < 4; o <<= 1) {
+      const T od = __shfl_xor_sync(SIRRT_FULL, bd, o);
+      const int of = __shfl_xor_sync(SIRRT_FULL, bf, o);
+      if (od < bd || (od == bd && of < bf)) { bd = od; bf = of; }
+    }
+    if (bf < 4) {
+      const int src = (lane & ~3) | bf;
+      v[0] = __shfl_sync(SIRRT_FULL, q[0], src); v[1] = __shfl_sync(SIRRT_FULL, q[1], src); v[2] = __shfl_sync(SIRRT_FULL, q[2], src);
+      m = __shfl_sync(SIRRT_FULL, m, src);
+      const int j0 = bf == 3 ? 1 : 0, j1 = bf == 0 ? 1 : (bf == 1 ? 2 : 3), j2 = bf == 0 ? 2 : (bf == 1 ? 3 : (bf == 2 ? 1 : 2));
+      keep = ((m & 1) ? 1 << j0 : 0) | ((m & 2) ? 1 << j1 : 0) | ((m & 4) ? 1 << j2 : 0);
     }
   }
   int j = 0;
@@ -547,7 +561,7 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
     if (done) break;
     s.w[s.n][0] = w[0]; s.w[s.n][1] = w[1]; s.w[s.n][2] = w[2]; s.id[s.n] = id; s.n++;
     T nvv[3];
-    if (simplex_closest(s, nvv, min_face)) {
+    if (simplex_closest(s, nvv, min_face, lane)) {
       if (dist_out) *dist_out = -rsum;
       if (FINAL) return RES_HIT;  // core distance 0 <= threshold + rsum
       if (rsum > band) return RES_HIT;

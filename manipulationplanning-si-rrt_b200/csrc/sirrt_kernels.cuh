@@ -521,6 +521,7 @@ struct IvParams {
   int n_words, T, Kmax;
   int32_t* table;  // [N][1+2*Kmax]
   int16_t* table16 = nullptr;  // compact form of the same rows (frames < 32768); used instead of `table` when set
+  int no_fill = 0;             // single-call path: the caller reads only the first `count` pairs, skip the -1 padding
   int clear_rows = 0;          // fused latency path: the rows are an internal buffer that must read zero again for the next call
 };
 
@@ -566,7 +567,8 @@ template <typename OutT> __device__ inline void row_to_intervals_t(const IvParam
     prev_safe = __shfl_sync(SIRRT_FULL, s >> 31, 31);
   }
   // unused pairs = -1; the count is the true number of intervals even when it exceeds Kmax
-  for (int k = 2 * min(n_starts, P.Kmax) + lane; k < 2 * P.Kmax; k += 32) out[1 + k] = (OutT)-1;
+  if (!P.no_fill)
+    for (int k = 2 * min(n_starts, P.Kmax) + lane; k < 2 * P.Kmax; k += 32) out[1 + k] = (OutT)-1;
   if (lane == 0) out[0] = (OutT)n_starts;
 }
 __device__ inline void row_to_intervals(const IvParams& P, long long n, int lane) {
@@ -601,7 +603,31 @@ struct RecheckParams {
   unsigned int* done;
   unsigned int done_seq;
   IvParams iv;              // latency path with a small table: iv.table != null -> the last block also turns the rows into intervals
+  // early completion: when the task kernel in front of this one found the FP64 list empty its last block has already done
+  // everything below (finish_call) and left fin_seq in *fin -- this kernel then returns at once
+  unsigned int* fin;
+  unsigned int fin_seq;
 };
+
+// End of a latency-path call, run by ONE block (all its threads) once every result of the call is visible to it: rows ->
+// intervals (fused table), launch counters published to the pinned block and cleared for the next call, completion flag.
+__device__ inline void finish_call(const IvParams& iv, unsigned int* counters, unsigned int* ticket, unsigned int* publish, unsigned int* done,
+                                   unsigned int done_seq, unsigned int* fin, unsigned int fin_seq) {
+  const int lane = threadIdx.x & 31;
+  if (iv.table) {
+    for (long long n = threadIdx.x >> 5; n < iv.N; n += SIRRT_WARPS_PER_BLOCK) row_to_intervals(iv, n, lane);
+    __syncthreads();  // thread 0's system fence below is cumulative over what the block wrote before this barrier
+    if (iv.clear_rows)
+      for (long long i = threadIdx.x; i < iv.N * iv.n_words; i += blockDim.x) ((uint32_t*)iv.bits)[i] = 0u;
+  }
+  if (threadIdx.x == 0) {
+    volatile unsigned int* c = counters;
+    for (int i = 0; i < 4; i++) { const unsigned int v = c[i]; if (publish) publish[i] = v; c[i] = 0u; }
+    if (ticket) *ticket = 0u;
+    if (fin) *fin = fin_seq;
+    if (done) { __threadfence_system(); *(volatile unsigned int*)done = done_seq; }
+  }
+}
 
 __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const LinkXfD& X, int l, const DShape& sh,
                                       const double* pose, int lane, int* res, const int* enc_ids = nullptr, bool* near = nullptr) {
@@ -831,7 +857,12 @@ __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
 k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckParams P) {
   const int lane = threadIdx.x & 31;
   const DScene& sc = P.sc;
+  if (P.fin && *(volatile unsigned int*)P.fin == P.fin_seq) return;  // the task kernel's last block has completed the call
   const unsigned int n_items = min(*P.count, P.cap);
+  if (P.ticket && n_items == 0) {  // nothing to re-check (the common planner call): one block completes the call at once
+    if (blockIdx.x == 0) finish_call(P.iv, P.counters, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
+    return;
+  }
   const unsigned int warp0 = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5), n_warps = gridDim.x * SIRRT_WARPS_PER_BLOCK;
   unsigned int n_near = 0;
   for (unsigned int base = warp0 * 32; base < n_items; base += n_warps * 32) {
@@ -895,25 +926,14 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
   }
   if (P.ticket) {  // latency path: last block out (fuses the interval reduction,) publishes and clears the launch counters
     __shared__ bool last;
-    if (P.done) __threadfence_system(); else __threadfence();  // results may live in the pinned host block
+    // this block's results: bits / counters in device memory; in cell mode on the latency path the flags are the pinned host block
+    if (P.done && P.cells) __threadfence_system(); else __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) last = atomicAdd(P.ticket, 1u) == gridDim.x - 1;
     __syncthreads();
     if (!last) return;
     __threadfence();
-    if (P.iv.table) {
-      for (long long n = threadIdx.x >> 5; n < P.iv.N; n += SIRRT_WARPS_PER_BLOCK) row_to_intervals(P.iv, n, lane);
-      if (P.done) __threadfence_system();
-      __syncthreads();
-      if (P.iv.clear_rows)
-        for (long long i = threadIdx.x; i < P.iv.N * P.iv.n_words; i += blockDim.x) ((uint32_t*)P.iv.bits)[i] = 0u;
-    }
-    if (threadIdx.x == 0) {
-      volatile unsigned int* c = P.counters;
-      for (int i = 0; i < 4; i++) { const unsigned int v = c[i]; if (P.publish) P.publish[i] = v; c[i] = 0u; }
-      *P.ticket = 0u;
-      if (P.done) { __threadfence_system(); *(volatile unsigned int*)P.done = P.done_seq; }
-    }
+    finish_call(P.iv, P.counters, P.ticket, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
   }
 }
 
@@ -940,6 +960,15 @@ struct GjkTaskParams {
   int n_words;
   uint8_t* cells;             // cell mode: [N]
   float band;
+  // latency path (ticket != null): when the FP64 re-check list is still empty after the last task, the last block out
+  // completes the call here (finish_call) and k_recheck, already queued behind this kernel, returns at once
+  unsigned int* ticket;       // this kernel's own ticket word
+  unsigned int* publish;
+  unsigned int* done;
+  unsigned int done_seq;
+  unsigned int* fin;
+  unsigned int fin_seq;
+  IvParams iv;
 };
 
 __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
@@ -947,6 +976,11 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
   const int lane = threadIdx.x & 31;
   const DScene& sc = P.sc;
   const unsigned int n_items = min(*P.count, P.cap);
+  if (P.ticket && n_items == 0) {  // no deferred pair test at all
+    if (blockIdx.x == 0 && *(volatile unsigned int*)P.wl.count == 0u)  // ... and nothing for the FP64 re-check either
+      finish_call(P.iv, P.wl.count, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
+    return;
+  }
   for (unsigned int w = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5); w < n_items; w += gridDim.x * SIRRT_WARPS_PER_BLOCK) {
     const WorkItem it = P.items[w];
     const int l = it.link, f = it.frame < 0 ? 0 : it.frame;
@@ -1002,6 +1036,17 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
         atomicOr(row + wd, m);
       }
     }
+  }
+  if (P.ticket) {
+    __shared__ bool last;
+    if (P.done && P.cells) __threadfence_system(); else __threadfence();  // cell flags of the latency path are the pinned host block
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(P.ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    if (threadIdx.x == 0) *P.ticket = 0u;
+    if (*(volatile unsigned int*)P.wl.count == 0u) finish_call(P.iv, P.wl.count, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
   }
 }
 

@@ -234,7 +234,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
 #define UP(field, vec) if ((rc = upload(s, vec, &field))) return bail(rc)
   UP(d.shapes, tb.shapes); UP(d.slots, tb.slots); UP(d.static_slots, tb.static_slots); UP(d.dynamic_slots, tb.dynamic_slots);
   UP(d.pose_f, tb.pose_f); UP(d.bcw_f, tb.bcw_f); UP(d.tight_f, tb.tight_f); UP(d.pose_d, tb.pose_d); UP(d.tile_bounds, tb.tile_bounds);
-  UP(d.verts_f, tb.verts_f); UP(d.verts_d, tb.verts_d); UP(d.hull_cells, tb.hull_cells); UP(d.hull_cand, tb.hull_cand); UP(s->d_aabb_f, tb.aabb_f); UP(s->d_aabb_d, tb.aabb_d);
+  UP(d.verts_f, tb.verts_f); UP(d.verts_d, tb.verts_d); UP(d.hull_cells, tb.hull_cells); UP(d.hull_cand, tb.hull_cand); UP(d.hull_rec, tb.hull_rec); UP(s->d_aabb_f, tb.aabb_f); UP(s->d_aabb_d, tb.aabb_d);
 #undef UP
   // FP32 uncertainty band: the fast path decides a pair only when |signed distance| exceeds it;
   // everything inside is re-evaluated in FP64 (k_recheck).  Scales with the coordinate magnitudes
@@ -335,6 +335,12 @@ extern "C" int sirrt_debug_gjk_hist(unsigned int* out, int reset) {  // diagnost
   if (cudaDeviceSynchronize() != cudaSuccess) return SIRRT_E_CUDA;
   if (out && cudaMemcpyFromSymbol(out, g_gjk_hist, sizeof(unsigned int) * 4 * 64) != cudaSuccess) return SIRRT_E_CUDA;
   if (reset) { static unsigned int z[4 * 64]; if (cudaMemcpyToSymbol(g_gjk_hist, z, sizeof z) != cudaSuccess) return SIRRT_E_CUDA; }
+  return SIRRT_OK;
+}
+extern "C" int sirrt_debug_phases(unsigned long long* out, int reset) {
+  if (cudaDeviceSynchronize() != cudaSuccess) return SIRRT_E_CUDA;
+  if (out && cudaMemcpyFromSymbol(out, g_phase, sizeof(unsigned long long) * 16) != cudaSuccess) return SIRRT_E_CUDA;
+  if (reset) { static unsigned long long z[16]; if (cudaMemcpyToSymbol(g_phase, z, sizeof z) != cudaSuccess) return SIRRT_E_CUDA; }
   return SIRRT_OK;
 }
 #endif

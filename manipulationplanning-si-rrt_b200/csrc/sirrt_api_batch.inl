@@ -94,18 +94,18 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         P.tiles_per_chunk = (Wr + n_chunks - 1) / n_chunks;
         P.n_chunks = (Wr + P.tiles_per_chunk - 1) / P.tiles_per_chunk;
         // planner-sized batches leave most of the machine idle with one warp per (row, tile): split the dynamic slots of each
-        // over several warps as well (>= 8 slots per warp), words OR-ed into zeroed rows
+        // over several warps as well (>= 4 slots per warp; the static slots of a row become one more item), words OR-ed into zeroed rows
         P.n_schunks = 1; P.slots_per_chunk = s->tb.n_dynamic;
         const long long row_warps = qv.cnt * P.n_chunks;
         if (s->slot_split && s->tb.n_dynamic >= 16 && row_warps * 2 <= target) {
-          const int want = (int)std::min<long long>((s->tb.n_dynamic + 7) / 8, target / row_warps);
+          const int want = (int)std::min<long long>((s->tb.n_dynamic + 3) / 4, target / row_warps);
           if (want > 1) {
             P.slots_per_chunk = (s->tb.n_dynamic + want - 1) / want;
             P.n_schunks = (s->tb.n_dynamic + P.slots_per_chunk - 1) / P.slots_per_chunk;
           }
         }
         if (P.n_schunks > 1 && !bits_clean) CU(cudaMemsetAsync(d_bits + (size_t)qv.n0 * W, 0, (size_t)qv.cnt * W * sizeof(uint32_t), st));
-        const int grid = grid_for(row_warps * P.n_schunks, s->n_sm, 8);
+        const int grid = grid_for(row_warps * P.n_schunks + ((P.n_schunks > 1 && s->tb.n_static > 0) ? qv.cnt : 0), s->n_sm, 8);
         if (s->tb.has_hull) k_collide_bits<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         else k_collide_bits<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         launches++;

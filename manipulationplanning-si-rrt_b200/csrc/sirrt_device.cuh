@@ -55,7 +55,8 @@ struct DSlot {
   int is_robot;     // robot-obstacle link
   int rot_identity; // every pose has R == I exactly (skip the rotation on the fast path)
   float br;         // bounding-sphere radius around bcw (covers the shifted geometry too)
-  int pad[2];
+  int type;         // shapes[shape].type / shapes[shape_shift].type (-1: none) -- saves the dependent load of the shape record
+  int type_shift;   // where only "is a hull involved?" has to be decided
 };
 
 struct DScene {
@@ -76,6 +77,7 @@ struct DScene {
   // each cube-map cell of directions every vertex that can be the support vertex for a direction of that cell
   const unsigned int* hull_cells;
   const unsigned short* hull_cand;  // vertex indices local to the hull, ascending within a cell
+  const float4* hull_rec;           // FP32 inline records parallel to hull_cells: SIRRT_HULL_REC x (x, y, z, index bits) per cell
 };
 
 // Cube-map cell of a (non-zero, finite) direction: dominant axis and sign pick the face, the two other components
@@ -84,6 +86,7 @@ struct DScene {
 #define SIRRT_HULL_K 16
 #define SIRRT_HULL_CELLS (6 * SIRRT_HULL_K * SIRRT_HULL_K)
 #define SIRRT_HULL_CELL_PAD 1e-3
+#define SIRRT_HULL_REC 16   // candidate slots per inline FP32 cell record (DScene::hull_rec)
 template <typename T> __host__ __device__ inline int hull_cell(const T* d) {
   const T ax = d[0] < T(0) ? -d[0] : d[0], ay = d[1] < T(0) ? -d[1] : d[1], az = d[2] < T(0) ? -d[2] : d[2];
   int a = 0;
@@ -178,35 +181,48 @@ __device__ inline void fk_links(const DRobot& rb, const double* q, LinkXfD* out)
   }
 }
 
-// Warp form of the same chain for the latency kernels (one warp per configuration): lane j evaluates sincos of joint j,
-// so the n_joints dependent sincos expansions of fk_links collapse into one, and lane l keeps only the transform of link l
-// (no per-thread array of every link in local memory).  Same operations in the same order per link: bit-identical to
-// fk_links.  my_q = angle of joint `lane` (0 for lanes without a joint); every lane of the warp must call.
+// Warp form of the same chain for the latency kernels (one warp per configuration).  FP64 instructions are the scarce
+// resource there (a warp-wide DFMA occupies the FP64 pipe for ~8 cycles on B200; measured: the per-lane chain cost a warp
+// ~7 000 cycles), so the 3x3 products are spread over the lanes: lane e < 9 holds element e of the running rotation R,
+// lane 9 + i element i of the running translation t, and every product costs each lane ONE row-times-column (3 multiply-
+// adds) instead of nine.  Lane j evaluates sincos of joint j, so the n_joints dependent sincos expansions collapse into one.
+// At the end lane l holds the transform of link l.  Same formulas per element as fk_links (out = A row . B column);
+// my_q = angle of joint `lane` (0 for lanes without a joint); every lane of the warp must call.
 __device__ inline void fk_link_of_lane(const DRobot& rb, double my_q, int lane, LinkXfD& mine) {
   double my_sn, my_cs;
   sincos(my_q, &my_sn, &my_cs);
-  double t[3] = {rb.base_t[0], rb.base_t[1], rb.base_t[2]}, R[9];
-#pragma unroll
-  for (int i = 0; i < 9; i++) R[i] = rb.base_R[i];
+  const int e = lane < 12 ? lane : 0;
+  const int row = e < 9 ? e / 3 : e - 9, col = e < 9 ? e - 3 * (e / 3) : 0;
+  const bool is_t = e >= 9;
+  double val = is_t ? rb.base_t[row] : rb.base_R[e];
   int l = 0;
   for (int k = 0; k <= rb.n_joints; k++) {
+    // row `row` of the running R, for the link emissions at this joint count and for the joint's own products
+    const double a0 = __shfl_sync(SIRRT_FULL, val, 3 * row), a1 = __shfl_sync(SIRRT_FULL, val, 3 * row + 1), a2 = __shfl_sync(SIRRT_FULL, val, 3 * row + 2);
     while (l < rb.n_links && rb.link_jb[l] == k) {
-      if (l == lane) {
-        double w[3];
-        matvec(w, R, rb.lo_t[l]);  // :335
-        mine.t[0] = t[0] + w[0]; mine.t[1] = t[1] + w[1]; mine.t[2] = t[2] + w[2];  // :336
-        matmul3(mine.R, R, rb.lo_R[l]);  // :347
-      }
+      // link l: t_l = t + R lo_t (:335-336), R_l = R lo_R (:347); element e lands in lane e, then everything moves to lane l
+      const double b0 = is_t ? rb.lo_t[l][0] : rb.lo_R[l][col], b1 = is_t ? rb.lo_t[l][1] : rb.lo_R[l][3 + col], b2 = is_t ? rb.lo_t[l][2] : rb.lo_R[l][6 + col];
+      const double p = a0 * b0 + a1 * b1 + a2 * b2;
+      const double o = is_t ? val + p : p;
+#pragma unroll
+      for (int x = 0; x < 9; x++) { const double v = __shfl_sync(SIRRT_FULL, o, x); if (lane == l) mine.R[x] = v; }
+#pragma unroll
+      for (int x = 0; x < 3; x++) { const double v = __shfl_sync(SIRRT_FULL, o, 9 + x); if (lane == l) mine.t[x] = v; }
       l++;
     }
     if (k == rb.n_joints) break;
-    double w[3];
-    matvec(w, R, rb.jt[k]);  // :319,361
-    t[0] += w[0]; t[1] += w[1]; t[2] += w[2];
-    matmul3(R, R, rb.jR[k]);  // :320,362
-    const double sn = __shfl_sync(SIRRT_FULL, my_sn, k), cs = __shfl_sync(SIRRT_FULL, my_cs, k);
-    double Rz[9] = {cs, -sn, 0, sn, cs, 0, 0, 0, (1.0 - cs) * 1.0 + cs};
-    matmul3(R, R, Rz);
+    {  // t += R jt (:319,361); R = R jR (:320,362)
+      const double b0 = is_t ? rb.jt[k][0] : rb.jR[k][col], b1 = is_t ? rb.jt[k][1] : rb.jR[k][3 + col], b2 = is_t ? rb.jt[k][2] : rb.jR[k][6 + col];
+      const double p = a0 * b0 + a1 * b1 + a2 * b2;
+      val = is_t ? val + p : p;
+    }
+    {  // R = R Rz(q_k), Rz = AngleAxisd(q_k, UnitZ) (:321,363): columns (cs, sn, 0), (-sn, cs, 0), (0, 0, (1 - cs) + cs)
+      const double sn = __shfl_sync(SIRRT_FULL, my_sn, k), cs = __shfl_sync(SIRRT_FULL, my_cs, k);
+      const double c0 = __shfl_sync(SIRRT_FULL, val, 3 * row), c1 = __shfl_sync(SIRRT_FULL, val, 3 * row + 1), c2 = __shfl_sync(SIRRT_FULL, val, 3 * row + 2);
+      const double b0 = col == 0 ? cs : (col == 1 ? -sn : 0.0), b1 = col == 0 ? sn : (col == 1 ? cs : 0.0), b2 = col == 2 ? (1.0 - cs) * 1.0 + cs : 0.0;
+      const double p = c0 * b0 + c1 * b1 + c2 * b2;
+      if (!is_t) val = p;
+    }
   }
 }
 
@@ -312,10 +328,38 @@ template <typename T> struct GShape {
   const T* verts;  // hull: xyz interleaved
   const unsigned int* cells;     // hull: support-candidate cell offsets (null: scan every vertex)
   const unsigned short* cand;
+  const float4* rec;             // hull, FP32 only: inline candidate records of the same cells (null: use cells / cand)
   int n;
   T half[3];       // box
   T half_len;      // capsule core
 };
+
+// FP32 hull support through the inline cell record: one load per lane (slot `lane` of the cell's record), the winner's
+// coordinates come back by shuffle -- no dependent loads.  Same winner as the candidate-list scan (largest dot product,
+// lowest vertex index on ties: slots hold the candidates in ascending index order).  Returns false when the cell overflows
+// its record (the caller scans the candidate list instead).
+__device__ __forceinline__ bool hull_rec_support(const GShape<double>&, int, const double*, double*, int, int*) { return false; }
+__device__ __forceinline__ bool hull_rec_support(const GShape<float>& s, int cell, const float* d, float* out, int lane, int* id) {
+  if (!s.rec) return false;
+  float4 r = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+  if (lane < SIRRT_HULL_REC) r = __ldg(s.rec + (size_t)cell * SIRRT_HULL_REC + lane);
+  const int i = __float_as_int(r.w);
+  if (__any_sync(SIRRT_FULL, i == -2)) return false;
+  float bv = -3.0e38f;
+  int bl = 32;
+  if (i >= 0) { bv = r.x * d[0] + r.y * d[1] + r.z * d[2]; bl = lane; }
+#pragma unroll
+  for (int o = SIRRT_HULL_REC / 2; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(SIRRT_FULL, bv, o);
+    const int ol = __shfl_xor_sync(SIRRT_FULL, bl, o);
+    if (ov > bv || (ov == bv && ol < bl)) { bv = ov; bl = ol; }
+  }
+  bl = __shfl_sync(SIRRT_FULL, bl, 0);  // lanes >= SIRRT_HULL_REC reduced among themselves: take the record lanes' answer
+  if (bl >= 32) return false;           // empty cell (cannot happen for a built table): full scan
+  out[0] = __shfl_sync(SIRRT_FULL, r.x, bl); out[1] = __shfl_sync(SIRRT_FULL, r.y, bl); out[2] = __shfl_sync(SIRRT_FULL, r.z, bl);
+  *id = __shfl_sync(SIRRT_FULL, i, bl);
+  return true;
+}
 
 template <typename T>
 __device__ inline int warp_support(const GShape<T>& s, const T* d, T* out, int lane) {
@@ -323,6 +367,7 @@ __device__ inline int warp_support(const GShape<T>& s, const T* d, T* out, int l
     T bv = T(-3.0e38);
     int bi = 0x7fffffff;
     const int cell = s.cells ? hull_cell(d) : -1;
+    if (cell >= 0 && hull_rec_support(s, cell, d, out, lane, &bi)) return bi;
     if (cell >= 0) {
       // every vertex that can win the full scan for a direction of this cell is listed (ascending index), so the
       // winner -- largest dot product, lowest index on ties -- is the one the full scan finds, bit for bit

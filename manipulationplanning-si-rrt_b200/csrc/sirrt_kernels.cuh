@@ -43,6 +43,19 @@ __device__ __forceinline__ void push_work(const WorkList& wl, int config, int fr
   }
 }
 
+#ifdef SIRRT_GJK_STATS
+// diagnostics build: FP32 GJK iterations per task, by verdict (0 FREE, 1 HIT, 2 AMBIGUOUS, 3 AMBIGUOUS with a thin enclosing tetrahedron)
+__device__ unsigned int g_gjk_hist[4][64];
+// cycles per phase, summed over warps: [0] k_collide_bits warps, [1] FK + link table, [2] static slots, [3] dynamic tiles,
+// [4] whole item; [8] k_gjk_tasks tasks, [9] task prologue (up to the GJK call), [10] GJK + verdict, [11] kernel entry to first task
+__device__ unsigned long long g_phase[16];
+#define PHASE_T(v) const long long v = clock64()
+#define PHASE_ADD(i, d) do { if (lane == 0) atomicAdd(&g_phase[i], (unsigned long long)(d)); } while (0)
+#else
+#define PHASE_T(v)
+#define PHASE_ADD(i, d)
+#endif
+
 struct WarpCtx {   // per-warp shared memory: the planned robot's links in world space (FP32)
   float a[SIRRT_MAXL][3], b[SIRRT_MAXL][3], r[SIRRT_MAXL];   // capsule core end points + radius
   float bc[SIRRT_MAXL][3], br[SIRRT_MAXL];                   // bounding sphere
@@ -147,6 +160,8 @@ __device__ inline int coop_test(const DScene& sc, const float* RA, const float* 
   A.half[0] = lsh.half[0]; A.half[1] = lsh.half[1]; A.half[2] = lsh.half[2];
   B.type = sh.type; B.verts = sc.verts_f + 3 * (size_t)sh.vert_off; B.n = sh.n_verts; B.cells = (sc.hull_cells && sh.cell_off >= 0) ? sc.hull_cells + sh.cell_off : nullptr; B.cand = sc.hull_cand; B.half_len = sh.half_len;
   B.half[0] = sh.half[0]; B.half[1] = sh.half[1]; B.half[2] = sh.half[2];
+  A.rec = (A.cells && sc.hull_rec) ? sc.hull_rec + (size_t)lsh.cell_off * SIRRT_HULL_REC : nullptr;
+  B.rec = (B.cells && sc.hull_rec) ? sc.hull_rec + (size_t)sh.cell_off * SIRRT_HULL_REC : nullptr;
   float Rrel[9], trel[3], dt[3];
   matTmul3(Rrel, RA, RB);
   sub3(dt, tB, tA);
@@ -213,7 +228,9 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   WarpCtx& W = ctx[wib];
   const DScene& sc = P.sc;
   const int n_sch = P.n_schunks > 1 ? P.n_schunks : 1;
-  const long long n_items = P.q.cnt * P.n_chunks * n_sch;
+  // split rows: the static slots of a row are one more item of their own (beside the (tile chunk, slot chunk) items)
+  const int per_row = P.n_chunks * n_sch + ((n_sch > 1 && sc.n_static > 0) ? 1 : 0);
+  const long long n_items = P.q.cnt * per_row;
   const long long warp0 = (long long)blockIdx.x * SIRRT_WARPS_PER_BLOCK + wib;
   const long long n_warps = (long long)gridDim.x * SIRRT_WARPS_PER_BLOCK;
   const bool want_true_rob = (sc.parity_mode == 1) || (P.semantics == 0);
@@ -222,27 +239,29 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   unsigned int n_exact = 0;  // narrowphase pair tests evaluated by this lane (roofline accounting)
 
   for (long long item = warp0; item < n_items; item += n_warps) {
-    const long long n = P.q.n0 + item / (P.n_chunks * n_sch);
-    const int sub = (int)(item % (P.n_chunks * n_sch));
-    const int chunk = sub / n_sch, sch = sub % n_sch;
+    const long long n = P.q.n0 + item / per_row;
+    const int sub = (int)(item % per_row);
+    const bool static_item = n_sch > 1 && sub == P.n_chunks * n_sch;
+    const int chunk = static_item ? 0 : sub / n_sch, sch = static_item ? 0 : sub % n_sch;
     const int j_lo = n_sch > 1 ? sch * P.slots_per_chunk : 0, j_hi = n_sch > 1 ? min(j_lo + P.slots_per_chunk, sc.n_dynamic) : sc.n_dynamic;
     int tile_lo = chunk * P.tiles_per_chunk, tile_end = sc.n_tiles;
     if (P.row_tiles) { const int2 rt = P.row_tiles[n - P.q.n0]; tile_lo += rt.x; tile_end = min(rt.y, sc.n_tiles); }
     const int tile_hi = min(tile_lo + P.tiles_per_chunk, tile_end);
-    if (P.row_tiles && tile_lo >= tile_hi) continue;  // this chunk lies past the row's window
+    if (P.row_tiles && tile_lo >= tile_hi && !static_item) continue;  // this chunk lies past the row's window
     __syncwarp();
+    PHASE_T(t_item);
     setup_links(rb, sc, P.q, n, W, lane, P.xf);
+    PHASE_T(t_fk);
+    PHASE_ADD(0, 1); PHASE_ADD(1, t_fk - t_item);
     const int L = rb.n_links;
 
     // evaluates one candidate for this lane; returns hit bit, pushes ambiguous work
-    auto eval_lane = [&](int l, int slot, int f, int frame_tag, bool pass) -> bool {
+    auto eval_lane = [&](int l, int slot, const DSlot& S, int f, int frame_tag, bool pass) -> bool {
       // pass: this lane's (link, slot, frame) survived its cull
-      const DSlot S = sc.slots[slot];
-      const DShape& lsh = sc.shapes[rb.link_shape[l]];
+      const int ltype = W.type[l];
       bool hit = false;
       float R[9], t[3];
-      const DShape& sh = sc.shapes[S.shape];
-      const bool coop_true = HAS_HULL && (lsh.type == SH_HULL || sh.type == SH_HULL);
+      const bool coop_true = HAS_HULL && (ltype == SH_HULL || S.type == SH_HULL);
       bool do_true = pass && (!S.is_robot || want_true_rob);
       bool do_shift = pass && S.is_robot && want_shift_rob && S.shape_shift >= 0;
       if (do_shift) {  // broadphase gate on the true geometries' AABBs
@@ -254,8 +273,8 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
         else if (g == RES_AMBIG) { push_work(P.wl, (int)n, frame_tag, l, slot, 1); do_shift = false; }
       }
       if (do_true && !coop_true) {
-        load_pose(sc, slot, f, R, t, sh.type != SH_SPHERE && !S.rot_identity);
-        int r = lane_exact(W, l, sh, R, t, S.rot_identity != 0, band);
+        load_pose(sc, slot, f, R, t, S.type != SH_SPHERE && !S.rot_identity);
+        int r = lane_exact(W, l, sc.shapes[S.shape], R, t, S.rot_identity != 0, band);
         n_exact++;
         if (r == RES_HIT) hit = true;
         else if (r == RES_AMBIG) push_work(P.wl, (int)n, frame_tag, l, slot, 0);
@@ -263,11 +282,10 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
       bool q_true = do_true && coop_true;
       bool coop_shift = false;
       if (do_shift) {
-        const DShape& ss = sc.shapes[S.shape_shift];
-        coop_shift = HAS_HULL && (lsh.type == SH_HULL || ss.type == SH_HULL);
+        coop_shift = HAS_HULL && (ltype == SH_HULL || S.type_shift == SH_HULL);
         if (!coop_shift) {
           load_pose(sc, slot, f, R, t, true);
-          int r = lane_exact(W, l, ss, R, t, false, band);
+          int r = lane_exact(W, l, sc.shapes[S.shape_shift], R, t, false, band);
           if (r == RES_HIT) hit = true;
           else if (r == RES_AMBIG) push_work(P.wl, (int)n, frame_tag, l, slot, 2);  // gate already passed
         }
@@ -309,20 +327,22 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
 
     // ---- static slots: one test per (link, slot), valid for every frame --------------------
     bool static_hit = false;
-    if (sch == 0) {
+    if (n_sch == 1 || static_item) {
       const int n_pairs = L * sc.n_static;
       for (int p0 = 0; p0 < n_pairs; p0 += 32) {
         int p = p0 + lane;
         bool pass = false;
         int l = 0, slot = 0;
+        DSlot S{};
         if (p < n_pairs) {
           l = p / sc.n_static; slot = sc.static_slots[p % sc.n_static];
+          S = sc.slots[slot];
           const float* c = sc.bcw_f + (size_t)slot * 3 * sc.Tp;
           float dx = W.bc[l][0] - c[0], dy = W.bc[l][1] - c[sc.Tp], dz = W.bc[l][2] - c[2 * (size_t)sc.Tp];
-          float rr = (W.br[l] + sc.slots[slot].br) * 1.000001f + 1e-5f + band;
+          float rr = (W.br[l] + S.br) * 1.000001f + 1e-5f + band;
           pass = dx * dx + dy * dy + dz * dz <= rr * rr && tight_overlap(sc, W, l, slot, 0, band);
         }
-        bool h = eval_lane(l, slot, 0, -1, pass);
+        bool h = eval_lane(l, slot, S, 0, -1, pass);
         bool lane_hit = false, any_hit = false;
         if (HAS_HULL && W.qn > SIRRT_QCAP - 64) drain(-1, lane_hit, any_hit);
         static_hit |= __any_sync(SIRRT_FULL, h) | any_hit;
@@ -330,6 +350,17 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
       bool lane_hit = false, any_hit = false;
       drain(-1, lane_hit, any_hit);
       static_hit |= any_hit;
+    }
+    PHASE_T(t_static);
+    PHASE_ADD(2, t_static - t_fk);
+    if (static_item) {  // split rows: a static hit colours every frame of the row (OR-ed like the dynamic words)
+      if (static_hit)
+        for (int w = lane; w < P.n_words; w += 32) {
+          uint32_t m = 0xffffffffu;
+          if (sc.T - w * 32 < 32) m = (1u << (sc.T - w * 32)) - 1u;
+          atomicOr(P.bits + (size_t)n * P.n_words + w, m);
+        }
+      continue;
     }
 
     // ---- dynamic slots, tile by tile ------------------------------------------------------
@@ -361,14 +392,22 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
             const float cx = c[0], cy = c[sc.Tp], cz = c[2 * (size_t)sc.Tp];
             const DSlot S = sc.slots[slot];
             const float sbr = S.br;
+            float tlo[3], thi[3];  // the slot's tight world AABB at this lane's frame (link-independent: loaded once per slot)
+            {
+              const float* tb = sc.tight_f + (size_t)slot * 6 * sc.Tp + fc;
+#pragma unroll
+              for (int k = 0; k < 3; k++) { tlo[k] = tb[(size_t)k * sc.Tp]; thi[k] = tb[(size_t)(3 + k) * sc.Tp]; }
+            }
             while (m) {
               const int l = __ffs(m) - 1;
               m &= m - 1;
               float dx = W.bc[l][0] - cx, dy = W.bc[l][1] - cy, dz = W.bc[l][2] - cz;
               float rr = (W.br[l] + sbr) * 1.000001f + 1e-5f + band;
-              bool pass = valid && (dx * dx + dy * dy + dz * dz <= rr * rr) && tight_overlap(sc, W, l, slot, fc, band);
+              bool pass = valid && (dx * dx + dy * dy + dz * dz <= rr * rr);
+#pragma unroll
+              for (int k = 0; k < 3; k++) pass &= (W.tlo[l][k] - band <= thi[k]) && (W.thi[l][k] + band >= tlo[k]);
               if (!__any_sync(SIRRT_FULL, pass)) continue;
-              hit |= eval_lane(l, slot, fc, fc, pass);
+              hit |= eval_lane(l, slot, S, fc, fc, pass);
               if (HAS_HULL && W.qn > SIRRT_QCAP - 64) { bool any = false; drain(tile * 32, hit, any); }
             }
           }
@@ -389,6 +428,8 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
         my_word = 0;
       }
     }
+    PHASE_T(t_end);
+    PHASE_ADD(3, t_end - t_static); PHASE_ADD(4, t_end - t_item);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) n_exact += __shfl_xor_sync(SIRRT_FULL, n_exact, o);
@@ -944,10 +985,6 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
 // few hundred GJK runs over all SMs instead of serialising them in the <= W warps that own the row.
 // Decisions are the same as in the producing warp: HIT sets the bit / cell, AMBIGUOUS goes to the FP64 list.
 // ------------------------------------------------------------------------------------------------
-#ifdef SIRRT_GJK_STATS
-// diagnostics build: FP32 GJK iterations per task, by verdict (0 FREE, 1 HIT, 2 AMBIGUOUS, 3 AMBIGUOUS with a thin enclosing tetrahedron)
-__device__ unsigned int g_gjk_hist[4][64];
-#endif
 struct GjkTaskParams {
   DScene sc;
   QView q;
@@ -982,6 +1019,7 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
     return;
   }
   for (unsigned int w = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5); w < n_items; w += gridDim.x * SIRRT_WARPS_PER_BLOCK) {
+    PHASE_T(t_task);
     const WorkItem it = P.items[w];
     const int l = it.link, f = it.frame < 0 ? 0 : it.frame;
     LinkXfD Xl;
@@ -1008,8 +1046,11 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
     int enc_ids[4];
 #ifdef SIRRT_GJK_STATS
     int n_iter = 0;
+    PHASE_T(t_pro);
     int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids, &n_iter);
     if (lane == 0) atomicAdd(&g_gjk_hist[r == RES_AMBIG ? (enc_ids[0] >= 0 ? 3 : 2) : r][n_iter < 63 ? n_iter : 63], 1u);
+    PHASE_T(t_gjk);
+    PHASE_ADD(8, 1); PHASE_ADD(9, t_pro - t_task); PHASE_ADD(10, t_gjk - t_pro); PHASE_ADD(12, n_iter);
 #else
     int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids);
 #endif

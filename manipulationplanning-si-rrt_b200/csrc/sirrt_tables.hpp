@@ -17,6 +17,10 @@ struct HostTables {
   std::vector<float4> tile_bounds;
   std::vector<unsigned int> hull_cells;     // per hull SIRRT_HULL_CELLS + 1 offsets into hull_cand
   std::vector<unsigned short> hull_cand;
+  // FP32 inline form of the same cells: SIRRT_HULL_REC float4 (x, y, z, vertex index as int bits; -1 = empty slot) per entry
+  // of hull_cells, so that a support query is ONE load per lane instead of the chain offsets -> candidate list -> vertices;
+  // a cell with more candidates than slots carries -2 in its last slot and is scanned through hull_cand
+  std::vector<float4> hull_rec;
   double extent = 0;  // largest |coordinate| the FP32 path can meet near the arm (band scaling)
 };
 
@@ -265,6 +269,11 @@ inline int build_tables(const HScene& sc, int parity_mode, HostTables& tb, std::
     }
   }
 
+  for (int s = 0; s < n_slots; s++) {
+    DSlot& S = tb.slots[s];
+    S.type = tb.shapes[S.shape].type;
+    S.type_shift = S.shape_shift >= 0 ? tb.shapes[S.shape_shift].type : -1;
+  }
   for (int s = 0; s < n_slots; s++) (tb.slots[s].is_static ? tb.static_slots : tb.dynamic_slots).push_back(s);
   const int nd = (int)tb.dynamic_slots.size();
   tb.n_dynamic = nd; tb.n_static = (int)tb.static_slots.size();
@@ -288,6 +297,27 @@ inline int build_tables(const HScene& sc, int parity_mode, HostTables& tb, std::
       const double rad = (sqrt(r2) + (double)tb.slots[s].br) * (1 + 1e-6) + 1e-5;
       tb.tile_bounds[(size_t)tile * nd + j] = make_float4((float)c[0], (float)c[1], (float)c[2], (float)rad);
     }
+  // ---- inline support-candidate records (FP32)
+  {
+    float4 empty = make_float4(0.f, 0.f, 0.f, 0.f), over = empty;
+    const int m1 = -1, m2 = -2;
+    memcpy(&empty.w, &m1, 4); memcpy(&over.w, &m2, 4);
+    tb.hull_rec.assign(tb.hull_cells.size() * SIRRT_HULL_REC, empty);
+    for (const DShape& d : tb.shapes) {
+      if (d.type != SH_HULL || d.cell_off < 0) continue;
+      for (int cell = 0; cell < SIRRT_HULL_CELLS; cell++) {
+        const unsigned c0 = tb.hull_cells[d.cell_off + cell], c1 = tb.hull_cells[d.cell_off + cell + 1];
+        float4* rec = &tb.hull_rec[((size_t)d.cell_off + cell) * SIRRT_HULL_REC];
+        if (c1 - c0 > SIRRT_HULL_REC) { rec[SIRRT_HULL_REC - 1] = over; continue; }
+        for (unsigned k = c0; k < c1; k++) {
+          const int i = tb.hull_cand[k];
+          float4 r = make_float4(tb.verts_f[3 * ((size_t)d.vert_off + i)], tb.verts_f[3 * ((size_t)d.vert_off + i) + 1], tb.verts_f[3 * ((size_t)d.vert_off + i) + 2], 0.f);
+          memcpy(&r.w, &i, 4);
+          rec[k - c0] = r;
+        }
+      }
+    }
+  }
   if (tb.static_slots.empty()) tb.static_slots.push_back(0);  // keep the device arrays non-empty
   if (tb.dynamic_slots.empty()) tb.dynamic_slots.push_back(0);
   return 0;

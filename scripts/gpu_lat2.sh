@@ -26,7 +26,8 @@ if [ -x scripts/micro/_build/gjk_hist ]; then
 import json
 for line in open("$OUT/${TAG}_gjk_hist.json"):
     d = json.loads(line)
-    print(d["call"], d["calls"], {k: (v["tasks"], v["mean_iter"], v["max_iter"]) for k, v in d.items() if isinstance(v, dict)})
+    print(d["call"], d["calls"], {k: (v["tasks"], v["mean_iter"], v["max_iter"]) for k, v in d.items() if isinstance(v, dict) and "mean_iter" in v},
+          d.get("collide_bits_cycles_per_warp"), d.get("gjk_task_cycles"))
 PY
 fi
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --cache-control none -c 400 --csv --log-file $OUT/${TAG}_launches_fb.csv manipulationplanning-si-rrt_b200/host/sirrt_latency /tmp/packs/flying_boxes.pack 40 > $OUT/${TAG}_ncu.log 2>&1; echo "ncu rc=$?"

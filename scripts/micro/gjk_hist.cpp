@@ -9,6 +9,7 @@
 #include "CollisionManager.hpp"
 
 extern "C" int sirrt_debug_gjk_hist(unsigned int* out, int reset);
+extern "C" int sirrt_debug_phases(unsigned long long* out, int reset);
 
 static void dump(const char* what, int calls) {
   unsigned int h[4][64];
@@ -22,6 +23,12 @@ static void dump(const char* what, int calls) {
     for (int i = 0; i <= mx; i++) printf("%s%u", i ? "," : "", h[v][i]);
     printf("]}");
   }
+  unsigned long long ph[16];
+  sirrt_debug_phases(ph, 1);
+  const double cw = ph[0] ? (double)ph[0] : 1.0, tk = ph[8] ? (double)ph[8] : 1.0;
+  printf(", \"collide_bits_cycles_per_warp\": {\"warps\": %llu, \"fk_and_link_table\": %.0f, \"static\": %.0f, \"dynamic\": %.0f, \"item\": %.0f}",
+         ph[0], ph[1] / cw, ph[2] / cw, ph[3] / cw, ph[4] / cw);
+  printf(", \"gjk_task_cycles\": {\"tasks\": %llu, \"prologue\": %.0f, \"gjk\": %.0f, \"iters\": %.2f}", ph[8], ph[9] / tk, ph[10] / tk, ph[12] / tk);
   printf("}\n");
 }
 

@@ -337,6 +337,7 @@ extern "C" int sirrt_debug_gjk_hist(unsigned int* out, int reset) {  // diagnost
   if (reset) { static unsigned int z[4 * 64]; if (cudaMemcpyToSymbol(g_gjk_hist, z, sizeof z) != cudaSuccess) return SIRRT_E_CUDA; }
   return SIRRT_OK;
 }
+extern "C" int sirrt_debug_fk_mode(int mode) { return cudaMemcpyToSymbol(g_fk_mode, &mode, sizeof mode) == cudaSuccess ? SIRRT_OK : SIRRT_E_CUDA; }
 extern "C" int sirrt_debug_phases(unsigned long long* out, int reset) {
   if (cudaDeviceSynchronize() != cudaSuccess) return SIRRT_E_CUDA;
   if (out && cudaMemcpyFromSymbol(out, g_phase, sizeof(unsigned long long) * 16) != cudaSuccess) return SIRRT_E_CUDA;

@@ -94,11 +94,14 @@ template <typename T> __host__ __device__ inline int hull_cell(const T* d) {
   if (ay > m) { a = 1; m = ay; }
   if (az > m) { a = 2; m = az; }
   if (!(m > T(0)) || !(m < T(3.0e38))) return -1;  // zero / NaN / inf direction: caller scans every vertex
-  const T u = d[(a + 1) % 3] / m, v = d[(a + 2) % 3] / m;
+  // components picked by selects (a dynamically indexed d[] would live in local memory on the device), one reciprocal
+  const T d1 = a == 0 ? d[1] : (a == 1 ? d[2] : d[0]), d2 = a == 0 ? d[2] : (a == 1 ? d[0] : d[1]), da = a == 0 ? d[0] : (a == 1 ? d[1] : d[2]);
+  const T inv = T(1) / m;
+  const T u = d1 * inv, v = d2 * inv;
   int iu = (int)((u + T(1)) * T(0.5 * SIRRT_HULL_K)), iv = (int)((v + T(1)) * T(0.5 * SIRRT_HULL_K));
   iu = iu < 0 ? 0 : (iu > SIRRT_HULL_K - 1 ? SIRRT_HULL_K - 1 : iu);
   iv = iv < 0 ? 0 : (iv > SIRRT_HULL_K - 1 ? SIRRT_HULL_K - 1 : iv);
-  const int face = 2 * a + (d[a] < T(0) ? 1 : 0);
+  const int face = 2 * a + (da < T(0) ? 1 : 0);
   return (face * SIRRT_HULL_K + iu) * SIRRT_HULL_K + iv;
 }
 
@@ -181,50 +184,95 @@ __device__ inline void fk_links(const DRobot& rb, const double* q, LinkXfD* out)
   }
 }
 
-// Warp form of the same chain for the latency kernels (one warp per configuration).  FP64 instructions are the scarce
-// resource there (a warp-wide DFMA occupies the FP64 pipe for ~8 cycles on B200; measured: the per-lane chain cost a warp
-// ~7 000 cycles), so the 3x3 products are spread over the lanes: lane e < 9 holds element e of the running rotation R,
-// lane 9 + i element i of the running translation t, and every product costs each lane ONE row-times-column (3 multiply-
-// adds) instead of nine.  Lane j evaluates sincos of joint j, so the n_joints dependent sincos expansions collapse into one.
-// At the end lane l holds the transform of link l.  Same formulas per element as fk_links (out = A row . B column);
-// my_q = angle of joint `lane` (0 for lanes without a joint); every lane of the warp must call.
-__device__ inline void fk_link_of_lane(const DRobot& rb, double my_q, int lane, LinkXfD& mine) {
+// Warp form of the same chain for the latency kernels (one warp per configuration): a PARALLEL PREFIX over the joints.
+// Measured on B200 (scripts/micro/gjk_hist, clock64): the per-lane sequential chain costs a warp ~7 100 cycles for six
+// joints (~600 dependent FP64 operations at ~6 cycles each, every lane repeating all of them).  Here lane e builds chain
+// element e on its own -- element 0 = the base transform, element k + 1 = joint k's local transform (jt_k, jR_k Rz(q_k))
+// with ITS sincos -- and an inclusive scan (log2 steps, one affine composition = 36 multiply-adds per step and lane)
+// leaves "base and the first e joints applied" in lane e; lane l then takes the state at link_jb[l] by shuffle and applies
+// the link's own offset.  ~170 FP64 operations per lane instead of ~600.  The products associate differently from
+// fk_links, so the transforms agree with it to rounding (1e-16 relative), not bit for bit: they feed the FP32 link table
+// (narrowed, consumers decide outside a 2e-5 m band only) and the FP64 enclosure certificate (1e-9 m margin); every
+// FP64 DECISION of the re-check recomputes its link with fk_one_link.
+// my_q = angle of joint (lane - 1) (0 for lanes without one); every lane of the warp must call.
+__device__ inline void fk_link_of_lane(const DRobot& rb, double my_q, int lane, LinkXfD& mine, long long* t_sincos = nullptr) {
+  double sn, cs;
+  sincos(my_q, &sn, &cs);
+  if (t_sincos) *t_sincos = clock64() + (long long)(sn == 2.0);  // diagnostics builds: the time stamp waits for the result
+  double R[9], t[3];
+  if (lane >= 1 && lane <= rb.n_joints) {
+    const int k = lane - 1;
+    const double z = (1.0 - cs) * 1.0 + cs;  // Eigen::AngleAxisd(q, UnitZ).toRotationMatrix()(2, 2)  (:321,363)
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const double a = rb.jR[k][3 * i], b = rb.jR[k][3 * i + 1], c = rb.jR[k][3 * i + 2];
+      R[3 * i] = a * cs + b * sn; R[3 * i + 1] = b * cs - a * sn; R[3 * i + 2] = c * z;
+      t[i] = rb.jt[k][i];
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 9; i++) R[i] = lane == 0 ? rb.base_R[i] : ((i & 3) == 0 ? 1.0 : 0.0);
+#pragma unroll
+    for (int i = 0; i < 3; i++) t[i] = lane == 0 ? rb.base_t[i] : 0.0;
+  }
+  for (int d = 1; d <= rb.n_joints; d <<= 1) {  // inclusive scan of X_e = X_(e-d) o X_e
+    double Rp[9], tp[3];
+#pragma unroll
+    for (int i = 0; i < 9; i++) Rp[i] = __shfl_up_sync(SIRRT_FULL, R[i], d);
+#pragma unroll
+    for (int i = 0; i < 3; i++) tp[i] = __shfl_up_sync(SIRRT_FULL, t[i], d);
+    if (lane >= d) {
+      double w[3];
+      matvec(w, Rp, t);
+      t[0] = tp[0] + w[0]; t[1] = tp[1] + w[1]; t[2] = tp[2] + w[2];
+      matmul3(R, Rp, R);
+    }
+  }
+  const int l = lane < rb.n_links ? lane : 0;
+  const int src = rb.link_jb[l];
+  double Rs[9], ts[3];
+#pragma unroll
+  for (int i = 0; i < 9; i++) Rs[i] = __shfl_sync(SIRRT_FULL, R[i], src);
+#pragma unroll
+  for (int i = 0; i < 3; i++) ts[i] = __shfl_sync(SIRRT_FULL, t[i], src);
+  double w[3];
+  matvec(w, Rs, rb.lo_t[l]);  // :335
+  mine.t[0] = ts[0] + w[0]; mine.t[1] = ts[1] + w[1]; mine.t[2] = ts[2] + w[2];  // :336
+  matmul3(mine.R, Rs, rb.lo_R[l]);  // :347
+}
+
+#ifdef SIRRT_GJK_STATS
+// diagnostics builds: the per-lane chain with the sincos spread over the lanes (what fk_link_of_lane replaced), for A/B timing
+__device__ int g_fk_mode;
+__device__ inline void fk_link_of_lane_serial(const DRobot& rb, double my_q, int lane, LinkXfD& mine, long long* t_sincos) {
   double my_sn, my_cs;
   sincos(my_q, &my_sn, &my_cs);
-  const int e = lane < 12 ? lane : 0;
-  const int row = e < 9 ? e / 3 : e - 9, col = e < 9 ? e - 3 * (e / 3) : 0;
-  const bool is_t = e >= 9;
-  double val = is_t ? rb.base_t[row] : rb.base_R[e];
+  if (t_sincos) *t_sincos = clock64() + (long long)(my_sn == 2.0);
+  double t[3] = {rb.base_t[0], rb.base_t[1], rb.base_t[2]}, R[9];
+#pragma unroll
+  for (int i = 0; i < 9; i++) R[i] = rb.base_R[i];
   int l = 0;
   for (int k = 0; k <= rb.n_joints; k++) {
-    // row `row` of the running R, for the link emissions at this joint count and for the joint's own products
-    const double a0 = __shfl_sync(SIRRT_FULL, val, 3 * row), a1 = __shfl_sync(SIRRT_FULL, val, 3 * row + 1), a2 = __shfl_sync(SIRRT_FULL, val, 3 * row + 2);
     while (l < rb.n_links && rb.link_jb[l] == k) {
-      // link l: t_l = t + R lo_t (:335-336), R_l = R lo_R (:347); element e lands in lane e, then everything moves to lane l
-      const double b0 = is_t ? rb.lo_t[l][0] : rb.lo_R[l][col], b1 = is_t ? rb.lo_t[l][1] : rb.lo_R[l][3 + col], b2 = is_t ? rb.lo_t[l][2] : rb.lo_R[l][6 + col];
-      const double p = a0 * b0 + a1 * b1 + a2 * b2;
-      const double o = is_t ? val + p : p;
-#pragma unroll
-      for (int x = 0; x < 9; x++) { const double v = __shfl_sync(SIRRT_FULL, o, x); if (lane == l) mine.R[x] = v; }
-#pragma unroll
-      for (int x = 0; x < 3; x++) { const double v = __shfl_sync(SIRRT_FULL, o, 9 + x); if (lane == l) mine.t[x] = v; }
+      if (l == lane) {
+        double w[3];
+        matvec(w, R, rb.lo_t[l]);
+        mine.t[0] = t[0] + w[0]; mine.t[1] = t[1] + w[1]; mine.t[2] = t[2] + w[2];
+        matmul3(mine.R, R, rb.lo_R[l]);
+      }
       l++;
     }
     if (k == rb.n_joints) break;
-    {  // t += R jt (:319,361); R = R jR (:320,362)
-      const double b0 = is_t ? rb.jt[k][0] : rb.jR[k][col], b1 = is_t ? rb.jt[k][1] : rb.jR[k][3 + col], b2 = is_t ? rb.jt[k][2] : rb.jR[k][6 + col];
-      const double p = a0 * b0 + a1 * b1 + a2 * b2;
-      val = is_t ? val + p : p;
-    }
-    {  // R = R Rz(q_k), Rz = AngleAxisd(q_k, UnitZ) (:321,363): columns (cs, sn, 0), (-sn, cs, 0), (0, 0, (1 - cs) + cs)
-      const double sn = __shfl_sync(SIRRT_FULL, my_sn, k), cs = __shfl_sync(SIRRT_FULL, my_cs, k);
-      const double c0 = __shfl_sync(SIRRT_FULL, val, 3 * row), c1 = __shfl_sync(SIRRT_FULL, val, 3 * row + 1), c2 = __shfl_sync(SIRRT_FULL, val, 3 * row + 2);
-      const double b0 = col == 0 ? cs : (col == 1 ? -sn : 0.0), b1 = col == 0 ? sn : (col == 1 ? cs : 0.0), b2 = col == 2 ? (1.0 - cs) * 1.0 + cs : 0.0;
-      const double p = c0 * b0 + c1 * b1 + c2 * b2;
-      if (!is_t) val = p;
-    }
+    double w[3];
+    matvec(w, R, rb.jt[k]);
+    t[0] += w[0]; t[1] += w[1]; t[2] += w[2];
+    matmul3(R, R, rb.jR[k]);
+    const double sn = __shfl_sync(SIRRT_FULL, my_sn, k), cs = __shfl_sync(SIRRT_FULL, my_cs, k);
+    double Rz[9] = {cs, -sn, 0, sn, cs, 0, 0, 0, (1.0 - cs) * 1.0 + cs};
+    matmul3(R, R, Rz);
   }
 }
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // closed-form core distances (same formulas as the test-only CPU checker, written independently of
@@ -540,10 +588,14 @@ template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v,
       keep = ((m & 1) ? 1 << j0 : 0) | ((m & 2) ? 1 << j1 : 0) | ((m & 4) ? 1 << j2 : 0);
     }
   }
+  // compaction with static indices only (entry i can only move down to a slot jj < i): the simplex stays in registers
   int j = 0;
-  for (int i = 0; i < s.n; i++)
-    if (keep & (1 << i)) {
-      if (i != j) { s.w[j][0] = s.w[i][0]; s.w[j][1] = s.w[i][1]; s.w[j][2] = s.w[i][2]; s.id[j] = s.id[i]; }
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+    if (i < s.n && (keep & (1 << i))) {
+#pragma unroll
+      for (int jj = 0; jj < i; jj++)
+        if (jj == j) { s.w[jj][0] = s.w[i][0]; s.w[jj][1] = s.w[i][1]; s.w[jj][2] = s.w[i][2]; s.id[jj] = s.id[i]; }
       j++;
     }
   s.n = j;
@@ -602,9 +654,13 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
     }
     T gap = vv - vw;
     bool done = gap <= REL * vv;
-    for (int i = 0; i < s.n; i++) done |= (s.id[i] == id);
+#pragma unroll
+    for (int i = 0; i < 4; i++) done |= (i < s.n && s.id[i] == id);
     if (done) break;
-    s.w[s.n][0] = w[0]; s.w[s.n][1] = w[1]; s.w[s.n][2] = w[2]; s.id[s.n] = id; s.n++;
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+      if (i == s.n) { s.w[i][0] = w[0]; s.w[i][1] = w[1]; s.w[i][2] = w[2]; s.id[i] = id; }
+    s.n++;
     T nvv[3];
     if (simplex_closest(s, nvv, min_face, lane)) {
       if (dist_out) *dist_out = -rsum;

@@ -47,7 +47,7 @@ __device__ __forceinline__ void push_work(const WorkList& wl, int config, int fr
 // diagnostics build: FP32 GJK iterations per task, by verdict (0 FREE, 1 HIT, 2 AMBIGUOUS, 3 AMBIGUOUS with a thin enclosing tetrahedron)
 __device__ unsigned int g_gjk_hist[4][64];
 // cycles per phase, summed over warps: [0] k_collide_bits warps, [1] FK + link table, [2] static slots, [3] dynamic tiles,
-// [4] whole item; [8] k_gjk_tasks tasks, [9] task prologue (up to the GJK call), [10] GJK + verdict, [11] kernel entry to first task
+// [4] whole item, [5] angle load + sincos, [6] FK chain, [7] link table; [8] k_gjk_tasks tasks, [9] task prologue (up to the GJK call), [10] GJK + verdict, [11] kernel entry to first task
 __device__ unsigned long long g_phase[16];
 #define PHASE_T(v) const long long v = clock64()
 #define PHASE_ADD(i, d) do { if (lane == 0) atomicAdd(&g_phase[i], (unsigned long long)(d)); } while (0)
@@ -70,9 +70,18 @@ struct WarpCtx {   // per-warp shared memory: the planned robot's links in world
 // FK in FP64 (warp form: lane j takes the sincos of joint j, lane l ends up with link l), then lane l narrows link l to
 // the FP32 world-space link table.
 __device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QView& qv, long long n, WarpCtx& W, int lane, double* xf_out = nullptr) {
-  const double my_q = (lane < rb.n_joints && lane < qv.dof) ? load_q(qv, n, lane) : 0.0;
+  const double my_q = (lane >= 1 && lane <= rb.n_joints && lane <= qv.dof) ? load_q(qv, n, lane - 1) : 0.0;  // lane e: chain element e = joint e - 1
   LinkXfD X;
+#ifdef SIRRT_GJK_STATS
+  const long long t_s0 = clock64() + (long long)(my_q == 1e300);
+  long long t_s1 = 0;
+  if (g_fk_mode == 1) fk_link_of_lane_serial(rb, __shfl_down_sync(SIRRT_FULL, my_q, 1), lane, X, &t_s1);
+  else fk_link_of_lane(rb, my_q, lane, X, &t_s1);
+  const long long t_s2 = clock64() + (long long)(X.t[0] == 1e300);
+  PHASE_ADD(5, t_s1 - t_s0); PHASE_ADD(6, t_s2 - t_s1);
+#else
   fk_link_of_lane(rb, my_q, lane, X);
+#endif
   if (lane < rb.n_links) {
     {
       const int l = lane;
@@ -89,34 +98,52 @@ __device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QVi
       W.type[l] = sh.type;
       W.r[l] = sh.radius;
       W.br[l] = sh.br;
-      double bc[3] = {sh.bc[0], sh.bc[1], sh.bc[2]}, w[3];
-      matvec(w, R, bc);
-      for (int k = 0; k < 3; k++) W.bc[l][k] = (float)(w[k] + t[k]);
-      for (int k = 0; k < 3; k++) {  // capsule core: local (0,0,+-half_len)
-        W.a[l][k] = (float)(t[k] - R[3 * k + 2] * sh.d_half_len);
-        W.b[l][k] = (float)(t[k] + R[3 * k + 2] * sh.d_half_len);
+      // Everything below is derived from the NARROWED transform in FP32 (FP64 instructions are what a single warp waits for
+      // on this path): the values feed culls with explicit margins and FP32 tests that only decide outside the band, so
+      // the ~1e-7 m this adds is inside their budget; the boxes get an outward margin instead of directed rounding.
+      float Rf[9], tf[3];
+#pragma unroll
+      for (int k = 0; k < 9; k++) Rf[k] = W.R[l][k];
+#pragma unroll
+      for (int k = 0; k < 3; k++) tf[k] = W.t[l][k];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        W.bc[l][k] = Rf[3 * k] * sh.bc[0] + Rf[3 * k + 1] * sh.bc[1] + Rf[3 * k + 2] * sh.bc[2] + tf[k];
+        W.a[l][k] = tf[k] - Rf[3 * k + 2] * sh.half_len;  // capsule core: local (0,0,+-half_len)
+        W.b[l][k] = tf[k] + Rf[3 * k + 2] * sh.half_len;
       }
-      {  // tight world AABB: centre R*ac + t, half extents sum_j |R_kj| (amax_j - amin_j)/2, rounded outwards
-        double c[3]; matvec(c, R, sh.d_ac);
-        for (int k = 0; k < 3; k++) {
-          double e = 0;
-          for (int j = 0; j < 3; j++) e += fabs(R[3 * k + j]) * 0.5 * (sh.d_amax[j] - sh.d_amin[j]);
-          W.tlo[l][k] = __double2float_rd(c[k] + t[k] - e); W.thi[l][k] = __double2float_ru(c[k] + t[k] + e);
-        }
+      float cw[3];  // world position of the local AABB centre
+#pragma unroll
+      for (int k = 0; k < 3; k++) cw[k] = Rf[3 * k] * sh.ac[0] + Rf[3 * k + 1] * sh.ac[1] + Rf[3 * k + 2] * sh.ac[2] + tf[k];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {  // tight world AABB: centre R*ac + t, half extents sum_j |R_kj| (amax_j - amin_j)/2, widened
+        float e = 0.f;
+#pragma unroll
+        for (int j = 0; j < 3; j++) e += fabsf(Rf[3 * k + j]) * 0.5f * (sh.amax[j] - sh.amin[j]);
+        const float m = 2e-6f * (1.f + fabsf(cw[k]) + e);
+        W.tlo[l][k] = cw[k] - e - m; W.thi[l][k] = cw[k] + e + m;
       }
-      // coal CollisionObject::computeAABB (identity rotation -> translated local AABB)
+      // coal CollisionObject::computeAABB (identity rotation, |R - I| <= 1e-12 elementwise -> translated local AABB); the
+      // exact FP64 comparison only runs when the narrowed matrix looks like the identity at all
       bool ident = true;
-      for (int k = 0; k < 9; k++) ident &= fabs(R[k] - ((k % 4) == 0 ? 1.0 : 0.0)) <= 1e-12;
+#pragma unroll
+      for (int k = 0; k < 9; k++) ident &= fabsf(Rf[k] - ((k % 4) == 0 ? 1.f : 0.f)) <= 1e-6f;
+      if (ident)
+        for (int k = 0; k < 9; k++) ident &= fabs(R[k] - ((k % 4) == 0 ? 1.0 : 0.0)) <= 1e-12;
       if (ident) {
-        for (int k = 0; k < 3; k++) { W.alo[l][k] = (float)(sh.d_amin[k] + t[k]); W.ahi[l][k] = (float)(sh.d_amax[k] + t[k]); }
+#pragma unroll
+        for (int k = 0; k < 3; k++) { W.alo[l][k] = sh.amin[k] + tf[k]; W.ahi[l][k] = sh.amax[k] + tf[k]; }
       } else {
-        double c[3]; matvec(c, R, sh.d_ac);
-        for (int k = 0; k < 3; k++) { W.alo[l][k] = (float)(c[k] + t[k] - sh.d_ar); W.ahi[l][k] = (float)(c[k] + t[k] + sh.d_ar); }
+#pragma unroll
+        for (int k = 0; k < 3; k++) { W.alo[l][k] = cw[k] - sh.ar; W.ahi[l][k] = cw[k] + sh.ar; }
       }
     }
   }
   if (lane == 0) W.qn = 0;
   __syncwarp();
+#ifdef SIRRT_GJK_STATS
+  PHASE_ADD(7, clock64() - t_s2);
+#endif
 }
 
 __device__ __forceinline__ int classify(float d, float band) { return d < -band ? RES_HIT : (d > band ? RES_FREE : RES_AMBIG); }

@@ -10,6 +10,7 @@
 
 extern "C" int sirrt_debug_gjk_hist(unsigned int* out, int reset);
 extern "C" int sirrt_debug_phases(unsigned long long* out, int reset);
+extern "C" int sirrt_debug_fk_mode(int mode);
 
 static void dump(const char* what, int calls) {
   unsigned int h[4][64];
@@ -26,8 +27,8 @@ static void dump(const char* what, int calls) {
   unsigned long long ph[16];
   sirrt_debug_phases(ph, 1);
   const double cw = ph[0] ? (double)ph[0] : 1.0, tk = ph[8] ? (double)ph[8] : 1.0;
-  printf(", \"collide_bits_cycles_per_warp\": {\"warps\": %llu, \"fk_and_link_table\": %.0f, \"static\": %.0f, \"dynamic\": %.0f, \"item\": %.0f}",
-         ph[0], ph[1] / cw, ph[2] / cw, ph[3] / cw, ph[4] / cw);
+  printf(", \"collide_bits_cycles_per_warp\": {\"warps\": %llu, \"fk_and_link_table\": %.0f, \"static\": %.0f, \"dynamic\": %.0f, \"item\": %.0f, \"sincos\": %.0f, \"chain\": %.0f, \"table\": %.0f}",
+         ph[0], ph[1] / cw, ph[2] / cw, ph[3] / cw, ph[4] / cw, ph[5] / cw, ph[6] / cw, ph[7] / cw);
   printf(", \"gjk_task_cycles\": {\"tasks\": %llu, \"prologue\": %.0f, \"gjk\": %.0f, \"iters\": %.2f}", ph[8], ph[9] / tk, ph[10] / tk, ph[12] / tk);
   printf("}\n");
 }
@@ -43,8 +44,13 @@ int main(int argc, char** argv) {
   for (auto& q : qs)
     for (int j = 0; j < dof; j++) q[j] = std::uniform_real_distribution<double>(lim[j].first, lim[j].second)(rng);
   sirrt_debug_gjk_hist(nullptr, 1);
+  sirrt_debug_phases(nullptr, 1);
   for (int i = 0; i < n; i++) cm.get_safe_intervals(qs[i]);
   dump("get_safe_intervals", n);
+  sirrt_debug_fk_mode(1);
+  for (int i = 0; i < n; i++) cm.get_safe_intervals(qs[i]);
+  dump("get_safe_intervals_fk_serial_chain", n);
+  sirrt_debug_fk_mode(0);
   std::vector<double> states(32 * (size_t)dof);
   std::vector<int32_t> frames(32);
   std::vector<uint8_t> cells(32);

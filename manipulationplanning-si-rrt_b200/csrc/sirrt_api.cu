@@ -10,6 +10,7 @@
 #include <stdio.h>
 
 #include <algorithm>
+#include <utility>
 #include <mutex>
 #include <new>
 
@@ -171,6 +172,7 @@ struct sirrt_scene {
   long long sweep_min_configs = 8192;
   long long defer_max_configs = 4096;  // hull scenes: batches up to this size hand their GJK runs to k_gjk_tasks
   DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2, xf, row1;
+  int pdl = 1;         // latency path: the kernels of a call are chained by programmatic dependent launch (SIRRT_OPT_PDL)
   int slot_split = 1;  // planner-sized batches: dynamic slots of a row split over several warps (SIRRT_OPT_SLOT_SPLIT)
   // Latency path (planner in the loop): one pinned host block that the GPU reads and writes in place
   // (cudaMallocHost memory is device-addressable under UVA).  Small host inputs are memcpy'd into it and read
@@ -319,6 +321,7 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
     case SIRRT_OPT_DEFER_MAX_CONFIGS: if (value < 0) return fail(SIRRT_E_ARG, "bad threshold"); s->defer_max_configs = value; break;
     case SIRRT_OPT_PIPELINE: s->pipeline = value != 0; break;
     case SIRRT_OPT_SLOT_SPLIT: s->slot_split = value != 0; break;
+    case SIRRT_OPT_PDL: s->pdl = value != 0; break;
     case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
     default: return fail(SIRRT_E_ARG, "unknown option");
   }

@@ -9,6 +9,20 @@ static int grid_for(long long warps_wanted, int n_sm, int blocks_per_sm) {
 
 struct Range { long long n0, cnt; };
 
+// Launch of a kernel that follows another kernel of the same latency-path call: with pdl the launch carries the
+// programmatic-stream-serialization attribute (the kernel's blocks may become resident while its predecessor still runs;
+// it calls pdl_wait() before it touches the predecessor's results)
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_after(bool pdl, void (*kernel)(KArgs...), unsigned grid, unsigned block, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 // the call's last kernel (k_recheck on the latency path) will write the next sequence number to PIN_FLAG
 static void arm_done(sirrt_scene* s, RecheckParams& R) {
   R.done = (unsigned int*)(s->pinned + PIN_FLAG);
@@ -116,13 +130,13 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
           if (self_clearing) {  // the task kernel's last block completes the call when nothing is left for the FP64 re-check
             G.ticket = s->lazy_cnt + 6; G.publish = R.publish; G.done = R.done; G.done_seq = R.done_seq; G.fin = R.fin; G.fin_seq = R.fin_seq; G.iv = R.iv;
           }
-          k_gjk_tasks<<<s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, G);
+          CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, (unsigned)s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
           launches++;
         }
       }
       if (timed) cudaEventRecord(s->ev[2 * i + 1], st);
       // a handful of rows leaves a handful of ambiguous pair tests: a small grid shortens the last-block hand-over
-      k_recheck<<<(self_clearing && N <= 64) ? 16 : s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
+      CU(launch_after(self_clearing && s->pdl && !sweep, k_recheck, (self_clearing && N <= 64) ? 16u : (unsigned)s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, R));
       launches++;
       CU(cudaGetLastError());
     }
@@ -470,10 +484,10 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
       G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl; G.xf = P.xf;
       G.bits = nullptr; G.n_words = s->tb.n_tiles; G.cells = d_out; G.band = (float)s->band;
       if (self_clearing) { G.ticket = s->lazy_cnt + 6; G.publish = R.publish; G.done = R.done; G.done_seq = R.done_seq; G.fin = R.fin; G.fin_seq = R.fin_seq; }
-      k_gjk_tasks<<<s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, G);
+      CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, (unsigned)s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
       s->stats[0]++;
     }
-    k_recheck<<<(self_clearing && qv.cnt <= 256) ? 16 : s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, R);
+    CU(launch_after(self_clearing && s->pdl, k_recheck, (self_clearing && qv.cnt <= 256) ? 16u : (unsigned)s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, R));
     s->stats[0] += 2;
     CU(cudaGetLastError());
   }

@@ -19,6 +19,20 @@ enum { RES_FREE = 0, RES_HIT = 1, RES_AMBIG = 2 };
 #define SIRRT_SECURITY_MARGIN 1e-21
 #define SIRRT_COLLISION_THRESHOLD 1e-12
 
+#ifdef SIRRT_GJK_STATS
+// diagnostics build: FP32 GJK iterations per task, by verdict (0 FREE, 1 HIT, 2 AMBIGUOUS, 3 AMBIGUOUS with a thin enclosing tetrahedron)
+__device__ unsigned int g_gjk_hist[4][64];
+// cycles per phase, summed over warps: [0] k_collide_bits warps, [1] FK + link table, [2] static slots, [3] dynamic tiles,
+// [4] whole item, [5] angle load + sincos, [6] FK chain, [7] link table; [8] k_gjk_tasks tasks, [9] task prologue (up to the GJK call), [10] GJK + verdict, [11] kernel entry to first task,
+// [12] GJK iterations, [13] hull support of A, [14] support of B + transforms, [15] simplex_closest (FP32 task GJK only)
+__device__ unsigned long long g_phase[16];
+#define PHASE_T(v) const long long v = clock64()
+#define PHASE_ADD(i, d) do { if (lane == 0) atomicAdd(&g_phase[i], (unsigned long long)(d)); } while (0)
+#else
+#define PHASE_T(v)
+#define PHASE_ADD(i, d)
+#endif
+
 // ---------------------------------------------------------------------------------------------
 // Device tables
 // ---------------------------------------------------------------------------------------------
@@ -588,14 +602,13 @@ template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v,
       keep = ((m & 1) ? 1 << j0 : 0) | ((m & 2) ? 1 << j1 : 0) | ((m & 4) ? 1 << j2 : 0);
     }
   }
-  // compaction with static indices only (entry i can only move down to a slot jj < i): the simplex stays in registers
+  // (the simplex is indexed dynamically here and in warp_gjk and so lives in local memory; a register-resident variant
+  // -- static indices, selects -- was measured on B200: same GJK cycles per task, 124 -> 166 registers and -45 % on the
+  // hull-batch throughput of k_collide_bits, so it was not kept)
   int j = 0;
-#pragma unroll
-  for (int i = 0; i < 4; i++)
-    if (i < s.n && (keep & (1 << i))) {
-#pragma unroll
-      for (int jj = 0; jj < i; jj++)
-        if (jj == j) { s.w[jj][0] = s.w[i][0]; s.w[jj][1] = s.w[i][1]; s.w[jj][2] = s.w[i][2]; s.id[jj] = s.id[i]; }
+  for (int i = 0; i < s.n; i++)
+    if (keep & (1 << i)) {
+      if (i != j) { s.w[j][0] = s.w[i][0]; s.w[j][1] = s.w[i][1]; s.w[j][2] = s.w[i][2]; s.id[j] = s.id[i]; }
       j++;
     }
   s.n = j;
@@ -619,13 +632,22 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
   T pa[3], pb[3], dl[3], nv[3], min_face = T(0);
   const T REL = FINAL ? T(1e-15) : T(1e-6);
   auto support = [&](const T* dir, T* w) -> int {  // support of A - B in direction dir
+#ifdef SIRRT_GJK_STATS
+    const long long c0 = clock64() + (long long)(dir[0] == T(3e38));
+#endif
     int ia = warp_support(A, dir, pa, lane);
+#ifdef SIRRT_GJK_STATS
+    const long long c1 = clock64() + (long long)(pa[0] == T(3e38));
+#endif
     T nd[3] = {-dir[0], -dir[1], -dir[2]};
     matTvec(dl, Rrel, nd);
     T u[3];
     int ib = warp_support(B, dl, u, lane);
     matvec(pb, Rrel, u);
     w[0] = pa[0] - (pb[0] + trel[0]); w[1] = pa[1] - (pb[1] + trel[1]); w[2] = pa[2] - (pb[2] + trel[2]);
+#ifdef SIRRT_GJK_STATS
+    if (!FINAL) { const long long c2 = clock64() + (long long)(w[0] == T(3e38)); PHASE_ADD(13, c1 - c0); PHASE_ADD(14, c2 - c1); }
+#endif
     return (ia << 12) | ib;
   };
   nv[0] = -v[0]; nv[1] = -v[1]; nv[2] = -v[2];
@@ -654,15 +676,18 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
     }
     T gap = vv - vw;
     bool done = gap <= REL * vv;
-#pragma unroll
-    for (int i = 0; i < 4; i++) done |= (i < s.n && s.id[i] == id);
+    for (int i = 0; i < s.n; i++) done |= (s.id[i] == id);
     if (done) break;
-#pragma unroll
-    for (int i = 0; i < 4; i++)
-      if (i == s.n) { s.w[i][0] = w[0]; s.w[i][1] = w[1]; s.w[i][2] = w[2]; s.id[i] = id; }
-    s.n++;
+    s.w[s.n][0] = w[0]; s.w[s.n][1] = w[1]; s.w[s.n][2] = w[2]; s.id[s.n] = id; s.n++;
     T nvv[3];
+#ifdef SIRRT_GJK_STATS
+    const long long cs0 = clock64() + (long long)(w[0] == T(3e38));
+    const int enclosed = simplex_closest(s, nvv, min_face, lane);
+    if (!FINAL) PHASE_ADD(15, clock64() + (long long)(nvv[0] == T(3e38)) - cs0);
+    if (enclosed) {
+#else
     if (simplex_closest(s, nvv, min_face, lane)) {
+#endif
       if (dist_out) *dist_out = -rsum;
       if (FINAL) return RES_HIT;  // core distance 0 <= threshold + rsum
       if (rsum > band) return RES_HIT;

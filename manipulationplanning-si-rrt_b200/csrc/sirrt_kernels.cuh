@@ -43,18 +43,12 @@ __device__ __forceinline__ void push_work(const WorkList& wl, int config, int fr
   }
 }
 
-#ifdef SIRRT_GJK_STATS
-// diagnostics build: FP32 GJK iterations per task, by verdict (0 FREE, 1 HIT, 2 AMBIGUOUS, 3 AMBIGUOUS with a thin enclosing tetrahedron)
-__device__ unsigned int g_gjk_hist[4][64];
-// cycles per phase, summed over warps: [0] k_collide_bits warps, [1] FK + link table, [2] static slots, [3] dynamic tiles,
-// [4] whole item, [5] angle load + sincos, [6] FK chain, [7] link table; [8] k_gjk_tasks tasks, [9] task prologue (up to the GJK call), [10] GJK + verdict, [11] kernel entry to first task
-__device__ unsigned long long g_phase[16];
-#define PHASE_T(v) const long long v = clock64()
-#define PHASE_ADD(i, d) do { if (lane == 0) atomicAdd(&g_phase[i], (unsigned long long)(d)); } while (0)
-#else
-#define PHASE_T(v)
-#define PHASE_ADD(i, d)
-#endif
+// Programmatic dependent launch (latency path): the kernels of one call are launched back to back with the
+// programmatic-stream-serialization attribute; a producer lets its dependents start launching at once (their blocks
+// become resident and run their prologue while the producer still works) and a consumer waits here until the producer
+// grid has completed and its writes are visible.  Both are no-ops for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 struct WarpCtx {   // per-warp shared memory: the planned robot's links in world space (FP32)
   float a[SIRRT_MAXL][3], b[SIRRT_MAXL][3], r[SIRRT_MAXL];   // capsule core end points + radius
@@ -251,6 +245,7 @@ template <bool HAS_HULL>
 __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
 k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsParams P) {
   __shared__ WarpCtx ctx[SIRRT_WARPS_PER_BLOCK];
+  pdl_launch_dependents();
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   WarpCtx& W = ctx[wib];
   const DScene& sc = P.sc;
@@ -487,6 +482,7 @@ template <bool HAS_HULL>
 __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
 k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellParams P) {
   __shared__ WarpCtx ctx[SIRRT_WARPS_PER_BLOCK];
+  pdl_launch_dependents();
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   WarpCtx& W = ctx[wib];
   const DScene& sc = P.sc;
@@ -925,6 +921,7 @@ __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
 k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckParams P) {
   const int lane = threadIdx.x & 31;
   const DScene& sc = P.sc;
+  pdl_wait();
   if (P.fin && *(volatile unsigned int*)P.fin == P.fin_seq) return;  // the task kernel's last block has completed the call
   const unsigned int n_items = min(*P.count, P.cap);
   if (P.ticket && n_items == 0) {  // nothing to re-check (the common planner call): one block completes the call at once
@@ -1039,6 +1036,8 @@ __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
 k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskParams P) {
   const int lane = threadIdx.x & 31;
   const DScene& sc = P.sc;
+  pdl_launch_dependents();
+  pdl_wait();
   const unsigned int n_items = min(*P.count, P.cap);
   if (P.ticket && n_items == 0) {  // no deferred pair test at all
     if (blockIdx.x == 0 && *(volatile unsigned int*)P.wl.count == 0u)  // ... and nothing for the FP64 re-check either
@@ -1059,9 +1058,7 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
     } else {
       double q[SIRRT_MAXJ];
       for (int j = 0; j < rb.n_joints; j++) q[j] = j < P.q.dof ? load_q(P.q, it.config, j) : 0.0;
-      LinkXfD X[SIRRT_MAXL];
-      fk_links(rb, q, X);
-      Xl = X[l];
+      fk_one_link(rb, q, l, Xl);
     }
     float RA[9], tA[3];
 #pragma unroll

@@ -29,7 +29,8 @@ static void dump(const char* what, int calls) {
   const double cw = ph[0] ? (double)ph[0] : 1.0, tk = ph[8] ? (double)ph[8] : 1.0;
   printf(", \"collide_bits_cycles_per_warp\": {\"warps\": %llu, \"fk_and_link_table\": %.0f, \"static\": %.0f, \"dynamic\": %.0f, \"item\": %.0f, \"sincos\": %.0f, \"chain\": %.0f, \"table\": %.0f}",
          ph[0], ph[1] / cw, ph[2] / cw, ph[3] / cw, ph[4] / cw, ph[5] / cw, ph[6] / cw, ph[7] / cw);
-  printf(", \"gjk_task_cycles\": {\"tasks\": %llu, \"prologue\": %.0f, \"gjk\": %.0f, \"iters\": %.2f}", ph[8], ph[9] / tk, ph[10] / tk, ph[12] / tk);
+  printf(", \"gjk_task_cycles\": {\"tasks\": %llu, \"prologue\": %.0f, \"gjk\": %.0f, \"iters\": %.2f, \"support_A\": %.0f, \"support_B\": %.0f, \"simplex\": %.0f}", ph[8], ph[9] / tk,
+         ph[10] / tk, ph[12] / tk, ph[13] / tk, ph[14] / tk, ph[15] / tk);
   printf("}\n");
 }
 

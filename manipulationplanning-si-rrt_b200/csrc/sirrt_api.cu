@@ -90,7 +90,7 @@ static cudaError_t sirrt_sync(cudaStream_t st) {
 
 // Completion through a flag in the object's pinned host block (latency path): the last block of the call's last kernel
 // writes `seq` behind everything the call produced (RecheckParams::done, k_knn_nearest1, k_knn_radius1), and the host polls
-// its own memory -- no driver call, so 16 planner threads waiting on one GPU do not queue on the driver's lock, and the
+// its own memory (the top bit, SIRRT_FLAG_CONTINUE, is the caller's business: scene_wait) -- no driver call, so 16 planner threads waiting on one GPU do not queue on the driver's lock, and the
 // wake-up does not pay cudaStreamSynchronize's hand-shake.  The stream is queried now and then only to surface a failed
 // launch (the flag would never arrive).
 static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int* flag, unsigned int seq, float* mean_us = nullptr) {
@@ -99,10 +99,10 @@ static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int*
     const double t0 = sirrt_now_us();
     sirrt_nap(*mean_us);
     for (unsigned spin = 1;; spin++) {
-      if (*flag == seq) { *mean_us += 0.25f * ((float)(sirrt_now_us() - t0) - *mean_us); return cudaSuccess; }
+      if ((*flag & 0x7fffffffu) == seq) { *mean_us += 0.25f * ((float)(sirrt_now_us() - t0) - *mean_us); return cudaSuccess; }
       if ((spin & 0xffu) == 0) {
         const cudaError_t e = cudaStreamQuery(st);
-        if (e == cudaSuccess) return *flag == seq ? cudaSuccess : cudaErrorUnknown;
+        if (e == cudaSuccess) return (*flag & 0x7fffffffu) == seq ? cudaSuccess : cudaErrorUnknown;
         if (e != cudaErrorNotReady) return e;
       }
       sched_yield();
@@ -110,13 +110,13 @@ static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int*
   }
   if (mode == 2) {  // sleeping wait: the stream's completion implies the flag
     const cudaError_t e = cudaStreamSynchronize(st);
-    return e != cudaSuccess ? e : (*flag == seq ? cudaSuccess : cudaErrorUnknown);
+    return e != cudaSuccess ? e : ((*flag & 0x7fffffffu) == seq ? cudaSuccess : cudaErrorUnknown);
   }
   for (unsigned spin = 1;; spin++) {
-    if (*flag == seq) return cudaSuccess;
+    if ((*flag & 0x7fffffffu) == seq) return cudaSuccess;
     if ((spin & (mode ? 0xffu : 0xffffu)) == 0) {
       const cudaError_t e = cudaStreamQuery(st);
-      if (e == cudaSuccess) return *flag == seq ? cudaSuccess : cudaErrorUnknown;
+      if (e == cudaSuccess) return (*flag & 0x7fffffffu) == seq ? cudaSuccess : cudaErrorUnknown;
       if (e != cudaErrorNotReady) return e;
     }
     if (mode) sched_yield();
@@ -172,7 +172,14 @@ struct sirrt_scene {
   long long sweep_min_configs = 8192;
   long long defer_max_configs = 4096;  // hull scenes: batches up to this size hand their GJK runs to k_gjk_tasks
   DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2, xf, row1;
-  int pdl = 1;         // latency path: the kernels of a call are chained by programmatic dependent launch (SIRRT_OPT_PDL)
+  // latency path: the kernels of a call chained by programmatic dependent launch (SIRRT_OPT_PDL).  OFF by default: it saves
+  // ~1 us of a 50 us call on an idle GPU, but the pre-launched dependents hold SM slots while they wait, and 48 planner
+  // threads sharing one GPU lost 30 % of their throughput (mass test, profiles/r2e_mass_knobs_1gpu.json)
+  int pdl = 0;
+  int inline_recheck = 17;  // flag-armed hull calls: k_recheck is not queued, the task kernel's last block re-checks up to inline_recheck - 1 items (SIRRT_OPT_INLINE_RECHECK; 0 = always queue k_recheck)
+  bool k3_deferred = false;  // the pending call was launched without k_recheck; scene_wait launches it when the flag says CONTINUE
+  RecheckParams k3{};
+  unsigned k3_grid = 16;
   int slot_split = 1;  // planner-sized batches: dynamic slots of a row split over several warps (SIRRT_OPT_SLOT_SPLIT)
   // Latency path (planner in the loop): one pinned host block that the GPU reads and writes in place
   // (cudaMallocHost memory is device-addressable under UVA).  Small host inputs are memcpy'd into it and read
@@ -223,6 +230,10 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   int rc = build_tables(s->hs, parity_mode, s->tb, err);
   if (rc) { delete s; return fail(rc, "%s", err.c_str()); }
   s->device = device; s->parity_mode = parity_mode;
+  // environment overrides of the latency-path knobs (A/B measurements of whole programs, e.g. the mass test)
+  if (const char* e = getenv("SIRRT_OPT_PDL")) s->pdl = atoi(e) != 0;
+  if (const char* e = getenv("SIRRT_OPT_SLOT_SPLIT")) s->slot_split = atoi(e) != 0;
+  if (const char* e = getenv("SIRRT_OPT_INLINE_RECHECK")) s->inline_recheck = std::max(0, atoi(e));
   auto bail = [&](int code) { sirrt_scene_destroy(s); return code; };
   sirrt_apply_sync_mode(device);
   if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return bail(fail(SIRRT_E_CUDA, "cudaSetDevice failed")); }
@@ -322,6 +333,7 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
     case SIRRT_OPT_PIPELINE: s->pipeline = value != 0; break;
     case SIRRT_OPT_SLOT_SPLIT: s->slot_split = value != 0; break;
     case SIRRT_OPT_PDL: s->pdl = value != 0; break;
+    case SIRRT_OPT_INLINE_RECHECK: if (value < 0 || value > 4096) return fail(SIRRT_E_ARG, "bad inline re-check limit"); s->inline_recheck = (int)value; break;
     case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
     default: return fail(SIRRT_E_ARG, "unknown option");
   }

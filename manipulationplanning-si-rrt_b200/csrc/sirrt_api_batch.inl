@@ -26,14 +26,25 @@ static cudaError_t launch_after(bool pdl, void (*kernel)(KArgs...), unsigned gri
 // the call's last kernel (k_recheck on the latency path) will write the next sequence number to PIN_FLAG
 static void arm_done(sirrt_scene* s, RecheckParams& R) {
   R.done = (unsigned int*)(s->pinned + PIN_FLAG);
-  R.done_seq = ++s->done_seq;
+  if (++s->done_seq >= 0x40000000u) s->done_seq = 1;  // the top bit of the flag is SIRRT_FLAG_CONTINUE
+  R.done_seq = s->done_seq;
   s->done_armed = true;
+  s->k3_deferred = false;
 }
 // wait for the call in flight: by the pinned flag when its last kernel carries one, else by the stream
 static cudaError_t scene_wait(sirrt_scene* s) {
   if (!s->done_armed) return sirrt_sync(s->stream);
   s->done_armed = false;
-  return sirrt_wait_flag(s->stream, (const volatile unsigned int*)(s->pinned + PIN_FLAG), s->done_seq, &s->wait_mean_us);
+  const volatile unsigned int* flag = (const volatile unsigned int*)(s->pinned + PIN_FLAG);
+  cudaError_t e = sirrt_wait_flag(s->stream, flag, s->done_seq, &s->wait_mean_us);
+  if (e != cudaSuccess || !s->k3_deferred) return e;
+  s->k3_deferred = false;
+  if (*flag != (s->done_seq | SIRRT_FLAG_CONTINUE)) return cudaSuccess;
+  // the task kernel's last block found more FP64 items than it re-checks itself: k_recheck after all (it completes the call)
+  k_recheck<<<s->k3_grid, SIRRT_WARPS_PER_BLOCK * 32, 0, s->stream>>>(s->tb.robot, s->k3);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  s->stats[0]++;
+  return sirrt_wait_flag(s->stream, flag, s->done_seq, &s->wait_mean_us);
 }
 
 // Collision bit rows of configurations [0, N) (global indexing into q / d_bits).  Work is cut into
@@ -88,6 +99,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         arm_done(s, R);  // the table is the pinned host block and nothing follows this kernel: the caller waits on the flag (scene_wait)
       }
       if (timed) cudaEventRecord(s->ev[2 * i], st);
+      bool skip_k3 = false;
       if (sweep) {
         launches += sweep_launch(s->sweep, s->tb.robot, s->d, qv, wl, d_bits, W, (float)s->band, s->n_sm, st);
       } else {
@@ -129,15 +141,22 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
           G.bits = d_bits; G.n_words = W; G.cells = nullptr; G.band = (float)s->band;
           if (self_clearing) {  // the task kernel's last block completes the call when nothing is left for the FP64 re-check
             G.ticket = s->lazy_cnt + 6; G.publish = R.publish; G.done = R.done; G.done_seq = R.done_seq; G.fin = R.fin; G.fin_seq = R.fin_seq; G.iv = R.iv;
+            // flag-armed calls: k_recheck is not queued at all (the last block re-checks a handful of items itself; with more
+            // it raises SIRRT_FLAG_CONTINUE and scene_wait launches k_recheck)
+            if (R.done && s->inline_recheck) { G.inline_recheck = s->inline_recheck; G.aabb_d = s->d_aabb_d; skip_k3 = true; }
           }
-          CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, (unsigned)s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
+          // a single row rarely defers more than a few hundred pair tests: a grid of one block per SM (1184 warps) leaves fewer
+          // idle blocks to launch, fence and count out
+          CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, (unsigned)s->n_sm * (qv.cnt <= 2 ? 1 : 4), SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
           launches++;
         }
       }
       if (timed) cudaEventRecord(s->ev[2 * i + 1], st);
+      if (skip_k3) { s->k3 = R; s->k3_grid = 16; s->k3_deferred = true; }
+      else
       // a handful of rows leaves a handful of ambiguous pair tests: a small grid shortens the last-block hand-over
       CU(launch_after(self_clearing && s->pdl && !sweep, k_recheck, (self_clearing && N <= 64) ? 16u : (unsigned)s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, R));
-      launches++;
+      if (!skip_k3) launches++;
       CU(cudaGetLastError());
     }
     if (self_clearing) {
@@ -476,6 +495,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
     if (self_clearing) { R.ticket = s->lazy_cnt + 4; R.fin = s->lazy_cnt + 7; R.fin_seq = ++s->fin_seq; }
     if (self_clearing && flag_when_done && n0 + per >= N) arm_done(s, R);
+    bool skip_k3 = false;
     const int grid = grid_for(qv.cnt * P.n_pchunks, s->n_sm, 8);
     if (s->tb.has_hull) k_check_cells<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
     else k_check_cells<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
@@ -484,11 +504,15 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
       G.sc = s->d; G.q = qv; G.items = P.tasks.items; G.count = P.tasks.count; G.cap = P.tasks.cap; G.wl = wl; G.xf = P.xf;
       G.bits = nullptr; G.n_words = s->tb.n_tiles; G.cells = d_out; G.band = (float)s->band;
       if (self_clearing) { G.ticket = s->lazy_cnt + 6; G.publish = R.publish; G.done = R.done; G.done_seq = R.done_seq; G.fin = R.fin; G.fin_seq = R.fin_seq; }
-      CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, (unsigned)s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
+      if (self_clearing && R.done && s->inline_recheck) { G.inline_recheck = s->inline_recheck; G.aabb_d = s->d_aabb_d; skip_k3 = true; }
+      CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, (unsigned)s->n_sm * (qv.cnt <= 8 ? 1 : 4), SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
       s->stats[0]++;
     }
-    CU(launch_after(self_clearing && s->pdl, k_recheck, (self_clearing && qv.cnt <= 256) ? 16u : (unsigned)s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, R));
-    s->stats[0] += 2;
+    if (skip_k3) { s->k3 = R; s->k3_grid = 16; s->k3_deferred = true; s->stats[0] += 1; }
+    else {
+      CU(launch_after(self_clearing && s->pdl, k_recheck, (self_clearing && qv.cnt <= 256) ? 16u : (unsigned)s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, R));
+      s->stats[0] += 2;
+    }
     CU(cudaGetLastError());
   }
   return SIRRT_OK;

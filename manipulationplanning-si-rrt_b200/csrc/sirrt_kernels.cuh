@@ -917,18 +917,11 @@ __device__ __forceinline__ bool recheck_is_closed(const DRobot& rb, const DScene
 // 2^20 configurations; a warp per item idled 31 lanes through an FP64 FK of the whole chain).  Pass 2: one WARP per
 // item that needs the warp-cooperative FP64 GJK (hull links / hull obstacles), spread over the machine because a
 // planner-sized call has a handful of them and each is a long dependent chain.
-__global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
-k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckParams P) {
+// the two passes for warps warp0, warp0 + n_warps, ... (the whole grid of k_recheck, or the 8 warps of the task kernel's
+// last block when a planner-sized call left only a few items: GjkTaskParams::inline_recheck)
+__device__ __noinline__ void recheck_items(const DRobot& rb, const RecheckParams& P, unsigned int n_items, unsigned int warp0, unsigned int n_warps) {
   const int lane = threadIdx.x & 31;
   const DScene& sc = P.sc;
-  pdl_wait();
-  if (P.fin && *(volatile unsigned int*)P.fin == P.fin_seq) return;  // the task kernel's last block has completed the call
-  const unsigned int n_items = min(*P.count, P.cap);
-  if (P.ticket && n_items == 0) {  // nothing to re-check (the common planner call): one block completes the call at once
-    if (blockIdx.x == 0) finish_call(P.iv, P.counters, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
-    return;
-  }
-  const unsigned int warp0 = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5), n_warps = gridDim.x * SIRRT_WARPS_PER_BLOCK;
   unsigned int n_near = 0;
   for (unsigned int base = warp0 * 32; base < n_items; base += n_warps * 32) {
     const unsigned int w = base + lane;
@@ -989,6 +982,18 @@ k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckPara
     }
   }
   }
+}
+
+__global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
+k_recheck(const __grid_constant__ DRobot rb, const __grid_constant__ RecheckParams P) {
+  pdl_wait();
+  if (P.fin && *(volatile unsigned int*)P.fin == P.fin_seq) return;  // the task kernel's last block has completed the call
+  const unsigned int n_items = min(*P.count, P.cap);
+  if (P.ticket && n_items == 0) {  // nothing to re-check (the common planner call): one block completes the call at once
+    if (blockIdx.x == 0) finish_call(P.iv, P.counters, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
+    return;
+  }
+  recheck_items(rb, P, n_items, blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5), gridDim.x * SIRRT_WARPS_PER_BLOCK);
   if (P.ticket) {  // latency path: last block out (fuses the interval reduction,) publishes and clears the launch counters
     __shared__ bool last;
     // this block's results: bits / counters in device memory; in cell mode on the latency path the flags are the pinned host block
@@ -1030,7 +1035,13 @@ struct GjkTaskParams {
   unsigned int* fin;
   unsigned int fin_seq;
   IvParams iv;
+  // inline_recheck: k_recheck has NOT been queued behind this kernel (one launch fewer per call: the mass test is bound by
+  // the GPU's kernel-launch rate).  The last block re-checks a handful of items itself before it completes the
+  // call; with more it raises SIRRT_FLAG_CONTINUE on the completion flag and the host launches k_recheck after all.
+  int inline_recheck;         // 0: off; n: up to n - 1 items are re-checked by the last block
+  const double* aabb_d;
 };
+#define SIRRT_FLAG_CONTINUE 0x80000000u
 
 __global__ void __launch_bounds__(SIRRT_WARPS_PER_BLOCK * 32)
 k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskParams P) {
@@ -1039,7 +1050,7 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
   pdl_launch_dependents();
   pdl_wait();
   const unsigned int n_items = min(*P.count, P.cap);
-  if (P.ticket && n_items == 0) {  // no deferred pair test at all
+  if (P.ticket && n_items == 0 && (!P.inline_recheck || *(volatile unsigned int*)P.wl.count == 0u)) {  // no deferred pair test at all
     if (blockIdx.x == 0 && *(volatile unsigned int*)P.wl.count == 0u)  // ... and nothing for the FP64 re-check either
       finish_call(P.iv, P.wl.count, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
     return;
@@ -1111,7 +1122,22 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
     if (!last) return;
     __threadfence();
     if (threadIdx.x == 0) *P.ticket = 0u;
-    if (*(volatile unsigned int*)P.wl.count == 0u) finish_call(P.iv, P.wl.count, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
+    const unsigned int n_fp64 = *(volatile unsigned int*)P.wl.count;
+    if (n_fp64 == 0u) finish_call(P.iv, P.wl.count, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
+    else if (P.inline_recheck) {
+      if (n_fp64 < (unsigned int)P.inline_recheck && n_fp64 <= P.wl.cap) {  // a handful: this block's 8 warps are the re-check
+        RecheckParams R{};
+        R.sc = P.sc; R.q = P.q; R.items = P.wl.items; R.count = P.wl.count; R.cap = P.wl.cap; R.aabb_d = P.aabb_d;
+        R.bits = P.bits; R.n_words = P.n_words; R.cells = P.cells; R.counters = P.wl.count; R.done = P.done;
+        recheck_items(rb, R, n_fp64, threadIdx.x >> 5, SIRRT_WARPS_PER_BLOCK);
+        if (P.done && P.cells) __threadfence_system(); else __threadfence();
+        __syncthreads();
+        finish_call(P.iv, P.wl.count, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
+      } else if (threadIdx.x == 0 && P.done) {  // too many for one block: the host queues k_recheck (which completes the call)
+        __threadfence_system();
+        *(volatile unsigned int*)P.done = P.done_seq | SIRRT_FLAG_CONTINUE;
+      }
+    }
   }
 }
 

@@ -592,3 +592,22 @@ def test_slot_split_equals_whole_rows(pkg, orc, sp, packs, name, mode):
         for qq, f in zip(qd[:6], fr[:6]):
             if 0 <= f < ref.n_frames:
                 assert a.check_frame(qq, int(f)) == b.check_frame(qq, int(f)) == bool(ref.check_frame(qq, int(f)))
+    # the same calls with the kernels of a call chained as programmatic dependent launches
+    c = pkg.Scene(pk, 0, mode)
+    c.set_option(pkg.OPT_PDL, 1)
+    c.set_option(pkg.OPT_INLINE_RECHECK, 0)  # ... and with the FP64 re-check kernel always queued
+    for qq, f in zip(qd[:8], fr[:8]):
+        assert c.safe_intervals(qq) == a.safe_intervals(qq)
+        if 0 <= f < ref.n_frames:
+            assert c.check_frame(qq, int(f)) == a.check_frame(qq, int(f))
+    assert np.array_equal(c.check_frames_batch_f64(qd, fr), ca)
+    # every FP64 item handed back to the host (the CONTINUE path of the completion flag)
+    d = pkg.Scene(pk, 0, mode)
+    d.set_option(pkg.OPT_INLINE_RECHECK, 1)
+    for qq, f in zip(qd, fr):
+        assert d.safe_intervals(qq) == a.safe_intervals(qq)
+    assert np.array_equal(d.check_frames_batch_f64(qd, fr), ca)
+    wc = c.collision_bits_window_f64(qd, ft, 3, pkg.SEM_FRAME)
+    for i in range(24):
+        lo, hi = int(ft[i]), min(W, int(ft[i]) + 3)
+        assert np.array_equal(wc[i, lo:hi], wa[i, lo:hi]), (name, i)

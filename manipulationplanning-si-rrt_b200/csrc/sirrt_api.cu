@@ -93,16 +93,17 @@ static cudaError_t sirrt_sync(cudaStream_t st) {
 // its own memory (the top bit, SIRRT_FLAG_CONTINUE, is the caller's business: scene_wait) -- no driver call, so 16 planner threads waiting on one GPU do not queue on the driver's lock, and the
 // wake-up does not pay cudaStreamSynchronize's hand-shake.  The stream is queried now and then only to surface a failed
 // launch (the flag would never arrive).
-static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int* flag, unsigned int seq, float* mean_us = nullptr) {
+static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int* flag, unsigned int seq, float* mean_us = nullptr, bool or_continue = false) {
   const int mode = sirrt_sync_mode();
+  const unsigned int mask = or_continue ? 0x7fffffffu : 0xffffffffu;  // or_continue: seq | SIRRT_FLAG_CONTINUE also ends the wait
   if (mode == 3 && mean_us) {  // sleep through the first half of the expected wait, then poll
     const double t0 = sirrt_now_us();
     sirrt_nap(*mean_us);
     for (unsigned spin = 1;; spin++) {
-      if ((*flag & 0x7fffffffu) == seq) { *mean_us += 0.25f * ((float)(sirrt_now_us() - t0) - *mean_us); return cudaSuccess; }
+      if ((*flag & mask) == seq) { *mean_us += 0.25f * ((float)(sirrt_now_us() - t0) - *mean_us); return cudaSuccess; }
       if ((spin & 0xffu) == 0) {
         const cudaError_t e = cudaStreamQuery(st);
-        if (e == cudaSuccess) return (*flag & 0x7fffffffu) == seq ? cudaSuccess : cudaErrorUnknown;
+        if (e == cudaSuccess) return (*flag & mask) == seq ? cudaSuccess : cudaErrorUnknown;
         if (e != cudaErrorNotReady) return e;
       }
       sched_yield();
@@ -110,13 +111,13 @@ static cudaError_t sirrt_wait_flag(cudaStream_t st, const volatile unsigned int*
   }
   if (mode == 2) {  // sleeping wait: the stream's completion implies the flag
     const cudaError_t e = cudaStreamSynchronize(st);
-    return e != cudaSuccess ? e : ((*flag & 0x7fffffffu) == seq ? cudaSuccess : cudaErrorUnknown);
+    return e != cudaSuccess ? e : ((*flag & mask) == seq ? cudaSuccess : cudaErrorUnknown);
   }
   for (unsigned spin = 1;; spin++) {
-    if ((*flag & 0x7fffffffu) == seq) return cudaSuccess;
+    if ((*flag & mask) == seq) return cudaSuccess;
     if ((spin & (mode ? 0xffu : 0xffffu)) == 0) {
       const cudaError_t e = cudaStreamQuery(st);
-      if (e == cudaSuccess) return (*flag & 0x7fffffffu) == seq ? cudaSuccess : cudaErrorUnknown;
+      if (e == cudaSuccess) return (*flag & mask) == seq ? cudaSuccess : cudaErrorUnknown;
       if (e != cudaErrorNotReady) return e;
     }
     if (mode) sched_yield();
@@ -177,6 +178,8 @@ struct sirrt_scene {
   // threads sharing one GPU lost 30 % of their throughput (mass test, profiles/r2e_mass_knobs_1gpu.json)
   int pdl = 0;
   int inline_recheck = 17;  // flag-armed hull calls: k_recheck is not queued, the task kernel's last block re-checks up to inline_recheck - 1 items (SIRRT_OPT_INLINE_RECHECK; 0 = always queue k_recheck)
+  unsigned pred_tasks[3] = {1024, 256, 4096};  // deferred pair tests the last single-row / cell / table call left (task_grid)
+  int pred_kind = -1;
   bool k3_deferred = false;  // the pending call was launched without k_recheck; scene_wait launches it when the flag says CONTINUE
   RecheckParams k3{};
   unsigned k3_grid = 16;

@@ -1,6 +1,16 @@
 // sirrt_api_batch.inl -- batched collision bits / safe intervals / cell checks / edge validation.
 // Included by sirrt_api.cu.
 
+// Grid of the deferred-task kernel on the latency path: sized from the task count the same kind of call left last time on
+// this scene (x2 + slack; tasks beyond the grid are looped over, so a wrong guess costs time, never results) -- a fixed
+// machine-wide grid put ~550 idle blocks per call in front of the other planner threads' kernels.
+static unsigned task_grid(const sirrt_scene* s, int kind, long long rows) {
+  const unsigned full = (unsigned)s->n_sm * 4;
+  if (rows > 64) return full;
+  const unsigned want = (2u * s->pred_tasks[kind] + 64u + SIRRT_WARPS_PER_BLOCK - 1) / SIRRT_WARPS_PER_BLOCK;
+  return std::max(8u, std::min(full, want));
+}
+
 static int grid_for(long long warps_wanted, int n_sm, int blocks_per_sm) {
   long long blocks = (warps_wanted + SIRRT_WARPS_PER_BLOCK - 1) / SIRRT_WARPS_PER_BLOCK;
   long long cap = (long long)n_sm * blocks_per_sm;
@@ -36,7 +46,7 @@ static cudaError_t scene_wait(sirrt_scene* s) {
   if (!s->done_armed) return sirrt_sync(s->stream);
   s->done_armed = false;
   const volatile unsigned int* flag = (const volatile unsigned int*)(s->pinned + PIN_FLAG);
-  cudaError_t e = sirrt_wait_flag(s->stream, flag, s->done_seq, &s->wait_mean_us);
+  cudaError_t e = sirrt_wait_flag(s->stream, flag, s->done_seq, &s->wait_mean_us, s->k3_deferred);
   if (e != cudaSuccess || !s->k3_deferred) return e;
   s->k3_deferred = false;
   if (*flag != (s->done_seq | SIRRT_FLAG_CONTINUE)) return cudaSuccess;
@@ -60,7 +70,7 @@ static cudaError_t scene_wait(sirrt_scene* s) {
 // cleared here first).  fuse_clear: the fused interval reduction leaves the rows zeroed again (internal row buffers).
 static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_t* d_bits, bool lazy = false, int32_t* fuse_table = nullptr,
                     int fuse_kmax = 0, bool* fused = nullptr, const int2* row_tiles = nullptr, int win_tiles = 0, bool bits_clean = false,
-                    bool fuse_clear = false) {
+                    bool fuse_clear = false, uint32_t* rows_out = nullptr) {
   if (fused) *fused = false;
   s->done_armed = false;
   const int W = s->tb.n_tiles;
@@ -97,6 +107,11 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         R.iv.no_fill = fuse_clear ? 1 : 0;  // sirrt_safe_intervals reads the first `count` pairs only
         if (fused) *fused = true;
         arm_done(s, R);  // the table is the pinned host block and nothing follows this kernel: the caller waits on the flag (scene_wait)
+      } else if (self_clearing && rows_out) {  // edge tables: the call's last block copies the raw rows to the pinned block, then the flag
+        R.iv = IvParams{d_bits + (size_t)qv.n0 * W, qv.cnt, W, s->tb.T, 0, nullptr};
+        R.iv.rows_out = rows_out;
+        if (fused) *fused = true;
+        arm_done(s, R);
       }
       if (timed) cudaEventRecord(s->ev[2 * i], st);
       bool skip_k3 = false;
@@ -147,7 +162,9 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
           }
           // a single row rarely defers more than a few hundred pair tests: a grid of one block per SM (1184 warps) leaves fewer
           // idle blocks to launch, fence and count out
-          CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, (unsigned)s->n_sm * (qv.cnt <= 2 ? 1 : 4), SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
+          s->pred_kind = N == 1 ? 0 : 2;
+          CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, self_clearing ? task_grid(s, s->pred_kind, N) : (unsigned)s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, st,
+                          s->tb.robot, G));
           launches++;
         }
       }
@@ -197,6 +214,7 @@ static int finish_lazy(sirrt_scene* s) {
   const unsigned* host = (const unsigned*)(s->pinned + PIN_CNT);
   if (host[0] > s->wl_cap || host[3] > s->wl_cap) return 1;
   s->stats[1] += host[0]; s->stats[3] += host[1] + host[3]; s->stats[2] += host[2];
+  if (s->pred_kind >= 0) { s->pred_tasks[s->pred_kind] = host[3]; s->pred_kind = -1; }  // sizes the next task grid of this kind of call
   return 0;
 }
 
@@ -241,8 +259,19 @@ static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, i
   for (int attempt = 0; attempt < 2; attempt++) {
     const bool lazy = small && attempt == 0;
     if (row_tiles) CU(cudaMemsetAsync(d_bits, 0, bbytes, s->stream));  // defined content outside the rows' windows (callers only look inside)
-    int rc = run_bits(s, q, N, semantics, d_bits, lazy, nullptr, 0, nullptr, row_tiles, win_tiles, row_tiles != nullptr);
+    // planner-sized edge tables (host rows, no interval table): no copy operation and no stream synchronisation -- the
+    // call's last block leaves the rows in the pinned block and raises the completion flag
+    const bool rows_by_flag = lazy && !table && bits && !bits_dev && bbytes <= (16u << 10);
+    bool armed = false;
+    int rc = run_bits(s, q, N, semantics, d_bits, lazy, nullptr, 0, &armed, row_tiles, win_tiles, row_tiles != nullptr, false,
+                      rows_by_flag ? (uint32_t*)(s->pinned + PIN_OUT + PIN_OUT_CAP / 2) : nullptr);
     if (rc) return rc;
+    if (armed) {
+      CU(scene_wait(s));
+      if (finish_lazy(s)) continue;
+      memcpy(bits, s->pinned + PIN_OUT + PIN_OUT_CAP / 2, bbytes);
+      break;
+    }
     int32_t* t_host = nullptr;
     uint32_t* b_host = nullptr;
     if (table) {
@@ -494,7 +523,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
     R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
     if (self_clearing) { R.ticket = s->lazy_cnt + 4; R.fin = s->lazy_cnt + 7; R.fin_seq = ++s->fin_seq; }
-    if (self_clearing && flag_when_done && n0 + per >= N) arm_done(s, R);
+    if (self_clearing && flag_when_done && n0 + per >= N) { arm_done(s, R); R.publish = (unsigned int*)(s->pinned + PIN_CNT); }
     bool skip_k3 = false;
     const int grid = grid_for(qv.cnt * P.n_pchunks, s->n_sm, 8);
     if (s->tb.has_hull) k_check_cells<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
@@ -505,7 +534,8 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
       G.bits = nullptr; G.n_words = s->tb.n_tiles; G.cells = d_out; G.band = (float)s->band;
       if (self_clearing) { G.ticket = s->lazy_cnt + 6; G.publish = R.publish; G.done = R.done; G.done_seq = R.done_seq; G.fin = R.fin; G.fin_seq = R.fin_seq; }
       if (self_clearing && R.done && s->inline_recheck) { G.inline_recheck = s->inline_recheck; G.aabb_d = s->d_aabb_d; skip_k3 = true; }
-      CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, (unsigned)s->n_sm * (qv.cnt <= 8 ? 1 : 4), SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
+      s->pred_kind = 1;
+      CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, self_clearing ? task_grid(s, 1, qv.cnt) : (unsigned)s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
       s->stats[0]++;
     }
     if (skip_k3) { s->k3 = R; s->k3_grid = 16; s->k3_deferred = true; s->stats[0] += 1; }
@@ -540,6 +570,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
     d_out1[0] = 0;
     if ((rc = run_cells(s, q1, 1, nullptr, d_out1, SIRRT_SEM_FRAME, frames[0], true, true))) return rc;
     CU(scene_wait(s));
+    if (s->tb.has_hull) s->pred_tasks[1] = ((const unsigned*)(s->pinned + PIN_CNT))[3];
     collided[0] = d_out1[0];
     return SIRRT_OK;
   }
@@ -559,6 +590,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME, 0, opin, opin))) return rc;
   if (!odev && !opin) CU(cudaMemcpyAsync(collided, d_out, (size_t)N, cudaMemcpyDeviceToHost, s->stream));
   CU(scene_wait(s));
+  if (opin && s->tb.has_hull) s->pred_tasks[1] = ((const unsigned*)(s->pinned + PIN_CNT))[3];
   if (opin) memcpy(collided, d_out, (size_t)N);
   return SIRRT_OK;
 }

@@ -585,6 +585,7 @@ struct IvParams {
   int n_words, T, Kmax;
   int32_t* table;  // [N][1+2*Kmax]
   int16_t* table16 = nullptr;  // compact form of the same rows (frames < 32768); used instead of `table` when set
+  uint32_t* rows_out = nullptr;  // latency path of the edge tables: the raw rows are copied here (pinned host block) by finish_call
   int no_fill = 0;             // single-call path: the caller reads only the first `count` pairs, skip the -1 padding
   int clear_rows = 0;          // fused latency path: the rows are an internal buffer that must read zero again for the next call
 };
@@ -678,6 +679,10 @@ struct RecheckParams {
 __device__ inline void finish_call(const IvParams& iv, unsigned int* counters, unsigned int* ticket, unsigned int* publish, unsigned int* done,
                                    unsigned int done_seq, unsigned int* fin, unsigned int fin_seq) {
   const int lane = threadIdx.x & 31;
+  if (iv.rows_out) {  // covered, like the table, by thread 0's system fence behind the barrier below
+    for (long long i = threadIdx.x; i < iv.N * iv.n_words; i += blockDim.x) iv.rows_out[i] = __ldcg(iv.bits + i);
+    if (!iv.table) __syncthreads();
+  }
   if (iv.table) {
     for (long long n = threadIdx.x >> 5; n < iv.N; n += SIRRT_WARPS_PER_BLOCK) row_to_intervals(iv, n, lane);
     __syncthreads();  // thread 0's system fence below is cumulative over what the block wrote before this barrier
@@ -1055,6 +1060,10 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
       finish_call(P.iv, P.wl.count, nullptr, P.publish, P.done, P.done_seq, P.fin, P.fin_seq);
     return;
   }
+  // blocks without a task leave at once and take no ticket: under load (16+ planner threads per GPU) every resident block
+  // of this grid is an SM slot another call is waiting for
+  const unsigned int n_active = max(1u, min(gridDim.x, (n_items + SIRRT_WARPS_PER_BLOCK - 1) / SIRRT_WARPS_PER_BLOCK));
+  if (P.ticket && blockIdx.x >= n_active) return;
   for (unsigned int w = blockIdx.x * SIRRT_WARPS_PER_BLOCK + (threadIdx.x >> 5); w < n_items; w += gridDim.x * SIRRT_WARPS_PER_BLOCK) {
     PHASE_T(t_task);
     const WorkItem it = P.items[w];
@@ -1117,7 +1126,7 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
     __shared__ bool last;
     if (P.done && P.cells) __threadfence_system(); else __threadfence();  // cell flags of the latency path are the pinned host block
     __syncthreads();
-    if (threadIdx.x == 0) last = atomicAdd(P.ticket, 1u) == gridDim.x - 1;
+    if (threadIdx.x == 0) last = atomicAdd(P.ticket, 1u) == n_active - 1;
     __syncthreads();
     if (!last) return;
     __threadfence();

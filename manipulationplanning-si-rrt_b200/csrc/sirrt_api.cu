@@ -10,6 +10,7 @@
 #include <stdio.h>
 
 #include <algorithm>
+#include <atomic>
 #include <utility>
 #include <mutex>
 #include <new>
@@ -133,6 +134,21 @@ extern "C" int sirrt_device_count(void) {
   return n;
 }
 
+// Planner-sized calls in flight per device, over all scenes of the process.  Splitting a row's slots / a cell's pairs over
+// extra warps (SIRRT_OPT_SLOT_SPLIT) shortens a call on an idle GPU (k_collide_bits 23 -> 17 us) but multiplies the warps --
+// each repeating the FP64 FK -- and under load that is paid by the other callers: with 16 planner threads per GPU the
+// mass test's p50 solve time was 32-42 ms with the split against 27-29 ms without (profiles/r2e_mass_knobs_1gpu.json).  So a
+// call splits only while fewer than SIRRT_SPLIT_MAX_LOAD other calls are in flight on its device.
+#define SIRRT_SPLIT_MAX_LOAD 2
+static std::atomic<int> g_inflight[64];
+struct InFlight {
+  int dev, load;
+  explicit InFlight(int d) : dev(d >= 0 && d < 64 ? d : 0) { load = g_inflight[dev].fetch_add(1, std::memory_order_relaxed); }
+  ~InFlight() { g_inflight[dev].fetch_sub(1, std::memory_order_relaxed); }
+  InFlight(const InFlight&) = delete;
+  InFlight& operator=(const InFlight&) = delete;
+};
+
 // growable device scratch buffer
 struct DevBuf {
   void* p = nullptr;
@@ -183,6 +199,7 @@ struct sirrt_scene {
   bool k3_deferred = false;  // the pending call was launched without k_recheck; scene_wait launches it when the flag says CONTINUE
   RecheckParams k3{};
   unsigned k3_grid = 16;
+  int cur_load = 0;    // other planner-sized calls in flight on the device when the current call started (InFlight)
   int slot_split = 1;  // planner-sized batches: dynamic slots of a row split over several warps (SIRRT_OPT_SLOT_SPLIT)
   // Latency path (planner in the loop): one pinned host block that the GPU reads and writes in place
   // (cudaMallocHost memory is device-addressable under UVA).  Small host inputs are memcpy'd into it and read

@@ -138,7 +138,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         // over several warps as well (>= 4 slots per warp; the static slots of a row become one more item), words OR-ed into zeroed rows
         P.n_schunks = 1; P.slots_per_chunk = s->tb.n_dynamic;
         const long long row_warps = qv.cnt * P.n_chunks;
-        if (s->slot_split && s->tb.n_dynamic >= 16 && row_warps * 2 <= target) {
+        if (s->slot_split && s->cur_load < SIRRT_SPLIT_MAX_LOAD && s->tb.n_dynamic >= 16 && row_warps * 2 <= target) {
           const int want = (int)std::min<long long>((s->tb.n_dynamic + 3) / 4, target / row_warps);
           if (want > 1) {
             P.slots_per_chunk = (s->tb.n_dynamic + want - 1) / want;
@@ -243,6 +243,8 @@ static int stage_in(sirrt_scene* s, DevBuf& buf, const void* src, size_t bytes, 
 static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, int32_t* table, int Kmax, uint32_t* bits,
                           uint64_t* near_contact_count, const int2* row_tiles = nullptr, int win_tiles = 0) {
   const int W = s->tb.n_tiles;
+  InFlight in_flight(s->device);
+  s->cur_load = in_flight.load;
   CU(cudaSetDevice(s->device));
   memset(s->stats, 0, sizeof s->stats);
   uint32_t* d_bits = nullptr;
@@ -513,7 +515,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     P.n_pchunks = 1; P.pairs_per_chunk = 0;
     const long long target = (long long)s->n_sm * 32;
     const int rounds = (s->tb.robot.n_links * s->tb.n_slots + 31) / 32;
-    if (out_zeroed && s->slot_split && rounds >= 2 && qv.cnt * 2 <= target) {
+    if (out_zeroed && s->slot_split && s->cur_load < SIRRT_SPLIT_MAX_LOAD && rounds >= 2 && qv.cnt * 2 <= target) {
       const int want = (int)std::min<long long>(rounds, target / qv.cnt);
       const int rpc = (rounds + want - 1) / want;  // 32-pair rounds per warp
       P.pairs_per_chunk = 32 * rpc;
@@ -552,6 +554,8 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   if (!s || (!q_soa && !q_aos) || !frames || !collided || N < 0) return fail(SIRRT_E_ARG, "sirrt_check_frames_batch: bad argument");
   if (N == 0) return SIRRT_OK;
   if (N > 0x7fffffffll) return fail(SIRRT_E_ARG, "N exceeds 2^31-1 cells per call");
+  InFlight in_flight(s->device);
+  s->cur_load = in_flight.load;
   CU(cudaSetDevice(s->device));
   memset(s->stats, 0, sizeof s->stats);
   if (s->tb.n_slots == 0 && !is_device_ptr(frames) && !is_device_ptr(collided)) {
@@ -604,6 +608,8 @@ extern "C" int sirrt_check_frames_batch_f64(sirrt_scene* s, const double* q_aos,
 // ---- single-call drop-ins ------------------------------------------------------------------------
 extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo_hi, int cap, int* n_out) {
   if (!s || !q || !n_out || cap < 0 || (cap > 0 && !lo_hi)) return fail(SIRRT_E_ARG, "sirrt_safe_intervals: bad argument");
+  InFlight in_flight(s->device);
+  s->cur_load = in_flight.load;
   CU(cudaSetDevice(s->device));
   memset(s->stats, 0, sizeof s->stats);
   const int dof = s->hs.dof, W = s->tb.n_tiles, T = s->tb.T;

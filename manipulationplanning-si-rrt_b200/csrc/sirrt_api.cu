@@ -376,7 +376,8 @@ extern "C" int sirrt_debug_fk_mode(int mode) { return cudaMemcpyToSymbol(g_fk_mo
 extern "C" int sirrt_debug_phases(unsigned long long* out, int reset) {
   if (cudaDeviceSynchronize() != cudaSuccess) return SIRRT_E_CUDA;
   if (out && cudaMemcpyFromSymbol(out, g_phase, sizeof(unsigned long long) * 16) != cudaSuccess) return SIRRT_E_CUDA;
-  if (reset) { static unsigned long long z[16]; if (cudaMemcpyToSymbol(g_phase, z, sizeof z) != cudaSuccess) return SIRRT_E_CUDA; }
+  if (out && cudaMemcpyFromSymbol(out + 16, g_phase_max, sizeof(unsigned long long) * 16) != cudaSuccess) return SIRRT_E_CUDA;
+  if (reset) { static unsigned long long z[16]; if (cudaMemcpyToSymbol(g_phase, z, sizeof z) != cudaSuccess || cudaMemcpyToSymbol(g_phase_max, z, sizeof z) != cudaSuccess) return SIRRT_E_CUDA; }
   return SIRRT_OK;
 }
 #endif

@@ -1,14 +1,21 @@
 // sirrt_api_batch.inl -- batched collision bits / safe intervals / cell checks / edge validation.
 // Included by sirrt_api.cu.
 
-// Grid of the deferred-task kernel on the latency path: sized from the task count the same kind of call left last time on
-// this scene (x2 + slack; tasks beyond the grid are looped over, so a wrong guess costs time, never results) -- a fixed
-// machine-wide grid put ~550 idle blocks per call in front of the other planner threads' kernels.
+// Grid of the deferred-task kernel on the latency path (tasks beyond the grid are looped over, so its size costs time,
+// never results).  Task counts vary from 0 to several hundred between consecutive planner calls, and a call on an idle
+// GPU lasts as long as its slowest task, so an idle GPU gets at least one block per SM (a warp per task for 1184 tasks).
+// With other calls in flight on the device every resident block is an SM slot another planner thread waits for (a fixed
+// 592-block grid doubled the mass test's p50 solve time at 16 threads per GPU): the grid then follows a decaying maximum of
+// the task counts this kind of call left on the scene.
 static unsigned task_grid(const sirrt_scene* s, int kind, long long rows) {
   const unsigned full = (unsigned)s->n_sm * 4;
   if (rows > 64) return full;
   const unsigned want = (2u * s->pred_tasks[kind] + 64u + SIRRT_WARPS_PER_BLOCK - 1) / SIRRT_WARPS_PER_BLOCK;
-  return std::max(8u, std::min(full, want));
+  const unsigned floor_blocks = s->cur_load < SIRRT_SPLIT_MAX_LOAD ? (unsigned)s->n_sm : 8u;
+  return std::max(floor_blocks, std::min(full, want));
+}
+static void note_tasks(sirrt_scene* s, int kind, unsigned tasks) {
+  s->pred_tasks[kind] = std::max(tasks, s->pred_tasks[kind] - s->pred_tasks[kind] / 8);
 }
 
 static int grid_for(long long warps_wanted, int n_sm, int blocks_per_sm) {
@@ -135,18 +142,20 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         P.tiles_per_chunk = (Wr + n_chunks - 1) / n_chunks;
         P.n_chunks = (Wr + P.tiles_per_chunk - 1) / P.tiles_per_chunk;
         // planner-sized batches leave most of the machine idle with one warp per (row, tile): split the dynamic slots of each
-        // over several warps as well (>= 4 slots per warp; the static slots of a row become one more item), words OR-ed into zeroed rows
+        // over several warps as well (the static slots of a row become items of 32 pairs), words OR-ed into zeroed rows
         P.n_schunks = 1; P.slots_per_chunk = s->tb.n_dynamic;
         const long long row_warps = qv.cnt * P.n_chunks;
-        if (s->slot_split && s->cur_load < SIRRT_SPLIT_MAX_LOAD && s->tb.n_dynamic >= 16 && row_warps * 2 <= target) {
-          const int want = (int)std::min<long long>((s->tb.n_dynamic + 3) / 4, target / row_warps);
+        if (s->slot_split && s->cur_load < SIRRT_SPLIT_MAX_LOAD && s->tb.n_dynamic >= 2 && row_warps * 2 <= target) {
+          // down to ONE slot per warp: the launch lasts as long as its slowest warp, and a warp's (slot, link) pairs are serial
+          const int want = (int)std::min<long long>(s->tb.n_dynamic, target / row_warps);
           if (want > 1) {
             P.slots_per_chunk = (s->tb.n_dynamic + want - 1) / want;
             P.n_schunks = (s->tb.n_dynamic + P.slots_per_chunk - 1) / P.slots_per_chunk;
           }
         }
         if (P.n_schunks > 1 && !bits_clean) CU(cudaMemsetAsync(d_bits + (size_t)qv.n0 * W, 0, (size_t)qv.cnt * W * sizeof(uint32_t), st));
-        const int grid = grid_for(row_warps * P.n_schunks + ((P.n_schunks > 1 && s->tb.n_static > 0) ? qv.cnt : 0), s->n_sm, 8);
+        const long long static_items = (P.n_schunks > 1 && s->tb.n_static > 0) ? (long long)(s->tb.robot.n_links * s->tb.n_static + 31) / 32 : 0;
+        const int grid = grid_for(row_warps * P.n_schunks + static_items * qv.cnt, s->n_sm, 8);
         if (s->tb.has_hull) k_collide_bits<true><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         else k_collide_bits<false><<<grid, SIRRT_WARPS_PER_BLOCK * 32, 0, st>>>(s->tb.robot, P);
         launches++;
@@ -214,7 +223,7 @@ static int finish_lazy(sirrt_scene* s) {
   const unsigned* host = (const unsigned*)(s->pinned + PIN_CNT);
   if (host[0] > s->wl_cap || host[3] > s->wl_cap) return 1;
   s->stats[1] += host[0]; s->stats[3] += host[1] + host[3]; s->stats[2] += host[2];
-  if (s->pred_kind >= 0) { s->pred_tasks[s->pred_kind] = host[3]; s->pred_kind = -1; }  // sizes the next task grid of this kind of call
+  if (s->pred_kind >= 0) { note_tasks(s, s->pred_kind, host[3]); s->pred_kind = -1; }  // sizes the next task grid of this kind of call
   return 0;
 }
 
@@ -574,7 +583,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
     d_out1[0] = 0;
     if ((rc = run_cells(s, q1, 1, nullptr, d_out1, SIRRT_SEM_FRAME, frames[0], true, true))) return rc;
     CU(scene_wait(s));
-    if (s->tb.has_hull) s->pred_tasks[1] = ((const unsigned*)(s->pinned + PIN_CNT))[3];
+    if (s->tb.has_hull) note_tasks(s, 1, ((const unsigned*)(s->pinned + PIN_CNT))[3]);
     collided[0] = d_out1[0];
     return SIRRT_OK;
   }
@@ -594,7 +603,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   if ((rc = run_cells(s, q, N, (const int32_t*)df, d_out, SIRRT_SEM_FRAME, 0, opin, opin))) return rc;
   if (!odev && !opin) CU(cudaMemcpyAsync(collided, d_out, (size_t)N, cudaMemcpyDeviceToHost, s->stream));
   CU(scene_wait(s));
-  if (opin && s->tb.has_hull) s->pred_tasks[1] = ((const unsigned*)(s->pinned + PIN_CNT))[3];
+  if (opin && s->tb.has_hull) note_tasks(s, 1, ((const unsigned*)(s->pinned + PIN_CNT))[3]);
   if (opin) memcpy(collided, d_out, (size_t)N);
   return SIRRT_OK;
 }

@@ -28,9 +28,12 @@ __device__ unsigned int g_gjk_hist[4][64];
 __device__ unsigned long long g_phase[16];
 #define PHASE_T(v) const long long v = clock64()
 #define PHASE_ADD(i, d) do { if (lane == 0) atomicAdd(&g_phase[i], (unsigned long long)(d)); } while (0)
+__device__ unsigned long long g_phase_max[16];  // largest single contribution per phase (the slowest warp decides a latency-bound launch)
+#define PHASE_MAX(i, d) do { if (lane == 0) atomicMax(&g_phase_max[i], (unsigned long long)(d)); } while (0)
 #else
 #define PHASE_T(v)
 #define PHASE_ADD(i, d)
+#define PHASE_MAX(i, d)
 #endif
 
 // ---------------------------------------------------------------------------------------------

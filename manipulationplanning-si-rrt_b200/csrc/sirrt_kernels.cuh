@@ -50,6 +50,35 @@ __device__ __forceinline__ void push_work(const WorkList& wl, int config, int fr
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// Warp-aggregated append of deferred tasks: every lane passes the links (bit l of mask0: the true geometry, bit l of mask2:
+// the shifted functor geometry) whose pair test (link l, slot, this lane's frame) it defers; ONE atomicAdd per warp
+// reserves the entries.  All 32 lanes must call.  (A lane-by-lane push_work is 32 same-address atomics and one L2 round
+// trip per (slot, link) on the warp's critical path.)
+__device__ __forceinline__ void push_tasks_warp(const WorkList& wl, unsigned mask0, unsigned mask2, int config, int frame, int slot, int lane) {
+  const int mine = __popc(mask0) + __popc(mask2);
+  int incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int u = __shfl_up_sync(SIRRT_FULL, incl, o); if (lane >= o) incl += u; }
+  const int total = __shfl_sync(SIRRT_FULL, incl, 31);
+  if (total == 0) return;
+  unsigned int base = 0;
+  if (lane == 0) base = atomicAdd(wl.count, (unsigned int)total);
+  unsigned int i = __shfl_sync(SIRRT_FULL, base, 0) + (unsigned int)(incl - mine);
+  for (int pass = 0; pass < 2; pass++) {
+    unsigned m = pass ? mask2 : mask0;
+    while (m) {
+      const int l = __ffs(m) - 1;
+      m &= m - 1;
+      if (i < wl.cap) {
+        WorkItem w;
+        w.config = config; w.frame = frame; w.link = (short)l; w.shifted = (short)(pass ? 2 : 0); w.slot = slot;
+        wl.items[i] = w;
+      }
+      i++;
+    }
+  }
+}
+
 struct WarpCtx {   // per-warp shared memory: the planned robot's links in world space (FP32)
   float a[SIRRT_MAXL][3], b[SIRRT_MAXL][3], r[SIRRT_MAXL];   // capsule core end points + radius
   float bc[SIRRT_MAXL][3], br[SIRRT_MAXL];                   // bounding sphere
@@ -250,8 +279,11 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   WarpCtx& W = ctx[wib];
   const DScene& sc = P.sc;
   const int n_sch = P.n_schunks > 1 ? P.n_schunks : 1;
-  // split rows: the static slots of a row are one more item of their own (beside the (tile chunk, slot chunk) items)
-  const int per_row = P.n_chunks * n_sch + ((n_sch > 1 && sc.n_static > 0) ? 1 : 0);
+  // split rows: the static slots of a row are items of their own, 32 (link, slot) pairs each (beside the (tile chunk, slot
+  // chunk) items): a latency-bound launch lasts as long as its slowest warp (measured: 35 000 cycles for the warp whose
+  // 4 slots all came near the arm, against a mean of 18 000)
+  const int n_static_items = (n_sch > 1 && sc.n_static > 0) ? (rb.n_links * sc.n_static + 31) / 32 : 0;
+  const int per_row = P.n_chunks * n_sch + n_static_items;
   const long long n_items = P.q.cnt * per_row;
   const long long warp0 = (long long)blockIdx.x * SIRRT_WARPS_PER_BLOCK + wib;
   const long long n_warps = (long long)gridDim.x * SIRRT_WARPS_PER_BLOCK;
@@ -263,7 +295,8 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   for (long long item = warp0; item < n_items; item += n_warps) {
     const long long n = P.q.n0 + item / per_row;
     const int sub = (int)(item % per_row);
-    const bool static_item = n_sch > 1 && sub == P.n_chunks * n_sch;
+    const bool static_item = n_sch > 1 && sub >= P.n_chunks * n_sch;
+    const int static_p0 = static_item ? (sub - P.n_chunks * n_sch) * 32 : 0;
     const int chunk = static_item ? 0 : sub / n_sch, sch = static_item ? 0 : sub % n_sch;
     const int j_lo = n_sch > 1 ? sch * P.slots_per_chunk : 0, j_hi = n_sch > 1 ? min(j_lo + P.slots_per_chunk, sc.n_dynamic) : sc.n_dynamic;
     int tile_lo = chunk * P.tiles_per_chunk, tile_end = sc.n_tiles;
@@ -278,6 +311,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
     const int L = rb.n_links;
 
     // evaluates one candidate for this lane; returns hit bit, pushes ambiguous work
+    unsigned defer0 = 0, defer2 = 0;  // deferred-task mode: links whose test against the current slot this lane hands to k_gjk_tasks
     auto eval_lane = [&](int l, int slot, const DSlot& S, int f, int frame_tag, bool pass) -> bool {
       // pass: this lane's (link, slot, frame) survived its cull
       const int ltype = W.type[l];
@@ -312,9 +346,9 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
           else if (r == RES_AMBIG) push_work(P.wl, (int)n, frame_tag, l, slot, 2);  // gate already passed
         }
       }
-      if (HAS_HULL && P.tasks.items) {  // small batches: spread the hull tests over the whole machine
-        if (q_true) push_work(P.tasks, (int)n, frame_tag, l, slot, 0);
-        if (do_shift && coop_shift) push_work(P.tasks, (int)n, frame_tag, l, slot, 2);
+      if (HAS_HULL && P.tasks.items) {  // small batches: spread the hull tests over the whole machine (appended by the caller, warp-aggregated)
+        if (q_true) defer0 |= 1u << l;
+        if (do_shift && coop_shift) defer2 |= 1u << l;
       } else if (HAS_HULL) {
         bool q_shift = do_shift && coop_shift;
         unsigned m1 = __ballot_sync(SIRRT_FULL, q_true), m2 = __ballot_sync(SIRRT_FULL, q_shift);
@@ -350,8 +384,8 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
     // ---- static slots: one test per (link, slot), valid for every frame --------------------
     bool static_hit = false;
     if (n_sch == 1 || static_item) {
-      const int n_pairs = L * sc.n_static;
-      for (int p0 = 0; p0 < n_pairs; p0 += 32) {
+      const int n_pairs = static_item ? min(L * sc.n_static, static_p0 + 32) : L * sc.n_static;
+      for (int p0 = static_p0; p0 < n_pairs; p0 += 32) {
         int p = p0 + lane;
         bool pass = false;
         int l = 0, slot = 0;
@@ -365,6 +399,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
           pass = dx * dx + dy * dy + dz * dz <= rr * rr && tight_overlap(sc, W, l, slot, 0, band);
         }
         bool h = eval_lane(l, slot, S, 0, -1, pass);
+        if (HAS_HULL && P.tasks.items) { push_tasks_warp(P.tasks, defer0, defer2, (int)n, -1, slot, lane); defer0 = defer2 = 0; }
         bool lane_hit = false, any_hit = false;
         if (HAS_HULL && W.qn > SIRRT_QCAP - 64) drain(-1, lane_hit, any_hit);
         static_hit |= __any_sync(SIRRT_FULL, h) | any_hit;
@@ -432,6 +467,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
               hit |= eval_lane(l, slot, S, fc, fc, pass);
               if (HAS_HULL && W.qn > SIRRT_QCAP - 64) { bool any = false; drain(tile * 32, hit, any); }
             }
+            if (HAS_HULL && P.tasks.items) { push_tasks_warp(P.tasks, defer0, defer2, (int)n, fc, slot, lane); defer0 = defer2 = 0; }
           }
         }
         bool any = false;
@@ -451,7 +487,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
       }
     }
     PHASE_T(t_end);
-    PHASE_ADD(3, t_end - t_static); PHASE_ADD(4, t_end - t_item);
+    PHASE_ADD(3, t_end - t_static); PHASE_ADD(4, t_end - t_item); PHASE_MAX(3, t_end - t_static); PHASE_MAX(4, t_end - t_item); PHASE_MAX(2, t_static - t_fk);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) n_exact += __shfl_xor_sync(SIRRT_FULL, n_exact, o);
@@ -553,8 +589,7 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
       }
       hit = __any_sync(SIRRT_FULL, h);
       if (HAS_HULL && P.tasks.items) {
-        if (q_true) push_work(P.tasks, (int)n, f, l, slot, 0);
-        if (q_shift) push_work(P.tasks, (int)n, f, l, slot, 2);
+        push_tasks_warp(P.tasks, q_true ? 1u << l : 0u, q_shift ? 1u << l : 0u, (int)n, f, slot, lane);
       } else if (HAS_HULL) {
         unsigned m1 = __ballot_sync(SIRRT_FULL, q_true), m2 = __ballot_sync(SIRRT_FULL, q_shift);
         for (int pass = 0; pass < 2 && !hit; pass++) {
@@ -1094,7 +1129,7 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
     int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids, &n_iter);
     if (lane == 0) atomicAdd(&g_gjk_hist[r == RES_AMBIG ? (enc_ids[0] >= 0 ? 3 : 2) : r][n_iter < 63 ? n_iter : 63], 1u);
     PHASE_T(t_gjk);
-    PHASE_ADD(8, 1); PHASE_ADD(9, t_pro - t_task); PHASE_ADD(10, t_gjk - t_pro); PHASE_ADD(12, n_iter);
+    PHASE_ADD(8, 1); PHASE_ADD(9, t_pro - t_task); PHASE_ADD(10, t_gjk - t_pro); PHASE_ADD(12, n_iter); PHASE_MAX(10, t_gjk - t_pro); PHASE_MAX(12, n_iter);
 #else
     int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids);
 #endif

@@ -16,5 +16,5 @@ python - <<PY
 import json
 for line in open("$OUT/${TAG}_gjk_hist.json"):
     d = json.loads(line)
-    print(d["call"], d.get("collide_bits_cycles_per_warp"), d.get("gjk_task_cycles"))
+    print(d["call"], d.get("collide_bits_cycles_per_warp"), d.get("gjk_task_cycles"), d.get("max_cycles_over_all_calls"))
 PY

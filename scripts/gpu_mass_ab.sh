@@ -6,6 +6,17 @@ OUT=gpurun_out
 mkdir -p $OUT
 python -c "import __graft_entry__ as g; g.load_build().build_host()" > $OUT/${TAG}_build.log 2>&1
 timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_planner.py -m gpu -q -x -k "slot_split or deferred or single_call or check_frames or reference_scenes or hull_support or edge_check or windowed or concurrent or collision_manager or edge_cases or planner" > $OUT/${TAG}_tests.log 2>&1; echo "tests rc=$?"; tail -3 $OUT/${TAG}_tests.log
+mkdir -p /tmp/packs
+python - <<PY
+import gzip
+for n in ("mass_test", "flying_boxes", "multiple_robots"):
+    open(f"/tmp/packs/{n}.pack", "wb").write(gzip.open(f"tests/golden/{n}.pack.gz").read())
+PY
+: > $OUT/${TAG}_latency.json
+for n in mass_test flying_boxes multiple_robots; do
+  timeout 120 manipulationplanning-si-rrt_b200/host/sirrt_latency /tmp/packs/$n.pack 500 >> $OUT/${TAG}_latency.json 2>> $OUT/${TAG}_err.log
+done
+cut -c1-260 $OUT/${TAG}_latency.json
 for rep in 1 2; do
   i=0
   for cfg in "$@"; do

@@ -24,13 +24,14 @@ static void dump(const char* what, int calls) {
     for (int i = 0; i <= mx; i++) printf("%s%u", i ? "," : "", h[v][i]);
     printf("]}");
   }
-  unsigned long long ph[16];
+  unsigned long long ph[32];
   sirrt_debug_phases(ph, 1);
   const double cw = ph[0] ? (double)ph[0] : 1.0, tk = ph[8] ? (double)ph[8] : 1.0;
   printf(", \"collide_bits_cycles_per_warp\": {\"warps\": %llu, \"fk_and_link_table\": %.0f, \"static\": %.0f, \"dynamic\": %.0f, \"item\": %.0f, \"sincos\": %.0f, \"chain\": %.0f, \"table\": %.0f}",
          ph[0], ph[1] / cw, ph[2] / cw, ph[3] / cw, ph[4] / cw, ph[5] / cw, ph[6] / cw, ph[7] / cw);
   printf(", \"gjk_task_cycles\": {\"tasks\": %llu, \"prologue\": %.0f, \"gjk\": %.0f, \"iters\": %.2f, \"support_A\": %.0f, \"support_B\": %.0f, \"simplex\": %.0f}", ph[8], ph[9] / tk,
          ph[10] / tk, ph[12] / tk, ph[13] / tk, ph[14] / tk, ph[15] / tk);
+  printf(", \"max_cycles_over_all_calls\": {\"static\": %llu, \"dynamic\": %llu, \"item\": %llu, \"gjk\": %llu, \"gjk_iters\": %llu}", ph[16 + 2], ph[16 + 3], ph[16 + 4], ph[16 + 10], ph[16 + 12]);
   printf("}\n");
 }
 

@@ -78,7 +78,8 @@ enum {
   SIRRT_OPT_HULL_CELLS = 5,     /* 1 (default): GJK support queries on hulls scan the direction cell's candidate vertices; 0: every vertex (same result) */
   SIRRT_OPT_PIPELINE = 6,       /* 1 (default): batches of more than 131072 configurations in HOST buffers run as a 3-stream pipeline (H2D || kernels || D2H) */
   SIRRT_OPT_PDL = 8,            /* 1: the kernels of one planner-sized call are chained by programmatic dependent launch (default 0: ~1 us faster per call on an idle GPU, 30 % slower when 48 planner threads share it) */
-  SIRRT_OPT_INLINE_RECHECK = 9, /* n > 0 (default 17): single-configuration / cell calls on hull scenes do not queue the FP64 re-check kernel; the task kernel's last block re-checks up to n - 1 items itself (one launch fewer per call), more are handed back to the host; 0: always queue the kernel */
+  SIRRT_OPT_INLINE_RECHECK = 9, /* n > 0 (default 9): single-configuration / cell calls on hull scenes do not queue the FP64 re-check kernel; the task kernel's last block re-checks up to n - 1 items itself (one launch fewer per call), more are handed back to the host; 0: always queue the kernel */
+  SIRRT_OPT_SEED_RECHECK = 10,  /* 1 (default): on planner-sized hull calls the FP64 re-check GJK starts from the simplex the FP32 run ended on */
   SIRRT_OPT_SLOT_SPLIT = 7,     /* 1 (default): planner-sized batches split the dynamic obstacles of a row over several warps (same result) */
   SIRRT_OPT_DEFER_MAX_CONFIGS = 4  /* hull scenes: batches up to this many configurations hand their GJK pair tests to a machine-wide task kernel (default 4096; 0 = never) */
 };

@@ -188,12 +188,13 @@ struct sirrt_scene {
   int use_sweep = 1;
   long long sweep_min_configs = 8192;
   long long defer_max_configs = 4096;  // hull scenes: batches up to this size hand their GJK runs to k_gjk_tasks
-  DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2, xf, row1;
+  DevBuf q, bits, table, frames, cells, work, tasks, counts, misc, misc2, xf, row1, seeds;
+  int seed_recheck = 1;  // latency path: the FP64 re-check of a deferred hull test starts from the FP32 run's simplex (SIRRT_OPT_SEED_RECHECK)
   // latency path: the kernels of a call chained by programmatic dependent launch (SIRRT_OPT_PDL).  OFF by default: it saves
   // ~1 us of a 50 us call on an idle GPU, but the pre-launched dependents hold SM slots while they wait, and 48 planner
   // threads sharing one GPU lost 30 % of their throughput (mass test, profiles/r2e_mass_knobs_1gpu.json)
   int pdl = 0;
-  int inline_recheck = 17;  // flag-armed hull calls: k_recheck is not queued, the task kernel's last block re-checks up to inline_recheck - 1 items (SIRRT_OPT_INLINE_RECHECK; 0 = always queue k_recheck)
+  int inline_recheck = 9;  // flag-armed hull calls: k_recheck is not queued, the task kernel's last block re-checks up to inline_recheck - 1 items -- one per warp of the block, a second round would take longer than handing them back (SIRRT_OPT_INLINE_RECHECK; 0 = always queue k_recheck)
   unsigned pred_tasks[3] = {1024, 256, 4096};  // deferred pair tests the last single-row / cell / table call left (task_grid)
   int pred_kind = -1;
   bool k3_deferred = false;  // the pending call was launched without k_recheck; scene_wait launches it when the flag says CONTINUE
@@ -253,6 +254,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   // environment overrides of the latency-path knobs (A/B measurements of whole programs, e.g. the mass test)
   if (const char* e = getenv("SIRRT_OPT_PDL")) s->pdl = atoi(e) != 0;
   if (const char* e = getenv("SIRRT_OPT_SLOT_SPLIT")) s->slot_split = atoi(e) != 0;
+  if (const char* e = getenv("SIRRT_OPT_SEED_RECHECK")) s->seed_recheck = atoi(e) != 0;
   if (const char* e = getenv("SIRRT_OPT_INLINE_RECHECK")) s->inline_recheck = std::max(0, atoi(e));
   auto bail = [&](int code) { sirrt_scene_destroy(s); return code; };
   sirrt_apply_sync_mode(device);
@@ -299,7 +301,7 @@ extern "C" void sirrt_scene_destroy(sirrt_scene* s) {
   cudaSetDevice(s->device);
   if (s->own_stream) { cudaStreamSynchronize(s->own_stream); }
   for (void* p : s->owned) cudaFree(p);
-  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->tasks, &s->counts, &s->misc, &s->misc2, &s->xf, &s->row1}) b->release();
+  for (DevBuf* b : {&s->q, &s->bits, &s->table, &s->frames, &s->cells, &s->work, &s->tasks, &s->counts, &s->misc, &s->misc2, &s->xf, &s->row1, &s->seeds}) b->release();
   if (s->pinned) cudaFreeHost(s->pinned);
   if (s->lazy_cnt) cudaFree(s->lazy_cnt);
   for (cudaEvent_t e : s->ev) cudaEventDestroy(e);
@@ -353,6 +355,7 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
     case SIRRT_OPT_PIPELINE: s->pipeline = value != 0; break;
     case SIRRT_OPT_SLOT_SPLIT: s->slot_split = value != 0; break;
     case SIRRT_OPT_PDL: s->pdl = value != 0; break;
+    case SIRRT_OPT_SEED_RECHECK: s->seed_recheck = value != 0; break;
     case SIRRT_OPT_INLINE_RECHECK: if (value < 0 || value > 4096) return fail(SIRRT_E_ARG, "bad inline re-check limit"); s->inline_recheck = (int)value; break;
     case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
     default: return fail(SIRRT_E_ARG, "unknown option");

@@ -25,6 +25,7 @@ static int grid_for(long long warps_wanted, int n_sm, int blocks_per_sm) {
 }
 
 struct Range { long long n0, cnt; };
+#define SIRRT_SEED_CAP (64u << 10)  // work-list entries that can carry a re-check seed (planner-sized calls leave a handful)
 
 // Launch of a kernel that follows another kernel of the same latency-path call: with pdl the launch carries the
 // programmatic-stream-serialization attribute (the kernel's blocks may become resident while its predecessor still runs;
@@ -100,10 +101,15 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       QView qv = q;
       qv.n0 = todo[i].n0; qv.cnt = todo[i].cnt;
       WorkList wl{s->work.as<WorkItem>(), self_clearing ? s->lazy_cnt : s->counts.as<unsigned>() + 4 * i, s->wl_cap};
+      if (self_clearing && may_defer && s->seed_recheck) {  // latency path on hull scenes: the FP64 re-check starts from the FP32 simplex
+        if (s->seeds.ensure((size_t)SIRRT_SEED_CAP * sizeof(int4))) return fail(SIRRT_E_CUDA, "cudaMalloc(re-check seeds) failed");
+        wl.seeds = s->seeds.as<int4>(); wl.seed_cap = SIRRT_SEED_CAP;
+      }
       const bool timed = !(lazy && nr == 1) && i < s->ev.size() / 2;
       RecheckParams R{};
       R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
       R.aabb_d = s->d_aabb_d; R.bits = d_bits; R.n_words = W; R.cells = nullptr; R.counters = wl.count;
+      R.seeds = wl.seeds; R.seed_cap = wl.seed_cap;
       if (self_clearing) {
         R.ticket = s->lazy_cnt + 4; R.publish = (unsigned int*)(s->pinned + PIN_CNT);
         R.fin = s->lazy_cnt + 7; R.fin_seq = ++s->fin_seq;
@@ -178,7 +184,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         }
       }
       if (timed) cudaEventRecord(s->ev[2 * i + 1], st);
-      if (skip_k3) { s->k3 = R; s->k3_grid = 16; s->k3_deferred = true; }
+      if (skip_k3) { s->k3 = R; s->k3_grid = (unsigned)s->n_sm; s->k3_deferred = true; }
       else
       // a handful of rows leaves a handful of ambiguous pair tests: a small grid shortens the last-block hand-over
       CU(launch_after(self_clearing && s->pdl && !sweep, k_recheck, (self_clearing && N <= 64) ? 16u : (unsigned)s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, R));
@@ -509,6 +515,10 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     qv.n0 = n0; qv.cnt = std::min(per, N - n0);
     if (!self_clearing) CU(cudaMemsetAsync(s->counts.p, 0, 4 * sizeof(unsigned), st));
     WorkList wl{s->work.as<WorkItem>(), self_clearing ? s->lazy_cnt : s->counts.as<unsigned>(), s->wl_cap};
+    if (self_clearing && s->tb.has_hull && s->defer_max_configs > 0 && s->seed_recheck) {
+      if (s->seeds.ensure((size_t)SIRRT_SEED_CAP * sizeof(int4))) return fail(SIRRT_E_CUDA, "cudaMalloc(re-check seeds) failed");
+      wl.seeds = s->seeds.as<int4>(); wl.seed_cap = SIRRT_SEED_CAP;
+    }
     CellParams P{};
     P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.frames = d_frames; P.frame_one = frame_one; P.out = d_out; P.semantics = semantics; P.band = (float)s->band;
     // hull scenes: every cell appends at most 2*L*slots tasks, the same bound `per` keeps under the list capacity
@@ -533,6 +543,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
     RecheckParams R{};
     R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
     R.aabb_d = s->d_aabb_d; R.bits = nullptr; R.n_words = s->tb.n_tiles; R.cells = d_out; R.counters = wl.count;
+    R.seeds = wl.seeds; R.seed_cap = wl.seed_cap;
     if (self_clearing) { R.ticket = s->lazy_cnt + 4; R.fin = s->lazy_cnt + 7; R.fin_seq = ++s->fin_seq; }
     if (self_clearing && flag_when_done && n0 + per >= N) { arm_done(s, R); R.publish = (unsigned int*)(s->pinned + PIN_CNT); }
     bool skip_k3 = false;
@@ -549,7 +560,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
       CU(launch_after(self_clearing && s->pdl, k_gjk_tasks, self_clearing ? task_grid(s, 1, qv.cnt) : (unsigned)s->n_sm * 4, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, G));
       s->stats[0]++;
     }
-    if (skip_k3) { s->k3 = R; s->k3_grid = 16; s->k3_deferred = true; s->stats[0] += 1; }
+    if (skip_k3) { s->k3 = R; s->k3_grid = (unsigned)s->n_sm; s->k3_deferred = true; s->stats[0] += 1; }
     else {
       CU(launch_after(self_clearing && s->pdl, k_recheck, (self_clearing && qv.cnt <= 256) ? 16u : (unsigned)s->n_sm * 2, SIRRT_WARPS_PER_BLOCK * 32, st, s->tb.robot, R));
       s->stats[0] += 2;

@@ -478,6 +478,7 @@ __device__ inline int warp_support(const GShape<T>& s, const T* d, T* out, int l
 }
 
 template <typename T> struct Simplex { T w[4][3]; int id[4]; int n; };
+template <typename T> __host__ __device__ __forceinline__ void gjk_point(const GShape<T>& s, int id, T* out);
 
 template <typename T> struct GjkEps;
 template <> struct GjkEps<float> { static __device__ __forceinline__ float tri() { return 1e-10f; } static __device__ __forceinline__ float tet() { return 1e-4f; } };
@@ -625,14 +626,20 @@ template <typename T> __device__ inline int simplex_closest(Simplex<T>& s, T* v,
 template <typename T, bool FINAL>
 __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* Rrel, const T* trel, T rsum, T band,
                                int lane, T* dist_out, int* enc_ids = nullptr, Simplex<T>* final_simplex = nullptr, T* final_v = nullptr,
-                               int* n_iter = nullptr) {
+                               int* n_iter = nullptr, int* last_ids = nullptr, const int* seed_ids = nullptr) {
   // enc_ids (FP32 pass only): when the answer is AMBIGUOUS because the enclosing tetrahedron is too thin to trust in
   // FP32, the four support-point ids -- the caller can certify the enclosure in FP64 from them (gjk_point / tetra_encloses)
+  // last_ids (FP32 pass): the support-point ids of the simplex an AMBIGUOUS verdict ended on (-1 = unused slot); seed_ids
+  // (FP64 re-check): start from that simplex instead of from scratch -- the same fixed point in two or three iterations
+  // instead of a dozen (a warp-wide FP64 instruction costs a lone warp 6-16 cycles on B200: 40 us per cold re-check)
   if (enc_ids) enc_ids[0] = -1;
   Simplex<T> s;
   T v[3] = {-trel[0], -trel[1], -trel[2]};  // A is centred near its origin, B near trel
   if (dot3(v, v) == T(0)) v[0] = T(1);
   T pa[3], pb[3], dl[3], nv[3], min_face = T(0);
+  auto note_last = [&]() {
+    if (last_ids) { for (int i = 0; i < 4; i++) last_ids[i] = i < s.n ? s.id[i] : -1; }
+  };
   const T REL = FINAL ? T(1e-15) : T(1e-6);
   auto support = [&](const T* dir, T* w) -> int {  // support of A - B in direction dir
 #ifdef SIRRT_GJK_STATS
@@ -653,10 +660,33 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
 #endif
     return (ia << 12) | ib;
   };
-  nv[0] = -v[0]; nv[1] = -v[1]; nv[2] = -v[2];
-  s.id[0] = support(nv, s.w[0]);
-  s.n = 1;
-  v[0] = s.w[0][0]; v[1] = s.w[0][1]; v[2] = s.w[0][2];
+  bool seeded = false;
+  if (FINAL && seed_ids && seed_ids[0] >= 0) {
+    s.n = 0;
+    for (int i = 0; i < 4; i++)
+      if (seed_ids[i] >= 0) {
+        T xa[3], xb[3], w[3];
+        gjk_point(A, seed_ids[i] >> 12, xa);
+        gjk_point(B, seed_ids[i] & 4095, xb);
+        matvec(w, Rrel, xb);
+        s.w[s.n][0] = xa[0] - (w[0] + trel[0]); s.w[s.n][1] = xa[1] - (w[1] + trel[1]); s.w[s.n][2] = xa[2] - (w[2] + trel[2]);
+        s.id[s.n] = seed_ids[i];
+        s.n++;
+      }
+    T sv[3];
+    if (simplex_closest(s, sv, min_face, lane)) {  // the seed already encloses the origin: the cores intersect
+      if (dist_out) *dist_out = -rsum;
+      return RES_HIT;
+    }
+    v[0] = sv[0]; v[1] = sv[1]; v[2] = sv[2];
+    seeded = true;
+  }
+  if (!seeded) {
+    nv[0] = -v[0]; nv[1] = -v[1]; nv[2] = -v[2];
+    s.id[0] = support(nv, s.w[0]);
+    s.n = 1;
+    v[0] = s.w[0][0]; v[1] = s.w[0][1]; v[2] = s.w[0][2];
+  }
   T vv = dot3(v, v);
   const int MAXIT = FINAL ? 256 : 48;
   for (int it = 0; it < MAXIT; it++) {
@@ -664,7 +694,9 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
     if (vv <= (FINAL ? T(1e-30) : T(1e-20))) {  // cores touch / intersect at a vertex
       if (dist_out) *dist_out = -rsum;
       if (FINAL) return RES_HIT;
-      return rsum > band ? RES_HIT : RES_AMBIG;
+      if (rsum > band) return RES_HIT;
+      note_last();
+      return RES_AMBIG;
     }
     T w[3];
     nv[0] = -v[0]; nv[1] = -v[1]; nv[2] = -v[2];
@@ -696,6 +728,7 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
       if (rsum > band) return RES_HIT;
       if (min_face > band) return RES_HIT;
       if (enc_ids && s.n == 4) { enc_ids[0] = s.id[0]; enc_ids[1] = s.id[1]; enc_ids[2] = s.id[2]; enc_ids[3] = s.id[3]; }
+      note_last();
       return RES_AMBIG;
     }
     T n2 = dot3(nvv, nvv);
@@ -707,6 +740,7 @@ __device__ inline int warp_gjk(const GShape<T>& A, const GShape<T>& B, const T* 
   if (final_simplex) { *final_simplex = s; final_v[0] = v[0]; final_v[1] = v[1]; final_v[2] = v[2]; }  // witness points (get_distances)
   if (FINAL) return ((double)d - SIRRT_SECURITY_MARGIN <= SIRRT_COLLISION_THRESHOLD) ? RES_HIT : RES_FREE;
   if (d < -band) return RES_HIT;
+  note_last();
   return RES_AMBIG;  // |d| <= band, or not converged enough to certify separation
 }
 

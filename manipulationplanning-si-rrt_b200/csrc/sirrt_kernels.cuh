@@ -33,13 +33,18 @@ struct WorkList {
   WorkItem* items;
   unsigned int* count;   // [0] entries pushed (may exceed cap), [1] exact tests, [2] near contacts
   unsigned int cap;
+  // latency path: seeds[i] = support-point ids of the FP32 GJK simplex item i ended on (x = -1: none); the FP64 re-check
+  // starts from it (warp_gjk seed_ids).  Every producer writes its entry, so a slot never carries a previous call's ids.
+  int4* seeds;
+  unsigned int seed_cap;
 };
-__device__ __forceinline__ void push_work(const WorkList& wl, int config, int frame, int link, int slot, int shifted) {
+__device__ __forceinline__ void push_work(const WorkList& wl, int config, int frame, int link, int slot, int shifted, const int* seed = nullptr) {
   unsigned int i = atomicAdd(wl.count, 1u);
   if (i < wl.cap) {
     WorkItem w;
     w.config = config; w.frame = frame; w.link = (short)link; w.shifted = (short)shifted; w.slot = slot;
     wl.items[i] = w;
+    if (wl.seeds && i < wl.seed_cap) wl.seeds[i] = seed ? make_int4(seed[0], seed[1], seed[2], seed[3]) : make_int4(-1, -1, -1, -1);
   }
 }
 
@@ -202,7 +207,7 @@ __device__ __forceinline__ void load_pose(const DScene& sc, int slot, int f, flo
 
 // warp-cooperative FP32 test of (link l, shape sh posed at slot/frame): anything involving a hull
 __device__ inline int coop_test(const DScene& sc, const float* RA, const float* tA, const DShape& lsh, const DShape& sh, int slot,
-                                int f, float band, int lane, int* enc_ids = nullptr, int* n_iter = nullptr) {
+                                int f, float band, int lane, int* enc_ids = nullptr, int* n_iter = nullptr, int* last_ids = nullptr) {
   float RB[9], tB[3];
   load_pose(sc, slot, f, RB, tB, true);
   GShape<float> A, B;
@@ -217,7 +222,7 @@ __device__ inline int coop_test(const DScene& sc, const float* RA, const float* 
   sub3(dt, tB, tA);
   matTvec(trel, RA, dt);
   float rsum = (lsh.type == SH_HULL ? 0.f : lsh.radius) + ((sh.type == SH_SPHERE || sh.type == SH_CAPSULE) ? sh.radius : 0.f);
-  return warp_gjk<float, false>(A, B, Rrel, trel, rsum, band, lane, (float*)nullptr, enc_ids, nullptr, nullptr, n_iter);
+  return warp_gjk<float, false>(A, B, Rrel, trel, rsum, band, lane, (float*)nullptr, enc_ids, nullptr, nullptr, n_iter, last_ids);
 }
 
 // Tight-AABB cull: a pair whose world AABBs are further apart than the FP32 uncertainty band on some axis cannot
@@ -707,6 +712,8 @@ struct RecheckParams {
   // everything below (finish_call) and left fin_seq in *fin -- this kernel then returns at once
   unsigned int* fin;
   unsigned int fin_seq;
+  const int4* seeds;        // per work item: the FP32 simplex to start the FP64 GJK from (WorkList::seeds), or null
+  unsigned int seed_cap;
 };
 
 // End of a latency-path call, run by ONE block (all its threads) once every result of the call is visible to it: rows ->
@@ -734,7 +741,8 @@ __device__ inline void finish_call(const IvParams& iv, unsigned int* counters, u
 }
 
 __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const LinkXfD& X, int l, const DShape& sh,
-                                      const double* pose, int lane, int* res, const int* enc_ids = nullptr, bool* near = nullptr) {
+                                      const double* pose, int lane, int* res, const int* enc_ids = nullptr, bool* near = nullptr,
+                                      const int* seed_ids = nullptr) {
   const DShape& lsh = sc.shapes[rb.link_shape[l]];
   const double *RB = pose, *tB = pose + 9;
   double d;
@@ -777,7 +785,7 @@ __device__ inline double recheck_pair(const DRobot& rb, const DScene& sc, const 
       return -rsum;
     }
   }
-  *res = warp_gjk<double, true>(A, B, Rrel, trel, rsum, 0.0, lane, &d);
+  *res = warp_gjk<double, true>(A, B, Rrel, trel, rsum, 0.0, lane, &d, nullptr, nullptr, nullptr, nullptr, nullptr, seed_ids);
   if (near) *near = fabs(d) < 1e-6;
   return d;
 }
@@ -1008,7 +1016,12 @@ __device__ __noinline__ void recheck_items(const DRobot& rb, const RecheckParams
   }
   const DShape& sh = sc.shapes[shifted ? S.shape_shift : S.shape];
   int res;
-  double d = recheck_pair(rb, sc, X, l, sh, pose, lane, &res);
+  int seed[4] = {-1, -1, -1, -1};
+  if (P.seeds && w < P.seed_cap && shifted == it.shifted) {  // (a gate item re-checks another geometry than the one its slot was pushed for: no seed)
+    const int4 sd = P.seeds[w];
+    seed[0] = sd.x; seed[1] = sd.y; seed[2] = sd.z; seed[3] = sd.w;
+  }
+  double d = recheck_pair(rb, sc, X, l, sh, pose, lane, &res, nullptr, nullptr, seed);
   if (lane == 0 && fabs(d) < 1e-6) atomicAdd(P.counters + 2, 1u);
   if (res != RES_HIT) continue;
   if (P.cells) { if (lane == 0) P.cells[it.config] = 1; continue; }
@@ -1122,16 +1135,16 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
     for (int k = 0; k < 3; k++) tA[k] = (float)Xl.t[k];
     const DSlot S = sc.slots[it.slot];
     const DShape& sh = sc.shapes[it.shifted ? S.shape_shift : S.shape];
-    int enc_ids[4];
+    int enc_ids[4], last_ids[4] = {-1, -1, -1, -1};
 #ifdef SIRRT_GJK_STATS
     int n_iter = 0;
     PHASE_T(t_pro);
-    int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids, &n_iter);
+    int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids, &n_iter, last_ids);
     if (lane == 0) atomicAdd(&g_gjk_hist[r == RES_AMBIG ? (enc_ids[0] >= 0 ? 3 : 2) : r][n_iter < 63 ? n_iter : 63], 1u);
     PHASE_T(t_gjk);
     PHASE_ADD(8, 1); PHASE_ADD(9, t_pro - t_task); PHASE_ADD(10, t_gjk - t_pro); PHASE_ADD(12, n_iter); PHASE_MAX(10, t_gjk - t_pro); PHASE_MAX(12, n_iter);
 #else
-    int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids);
+    int r = coop_test(sc, RA, tA, sc.shapes[rb.link_shape[l]], sh, it.slot, f, P.band, lane, enc_ids, nullptr, last_ids);
 #endif
     if (r == RES_AMBIG) {
       // a thin enclosing tetrahedron is certified here in FP64 by the warp that found it (it holds the FP64 link
@@ -1141,7 +1154,7 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
         r = RES_HIT;
         if (lane == 0 && near) atomicAdd(P.wl.count + 2, 1u);
       } else {
-        if (lane == 0) push_work(P.wl, it.config, it.frame, l, it.slot, it.shifted);
+        if (lane == 0) push_work(P.wl, it.config, it.frame, l, it.slot, it.shifted, last_ids);
         continue;
       }
     }
@@ -1173,6 +1186,7 @@ k_gjk_tasks(const __grid_constant__ DRobot rb, const __grid_constant__ GjkTaskPa
         RecheckParams R{};
         R.sc = P.sc; R.q = P.q; R.items = P.wl.items; R.count = P.wl.count; R.cap = P.wl.cap; R.aabb_d = P.aabb_d;
         R.bits = P.bits; R.n_words = P.n_words; R.cells = P.cells; R.counters = P.wl.count; R.done = P.done;
+        R.seeds = P.wl.seeds; R.seed_cap = P.wl.seed_cap;
         recheck_items(rb, R, n_fp64, threadIdx.x >> 5, SIRRT_WARPS_PER_BLOCK);
         if (P.done && P.cells) __threadfence_system(); else __threadfence();
         __syncthreads();

@@ -607,6 +607,13 @@ def test_slot_split_equals_whole_rows(pkg, orc, sp, packs, name, mode):
     for qq, f in zip(qd, fr):
         assert d.safe_intervals(qq) == a.safe_intervals(qq)
     assert np.array_equal(d.check_frames_batch_f64(qd, fr), ca)
+    # the FP64 re-check started from scratch instead of from the FP32 run's simplex
+    e = pkg.Scene(pk, 0, mode)
+    e.set_option(pkg.OPT_SEED_RECHECK, 0)
+    for qq in qd:
+        assert e.safe_intervals(qq) == a.safe_intervals(qq)
+    assert np.array_equal(e.check_frames_batch_f64(qd, fr), ca)
+    assert np.array_equal(e.collision_bits_f64(qd, pkg.SEM_INTERVAL), a.collision_bits_f64(qd, pkg.SEM_INTERVAL))
     wc = c.collision_bits_window_f64(qd, ft, 3, pkg.SEM_FRAME)
     for i in range(24):
         lo, hi = int(ft[i]), min(W, int(ft[i]) + 3)

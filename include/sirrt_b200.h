@@ -88,6 +88,10 @@ int sirrt_scene_set_option(sirrt_scene*, int key, long long value);
  * device FK the kernels use (RobotObstacleFCL::get_collision_object_for_robot_angles,
  * RobotObstacleFCL.cpp:197-201,287-386) */
 int sirrt_scene_fk(sirrt_scene*, const double* q, double* out);
+/* the same transforms from the warp-parallel form of the chain (parallel prefix over the joints) that the
+ * planner-sized kernels use to build their FP32 link table; agrees with sirrt_scene_fk to rounding (the
+ * products associate differently), not bit for bit -- exposed so that the tests can say how closely */
+int sirrt_scene_fk_warp(sirrt_scene*, const double* q, double* out);
 
 /* ---- single-call drop-ins (latency path) ------------------------------------------------- */
 /* CollisionManager::get_safe_intervals, CollisionManager.cpp:481-547.  lo_hi receives up to `cap`

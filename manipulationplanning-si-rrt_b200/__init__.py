@@ -44,6 +44,7 @@ EXPORTS = {
     "sirrt_scene_last_stats": (_i32, [_vp, _vp]),
     "sirrt_scene_set_option": (_i32, [_vp, _i32, C.c_longlong]),
     "sirrt_scene_fk": (_i32, [_vp, _vp, _vp]),
+    "sirrt_scene_fk_warp": (_i32, [_vp, _vp, _vp]),
     "sirrt_safe_intervals": (_i32, [_vp, _vp, _vp, _i32, _vp]),
     "sirrt_check_frame": (_i32, [_vp, _vp, _i32, _vp]),
     "sirrt_get_distances": (_i32, [_vp, _vp, _i32, _vp, _vp]),
@@ -161,6 +162,13 @@ class Scene:
         q = np.ascontiguousarray(q, np.float64)
         out = np.zeros((self.n_links, 12))
         _ck(_lib.sirrt_scene_fk(self._h, q.ctypes.data, out.ctypes.data))
+        return out[:, :9].reshape(-1, 3, 3), out[:, 9:]
+
+    def fk_warp(self, q):
+        """The warp-parallel FK of the planner-sized kernels (sirrt_scene_fk_warp)."""
+        q = np.ascontiguousarray(q, np.float64)
+        out = np.zeros((self.n_links, 12))
+        _ck(_lib.sirrt_scene_fk_warp(self._h, q.ctypes.data, out.ctypes.data))
         return out[:, :9].reshape(-1, 3, 3), out[:, 9:]
 
     def safe_intervals(self, q, cap: int = 1024):

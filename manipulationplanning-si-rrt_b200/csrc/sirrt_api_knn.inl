@@ -433,6 +433,31 @@ extern "C" int sirrt_scene_fk(sirrt_scene* s, const double* q, double* out) {
   return SIRRT_OK;
 }
 
+// the warp form of the FK (parallel prefix over the joints) that the planner-sized kernels use: lane l ends up with link l
+__global__ void k_fk_dump_warp(const __grid_constant__ DRobot rb, const double* q, int dof, double* out) {
+  const int lane = threadIdx.x & 31;
+  const double my_q = (lane >= 1 && lane <= rb.n_joints && lane <= dof) ? q[lane - 1] : 0.0;
+  LinkXfD X;
+  fk_link_of_lane(rb, my_q, lane, X);
+  if (lane < rb.n_links) {
+    for (int k = 0; k < 9; k++) out[12 * lane + k] = X.R[k];
+    for (int k = 0; k < 3; k++) out[12 * lane + 9 + k] = X.t[k];
+  }
+}
+extern "C" int sirrt_scene_fk_warp(sirrt_scene* s, const double* q, double* out) {
+  if (!s || !q || !out) return fail(SIRRT_E_ARG, "sirrt_scene_fk_warp: bad argument");
+  CU(cudaSetDevice(s->device));
+  const int L = s->hs.robot.n_links, dof = s->hs.dof;
+  if (s->misc.ensure(sizeof(double) * (dof + 12 * (size_t)L))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
+  double* dq = s->misc.as<double>();
+  CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyHostToDevice, s->stream));
+  k_fk_dump_warp<<<1, 32, 0, s->stream>>>(s->tb.robot, dq, dof, dq + dof);
+  CU(cudaGetLastError());
+  CU(cudaMemcpyAsync(out, dq + dof, sizeof(double) * 12 * L, cudaMemcpyDeviceToHost, s->stream));
+  CU(sirrt_sync(s->stream));
+  return SIRRT_OK;
+}
+
 // ---- multi-GPU inside one process: contiguous shards of the configuration batch, no collective ----
 struct sirrt_multi {
   std::vector<sirrt_scene*> scenes;

@@ -618,3 +618,23 @@ def test_slot_split_equals_whole_rows(pkg, orc, sp, packs, name, mode):
     for i in range(24):
         lo, hi = int(ft[i]), min(W, int(ft[i]) + 3)
         assert np.array_equal(wc[i, lo:hi], wa[i, lo:hi]), (name, i)
+
+
+@pytest.mark.parametrize("name", ["flying_boxes", "synA_32_200", "multiple_robots"])
+def test_warp_fk_agrees_with_the_sequential_chain(pkg, orc, sp, packs, name):
+    """The planner-sized kernels build their link table from a warp-parallel FK (parallel prefix over the joints,
+    fk_link_of_lane); the products associate differently from the sequential chain of fk_links (the one the FP64 re-check and
+    the oracle walk, RobotObstacleFCL.cpp:287-386), so the transforms agree to rounding, not bit for bit: 1e-13 here, against
+    the FP32 link table's 6e-8 and the enclosure certificate's 1e-9 m margin."""
+    pk = packs(name)
+    dev = pkg.Scene(pk)
+    ref = orc.Oracle(pk)
+    q = random_q(sp, pk, 64, 5).T.astype(np.float64)
+    worst = 0.0
+    for qq in q:
+        R1, t1 = dev.fk(qq)
+        R2, t2 = dev.fk_warp(qq)
+        worst = max(worst, float(np.abs(R1 - R2).max()), float(np.abs(t1 - t2).max()))
+        Ro, to = ref.fk(qq)
+        assert np.abs(R2 - Ro).max() < 1e-12 and np.abs(t2 - to).max() < 1e-12
+    assert worst < 1e-13, worst

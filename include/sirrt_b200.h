@@ -80,6 +80,7 @@ enum {
   SIRRT_OPT_PDL = 8,            /* 1: the kernels of one planner-sized call are chained by programmatic dependent launch (default 0: ~1 us faster per call on an idle GPU, 30 % slower when 48 planner threads share it) */
   SIRRT_OPT_INLINE_RECHECK = 9, /* n > 0 (default 9): single-configuration / cell calls on hull scenes do not queue the FP64 re-check kernel; the task kernel's last block re-checks up to n - 1 items itself (one launch fewer per call), more are handed back to the host; 0: always queue the kernel */
   SIRRT_OPT_SEED_RECHECK = 10,  /* 1 (default): on planner-sized hull calls the FP64 re-check GJK starts from the simplex the FP32 run ended on */
+  SIRRT_OPT_HOST_BUFFERS = 11,  /* 1: the caller promises HOST memory for every buffer it passes to any entry point of this scene (the C++ shim does: std::vector storage only) -- no pointer-attribute query per pointer and call; default 0 */
   SIRRT_OPT_SLOT_SPLIT = 7,     /* 1 (default): planner-sized batches split the dynamic obstacles of a row over several warps (same result) */
   SIRRT_OPT_DEFER_MAX_CONFIGS = 4  /* hull scenes: batches up to this many configurations hand their GJK pair tests to a machine-wide task kernel (default 4096; 0 = never) */
 };
@@ -164,6 +165,9 @@ int sirrt_knn_create(int dim, int64_t capacity, int device, sirrt_knn** out);
 int sirrt_knn_destroy(sirrt_knn*);
 int sirrt_knn_size(const sirrt_knn*, int64_t* n);
 int sirrt_knn_info(const sirrt_knn*, int* dim, int64_t* capacity, int* device); /* any pointer may be NULL */
+/* on != 0: the caller promises host memory for every buffer it passes to this store (as SIRRT_OPT_HOST_BUFFERS does
+ * for a scene): the single-point add / single-query calls of a planner then skip the pointer-attribute queries */
+int sirrt_knn_host_buffers(sirrt_knn*, int on);
 int sirrt_knn_clear(sirrt_knn*);
 int sirrt_knn_add(sirrt_knn*, const double* pts /*[n][dim]*/, int64_t n);
 /* nq == 1 with host buffers: single-launch latency path; nq > 1: tiled multi-query kernel (FP32 filter with a rigorous

@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_DIR, "libsirrt_b200.so")
 
 PARITY_REFERENCE_EXACT, PARITY_FIXED = 0, 1
 SEM_INTERVAL, SEM_FRAME = 0, 1
-OPT_USE_SWEEP, OPT_CHUNK_CONFIGS, OPT_WORKLIST_CAP, OPT_SWEEP_MIN_CONFIGS, OPT_DEFER_MAX_CONFIGS, OPT_HULL_CELLS, OPT_PIPELINE, OPT_SLOT_SPLIT, OPT_PDL, OPT_INLINE_RECHECK, OPT_SEED_RECHECK = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10
+OPT_USE_SWEEP, OPT_CHUNK_CONFIGS, OPT_WORKLIST_CAP, OPT_SWEEP_MIN_CONFIGS, OPT_DEFER_MAX_CONFIGS, OPT_HULL_CELLS, OPT_PIPELINE, OPT_SLOT_SPLIT, OPT_PDL, OPT_INLINE_RECHECK, OPT_SEED_RECHECK, OPT_HOST_BUFFERS = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(
@@ -45,6 +45,7 @@ EXPORTS = {
     "sirrt_scene_set_option": (_i32, [_vp, _i32, C.c_longlong]),
     "sirrt_scene_fk": (_i32, [_vp, _vp, _vp]),
     "sirrt_scene_fk_warp": (_i32, [_vp, _vp, _vp]),
+    "sirrt_knn_host_buffers": (_i32, [_vp, _i32]),
     "sirrt_safe_intervals": (_i32, [_vp, _vp, _vp, _i32, _vp]),
     "sirrt_check_frame": (_i32, [_vp, _vp, _i32, _vp]),
     "sirrt_get_distances": (_i32, [_vp, _vp, _i32, _vp, _vp]),

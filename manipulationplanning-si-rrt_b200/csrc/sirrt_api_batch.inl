@@ -24,6 +24,10 @@ static int grid_for(long long warps_wanted, int n_sm, int blocks_per_sm) {
   return (int)std::max(1ll, std::min(blocks, cap));
 }
 
+// pointer classification: a caller that has promised host buffers for the whole scene (SIRRT_OPT_HOST_BUFFERS; the C++ shim
+// passes std::vector storage only) is spared the driver query per pointer and call on the planner-in-the-loop entry points
+static inline bool dev_ptr(const sirrt_scene* s, const void* p) { return s->host_buffers ? false : is_device_ptr(p); }
+
 struct Range { long long n0, cnt; };
 #define SIRRT_SEED_CAP (64u << 10)  // work-list entries that can carry a re-check seed (planner-sized calls leave a handful)
 
@@ -243,7 +247,7 @@ static int run_intervals(sirrt_scene* s, const uint32_t* d_bits, long long N, in
 
 // bring a caller buffer onto the device (no-op for device pointers)
 static int stage_in(sirrt_scene* s, DevBuf& buf, const void* src, size_t bytes, const void** dev, size_t pin_off = 0, size_t pin_cap = 0) {
-  if (is_device_ptr(src)) { *dev = src; return 0; }
+  if (dev_ptr(s, src)) { *dev = src; return 0; }
   if (bytes <= pin_cap) {  // latency path: the kernels read the pinned block in place
     memcpy(s->pinned + pin_off, src, bytes);
     *dev = s->pinned + pin_off;
@@ -263,14 +267,14 @@ static int bits_and_table(sirrt_scene* s, QView q, long long N, int semantics, i
   CU(cudaSetDevice(s->device));
   memset(s->stats, 0, sizeof s->stats);
   uint32_t* d_bits = nullptr;
-  const bool bits_dev = bits && is_device_ptr(bits);
+  const bool bits_dev = bits && dev_ptr(s, bits);
   if (bits_dev) d_bits = bits;
   else {
     if (s->bits.ensure((size_t)N * W * sizeof(uint32_t))) return fail(SIRRT_E_CUDA, "cudaMalloc(bits) failed");
     d_bits = s->bits.as<uint32_t>();
   }
   const size_t tbytes = table ? (size_t)N * (1 + 2 * Kmax) * sizeof(int32_t) : 0, bbytes = (size_t)N * W * sizeof(uint32_t);
-  const bool tdev = table && is_device_ptr(table);
+  const bool tdev = table && dev_ptr(s, table);
   // latency path: one launch set, results through the pinned block, one synchronisation
   const bool small = N <= s->chunk_configs && (!table || tdev || tbytes <= PIN_OUT_CAP / 2) && (!bits || bits_dev || bbytes <= PIN_OUT_CAP / 2);
   for (int attempt = 0; attempt < 2; attempt++) {
@@ -578,7 +582,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   s->cur_load = in_flight.load;
   CU(cudaSetDevice(s->device));
   memset(s->stats, 0, sizeof s->stats);
-  if (s->tb.n_slots == 0 && !is_device_ptr(frames) && !is_device_ptr(collided)) {
+  if (s->tb.n_slots == 0 && !dev_ptr(s, frames) && !dev_ptr(s, collided)) {
     // EMPTY WORKLOAD, not a fallback: a scene without obstacles (STRRT/scene_task.json ships "obstacles": []) has
     // no (link, obstacle) pair to test, so no kernel has anything to compute; only the frame range rule remains
     for (int64_t i = 0; i < N; i++) collided[i] = (frames[i] < 0 || frames[i] >= s->tb.T) ? 1 : 0;
@@ -586,7 +590,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   }
   const void *dq = nullptr, *df = nullptr;
   int rc;
-  if (N == 1 && q_aos && !is_device_ptr(q_aos) && !is_device_ptr(frames) && !is_device_ptr(collided) && s->hs.dof <= SIRRT_MAXJ) {
+  if (N == 1 && q_aos && !dev_ptr(s, q_aos) && !dev_ptr(s, frames) && !dev_ptr(s, collided) && s->hs.dof <= SIRRT_MAXJ) {
     // latency path, one cell: angles and frame travel in the kernel parameters, the answer lands in the pinned block
     QView q1{nullptr, nullptr, 1, 0, 1, s->hs.dof, 1, {}};
     for (int j = 0; j < s->hs.dof; j++) q1.inl[j] = q_aos[j];
@@ -602,7 +606,7 @@ static int check_frames_common(sirrt_scene* s, const float* q_soa, const double*
   else rc = stage_in(s, s->q, q_aos, (size_t)N * s->hs.dof * sizeof(double), &dq, PIN_Q, 64 << 10);
   if (rc) return rc;
   if ((rc = stage_in(s, s->frames, frames, (size_t)N * sizeof(int32_t), &df, PIN_FR, PIN_FR_CAP))) return rc;
-  const bool odev = is_device_ptr(collided);
+  const bool odev = dev_ptr(s, collided);
   const bool opin = !odev && (size_t)N <= (size_t)(16 << 10);  // latency path: the kernels write the pinned block in place
   uint8_t* d_out = collided;
   if (opin) { d_out = (uint8_t*)(s->pinned + PIN_OUT); memset(d_out, 0, (size_t)N); }
@@ -650,7 +654,7 @@ extern "C" int sirrt_safe_intervals(sirrt_scene* s, const double* q, int32_t* lo
   }
   // latency path: q is read from, and the interval table written to, the pinned block in place; one synchronisation
   double* dq = (double*)(s->pinned + PIN_Q);
-  if (is_device_ptr(q)) { CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyDeviceToHost, s->stream)); CU(sirrt_sync(s->stream)); }
+  if (dev_ptr(s, q)) { CU(cudaMemcpyAsync(dq, q, sizeof(double) * dof, cudaMemcpyDeviceToHost, s->stream)); CU(sirrt_sync(s->stream)); }
   else memcpy(dq, q, sizeof(double) * dof);
   uint32_t* d_bits = s->row1.as<uint32_t>();
   const int32_t* host_table = (const int32_t*)(s->pinned + PIN_OUT);

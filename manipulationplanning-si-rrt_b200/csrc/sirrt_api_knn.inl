@@ -19,7 +19,14 @@ struct sirrt_knn {
   size_t hits_cap_zeroed = 0;      // capacity of `hits` whose counter word has been cleared
   unsigned int done_seq = 0;       // completion flag sequence (KPIN_FLAG), see sirrt_wait_flag
   float wait_mean_us = 0.f;        // SIRRT_SYNC=nap: running mean of this store's flag waits
+  int host_buffers = 0;            // sirrt_knn_host_buffers: every buffer the caller passes is host memory (no driver query per pointer)
 };
+static inline bool kdev_ptr(const sirrt_knn* k, const void* p) { return k->host_buffers ? false : is_device_ptr(p); }
+extern "C" int sirrt_knn_host_buffers(sirrt_knn* k, int on) {
+  if (!k) return fail(SIRRT_E_ARG, "null store");
+  k->host_buffers = on != 0;
+  return SIRRT_OK;
+}
 enum : size_t { KPIN_Q = 0, KPIN_Q_CAP = 16 << 10, KPIN_OUT = KPIN_Q_CAP, KPIN_OUT_CAP = 32 << 10, KPIN_RING = KPIN_OUT + KPIN_OUT_CAP,
                 KPIN_RING_SLOTS = 64, KPIN_FLAG = KPIN_RING + KPIN_RING_SLOTS * SIRRT_KNN_MAXDIM * sizeof(double), KPIN_BYTES = KPIN_FLAG + 64 };
 
@@ -115,7 +122,7 @@ extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
   { int rc = knn_grow(k, k->n + n); if (rc) return rc; }
   const size_t bytes = sizeof(double) * k->dim * (size_t)n;
   const double* src = pts;
-  if (n == 1 && !is_device_ptr(pts)) {
+  if (n == 1 && !kdev_ptr(k, pts)) {
     // Tree::add_vertex once per planner iteration: the point goes into a pinned ring slot that the append kernel
     // reads in place; nothing is synchronised (queries are ordered behind it on the same stream) except when the
     // ring wraps
@@ -127,7 +134,7 @@ extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
     k->n += 1;
     return SIRRT_OK;
   }
-  if (!is_device_ptr(pts)) {
+  if (!kdev_ptr(k, pts)) {
     if (k->stage.ensure(bytes)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
     CU(cudaMemcpyAsync(k->stage.p, pts, bytes, cudaMemcpyHostToDevice, k->stream));
     src = k->stage.as<double>();
@@ -184,7 +191,7 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
   if (k->n == 0) { for (int64_t i = 0; i < nq; i++) { idx[i] = -1; if (dist2) dist2[i] = 1.0 / 0.0; } return SIRRT_OK; }
   const double* dq = nullptr;
   int rc;
-  if (nq == 1 && !is_device_ptr(queries) && !is_device_ptr(idx) && !(dist2 && is_device_ptr(dist2))) {  // latency path: one launch, answer lands in the pinned block
+  if (nq == 1 && !kdev_ptr(k, queries) && !kdev_ptr(k, idx) && !(dist2 && kdev_ptr(k, dist2))) {  // latency path: one launch, answer lands in the pinned block
     const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
     if (k->part_d.ensure(sizeof(double) * (size_t)k->n_sm * 4) || k->part_i.ensure(sizeof(long long) * (size_t)k->n_sm * 4)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
     KnnStore S1{k->pts, k->cap, k->n, k->dim};
@@ -234,7 +241,7 @@ extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, in
   if (k->n == 0) return SIRRT_OK;
   CU(cudaSetDevice(k->device));
   KnnQuery Q{};
-  if (is_device_ptr(query)) CU(cudaMemcpy(Q.v, query, sizeof(double) * k->dim, cudaMemcpyDeviceToHost));
+  if (kdev_ptr(k, query)) CU(cudaMemcpy(Q.v, query, sizeof(double) * k->dim, cudaMemcpyDeviceToHost));
   else for (int j = 0; j < k->dim; j++) Q.v[j] = query[j];
   // hits layout on the device: [count][hit 0][hit 1]...; ONE launch: the last block to finish copies the count and
   // the first hits into the pinned block and clears the counter for the next query

@@ -110,6 +110,7 @@ class B200Backend {
       k = pool_->back(); pool_->pop_back();
       int dim = 0, dev = -1;
       if (sirrt_knn_info(k, &dim, nullptr, &dev) == SIRRT_OK && dim == dof() && dev == device_) {  // a pooled store of another robot / device is of no use
+        sirrt_knn_host_buffers(k, 1);
         knn_.push_back(k);
         return (int)knn_.size() - 1;
       }
@@ -118,6 +119,7 @@ class B200Backend {
     }
     // the reference reserves 1e6 vertices per tree (PlannerConnect.cpp:16-18); the store grows on demand instead
     if (sirrt_knn_create(dof(), 1 << 14, device_, &k) != SIRRT_OK) throw std::runtime_error(std::string("libsirrt_b200: ") + sirrt_last_error());
+    sirrt_knn_host_buffers(k, 1);  // the planner passes host vectors only
     knn_.push_back(k);
     return (int)knn_.size() - 1;
   }

@@ -32,6 +32,7 @@ class CollisionManager {
   explicit CollisionManager(const std::vector<unsigned char>& scene_pack, int device = 0, int parity_mode = SIRRT_PARITY_REFERENCE_EXACT) {
     if (sirrt_scene_create_from_pack(scene_pack.data(), scene_pack.size(), device, parity_mode, &scene_) != SIRRT_OK)
       throw std::runtime_error(std::string("CollisionManager: ") + sirrt_last_error());
+    sirrt_scene_set_option(scene_, SIRRT_OPT_HOST_BUFFERS, 1);  // this class and its users (B200Backend, the validators) pass host vectors only
     sirrt_scene_info(scene_, &dof_, &n_links_, &frame_count_, &fps_, nullptr);
     limits_.resize(2 * (size_t)dof_);
     sirrt_scene_info(scene_, nullptr, nullptr, nullptr, nullptr, limits_.data());

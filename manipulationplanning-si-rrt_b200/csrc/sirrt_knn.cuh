@@ -136,6 +136,15 @@ k_knn_nearest1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQu
     if (d < best) { best = d; bi = i; }  // ascending i per thread: strict < keeps the first
   }
   knn_block_min(best, bi, sd, si);
+  if (gridDim.x == 1) {  // small trees (up to one block of points): no partial results, no ticket -- the block minimum is the answer
+    if (threadIdx.x == 0) {
+      out_idx[0] = bi == 0x7fffffffffffffffll ? -1 : bi;
+      out_d2[0] = best;
+      __threadfence_system();
+      *(volatile unsigned int*)done = done_seq;
+    }
+    return;
+  }
   if (threadIdx.x == 0) {
     pd[blockIdx.x] = best; pi[blockIdx.x] = bi;
     __threadfence();
@@ -182,17 +191,19 @@ k_knn_radius1(const __grid_constant__ KnnStore S, const __grid_constant__ KnnQue
     base = __shfl_sync(0xffffffffu, base, 0);
     if (in) hits[1 + base + __popc(m & ((1u << lane) - 1))] = (int)i;
   }
-  __threadfence();
+  if (gridDim.x > 1) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+  }
+  __threadfence();  // (one block: its own atomics and stores, ordered for the reads below)
   __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
-  __syncthreads();
-  if (!last) return;
-  __threadfence();
   const unsigned cnt = *(volatile unsigned int*)count;
   const int ncopy = (int)min(cnt, (unsigned)first);
   for (int i = threadIdx.x; i < ncopy; i += blockDim.x) out[1 + i] = ((volatile int*)hits)[1 + i];
-  __threadfence_system();
-  __syncthreads();
+  __syncthreads();  // thread 0's system fence below is cumulative over the copies made before this barrier
   if (threadIdx.x == 0) {
     out[0] = (int)cnt; *count = 0; *ticket = 0;
     __threadfence_system();

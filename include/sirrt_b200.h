@@ -81,6 +81,7 @@ enum {
   SIRRT_OPT_INLINE_RECHECK = 9, /* n > 0 (default 9): single-configuration / cell calls on hull scenes do not queue the FP64 re-check kernel; the task kernel's last block re-checks up to n - 1 items itself (one launch fewer per call), more are handed back to the host; 0: always queue the kernel */
   SIRRT_OPT_SEED_RECHECK = 10,  /* 1 (default): on planner-sized hull calls the FP64 re-check GJK starts from the simplex the FP32 run ended on */
   SIRRT_OPT_HOST_BUFFERS = 11,  /* 1: the caller promises HOST memory for every buffer it passes to any entry point of this scene (the C++ shim does: std::vector storage only) -- no pointer-attribute query per pointer and call; default 0 */
+  SIRRT_OPT_OBB_CULL = 12,      /* 1 (default): pair tests that involve a convex hull are preceded by a 15-axis separating-axis test of the two shapes' oriented bounding boxes (decides "certainly free" only; same results, fewer GJK runs) */
   SIRRT_OPT_SLOT_SPLIT = 7,     /* 1 (default): planner-sized batches split the dynamic obstacles of a row over several warps (same result) */
   SIRRT_OPT_DEFER_MAX_CONFIGS = 4  /* hull scenes: batches up to this many configurations hand their GJK pair tests to a machine-wide task kernel (default 4096; 0 = never) */
 };

@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_DIR, "libsirrt_b200.so")
 
 PARITY_REFERENCE_EXACT, PARITY_FIXED = 0, 1
 SEM_INTERVAL, SEM_FRAME = 0, 1
-OPT_USE_SWEEP, OPT_CHUNK_CONFIGS, OPT_WORKLIST_CAP, OPT_SWEEP_MIN_CONFIGS, OPT_DEFER_MAX_CONFIGS, OPT_HULL_CELLS, OPT_PIPELINE, OPT_SLOT_SPLIT, OPT_PDL, OPT_INLINE_RECHECK, OPT_SEED_RECHECK, OPT_HOST_BUFFERS = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11
+OPT_USE_SWEEP, OPT_CHUNK_CONFIGS, OPT_WORKLIST_CAP, OPT_SWEEP_MIN_CONFIGS, OPT_DEFER_MAX_CONFIGS, OPT_HULL_CELLS, OPT_PIPELINE, OPT_SLOT_SPLIT, OPT_PDL, OPT_INLINE_RECHECK, OPT_SEED_RECHECK, OPT_HOST_BUFFERS, OPT_OBB_CULL = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12
 
 if not os.path.exists(LIB_PATH):
     raise ImportError(

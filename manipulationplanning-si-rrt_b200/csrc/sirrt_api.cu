@@ -200,6 +200,7 @@ struct sirrt_scene {
   bool k3_deferred = false;  // the pending call was launched without k_recheck; scene_wait launches it when the flag says CONTINUE
   RecheckParams k3{};
   unsigned k3_grid = 16;
+  int obb_cull = 1;      // hull pair tests preceded by the oriented-box separating-axis cull (SIRRT_OPT_OBB_CULL)
   int host_buffers = 0;  // the caller promises host memory for every buffer of the single-call / cell / edge-table entry points (SIRRT_OPT_HOST_BUFFERS)
   int cur_load = 0;    // other planner-sized calls in flight on the device when the current call started (InFlight)
   int slot_split = 1;  // planner-sized batches: dynamic slots of a row split over several warps (SIRRT_OPT_SLOT_SPLIT)
@@ -255,6 +256,7 @@ extern "C" int sirrt_scene_create_from_pack(const void* pack, size_t bytes, int 
   // environment overrides of the latency-path knobs (A/B measurements of whole programs, e.g. the mass test)
   if (const char* e = getenv("SIRRT_OPT_PDL")) s->pdl = atoi(e) != 0;
   if (const char* e = getenv("SIRRT_OPT_SLOT_SPLIT")) s->slot_split = atoi(e) != 0;
+  if (const char* e = getenv("SIRRT_OPT_OBB_CULL")) s->obb_cull = atoi(e) != 0;
   if (const char* e = getenv("SIRRT_OPT_SEED_RECHECK")) s->seed_recheck = atoi(e) != 0;
   if (const char* e = getenv("SIRRT_OPT_INLINE_RECHECK")) s->inline_recheck = std::max(0, atoi(e));
   auto bail = [&](int code) { sirrt_scene_destroy(s); return code; };
@@ -358,6 +360,7 @@ extern "C" int sirrt_scene_set_option(sirrt_scene* s, int key, long long value) 
     case SIRRT_OPT_PDL: s->pdl = value != 0; break;
     case SIRRT_OPT_SEED_RECHECK: s->seed_recheck = value != 0; break;
     case SIRRT_OPT_HOST_BUFFERS: s->host_buffers = value != 0; break;
+    case SIRRT_OPT_OBB_CULL: s->obb_cull = value != 0; break;
     case SIRRT_OPT_INLINE_RECHECK: if (value < 0 || value > 4096) return fail(SIRRT_E_ARG, "bad inline re-check limit"); s->inline_recheck = (int)value; break;
     case SIRRT_OPT_WORKLIST_CAP: if (value < 64 || value > (1ll << 28)) return fail(SIRRT_E_ARG, "bad worklist cap"); s->wl_cap = (unsigned)value; break;
     default: return fail(SIRRT_E_ARG, "unknown option");

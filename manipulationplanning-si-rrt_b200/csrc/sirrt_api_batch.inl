@@ -137,7 +137,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       } else {
         BitsParams P{};
         P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.bits = d_bits; P.n_words = W;
-        P.semantics = semantics; P.band = (float)s->band;
+        P.semantics = semantics; P.band = (float)s->band; P.obb_cull = s->obb_cull;
         P.row_tiles = row_tiles ? row_tiles + qv.n0 : nullptr;
         const bool defer = may_defer && qv.cnt <= s->defer_max_configs && nr == 1;  // one task list: one range at a time
         if (defer) {
@@ -377,7 +377,7 @@ static int bits_and_table_pipelined(sirrt_scene* s, const float* hq, long long N
     if (sweep) launches += sweep_launch(s->sweep, s->tb.robot, s->d, qv, wl, d_bits, W, (float)s->band, s->n_sm, st);
     else {
       BitsParams P{};
-      P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.bits = d_bits; P.n_words = W; P.semantics = SIRRT_SEM_INTERVAL; P.band = (float)s->band;
+      P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.bits = d_bits; P.n_words = W; P.semantics = SIRRT_SEM_INTERVAL; P.band = (float)s->band; P.obb_cull = s->obb_cull;
       const long long target = (long long)s->n_sm * 32;
       int n_chunks = (int)std::max(1ll, std::min((long long)W, target / std::max(1ll, cnt)));
       P.tiles_per_chunk = (W + n_chunks - 1) / n_chunks;
@@ -524,7 +524,7 @@ static int run_cells(sirrt_scene* s, QView q, long long N, const int32_t* d_fram
       wl.seeds = s->seeds.as<int4>(); wl.seed_cap = SIRRT_SEED_CAP;
     }
     CellParams P{};
-    P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.frames = d_frames; P.frame_one = frame_one; P.out = d_out; P.semantics = semantics; P.band = (float)s->band;
+    P.sc = s->d; P.q = qv; P.wl = wl; P.aabb_f = s->d_aabb_f; P.frames = d_frames; P.frame_one = frame_one; P.out = d_out; P.semantics = semantics; P.band = (float)s->band; P.obb_cull = s->obb_cull;
     // hull scenes: every cell appends at most 2*L*slots tasks, the same bound `per` keeps under the list capacity
     const bool defer = s->tb.has_hull && s->defer_max_configs > 0 && qv.cnt <= 64 * s->defer_max_configs;
     if (defer) {

@@ -90,6 +90,7 @@ struct WarpCtx {   // per-warp shared memory: the planned robot's links in world
   float R[SIRRT_MAXL][9], t[SIRRT_MAXL][3];                  // link transform
   float alo[SIRRT_MAXL][3], ahi[SIRRT_MAXL][3];              // coal AABB (QUIRK 7 broadphase gate)
   float tlo[SIRRT_MAXL][3], thi[SIRRT_MAXL][3];              // tight world AABB (cull before the narrowphase)
+  float oc[SIRRT_MAXL][3], oh[SIRRT_MAXL][3];                // oriented box of the link: world centre of its local AABB, local half extents (axes = columns of R)
   int type[SIRRT_MAXL];
   int qn;
   unsigned long long q[SIRRT_QCAP];                          // cooperative (hull) task queue
@@ -143,6 +144,8 @@ __device__ inline void setup_links(const DRobot& rb, const DScene& sc, const QVi
       float cw[3];  // world position of the local AABB centre
 #pragma unroll
       for (int k = 0; k < 3; k++) cw[k] = Rf[3 * k] * sh.ac[0] + Rf[3 * k + 1] * sh.ac[1] + Rf[3 * k + 2] * sh.ac[2] + tf[k];
+#pragma unroll
+      for (int k = 0; k < 3; k++) { W.oc[l][k] = cw[k]; W.oh[l][k] = 0.5f * (sh.amax[k] - sh.amin[k]); }
 #pragma unroll
       for (int k = 0; k < 3; k++) {  // tight world AABB: centre R*ac + t, half extents sum_j |R_kj| (amax_j - amin_j)/2, widened
         float e = 0.f;
@@ -239,6 +242,48 @@ __device__ __forceinline__ bool tight_overlap(const DScene& sc, const WarpCtx& W
   return ov;
 }
 
+// Oriented-box cull for pair tests that would otherwise become a GJK run (anything involving a hull): the link's local
+// AABB posed by the link transform against the obstacle shape's local AABB posed at (RB, tB), 15-axis separating-axis test.
+// Both boxes contain their shapes, so a separating axis with more than `margin` of clearance proves the pair FREE; nothing
+// else is decided here (results unchanged, GJK runs saved: 40-85 % of the deferred tasks end FREE).  The cross-product axes
+// are not normalised (|a x b| <= 1), which only makes the required clearance larger; EPS guards near-parallel axes.
+__device__ inline bool obb_separated(const WarpCtx& W, int l, const DShape& sb, const float* RB, const float* tB, float margin) {
+  const float* RA = W.R[l];
+  float hb[3], cb[3], d[3], t[3], R[3][3], AR[3][3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) hb[k] = 0.5f * (sb.amax[k] - sb.amin[k]);
+#pragma unroll
+  for (int k = 0; k < 3; k++) cb[k] = RB[3 * k] * sb.ac[0] + RB[3 * k + 1] * sb.ac[1] + RB[3 * k + 2] * sb.ac[2] + tB[k];
+#pragma unroll
+  for (int k = 0; k < 3; k++) d[k] = cb[k] - W.oc[l][k];
+#pragma unroll
+  for (int i = 0; i < 3; i++) {  // axes = columns of the rotations
+    t[i] = RA[i] * d[0] + RA[3 + i] * d[1] + RA[6 + i] * d[2];
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      R[i][j] = RA[i] * RB[j] + RA[3 + i] * RB[3 + j] + RA[6 + i] * RB[6 + j];
+      AR[i][j] = fabsf(R[i][j]) + 1e-6f;
+    }
+  }
+  const float* ha = W.oh[l];
+  bool sep = false;
+#pragma unroll
+  for (int i = 0; i < 3; i++) sep |= fabsf(t[i]) > ha[i] + hb[0] * AR[i][0] + hb[1] * AR[i][1] + hb[2] * AR[i][2] + margin;
+#pragma unroll
+  for (int j = 0; j < 3; j++)
+    sep |= fabsf(t[0] * R[0][j] + t[1] * R[1][j] + t[2] * R[2][j]) > ha[0] * AR[0][j] + ha[1] * AR[1][j] + ha[2] * AR[2][j] + hb[j] + margin;
+#pragma unroll
+  for (int i = 0; i < 3; i++) {
+    const int i1 = (i + 1) % 3, i2 = (i + 2) % 3;
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+      const int j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+      sep |= fabsf(t[i2] * R[i1][j] - t[i1] * R[i2][j]) > ha[i1] * AR[i2][j] + ha[i2] * AR[i1][j] + hb[j1] * AR[i][j2] + hb[j2] * AR[i][j1] + margin;
+    }
+  }
+  return sep;
+}
+
 // QUIRK 7 broadphase gate: do the coal AABBs of the TRUE geometries overlap?  FP32 with margin.
 __device__ __forceinline__ int aabb_gate(const WarpCtx& W, int l, const float* blo, const float* bhi) {
   const float eps = 1e-5f;
@@ -270,6 +315,7 @@ struct BitsParams {
   int n_schunks, slots_per_chunk;
   int semantics;
   float band;
+  int obb_cull;         // hull pair tests are preceded by the oriented-box separating-axis cull (SIRRT_OPT_OBB_CULL)
 };
 
 // process one (link, slot[, shifted]) candidate at lane-frame f, or queue it for cooperative work
@@ -295,6 +341,7 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
   const bool want_true_rob = (sc.parity_mode == 1) || (P.semantics == 0);
   const bool want_shift_rob = (sc.parity_mode == 0);
   const float band = P.band;
+  const bool obb_cull = P.obb_cull != 0;
   unsigned int n_exact = 0;  // narrowphase pair tests evaluated by this lane (roofline accounting)
 
   for (long long item = warp0; item < n_items; item += n_warps) {
@@ -341,10 +388,18 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
         else if (r == RES_AMBIG) push_work(P.wl, (int)n, frame_tag, l, slot, 0);
       }
       bool q_true = do_true && coop_true;
+      if (HAS_HULL && q_true && obb_cull) {  // oriented boxes of the link and the obstacle clear of each other: no GJK run
+        load_pose(sc, slot, f, R, t, true);
+        if (obb_separated(W, l, sc.shapes[S.shape], R, t, 1e-5f + band)) q_true = false;
+      }
       bool coop_shift = false;
       if (do_shift) {
         coop_shift = HAS_HULL && (ltype == SH_HULL || S.type_shift == SH_HULL);
-        if (!coop_shift) {
+        if (coop_shift && obb_cull) {
+          load_pose(sc, slot, f, R, t, true);
+          if (obb_separated(W, l, sc.shapes[S.shape_shift], R, t, 1e-5f + band)) { coop_shift = false; do_shift = false; }
+        }
+        if (!coop_shift && do_shift) {
           load_pose(sc, slot, f, R, t, true);
           int r = lane_exact(W, l, sc.shapes[S.shape_shift], R, t, false, band);
           if (r == RES_HIT) hit = true;
@@ -517,6 +572,7 @@ struct CellParams {
   // planner-sized batches: the (link, slot) pairs of a cell are split over n_pchunks warps of pairs_per_chunk pairs (a
   // multiple of 32); a warp then only ever WRITES 1 (hit) into flags the caller has zeroed
   int n_pchunks, pairs_per_chunk;
+  int obb_cull;           // as BitsParams::obb_cull
 };
 
 template <bool HAS_HULL>
@@ -572,8 +628,13 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
             else if (g == RES_AMBIG) { push_work(P.wl, (int)n, f, l, slot, 1); do_shift = false; }
           }
           if (do_true) {
-            if (HAS_HULL && (lsh.type == SH_HULL || sh.type == SH_HULL)) q_true = true;
-            else {
+            if (HAS_HULL && (lsh.type == SH_HULL || sh.type == SH_HULL)) {
+              q_true = true;
+              if (P.obb_cull) {  // oriented boxes clear of each other: no GJK run
+                load_pose(sc, slot, f, R, t, true);
+                if (obb_separated(W, l, sh, R, t, 1e-5f + band)) q_true = false;
+              }
+            } else {
               load_pose(sc, slot, f, R, t, sh.type != SH_SPHERE && !S.rot_identity);
               int r = lane_exact(W, l, sh, R, t, S.rot_identity != 0, band);
               if (r == RES_HIT) h = true;
@@ -582,8 +643,13 @@ k_check_cells(const __grid_constant__ DRobot rb, const __grid_constant__ CellPar
           }
           if (do_shift) {
             const DShape& ss = sc.shapes[S.shape_shift];
-            if (HAS_HULL && (lsh.type == SH_HULL || ss.type == SH_HULL)) q_shift = true;
-            else {
+            if (HAS_HULL && (lsh.type == SH_HULL || ss.type == SH_HULL)) {
+              q_shift = true;
+              if (P.obb_cull) {
+                load_pose(sc, slot, f, R, t, true);
+                if (obb_separated(W, l, ss, R, t, 1e-5f + band)) q_shift = false;
+              }
+            } else {
               load_pose(sc, slot, f, R, t, true);
               int r = lane_exact(W, l, ss, R, t, false, band);
               if (r == RES_HIT) h = true;

@@ -614,6 +614,15 @@ def test_slot_split_equals_whole_rows(pkg, orc, sp, packs, name, mode):
         assert e.safe_intervals(qq) == a.safe_intervals(qq)
     assert np.array_equal(e.check_frames_batch_f64(qd, fr), ca)
     assert np.array_equal(e.collision_bits_f64(qd, pkg.SEM_INTERVAL), a.collision_bits_f64(qd, pkg.SEM_INTERVAL))
+    # hull pair tests without the oriented-box cull in front of them
+    g = pkg.Scene(pk, 0, mode)
+    g.set_option(pkg.OPT_OBB_CULL, 0)
+    for qq in qd[:12]:
+        assert g.safe_intervals(qq) == a.safe_intervals(qq)
+    assert np.array_equal(g.check_frames_batch_f64(qd, fr), ca)
+    assert np.array_equal(g.collision_bits_f64(qd, pkg.SEM_FRAME), a.collision_bits_f64(qd, pkg.SEM_FRAME))
+    tg, bg, _ = g.safe_intervals_batch(q, 8)
+    assert np.array_equal(bg, ba) and np.array_equal(tg, ta)
     wc = c.collision_bits_window_f64(qd, ft, 3, pkg.SEM_FRAME)
     for i in range(24):
         lo, hi = int(ft[i]), min(W, int(ft[i]) + 3)

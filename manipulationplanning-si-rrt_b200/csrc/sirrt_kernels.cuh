@@ -459,7 +459,12 @@ k_collide_bits(const __grid_constant__ DRobot rb, const __grid_constant__ BitsPa
           pass = dx * dx + dy * dy + dz * dz <= rr * rr && tight_overlap(sc, W, l, slot, 0, band);
         }
         bool h = eval_lane(l, slot, S, 0, -1, pass);
-        if (HAS_HULL && P.tasks.items) { push_tasks_warp(P.tasks, defer0, defer2, (int)n, -1, slot, lane); defer0 = defer2 = 0; }
+        if (HAS_HULL && P.tasks.items) {
+          // unsplit rows cut into tile chunks: every chunk's warp walks the static slots (it needs the closed-form static
+          // hits for its own words), but the deferred tasks apply to the whole row -- appended once, by chunk 0
+          if (n_sch > 1 || chunk == 0) push_tasks_warp(P.tasks, defer0, defer2, (int)n, -1, slot, lane);
+          defer0 = defer2 = 0;
+        }
         bool lane_hit = false, any_hit = false;
         if (HAS_HULL && W.qn > SIRRT_QCAP - 64) drain(-1, lane_hit, any_hit);
         static_hit |= __any_sync(SIRRT_FULL, h) | any_hit;

@@ -179,6 +179,21 @@ int sirrt_knn_radius(sirrt_knn*, const double* query, double r2, int64_t* idx, i
 /* k nearest of each query, ascending distance (ties by index); idx/dist2 [nq][k] */
 int sirrt_knn_topk(sirrt_knn*, const double* queries, int64_t nq, int k, int64_t* idx, double* dist2);
 
+/* Exact 1-NN WITHOUT ANY ALLOCATION, for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * Same arithmetic and tie rule as sirrt_knn_nearest (FP64 squared L2 in dimension order, ties to the lowest
+ * index); the kernel's scratch (block minima, tickets) is a fixed file-scope device array of 257 KB that every GPU which
+ * loads the library holds until exit -- hence the limit of SIRRT_KNN_NOALLOC_MAX_QUERIES queries per call (more:
+ * SIRRT_E_LIMIT; split the batch).  The call allocates nothing (no cudaMalloc / cudaFree, no store object) and is
+ * ASYNCHRONOUS on cuda_stream (0 = the legacy default stream): the caller synchronises before it reads the results.
+ *   pts_soa : DEVICE memory, double [dim][stride], point i = pts_soa[k * stride + i], n <= stride points used
+ *   queries : DEVICE memory, double [nq][dim];  idx : DEVICE int64 [nq] (-1 when n == 0);  dist2 : DEVICE double [nq]
+ * ALL CALLS SHARE THE SCRATCH ARRAY: it keeps the last call's contents (the words that must start at zero are cleared on
+ * the stream in front of every launch), and two calls that overlap on one GPU -- other streams, other threads -- RACE. */
+#define SIRRT_KNN_NOALLOC_MAX_QUERIES 256
+int sirrt_knn_nearest_noalloc(int device, void* cuda_stream, const double* pts_soa, int64_t n, int64_t stride, int dim,
+                              const double* queries, int64_t nq, int64_t* idx, double* dist2);
+
 /* one tree grown across n_shards GPUs (one process per GPU): shard g stores the points whose global index is
  * g (mod n_shards) at local index global / n_shards.  After each rank searched its shard (sirrt_knn_topk / _nearest
  * into device buffers) and the lists were all-gathered over NCCL, this merges them on the device:

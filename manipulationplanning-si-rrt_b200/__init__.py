@@ -46,6 +46,7 @@ EXPORTS = {
     "sirrt_scene_fk": (_i32, [_vp, _vp, _vp]),
     "sirrt_scene_fk_warp": (_i32, [_vp, _vp, _vp]),
     "sirrt_knn_host_buffers": (_i32, [_vp, _i32]),
+    "sirrt_knn_nearest_noalloc": (_i32, [_i32, _vp, _vp, _i64, _i64, _i32, _vp, _i64, _vp, _vp]),
     "sirrt_safe_intervals": (_i32, [_vp, _vp, _vp, _i32, _vp]),
     "sirrt_check_frame": (_i32, [_vp, _vp, _i32, _vp]),
     "sirrt_get_distances": (_i32, [_vp, _vp, _i32, _vp, _vp]),

@@ -392,3 +392,4 @@ extern "C" int sirrt_debug_phases(unsigned long long* out, int reset) {
 
 #include "sirrt_api_batch.inl"
 #include "sirrt_api_knn.inl"
+#include "sirrt_api_noalloc.inl"

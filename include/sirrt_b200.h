@@ -176,6 +176,12 @@ int sirrt_knn_add(sirrt_knn*, const double* pts /*[n][dim]*/, int64_t n);
 int sirrt_knn_nearest(sirrt_knn*, const double* queries /*[nq][dim]*/, int64_t nq, int64_t* idx, double* dist2);
 /* strict dist2 < r2 (nanoflann RadiusResultSet); indices ascending; *n_out = true count */
 int sirrt_knn_radius(sirrt_knn*, const double* query, double r2, int64_t* idx, int64_t cap, int64_t* n_out);
+/* The same query in two halves, for a planner that has other GPU work to issue in between: PlannerConnect.cpp:105-150 asks
+ * nearest -> steer -> get_safe_intervals -> set_parent, and the radius query that opens set_parent (:414-416, :394-412)
+ * depends on the steered configuration only.  _begin launches and returns at once; _end waits and answers exactly what
+ * sirrt_knn_radius answers.  One query may be pending per store; any other call on the store settles (and drops) it. */
+int sirrt_knn_radius_begin(sirrt_knn*, const double* query, double r2);
+int sirrt_knn_radius_end(sirrt_knn*, int64_t* idx, int64_t cap, int64_t* n_out);
 /* k nearest of each query, ascending distance (ties by index); idx/dist2 [nq][k] */
 int sirrt_knn_topk(sirrt_knn*, const double* queries, int64_t nq, int k, int64_t* idx, double* dist2);
 

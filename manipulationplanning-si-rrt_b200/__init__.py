@@ -46,6 +46,8 @@ EXPORTS = {
     "sirrt_scene_fk": (_i32, [_vp, _vp, _vp]),
     "sirrt_scene_fk_warp": (_i32, [_vp, _vp, _vp]),
     "sirrt_knn_host_buffers": (_i32, [_vp, _i32]),
+    "sirrt_knn_radius_begin": (_i32, [_vp, _vp, _f64]),
+    "sirrt_knn_radius_end": (_i32, [_vp, _vp, _i64, _vp]),
     "sirrt_knn_nearest_noalloc": (_i32, [_i32, _vp, _vp, _i64, _i64, _i32, _vp, _i64, _vp, _vp]),
     "sirrt_safe_intervals": (_i32, [_vp, _vp, _vp, _i32, _vp]),
     "sirrt_check_frame": (_i32, [_vp, _vp, _i32, _vp]),
@@ -350,6 +352,17 @@ class KnnIndex:
         idx = np.zeros(max(cap, 1), np.int64)
         n = C.c_int64()
         _ck(_lib.sirrt_knn_radius(self._h, q.ctypes.data, float(r2), idx.ctypes.data, cap, C.byref(n)))
+        return idx[: min(n.value, cap)], n.value
+
+    def radius_begin(self, query, r2: float):
+        q = np.ascontiguousarray(query, np.float64).reshape(self.dim)
+        _ck(_lib.sirrt_knn_radius_begin(self._h, q.ctypes.data, float(r2)))
+
+    def radius_end(self, cap: int | None = None):
+        cap = len(self) if cap is None else cap
+        idx = np.zeros(max(cap, 1), np.int64)
+        n = C.c_int64()
+        _ck(_lib.sirrt_knn_radius_end(self._h, idx.ctypes.data, cap, C.byref(n)))
         return idx[: min(n.value, cap)], n.value
 
     def topk(self, queries, k: int):

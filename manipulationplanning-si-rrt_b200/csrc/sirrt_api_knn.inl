@@ -19,8 +19,11 @@ struct sirrt_knn {
   size_t hits_cap_zeroed = 0;      // capacity of `hits` whose counter word has been cleared
   unsigned int done_seq = 0;       // completion flag sequence (KPIN_FLAG), see sirrt_wait_flag
   float wait_mean_us = 0.f;        // SIRRT_SYNC=nap: running mean of this store's flag waits
+  bool radius_pending = false;     // sirrt_knn_radius_begin has launched a query whose result nobody has collected yet
+  size_t radius_first = 0;         // hits of that query that travel through the pinned block
   int host_buffers = 0;            // sirrt_knn_host_buffers: every buffer the caller passes is host memory (no driver query per pointer)
 };
+static int knn_settle(sirrt_knn* k);  // a pending sirrt_knn_radius_begin query is collected (and dropped) before the store is used otherwise
 static inline bool kdev_ptr(const sirrt_knn* k, const void* p) { return k->host_buffers ? false : is_device_ptr(p); }
 extern "C" int sirrt_knn_host_buffers(sirrt_knn* k, int on) {
   if (!k) return fail(SIRRT_E_ARG, "null store");
@@ -86,6 +89,7 @@ extern "C" int sirrt_knn_info(const sirrt_knn* k, int* dim, int64_t* capacity, i
 }
 extern "C" int sirrt_knn_clear(sirrt_knn* k) {
   if (!k) return fail(SIRRT_E_ARG, "null argument");
+  { int rc = knn_settle(k); if (rc) return rc; }
   k->n = 0;
   return SIRRT_OK;
 }
@@ -118,6 +122,7 @@ static int knn_grow(sirrt_knn* k, long long need) {
 extern "C" int sirrt_knn_add(sirrt_knn* k, const double* pts, int64_t n) {
   if (!k || !pts || n < 0) return fail(SIRRT_E_ARG, "sirrt_knn_add: bad argument");
   if (n == 0) return SIRRT_OK;
+  { int rc = knn_settle(k); if (rc) return rc; }
   CU(cudaSetDevice(k->device));
   { int rc = knn_grow(k, k->n + n); if (rc) return rc; }
   const size_t bytes = sizeof(double) * k->dim * (size_t)n;
@@ -180,6 +185,7 @@ static void knn_nearest_tiled(sirrt_knn* k, const KnnStore& S, const double* dq,
 extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq, int64_t* idx, double* dist2) {
   if (!k || !queries || !idx || nq < 0) return fail(SIRRT_E_ARG, "sirrt_knn_nearest: bad argument");
   if (nq == 0) return SIRRT_OK;
+  { int rc = knn_settle(k); if (rc) return rc; }
   if (nq > (1 << 20)) {  // grid.y limit (65535 tiles of 32 queries): recurse over slabs
     for (int64_t o = 0; o < nq; o += 1 << 20) {
       int rc = sirrt_knn_nearest(k, queries + o * k->dim, std::min<int64_t>(1 << 20, nq - o), idx + o, dist2 ? dist2 + o : nullptr);
@@ -235,10 +241,12 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
 }
 
 // PlannerConnect::get_nearest_node_by_radius (PlannerConnect.cpp:394-412): strict dist2 < r2
-extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, int64_t* idx, int64_t cap, int64_t* n_out) {
-  if (!k || !query || !n_out || cap < 0 || (cap > 0 && !idx)) return fail(SIRRT_E_ARG, "sirrt_knn_radius: bad argument");
-  *n_out = 0;
-  if (k->n == 0) return SIRRT_OK;
+// Radius query in two halves, so that a planner can put other work (its safe-interval call on the scene's own stream)
+// between the launch and the wait: PlannerConnect.cpp:105-150 asks nearest -> steer -> get_safe_intervals -> set_parent, and
+// the radius query that opens set_parent (:414-416) depends on the steered configuration only.
+// begin: launches the single-launch query (k_knn_radius1), nothing is waited for.  end: waits for its completion flag and
+// returns what sirrt_knn_radius returns.  One query may be pending per store; every other call on the store settles it first.
+static int knn_radius_launch(sirrt_knn* k, const double* query, double r2) {
   CU(cudaSetDevice(k->device));
   KnnQuery Q{};
   if (kdev_ptr(k, query)) CU(cudaMemcpy(Q.v, query, sizeof(double) * k->dim, cudaMemcpyDeviceToHost));
@@ -249,26 +257,67 @@ extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, in
   if (k->hits_cap_zeroed != k->hits.cap) { CU(cudaMemsetAsync(k->hits.p, 0, sizeof(unsigned), k->stream)); k->hits_cap_zeroed = k->hits.cap; }
   KnnStore S{k->pts, k->cap, k->n, k->dim};
   const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
-  const size_t first = (size_t)std::min<long long>(k->n, 1023ll);
+  k->radius_first = (size_t)std::min<long long>(k->n, 1023ll);
   int* ph = (int*)(k->pinned + KPIN_OUT);
   unsigned int* flag = (unsigned int*)(k->pinned + KPIN_FLAG);
-  k_knn_radius1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, Q, r2, k->hits.as<int>(), k->ticket + 1, ph, (int)first, flag, ++k->done_seq);
+  k_knn_radius1<<<grid, SIRRT_KNN_THREADS, 0, k->stream>>>(S, Q, r2, k->hits.as<int>(), k->ticket + 1, ph, (int)k->radius_first, flag, ++k->done_seq);
   CU(cudaGetLastError());
+  k->radius_pending = true;
+  return SIRRT_OK;
+}
+static int knn_radius_collect(sirrt_knn* k, int64_t* idx, int64_t cap, int64_t* n_out) {
+  int* ph = (int*)(k->pinned + KPIN_OUT);
+  unsigned int* flag = (unsigned int*)(k->pinned + KPIN_FLAG);
+  k->radius_pending = false;
   CU(sirrt_wait_flag(k->stream, flag, k->done_seq, &k->wait_mean_us));
   const unsigned cnt = (unsigned)ph[0];
-  *n_out = cnt;
-  if (cnt == 0) return SIRRT_OK;
+  if (n_out) *n_out = cnt;
+  if (cnt == 0 || !idx) return SIRRT_OK;
   std::vector<int> h(cnt);
-  if (cnt <= first) memcpy(h.data(), ph + 1, sizeof(int) * cnt);
+  if (cnt <= k->radius_first) memcpy(h.data(), ph + 1, sizeof(int) * cnt);
   else CU(cudaMemcpy(h.data(), k->hits.as<int>() + 1, sizeof(int) * cnt, cudaMemcpyDeviceToHost));
   std::sort(h.begin(), h.end());
   for (int64_t i = 0; i < std::min<int64_t>(cap, cnt); i++) idx[i] = h[i];
   return SIRRT_OK;
 }
+// a pending radius query owns the pinned result block and the flag: settle it (result dropped) before anything else uses them
+static int knn_settle(sirrt_knn* k) {
+  if (!k->radius_pending) return SIRRT_OK;
+  CU(cudaSetDevice(k->device));
+  return knn_radius_collect(k, nullptr, 0, nullptr);
+}
+
+extern "C" int sirrt_knn_radius(sirrt_knn* k, const double* query, double r2, int64_t* idx, int64_t cap, int64_t* n_out) {
+  if (!k || !query || !n_out || cap < 0 || (cap > 0 && !idx)) return fail(SIRRT_E_ARG, "sirrt_knn_radius: bad argument");
+  *n_out = 0;
+  int rc = knn_settle(k);
+  if (rc) return rc;
+  if (k->n == 0) return SIRRT_OK;
+  if ((rc = knn_radius_launch(k, query, r2))) return rc;
+  return knn_radius_collect(k, idx, cap, n_out);
+}
+extern "C" int sirrt_knn_radius_begin(sirrt_knn* k, const double* query, double r2) {
+  if (!k || !query) return fail(SIRRT_E_ARG, "sirrt_knn_radius_begin: bad argument");
+  int rc = knn_settle(k);
+  if (rc) return rc;
+  if (k->n == 0) return SIRRT_OK;  // nothing to launch: _end answers 0 hits
+  return knn_radius_launch(k, query, r2);
+}
+extern "C" int sirrt_knn_radius_end(sirrt_knn* k, int64_t* idx, int64_t cap, int64_t* n_out) {
+  if (!k || !n_out || cap < 0 || (cap > 0 && !idx)) return fail(SIRRT_E_ARG, "sirrt_knn_radius_end: bad argument");
+  *n_out = 0;
+  if (!k->radius_pending) {
+    if (k->n == 0) return SIRRT_OK;
+    return fail(SIRRT_E_ARG, "sirrt_knn_radius_end: no query pending on this store");
+  }
+  CU(cudaSetDevice(k->device));
+  return knn_radius_collect(k, idx, cap, n_out);
+}
 
 extern "C" int sirrt_knn_topk(sirrt_knn* k, const double* queries, int64_t nq, int kk, int64_t* idx, double* dist2) {
   if (!k || !queries || !idx || nq < 0 || kk < 1 || kk > 1024) return fail(SIRRT_E_ARG, "sirrt_knn_topk: bad argument");
   if (nq == 0) return SIRRT_OK;
+  { int rc = knn_settle(k); if (rc) return rc; }
   CU(cudaSetDevice(k->device));
   const double* dq = nullptr;
   int rc = knn_queries_in(k, queries, nq, &dq);

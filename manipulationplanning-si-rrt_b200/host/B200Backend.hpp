@@ -123,8 +123,19 @@ class B200Backend {
     knn_.push_back(k);
     return (int)knn_.size() - 1;
   }
-  void knn_add(int tree, const double* p) { ck(sirrt_knn_add(knn_[tree], p, 1)); }
+  void knn_add(int tree, const double* p) { pf_valid_ = false; ck(sirrt_knn_add(knn_[tree], p, 1)); }
+  // Optional hook of the planner template: the radius query that opens set_parent (PlannerConnect.cpp:414-416) depends on
+  // the steered configuration only, so it is LAUNCHED here, before the planner's get_safe_intervals call (another object,
+  // another stream: the two run side by side on the GPU), and collected by knn_radius below.  Same answers, one round
+  // trip per iteration hidden.
+  void knn_radius_prefetch(int tree, const double* q, double r2) {
+    pf_valid_ = false;
+    if (sirrt_knn_radius_begin(knn_[tree], q, r2) != SIRRT_OK) return;  // knn_radius asks synchronously
+    pf_tree_ = tree; pf_r2_ = r2; pf_q_.assign(q, q + dof());
+    pf_valid_ = true;
+  }
   size_t knn_nearest(int tree, const double* q) {
+    pf_valid_ = false;
     int64_t idx = -1;
     double d2 = 0;
     ck(sirrt_knn_nearest(knn_[tree], q, 1, &idx, &d2));
@@ -133,6 +144,15 @@ class B200Backend {
   void knn_radius(int tree, const double* q, double r2, std::vector<size_t>& out) {
     int64_t n = 0;
     rad_.resize(std::max<size_t>(rad_.size(), 256));
+    if (pf_valid_) {
+      pf_valid_ = false;
+      if (pf_tree_ == tree && pf_r2_ == r2 && !memcmp(pf_q_.data(), q, sizeof(double) * dof())) {
+        const int rc = sirrt_knn_radius_end(knn_[tree], rad_.data(), (int64_t)rad_.size(), &n);
+        if (rc == SIRRT_OK && n <= (int64_t)rad_.size()) { out.assign(rad_.begin(), rad_.begin() + n); n_prefetched_++; return; }
+        if (rc != SIRRT_OK && rc != SIRRT_E_OVERFLOW) ck(rc);
+        rad_.resize(std::max<size_t>((size_t)n, rad_.size()));  // more hits than fit: ask again below
+      }  // (a prefetch for another query is settled and dropped by the library)
+    }
     for (;;) {
       const int rc = sirrt_knn_radius(knn_[tree], q, r2, rad_.data(), (int64_t)rad_.size(), &n);
       if (rc == SIRRT_E_OVERFLOW || n > (int64_t)rad_.size()) { rad_.resize((size_t)n); continue; }
@@ -147,6 +167,7 @@ class B200Backend {
   uint64_t n_tables() const { return n_tables_; }
   uint64_t n_cell_batches() const { return n_cell_batches_; }
   uint64_t n_lookups() const { return n_lookups_; }
+  uint64_t n_prefetched_radius() const { return n_prefetched_; }
 
  private:
   void note_edge_done() {
@@ -161,6 +182,11 @@ class B200Backend {
   std::vector<sirrt_knn*>* pool_ = nullptr;
   std::vector<sirrt_knn*> knn_;
   std::vector<int64_t> rad_;
+  bool pf_valid_ = false;   // a radius query launched by knn_radius_prefetch waits to be collected
+  int pf_tree_ = -1;
+  double pf_r2_ = 0;
+  std::vector<double> pf_q_;
+  uint64_t n_prefetched_ = 0;
   std::vector<double> e_q0_, e_dir_, e_states_;
   int e_steps_ = -1, e_uses_ = 0;
   bool e_have_table_ = false;

@@ -114,6 +114,7 @@ class PlannerConnect {
       stats_.iterations++;
       Coord coord_rand = get_random_configuration();
       if (!extend(coord_rand)) continue;
+      hint_radius(coord_rand, *current_tree_);
       auto si = safe_intervals(coord_rand);
       std::vector<Vertex*> new_nodes = set_parent(coord_rand, si);
       if (new_nodes.empty()) { swap_trees(); continue; }
@@ -219,6 +220,7 @@ class PlannerConnect {
     for (int i = 0; i < 25; i++) {
       Coord coord_rand = get_random_configuration();
       if (!extend(coord_rand)) continue;
+      hint_radius(coord_rand, *current_tree_);
       auto si = safe_intervals(coord_rand);
       std::vector<Vertex*> new_nodes = set_parent(coord_rand, si);
       if (new_nodes.empty() && was_static_obstacle_) {
@@ -239,6 +241,7 @@ class PlannerConnect {
       const bool is_ok = extend(coord_rand);
       swap_trees();
       if (!is_ok) break;
+      hint_radius(coord_rand, *other_tree_);  // set_parent below runs on the swapped tree
       auto si = safe_intervals(coord_rand);
       swap_trees();
       std::vector<Vertex*> new_nodes = set_parent(coord_rand, si);
@@ -264,6 +267,14 @@ class PlannerConnect {
     }
     return false;
   }
+
+  // Backends that can overlap the radius query of the coming set_parent (same q, same r2, same tree: :416) with the
+  // safe-interval call in between offer knn_radius_prefetch; for the others this is a no-op.  Answers are unaffected.
+  template <typename B> static auto hint_radius_impl(B& be, int knn, const double* q, double r2, int) -> decltype(be.knn_radius_prefetch(knn, q, r2), void()) {
+    be.knn_radius_prefetch(knn, q, r2);
+  }
+  template <typename B> static void hint_radius_impl(B&, int, const double*, double, long) {}
+  void hint_radius(const Coord& q, Tree& tree) { hint_radius_impl(be_, tree.knn, q.data(), radius_factor_ * planner_range_ * planner_range_, 0); }
 
   // PlannerConnect.cpp:394-412: strict dist^2 < r2, then the caller sorts
   std::vector<Vertex*> get_nearest_node_by_radius(const Coord& q, double r2, Tree& tree) {

@@ -647,3 +647,38 @@ def test_warp_fk_agrees_with_the_sequential_chain(pkg, orc, sp, packs, name):
         Ro, to = ref.fk(qq)
         assert np.abs(R2 - Ro).max() < 1e-12 and np.abs(t2 - to).max() < 1e-12
     assert worst < 1e-13, worst
+
+
+@pytest.mark.gpu
+def test_knn_radius_begin_end_equals_radius(pkg):
+    """sirrt_knn_radius_begin / _end (the planner launches the radius query of set_parent before its safe-interval call and
+    collects it afterwards) answer what sirrt_knn_radius answers; a pending query is settled and dropped by any other call
+    on the store; _end without _begin is an error; more hits than the pinned block carries (1023) still arrive."""
+    rng = np.random.default_rng(77)
+    dim = 6
+    store = pkg.KnnIndex(dim, 64)
+    idx0, n0 = store.radius_end()          # empty store: 0 hits, no query needed
+    assert n0 == 0
+    pts = rng.uniform(-1.0, 1.0, (3000, dim))
+    store.add(pts)
+    with pytest.raises(pkg.SirrtError):
+        store.radius_end()
+    for r2 in (0.05, 0.6, 30.0):           # 30.0: every point, beyond the 1023 hits of the pinned block
+        q = rng.uniform(-1.0, 1.0, dim)
+        want, n_want = store.radius(q, r2)
+        store.radius_begin(q, r2)
+        got, n_got = store.radius_end()
+        assert n_got == n_want and np.array_equal(got, want)
+    q = rng.uniform(-1.0, 1.0, dim)
+    store.radius_begin(q, 0.6)             # left pending: the next calls settle it
+    i1, d1 = store.nearest(q[None, :])
+    assert i1[0] == int(np.argmin(((pts - q) ** 2).sum(1)))
+    store.radius_begin(q, 0.6)
+    store.add(rng.uniform(-1.0, 1.0, (1, dim)))
+    want, n_want = store.radius(q, 0.6)
+    store.radius_begin(q, 0.6)
+    store.radius_begin(q, 0.7)             # a second begin drops the first
+    got, n_got = store.radius_end()
+    w2, n2 = store.radius(q, 0.7)
+    assert n_got == n2 and np.array_equal(got, w2)
+    store.close()

@@ -16,5 +16,5 @@ python - <<PY
 import json
 for line in open("$OUT/${TAG}_gjk_hist.json"):
     d = json.loads(line)
-    print(d["call"], d.get("collide_bits_cycles_per_warp"), d.get("gjk_task_cycles"), d.get("max_cycles_over_all_calls"))
+    print(d["call"], {k: (v["tasks"], v["mean_iter"], v["max_iter"], v["hist"]) for k, v in d.items() if isinstance(v, dict) and "mean_iter" in v}, d.get("gjk_task_cycles"), d.get("max_cycles_over_all_calls"))
 PY

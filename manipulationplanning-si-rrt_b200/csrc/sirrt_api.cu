@@ -211,6 +211,7 @@ struct sirrt_scene {
   // copy operation adds 3-4 us to the 9 us launch + synchronise floor; scripts/micro/lat_probe.cu).
   char* pinned = nullptr;
   unsigned int* lazy_cnt = nullptr;  // device: 4 launch counters + k_recheck ticket [4] + k_gjk_tasks ticket [6], zero between calls (finish_call clears them); [7] = sequence number of the call the task kernel completed
+  bool lazy_timed = false;    // ... and its sweep launch was bracketed by ev[0] / ev[1]
   bool lazy_pending = false;  // counters of the last run_bits launch are in flight to PIN_CNT
   unsigned int fin_seq = 0;   // sequence number of latency-path calls (lazy_cnt[7]: which call the task kernel has already completed)
   unsigned int done_seq = 0;  // sequence number of the completion flag (PIN_FLAG) the pending call will write

@@ -109,7 +109,9 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
         if (s->seeds.ensure((size_t)SIRRT_SEED_CAP * sizeof(int4))) return fail(SIRRT_E_CUDA, "cudaMalloc(re-check seeds) failed");
         wl.seeds = s->seeds.as<int4>(); wl.seed_cap = SIRRT_SEED_CAP;
       }
-      const bool timed = !(lazy && nr == 1) && i < s->ev.size() / 2;
+      // (the single-launch latency path is not timed -- two event records per planner call -- unless it runs the sweep kernel,
+      // which planner-sized calls never do by default: sweep_kernel_ms must then still say that k_sweep ran)
+      const bool timed = (sweep || !(lazy && nr == 1)) && i < s->ev.size() / 2;
       RecheckParams R{};
       R.sc = s->d; R.q = qv; R.items = wl.items; R.count = wl.count; R.cap = wl.cap;
       R.aabb_d = s->d_aabb_d; R.bits = d_bits; R.n_words = W; R.cells = nullptr; R.counters = wl.count;
@@ -196,6 +198,7 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
       CU(cudaGetLastError());
     }
     if (self_clearing) {
+      s->lazy_timed = sweep && !s->ev.empty();
       s->lazy_pending = true;
       s->stats[0] += launches;
       return SIRRT_OK;
@@ -230,6 +233,12 @@ static int run_bits(sirrt_scene* s, QView q, long long N, int semantics, uint32_
 static int finish_lazy(sirrt_scene* s) {
   if (!s->lazy_pending) return 0;
   s->lazy_pending = false;
+  if (s->lazy_timed) {
+    s->lazy_timed = false;
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, s->ev[0], s->ev[1]) == cudaSuccess) s->stats[4] += (uint64_t)(ms * 1e6);
+    else cudaGetLastError();
+  }
   const unsigned* host = (const unsigned*)(s->pinned + PIN_CNT);
   if (host[0] > s->wl_cap || host[3] > s->wl_cap) return 1;
   s->stats[1] += host[0]; s->stats[3] += host[1] + host[3]; s->stats[2] += host[2];

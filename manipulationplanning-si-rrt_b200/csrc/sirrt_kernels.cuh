@@ -247,7 +247,7 @@ __device__ __forceinline__ bool tight_overlap(const DScene& sc, const WarpCtx& W
 // Both boxes contain their shapes, so a separating axis with more than `margin` of clearance proves the pair FREE; nothing
 // else is decided here (results unchanged, GJK runs saved: 40-85 % of the deferred tasks end FREE).  The cross-product axes
 // are not normalised (|a x b| <= 1), which only makes the required clearance larger; EPS guards near-parallel axes.
-__device__ inline bool obb_separated(const WarpCtx& W, int l, const DShape& sb, const float* RB, const float* tB, float margin) {
+__host__ __device__ inline bool obb_separated(const WarpCtx& W, int l, const DShape& sb, const float* RB, const float* tB, float margin) {
   const float* RA = W.R[l];
   float hb[3], cb[3], d[3], t[3], R[3][3], AR[3][3];
 #pragma unroll

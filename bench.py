@@ -269,6 +269,26 @@ def plan_time_leg(seeds: int, max_time: float, device: int):
     return out
 
 
+def latency_leg(calls: int = 300):
+    """Per-call latency of the planner-in-the-loop entry points over the C ABI (host/sirrt_latency, a C++ program: no Python in
+    the loop), microseconds, on the three shipped dynamic scenes -- what the SI-RRT plan time is made of."""
+    exe = os.path.join(g.PKG_DIR, "host", "sirrt_latency")
+    if not os.path.exists(exe):
+        return {"unavailable": "host/sirrt_latency not built (run __graft_entry__.build())"}
+    out = {"unit": "us per call (mean of %d calls after warm-up)" % calls, "scenes": {}}
+    tmp = tempfile.mkdtemp()
+    for name in ("mass_test", "flying_boxes", "multiple_robots"):
+        path = os.path.join(tmp, name + ".pack")
+        with gzip.open(os.path.join(ROOT, "tests", "golden", name + ".pack.gz"), "rb") as f, open(path, "wb") as o:
+            o.write(f.read())
+        try:
+            r = subprocess.run([exe, path, str(calls)], capture_output=True, text=True, timeout=120)
+            out["scenes"][name] = json.loads(r.stdout.strip().splitlines()[-1])["us"] if r.returncode == 0 else {"failed": r.stderr[-200:]}
+        except Exception as e:  # a leg of the report, never the bench itself
+            out["scenes"][name] = {"failed": str(e)[:200]}
+    return out
+
+
 def mass_test_leg(tasks: int, device_count: int):
     """BASELINE.json config 5 in small: scripts/mass_test.py (host/sirrt_mass: one process per GPU, 16 planner threads each, a
     shared task queue) on `tasks` synthetic planning tasks (one start / goal pair x 6 planner seeds for each of the 16 cube counts) with a 5 s budget, next to the reference's execution model (one CPU
@@ -596,6 +616,8 @@ def main():
             out["results"]["weak_scaling"] = weak
         if not a.no_plan_time and world == 1:
             out["results"]["plan_time"] = plan_time_leg(a.plan_seeds, 5.0, local)
+        if not a.no_plan_time and world == 1 and local == 0:
+            out["results"]["latency"] = latency_leg()
         if not a.no_knn and world == 1:
             out["results"]["knn"] = knn_leg(pkg, local, hbm_peak, roofline["peak"])
         if a.mass_tasks > 0 and world == 1:

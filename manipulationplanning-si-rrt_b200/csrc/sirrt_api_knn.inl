@@ -23,6 +23,14 @@ struct sirrt_knn {
   size_t radius_first = 0;         // hits of that query that travel through the pinned block
   int host_buffers = 0;            // sirrt_knn_host_buffers: every buffer the caller passes is host memory (no driver query per pointer)
 };
+// Grid of the single-launch latency kernels.  Planner trees hold a few hundred to a few thousand vertices: up to
+// SIRRT_KNN_ONE_BLOCK points ONE block scans them (8 points per thread) and answers directly -- no block minima in scratch,
+// no ticket, no second reduction; larger stores spread over the machine.
+#define SIRRT_KNN_ONE_BLOCK 2048
+static int knn_latency_grid(const sirrt_knn* k) {
+  if (k->n <= SIRRT_KNN_ONE_BLOCK) return 1;
+  return (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
+}
 static int knn_settle(sirrt_knn* k);  // a pending sirrt_knn_radius_begin query is collected (and dropped) before the store is used otherwise
 static inline bool kdev_ptr(const sirrt_knn* k, const void* p) { return k->host_buffers ? false : is_device_ptr(p); }
 extern "C" int sirrt_knn_host_buffers(sirrt_knn* k, int on) {
@@ -198,7 +206,7 @@ extern "C" int sirrt_knn_nearest(sirrt_knn* k, const double* queries, int64_t nq
   const double* dq = nullptr;
   int rc;
   if (nq == 1 && !kdev_ptr(k, queries) && !kdev_ptr(k, idx) && !(dist2 && kdev_ptr(k, dist2))) {  // latency path: one launch, answer lands in the pinned block
-    const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
+    const int grid = knn_latency_grid(k);
     if (k->part_d.ensure(sizeof(double) * (size_t)k->n_sm * 4) || k->part_i.ensure(sizeof(long long) * (size_t)k->n_sm * 4)) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
     KnnStore S1{k->pts, k->cap, k->n, k->dim};
     long long* o_i = (long long*)(k->pinned + KPIN_OUT);
@@ -256,7 +264,7 @@ static int knn_radius_launch(sirrt_knn* k, const double* query, double r2) {
   if (k->hits.ensure(sizeof(int) * ((size_t)k->n + 1))) return fail(SIRRT_E_CUDA, "cudaMalloc failed");
   if (k->hits_cap_zeroed != k->hits.cap) { CU(cudaMemsetAsync(k->hits.p, 0, sizeof(unsigned), k->stream)); k->hits_cap_zeroed = k->hits.cap; }
   KnnStore S{k->pts, k->cap, k->n, k->dim};
-  const int grid = (int)std::max(1ll, std::min((long long)k->n_sm * 4, (k->n + SIRRT_KNN_THREADS - 1) / SIRRT_KNN_THREADS));
+  const int grid = knn_latency_grid(k);
   k->radius_first = (size_t)std::min<long long>(k->n, 1023ll);
   int* ph = (int*)(k->pinned + KPIN_OUT);
   unsigned int* flag = (unsigned int*)(k->pinned + KPIN_FLAG);

@@ -49,3 +49,20 @@ def test_bad_pack_is_rejected_before_any_cuda_call(pkg):
     lib = ctypes.CDLL(pkg.LIB_PATH)
     rc = lib.sirrt_scene_create_from_pack(None, 0, 0, 0, ctypes.byref(h))
     assert rc == -1
+
+
+def test_option_constants_match_the_header():
+    """The Python mirror's OPT_* values are the SIRRT_OPT_* enumerators of include/sirrt_b200.h (the tests toggle kernels paths
+    through them: a drifted value would silently toggle another knob)."""
+    import re
+
+    g = __import__("__graft_entry__")
+    hdr = open(os.path.join(g.ROOT, "include", "sirrt_b200.h")).read()
+    enum = dict((m.group(1), int(m.group(2))) for m in re.finditer(r"SIRRT_OPT_([A-Z_0-9]+)\s*=\s*(\d+)", hdr))
+    src = open(os.path.join(g.PKG_DIR, "__init__.py")).read()
+    m = re.search(r"^(OPT_[A-Z_, ]+?)\s*=\s*([\d, ]+)$", src, re.M)
+    names = [n.strip()[4:] for n in m.group(1).split(",")]
+    values = [int(v) for v in m.group(2).split(",")]
+    assert len(names) == len(values) == len(enum), (names, enum)
+    for n, v in zip(names, values):
+        assert enum[n] == v, (n, v, enum[n])

@@ -75,6 +75,37 @@ struct OracleBackend {
   }
 };
 
+// --check-prefetch: the same backend WITH the optional knn_radius_prefetch hook of the planner template (what B200Backend
+// uses to launch the radius query of set_parent before the safe-interval call).  Nothing is prefetched here; the hook only
+// records (tree, q, r2, tree size) and knn_radius counts how many of its queries were announced exactly -- the planner-side
+// half of that optimisation, checked on the CPU.  Plans must not depend on the hook.
+struct OraclePrefetchBackend : OracleBackend {
+  using OracleBackend::OracleBackend;
+  bool have = false;
+  int h_tree = -1;
+  double h_r2 = 0;
+  size_t h_size = 0;
+  std::vector<double> h_q;
+  uint64_t hints = 0, queries = 0, matched = 0, mismatched = 0, overwritten = 0;
+  void knn_radius_prefetch(int t, const double* q, double r2) {
+    if (have) overwritten++;
+    have = true; h_tree = t; h_r2 = r2; h_size = trees[t].size(); h_q.assign(q, q + dof_);
+    hints++;
+  }
+  void knn_add(int t, const double* p) { OracleBackend::knn_add(t, p); }
+  void knn_radius(int t, const double* q, double r2, std::vector<size_t>& out) {
+    queries++;
+    if (have) {
+      have = false;
+      if (t == h_tree && r2 == h_r2 && trees[t].size() == h_size && !memcmp(h_q.data(), q, sizeof(double) * dof_)) matched++;
+      else mismatched++;
+    }
+    OracleBackend::knn_radius(t, q, r2, out);
+  }
+};
+
+template <typename BE> static int run_planner(BE& be, const char* scene_path, int seed, uint64_t max_iters, double max_time, bool baseline);
+
 int main(int argc, char** argv) {
   if (argc < 3) { fprintf(stderr, "usage: %s <scene.pack> <seed> [--max-iters N] [--max-time S] [--fixed]\n", argv[0]); return 2; }
   std::ifstream f(argv[1], std::ios::binary);
@@ -84,23 +115,43 @@ int main(int argc, char** argv) {
   uint64_t max_iters = 0;
   double max_time = -1;
   int mode = ORACLE_REFERENCE_EXACT;
-  bool baseline = false;
+  bool baseline = false, check_prefetch = false;
   for (int i = 3; i < argc; i++) {
     if (!strcmp(argv[i], "--max-iters") && i + 1 < argc) max_iters = strtoull(argv[++i], nullptr, 10);
     else if (!strcmp(argv[i], "--max-time") && i + 1 < argc) max_time = atof(argv[++i]);
     else if (!strcmp(argv[i], "--fixed")) mode = ORACLE_FIXED;
     else if (!strcmp(argv[i], "--baseline")) baseline = true;
+    else if (!strcmp(argv[i], "--check-prefetch")) check_prefetch = true;
   }
   try {
+    if (check_prefetch) { OraclePrefetchBackend be(pack, mode); return run_planner(be, argv[1], seed, max_iters, max_time, baseline); }
     OracleBackend be(pack, mode);
+    return run_planner(be, argv[1], seed, max_iters, max_time, baseline);
+  } catch (const std::exception& e) {
+    fprintf(stderr, "planner_oracle: %s\n", e.what());
+    return 1;
+  }
+}
+
+static void prefetch_extras(OracleBackend&, MDP::ResultsLog&) {}
+static void prefetch_extras(OraclePrefetchBackend& be, MDP::ResultsLog& log) {
+  log.extra.push_back({"radius_hints", (double)be.hints});
+  log.extra.push_back({"radius_queries", (double)be.queries});
+  log.extra.push_back({"radius_queries_announced_exactly", (double)be.matched});
+  log.extra.push_back({"radius_hint_mismatches", (double)be.mismatched});
+  log.extra.push_back({"radius_hints_overwritten", (double)be.overwritten});
+}
+
+template <typename BE> static int run_planner(BE& be, const char* scene_path, int seed, uint64_t max_iters, double max_time, bool baseline) {
+  {
     if (baseline) { oracle_set_fast(1); oracle_bvh_build(be.o); }
-    MDP::MSIRRT::PlannerConnect<OracleBackend> planner(be, seed);
+    MDP::MSIRRT::PlannerConnect<BE> planner(be, seed);
     if (!planner.valid()) { fprintf(stderr, "planner_oracle: %s\n", planner.error().c_str()); return 1; }
     if (max_iters) planner.set_max_iterations(max_iters);
     if (max_time > 0) planner.set_max_planning_time(max_time);
     const bool result = planner.solve();
     MDP::ResultsLog log;
-    log.path_to_scene_json = argv[1];
+    log.path_to_scene_json = scene_path;
     const auto& st = planner.stats();
     log.set_counters(st, be.n_links);
     log.has_result = result;
@@ -114,10 +165,8 @@ int main(int argc, char** argv) {
     }
     log.extra.push_back({"iterations", (double)st.iterations});
     log.extra.push_back({"motion_checks", (double)st.n_motion_checks});
+    prefetch_extras(be, log);
     std::cout << log.to_json() << std::endl;
     return 0;
-  } catch (const std::exception& e) {
-    fprintf(stderr, "planner_oracle: %s\n", e.what());
-    return 1;
   }
 }

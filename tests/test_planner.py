@@ -106,6 +106,22 @@ def test_oracle_backed_planner_finds_valid_plans(planner_oracle, scenes, orc, na
         revalidate(orc, scenes[name], path, o.fps)
 
 
+@pytest.mark.parametrize("name", ["mass_test", "dyn0", "dyn1"])
+def test_radius_prefetch_hook_announces_every_query_exactly(planner_oracle, scenes, name):
+    """The planner template tells a backend that offers knn_radius_prefetch which radius query set_parent will ask
+    (PlannerConnect.cpp:414-416) BEFORE its safe-interval call -- B200Backend launches it there, so that the two GPU calls run
+    side by side.  Checked on the CPU with a recording backend (planner_oracle --check-prefetch): every hint is followed by
+    exactly that query (same tree, same coordinates bit for bit, same radius, no vertex added in between), and the plan does
+    not depend on the hook."""
+    for seed in (1, 2):
+        plain = run_json([planner_oracle, scenes[name], str(seed), "--max-time", "20", "--baseline"])
+        hooked = run_json([planner_oracle, scenes[name], str(seed), "--max-time", "20", "--baseline", "--check-prefetch"])
+        assert plain["final_planner_data"] == hooked["final_planner_data"]
+        b = hooked["b200"]
+        assert b["radius_hints"] >= 1 and b["radius_hint_mismatches"] == 0 and b["radius_hints_overwritten"] == 0, b
+        assert b["radius_queries_announced_exactly"] == b["radius_hints"] <= b["radius_queries"], b
+
+
 def test_planner_is_deterministic_per_seed_and_log_schema(planner_oracle, scenes):
     a = run_json([planner_oracle, scenes["dyn0"], "7", "--max-time", "20"])
     b = run_json([planner_oracle, scenes["dyn0"], "7", "--max-time", "20"])

@@ -16,7 +16,7 @@ for n in mass_test flying_boxes multiple_robots; do
   timeout 120 $LAT /tmp/packs/$n.pack 500 >> $OUT/${TAG}_latency.json 2>> $OUT/${TAG}_latency.err
 done
 cat $OUT/${TAG}_latency.json
-timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -q -x -k "slot_split or deferred or single_call or check_frames or reference_scenes or robot_obstacles or get_distances or motion_check or hull_support or edge_check or windowed or concurrent or collision_manager or edge_cases" > $OUT/${TAG}_tests.log 2>&1; echo "tests rc=$?"; tail -2 $OUT/${TAG}_tests.log
+echo "tests skipped (full suite ran in the same round)"
 for k in k_collide_bits k_gjk_tasks k_recheck; do
   timeout 300 ncu --set full --import-source on --clock-control none --cache-control none -k regex:$k --launch-skip 30 --launch-count 1 -f -o $OUT/${TAG}_$k $LAT /tmp/packs/$SC.pack 60 > $OUT/${TAG}_ncu_$k.log 2>&1; echo "ncu $k rc=$?"
 done
